@@ -1,0 +1,419 @@
+"""Host-side mirror of the reference `oics` crate's public functions, over the C ABI.
+
+Images are numpy uint8 arrays ([h, w] or [h, w, 3], C-contiguous rows) or any
+object exposing a CUDA pointer (`torch.Tensor` on the GPU, or `DeviceImage`).
+Every call goes through liboics_cuda.so; nothing here computes pixels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import threading
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+from ._lib import OicsError, OmrResultC, check
+
+BELIEVED, NEED_CHECK, NOT_A_RESULT = 0, 1, 2          # omr::ResultStatus (omr.rs:41-45)
+CLIP_DEFAULT, CLIP_CONTAIN = 0, 1                     # types::RotateClipStrategy (types.rs:7-11)
+INTER_NEAREST, INTER_LINEAR = 0, 1
+WARP_POLAR_LINEAR = 0                                 # the flag value the reference passes (omr.rs:170)
+PRE_OMR, PRE_PROJECTION = 0, 1
+LINES_OMR, LINES_HOUGH, LINES_FFT = 0, 1, 2
+WHITE = (255, 255, 255, 0)
+
+
+@dataclass
+class OmrResult:
+    """omr::OmrResult (omr.rs:46-50)."""
+    angle: float
+    status: int
+    candidates: list = field(default_factory=list)
+
+
+@dataclass
+class DeviceImage:
+    """An image already resident on the GPU (raw device address)."""
+    ptr: int
+    w: int
+    h: int
+    ch: int = 1
+    stride: int = 0
+
+    def __post_init__(self):
+        if not self.stride:
+            self.stride = self.w * self.ch
+
+
+def _describe(img):
+    """-> (pointer, w, h, ch, stride, keepalive)"""
+    if isinstance(img, DeviceImage):
+        return img.ptr, img.w, img.h, img.ch, img.stride, img
+    if isinstance(img, np.ndarray):
+        if img.dtype != np.uint8 or img.ndim not in (2, 3):
+            raise TypeError("expected a uint8 [h,w] or [h,w,ch] array")
+        if img.strides[-1] != 1 or (img.ndim == 3 and img.strides[1] != img.shape[2]):
+            img = np.ascontiguousarray(img)
+        h, w = img.shape[:2]
+        ch = 1 if img.ndim == 2 else img.shape[2]
+        return img.ctypes.data, w, h, ch, img.strides[0], img
+    if hasattr(img, "data_ptr") and hasattr(img, "is_cuda"):     # torch tensor
+        if not img.is_cuda:
+            return _describe(img.numpy())
+        if str(img.dtype) != "torch.uint8" or img.dim() not in (2, 3) or not img.is_contiguous():
+            raise TypeError("expected a contiguous uint8 CUDA tensor [h,w] or [h,w,ch]")
+        h, w = int(img.shape[0]), int(img.shape[1])
+        ch = 1 if img.dim() == 2 else int(img.shape[2])
+        return img.data_ptr(), w, h, ch, w * ch, img
+    raise TypeError(f"unsupported image type {type(img)!r}")
+
+
+def _dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _result(cap: int):
+    buf = np.zeros(max(1, cap), np.float64)
+    r = OmrResultC(0.0, 0, 0, _dptr(buf), len(buf))
+    return r, buf
+
+
+def _unpack(r, buf) -> OmrResult:
+    n = min(r.n_candidates, len(buf))
+    return OmrResult(float(r.angle), int(r.status), [float(x) for x in buf[:n]])
+
+
+# --------------------------------------------------------------------------- pure host helpers
+def rotation_matrix_2d(cx, cy, angle, scale) -> np.ndarray:
+    M = np.zeros(6, np.float64)
+    _lib.load().oics_rotation_matrix_2d(C.c_float(cx), C.c_float(cy), angle, scale, _dptr(M))
+    return M
+
+
+def angle_half_range(max_angle: int, step: float) -> int:
+    return int(_lib.load().oics_angle_half_range(int(max_angle), float(step)))
+
+
+def sweep_matrices(w, h, max_angle, step, scale=1.0):
+    """-> (N, angles, M[2N, 6])"""
+    N = angle_half_range(max_angle, step)
+    M = np.zeros((max(1, 2 * N), 6), np.float64)
+    n = C.c_int32()
+    check(_lib.load().oics_sweep_matrices(w, h, int(max_angle), float(step), float(scale), _dptr(M), 2 * N, C.byref(n)))
+    return N, [float(d) * step for d in range(-N, N)], M[:2 * N]
+
+
+def rotate_geometry(cols, rows, angle, scale=1.0, clip=CLIP_DEFAULT):
+    M = np.zeros(6, np.float64)
+    dw, dh = C.c_int32(), C.c_int32()
+    check(_lib.load().oics_rotate_geometry(cols, rows, float(angle), float(scale), clip, _dptr(M), C.byref(dw), C.byref(dh)))
+    return M, dw.value, dh.value
+
+
+def projection_scale(w, h, max_w, max_h) -> float:
+    return float(_lib.load().oics_projection_scale(w, h, max_w, max_h))
+
+
+def rule_a(h_sd, v_sd, N, step) -> OmrResult:
+    h_sd = np.ascontiguousarray(h_sd, np.float64)
+    v_sd = np.ascontiguousarray(v_sd, np.float64)
+    r, buf = _result(2 * N)
+    check(_lib.load().oics_rule_a(_dptr(h_sd), _dptr(v_sd), N, float(step), C.byref(r)))
+    return _unpack(r, buf)
+
+
+def rule_b(v_sd, h_sd, N, step) -> float:
+    v_sd = np.ascontiguousarray(v_sd, np.float64)
+    h_sd = np.ascontiguousarray(h_sd, np.float64)
+    a = C.c_double()
+    check(_lib.load().oics_rule_b(_dptr(v_sd), _dptr(h_sd), N, float(step), C.byref(a)))
+    return a.value
+
+
+def lines_angle(lines, variant) -> OmrResult:
+    lines = np.ascontiguousarray(lines, np.int32).reshape(-1, 4)
+    r, buf = _result(len(lines))
+    check(_lib.load().oics_lines_angle(lines.ctypes.data_as(C.POINTER(C.c_int32)), len(lines), variant, C.byref(r)))
+    return _unpack(r, buf)
+
+
+def reconcile(p: OmrResult, edges_angle: float):
+    buf = np.ascontiguousarray(p.candidates if p.candidates else [0.0], np.float64)
+    r = OmrResultC(p.angle, p.status, len(p.candidates), _dptr(buf), len(p.candidates))
+    a, need = C.c_double(), C.c_int32()
+    check(_lib.load().oics_reconcile(C.byref(r), float(edges_angle), C.byref(a), C.byref(need)))
+    return a.value, bool(need.value)
+
+
+def hough_dims(w, h, rho=1.0, theta=math.pi / 180.0):
+    na, nr = C.c_int32(), C.c_int32()
+    check(_lib.load().oics_hough_dims(w, h, rho, theta, C.byref(na), C.byref(nr)))
+    return na.value, nr.value
+
+
+# --------------------------------------------------------------------------- device context
+class Context:
+    """One CUDA context handle (oics_ctx): device scratch + stream.  Use one per host thread."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        check(self._lib.oics_create(device, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.oics_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- plumbing
+    def set_stream(self, stream_ptr: int | None):
+        check(self._lib.oics_set_stream(self._h, C.c_void_p(stream_ptr or 0)))
+
+    def synchronize(self):
+        check(self._lib.oics_synchronize(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.oics_launch_count(self._h))
+
+    def last_sweep_kernel_ms(self):
+        ms, n = C.c_double(), C.c_int32()
+        check(self._lib.oics_last_sweep_kernel_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    # -- P0
+    def preprocess(self, bgr, mode=PRE_OMR, max_w=0, max_h=0, resize_scale=1.0):
+        """-> (binary [oh, ow] uint8, scale)"""
+        p, w, h, ch, stride, keep = _describe(bgr)
+        if ch != 3:
+            raise ValueError("pre-processing expects a 3-channel image")
+        scale = projection_scale(w, h, max_w, max_h) if mode == PRE_OMR else float(resize_scale)
+        ow = w if scale == 1.0 else int(float(w) * scale)
+        oh = h if scale == 1.0 else int(float(h) * scale)
+        out = np.empty((max(oh, 1), max(ow, 1)), np.uint8)
+        rw, rh, rs = C.c_int32(), C.c_int32(), C.c_double()
+        check(self._lib.oics_preprocess(self._h, p, w, h, stride, mode, max_w, max_h, float(resize_scale),
+                                        out.ctypes.data, out.size, C.byref(rw), C.byref(rh), C.byref(rs)))
+        return out[:rh.value, :rw.value], rs.value
+
+    # -- P2-P4
+    def projection_sweep(self, binary, M, want_sums=False):
+        """-> (v_sd, h_sd[, sums])"""
+        p, w, h, ch, stride, keep = _describe(binary)
+        M = np.ascontiguousarray(M, np.float64).reshape(-1, 6)
+        n = len(M)
+        v, hh = np.zeros(n, np.float64), np.zeros(n, np.float64)
+        sums = np.zeros((n, 4), np.int64) if want_sums else None
+        check(self._lib.oics_projection_sweep(self._h, p, w, h, stride, _dptr(M), n, v.ctypes.data, hh.ctypes.data,
+                                              sums.ctypes.data if want_sums else None))
+        return (v, hh, sums) if want_sums else (v, hh)
+
+    def projection_sweep_batch(self, bins, n_cards, w, h, M, card_stride=None, stride=None, out=None):
+        """bins: device pointer (int) or numpy [n, h, w]; -> (v_sd, h_sd) as [n_cards, n_angles]."""
+        M = np.ascontiguousarray(M, np.float64).reshape(-1, 6)
+        n = len(M)
+        if isinstance(bins, np.ndarray):
+            bins = np.ascontiguousarray(bins, np.uint8)
+            ptr, keep = bins.ctypes.data, bins
+        elif hasattr(bins, "data_ptr"):
+            ptr, keep = bins.data_ptr(), bins
+        else:
+            ptr, keep = int(bins), None
+        stride = stride or w
+        card_stride = card_stride or stride * h
+        if out is None:
+            v, hh = np.zeros((n_cards, n), np.float64), np.zeros((n_cards, n), np.float64)
+        else:
+            v, hh = out
+        check(self._lib.oics_projection_sweep_batch(self._h, ptr, n_cards, card_stride, w, h, stride, _dptr(M), n,
+                                                    v.ctypes.data, hh.ctypes.data))
+        return v, hh
+
+    def projection_counts(self, binary, M):
+        p, w, h, ch, stride, keep = _describe(binary)
+        M = np.ascontiguousarray(M, np.float64).reshape(6)
+        row, col = np.zeros(h, np.int32), np.zeros(w, np.int32)
+        check(self._lib.oics_projection_counts(self._h, p, w, h, stride, _dptr(M), row.ctypes.data, col.ctypes.data))
+        return row, col
+
+    def projection_standard_deviations(self, binary):
+        """transfer::get_projection_standard_deviations -> (vertical_sd, horizontal_sd)."""
+        p, w, h, ch, stride, keep = _describe(binary)
+        v, hh = C.c_double(), C.c_double()
+        check(self._lib.oics_projection_standard_deviations(self._h, p, w, h, stride, C.byref(v), C.byref(hh)))
+        return v.value, hh.value
+
+    # -- estimators
+    def result_from_projection(self, bgr, max_angle, step, max_w, max_h) -> OmrResult:
+        p, w, h, ch, stride, keep = _describe(bgr)
+        r, buf = _result(2 * angle_half_range(max_angle, step))
+        check(self._lib.oics_result_from_projection(self._h, p, w, h, stride, int(max_angle), float(step), max_w, max_h,
+                                                    C.byref(r)))
+        return _unpack(r, buf)
+
+    def angle_with_projections(self, bgr, max_angle, step, resize_scale, threads=1) -> float:
+        p, w, h, ch, stride, keep = _describe(bgr)
+        a = C.c_double()
+        check(self._lib.oics_angle_with_projections(self._h, p, w, h, stride, int(max_angle), float(step),
+                                                    float(resize_scale), int(threads), C.byref(a)))
+        return a.value
+
+    def result_from_edges_detection(self, img, min_len, max_gap) -> OmrResult:
+        p, w, h, ch, stride, keep = _describe(img)
+        r, buf = _result(1 << 16)
+        check(self._lib.oics_result_from_edges_detection(self._h, p, ch, w, h, stride, float(min_len), float(max_gap),
+                                                         C.byref(r)))
+        return _unpack(r, buf)
+
+    def angle_with_hough(self, gray, min_len, max_gap) -> float:
+        p, w, h, ch, stride, keep = _describe(gray)
+        a = C.c_double()
+        check(self._lib.oics_angle_with_hough(self._h, p, w, h, stride, float(min_len), float(max_gap), C.byref(a)))
+        return a.value
+
+    def angle_with_fft(self, gray, canny1, canny2, min_len, max_gap) -> float:
+        p, w, h, ch, stride, keep = _describe(gray)
+        a = C.c_double()
+        check(self._lib.oics_angle_with_fft(self._h, p, w, h, stride, float(canny1), float(canny2), float(min_len),
+                                            float(max_gap), C.byref(a)))
+        return a.value
+
+    def result_from_fourier_transform(self, bgr, canny_weak, canny_strong, min_len, max_gap) -> OmrResult:
+        p, w, h, ch, stride, keep = _describe(bgr)
+        r, buf = _result(1 << 16)
+        check(self._lib.oics_result_from_fourier_transform(self._h, p, w, h, stride, float(canny_weak),
+                                                           float(canny_strong), float(min_len), float(max_gap),
+                                                           C.byref(r)))
+        return _unpack(r, buf)
+
+    # -- building blocks
+    def canny(self, img, lo, hi) -> np.ndarray:
+        p, w, h, ch, stride, keep = _describe(img)
+        out = np.empty((h, w), np.uint8)
+        check(self._lib.oics_canny(self._h, p, ch, w, h, stride, float(lo), float(hi), out.ctypes.data, w))
+        return out
+
+    def hough_accumulate(self, edges, rho=1.0, theta=math.pi / 180.0) -> np.ndarray:
+        p, w, h, ch, stride, keep = _describe(edges)
+        na, nr = hough_dims(w, h, rho, theta)
+        acc = np.zeros((na, nr), np.int32)
+        check(self._lib.oics_hough_accumulate(self._h, p, w, h, stride, rho, theta, acc.ctypes.data))
+        return acc
+
+    def hough_lines_p(self, edges, threshold, min_len, max_gap, rho=1.0, theta=math.pi / 180.0) -> np.ndarray:
+        p, w, h, ch, stride, keep = _describe(edges)
+        cap = 1 << 14
+        while True:
+            lines = np.zeros((cap, 4), np.int32)
+            n = C.c_int32()
+            rc = self._lib.oics_hough_lines_p(self._h, p, w, h, stride, rho, theta, int(threshold), float(min_len),
+                                              float(max_gap), lines.ctypes.data_as(C.POINTER(C.c_int32)), cap, C.byref(n))
+            if rc == _lib.ERR_CAPACITY:
+                cap = n.value
+                continue
+            check(rc)
+            return lines[:n.value].copy()
+
+    def fft_image(self, gray, want_magnitude=False):
+        p, w, h, ch, stride, keep = _describe(gray)
+        log8 = np.empty((h, w), np.uint8)
+        mag8 = np.empty((h, w), np.uint8) if want_magnitude else None
+        check(self._lib.oics_fft_image(self._h, p, w, h, stride, mag8.ctypes.data if want_magnitude else None,
+                                       log8.ctypes.data))
+        return (mag8, log8)
+
+    # -- W1
+    def warp_affine(self, src, M, dsize, flags=INTER_NEAREST, border=WHITE, out=None):
+        p, w, h, ch, stride, keep = _describe(src)
+        dw, dh = dsize
+        M = np.ascontiguousarray(M, np.float64).reshape(6)
+        b = (C.c_uint8 * 4)(*[int(v) & 255 for v in border])
+        if out is None:
+            out = np.empty((dh, dw) if ch == 1 else (dh, dw, ch), np.uint8)
+        op, ow, oh, och, ostride, okeep = _describe(out)
+        check(self._lib.oics_warp_affine(self._h, p, ch, w, h, stride, _dptr(M), flags, b, op, dw, dh, ostride))
+        return out
+
+    def rotate_mat(self, src, angle, scale=1.0, flags=INTER_NEAREST, border=WHITE, clip=CLIP_DEFAULT):
+        """transfer::rotate_mat (transfer.rs:459-467)."""
+        p, w, h, ch, stride, keep = _describe(src)
+        _, dw, dh = rotate_geometry(w, h, angle, scale, clip)
+        out = np.empty((dh, dw) if ch == 1 else (dh, dw, ch), np.uint8)
+        b = (C.c_uint8 * 4)(*[int(v) & 255 for v in border])
+        rw, rh = C.c_int32(), C.c_int32()
+        check(self._lib.oics_rotate(self._h, p, ch, w, h, stride, float(angle), float(scale), flags, b, clip,
+                                    out.ctypes.data, out.size, C.byref(rw), C.byref(rh)))
+        return out
+
+    # -- pipeline
+    def correct_default(self, bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, want_image=True):
+        """omr::correct_default on memory buffers -> (angle, need_check, deskewed BGR or None)."""
+        p, w, h, ch, stride, keep = _describe(bgr)
+        out = None
+        cap = 0
+        if want_image:
+            # CONTAIN output is at most (w+h) x (w+h)
+            side = int(math.ceil(math.hypot(w, h))) + 2
+            out = np.empty(side * side * 3, np.uint8)
+            cap = out.size
+        dw, dh, a, need = C.c_int32(), C.c_int32(), C.c_double(), C.c_int32()
+        check(self._lib.oics_correct_default(self._h, p, w, h, stride, int(max_angle), float(step), max_w, max_h,
+                                             float(hough_min_len), float(hough_max_gap),
+                                             out.ctypes.data if want_image else None, cap, C.byref(dw), C.byref(dh),
+                                             C.byref(a), C.byref(need)))
+        img = out[:dw.value * dh.value * 3].reshape(dh.value, dw.value, 3) if want_image else None
+        return a.value, bool(need.value), img
+
+    def correct_batch(self, bgrs, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, outs=None):
+        """bgrs: numpy [n, h, w, 3] (host) or CUDA tensor of that shape.
+        outs: optional list of n writable uint8 numpy buffers for the deskewed cards.
+        -> (angles, need_checks, statuses, dst sizes [n, 2])"""
+        if isinstance(bgrs, np.ndarray):
+            bgrs = np.ascontiguousarray(bgrs, np.uint8)
+            ptr = bgrs.ctypes.data
+        else:
+            ptr = bgrs.data_ptr()
+        n, h, w = int(bgrs.shape[0]), int(bgrs.shape[1]), int(bgrs.shape[2])
+        angles = np.zeros(n, np.float64)
+        needs = np.zeros(n, np.int32)
+        stats = np.zeros(n, np.int32)
+        sizes = np.zeros((2, n), np.int32)
+        dsts = caps = None
+        if outs is not None:
+            dsts = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+            caps = (C.c_size_t * n)(*[o.size for o in outs])
+        ip = C.POINTER(C.c_int32)
+        check(self._lib.oics_correct_batch(self._h, ptr, n, w * h * 3, w, h, w * 3, int(max_angle), float(step), max_w,
+                                           max_h, float(hough_min_len), float(hough_max_gap), dsts, caps,
+                                           sizes[0].ctypes.data_as(ip), sizes[1].ctypes.data_as(ip), _dptr(angles),
+                                           needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
+        return angles, needs.astype(bool), stats, sizes.T.copy()
+
+
+_default = {}
+_default_lock = threading.Lock()
+
+
+def default_context(device: int = 0) -> Context:
+    """A lazily created per-(thread, device) context for the module-level mirror functions."""
+    key = (threading.get_ident(), device)
+    with _default_lock:
+        ctx = _default.get(key)
+        if ctx is None:
+            ctx = _default[key] = Context(device)
+        return ctx

@@ -1,0 +1,585 @@
+// The compute entry points of include/oics_cuda.h: argument checks, host/device
+// staging, and the reference's call sequences expressed over the device kernels.
+#include <cmath>
+
+#include "common.h"
+
+namespace oics {
+int32_t plain_std_devs_device(oics_ctx *ctx, const uint8_t *dbin, int w, int h, size_t stride, double *d_vsd,
+                              double *d_hsd);
+
+static int32_t check_image(const void *p, int w, int h, int stride, int ch)
+{
+    if (!p) { set_error("image pointer is null"); return OICS_ERR_INVALID_ARG; }
+    if (w <= 0 || h <= 0) { set_error("image size %dx%d is empty", w, h); return OICS_ERR_INVALID_ARG; }
+    if (stride < w * ch) { set_error("stride %d smaller than a row (%d bytes)", stride, w * ch); return OICS_ERR_INVALID_ARG; }
+    return OICS_OK;
+}
+
+// (int)((size.width as f64) * scale) of omr.rs:120-121 / transfer.rs:77-78
+static int scaled_dim(int v, double scale) { return (int)((double)v * scale); }
+
+// sweep over device-resident binary card(s); results to host or device pointers
+static int32_t sweep_to(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t card_stride, int w, int h,
+                        size_t stride, const double *M, int n_angles, double *v_sd, double *h_sd, int64_t *sums,
+                        int32_t *counts_out_host_or_dev)
+{
+    const size_t n = (size_t)n_cards * n_angles;
+    OICS_TRY(ctx->sd.ensure(2 * n * sizeof(double)));
+    double *dv = ctx->sd.as<double>(), *dh = dv + n;
+    int64_t *dsums = nullptr;
+    if (sums) {
+        OICS_TRY(ctx->sums.ensure(4 * n * sizeof(int64_t)));
+        dsums = ctx->sums.as<int64_t>();
+    }
+    int32_t *dcounts = nullptr;
+    if (counts_out_host_or_dev) {
+        OICS_TRY(ctx->misc.ensure((size_t)n_angles * (h + w) * sizeof(int32_t)));
+        dcounts = ctx->misc.as<int32_t>();
+    }
+    OICS_TRY(sweep_device(ctx, dbins, n_cards, card_stride, w, h, stride, M, n_angles, dv, dh, dsums, dcounts));
+    OICS_TRY(copy_out(ctx, v_sd, dv, n * sizeof(double)));
+    OICS_TRY(copy_out(ctx, h_sd, dh, n * sizeof(double)));
+    if (sums) OICS_TRY(copy_out(ctx, sums, dsums, 4 * n * sizeof(int64_t)));
+    if (dcounts) OICS_TRY(copy_out(ctx, counts_out_host_or_dev, dcounts, (size_t)n_angles * (h + w) * sizeof(int32_t)));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+// P0 + sweep for one BGR card already on the device -> host std-dev arrays
+static int32_t estimate_projection(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int mode,
+                                   double scale, uint16_t max_angle, double step, double rot_scale,
+                                   std::vector<double> *v_sd, std::vector<double> *h_sd, int *N_out)
+{
+    const int ow = scale == 1.0 ? w : scaled_dim(w, scale), oh = scale == 1.0 ? h : scaled_dim(h, scale);
+    if (ow <= 0 || oh <= 0) { set_error("scaled size %dx%d is empty", ow, oh); return OICS_ERR_INVALID_ARG; }
+    OICS_TRY(ctx->bin.ensure((size_t)ow * oh));
+    OICS_TRY(preprocess_device(ctx, dbgr, w, h, stride, mode, ow, oh, ctx->bin.as<uint8_t>()));
+    const int N = oics_angle_half_range(max_angle, step);
+    *N_out = N;
+    v_sd->assign((size_t)2 * N, 0.0);
+    h_sd->assign((size_t)2 * N, 0.0);
+    if (N == 0) return OICS_OK;
+    std::vector<double> M((size_t)2 * N * 6);
+    int n_angles = 0;
+    OICS_TRY(oics_sweep_matrices(ow, oh, max_angle, step, rot_scale, M.data(), 2 * N, &n_angles));
+    return sweep_to(ctx, ctx->bin.as<uint8_t>(), 1, 0, ow, oh, (size_t)ow, M.data(), n_angles, v_sd->data(),
+                    h_sd->data(), nullptr, nullptr);
+}
+
+static int32_t edges_result(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, double lo,
+                            double hi, int threshold, double min_len, double max_gap, int variant,
+                            oics_omr_result *result)
+{
+    OICS_TRY(ctx->edges.ensure((size_t)w * h));
+    if (lo > hi) std::swap(lo, hi);
+    OICS_TRY(canny_device(ctx, dsrc, ch, w, h, stride, (int)std::floor(lo), (int)std::floor(hi), ctx->edges.as<uint8_t>()));
+    std::vector<int32_t> lines;
+    int cap = 1 << 14, n = 0;
+    for (;;) {
+        lines.resize((size_t)cap * 4);
+        OICS_TRY(hough_lines_p_device(ctx, ctx->edges.as<uint8_t>(), w, h, (size_t)w, 1.0, 3.14159265358979323846 / 180.0,
+                                      threshold, (int)std::lrint(min_len), (int)std::lrint(max_gap), lines.data(), cap, &n));
+        if (n <= cap) break;
+        cap = n;
+    }
+    return oics_lines_angle(lines.data(), n, variant, result);
+}
+
+}  // namespace oics
+
+using namespace oics;
+
+extern "C" {
+
+OICS_API int32_t oics_preprocess(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h, int32_t stride,
+                                 int32_t mode, int32_t max_w, int32_t max_h, double resize_scale, uint8_t *out_bin,
+                                 size_t out_cap, int32_t *out_w, int32_t *out_h, double *out_scale)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(out_bin && out_w && out_h);
+    OICS_ARG(mode == OICS_PRE_OMR || mode == OICS_PRE_PROJECTION);
+    const double scale = mode == OICS_PRE_OMR ? oics_projection_scale(w, h, max_w, max_h) : resize_scale;
+    // omr.rs always calls resize (identity size = copy); scale_self early-outs on 1.0
+    const int ow = scale == 1.0 ? w : scaled_dim(w, scale), oh = scale == 1.0 ? h : scaled_dim(h, scale);
+    *out_w = ow;
+    *out_h = oh;
+    if (out_scale) *out_scale = scale;
+    if (ow <= 0 || oh <= 0) { set_error("scaled size %dx%d is empty", ow, oh); return OICS_ERR_INVALID_ARG; }
+    if ((size_t)ow * oh > out_cap) {
+        set_error("output needs %zu bytes, capacity %zu", (size_t)ow * oh, out_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    uint8_t *dout = is_device_ptr(out_bin) ? out_bin : nullptr;
+    if (!dout) {
+        OICS_TRY(ctx->bin.ensure((size_t)ow * oh));
+        dout = ctx->bin.as<uint8_t>();
+    }
+    OICS_TRY(preprocess_device(ctx, dsrc, w, h, dstride, mode, ow, oh, dout));
+    if (dout != out_bin) OICS_TRY(copy_out(ctx, out_bin, dout, (size_t)ow * oh));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_projection_sweep(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
+                                       const double *M, int32_t n_angles, double *v_sd, double *h_sd, int64_t *sums)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bin, w, h, stride, 1));
+    OICS_ARG(n_angles >= 0 && (n_angles == 0 || (M && v_sd && h_sd)));
+    if (n_angles == 0) return OICS_OK;
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bin, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    return sweep_to(ctx, dsrc, 1, 0, w, h, dstride, M, n_angles, v_sd, h_sd, sums, nullptr);
+}
+
+OICS_API int32_t oics_projection_sweep_batch(oics_ctx *ctx, const uint8_t *bins, int32_t n_cards, size_t card_stride,
+                                             int32_t w, int32_t h, int32_t stride, const double *M,
+                                             int32_t n_angles, double *v_sd, double *h_sd)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bins, w, h, stride, 1));
+    OICS_ARG(n_cards >= 0 && n_angles >= 0);
+    if (n_cards == 0 || n_angles == 0) return OICS_OK;
+    OICS_ARG(M && v_sd && h_sd);
+    OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
+    const uint8_t *dsrc = bins;
+    size_t dcard = card_stride, dstride = (size_t)stride;
+    if (!is_device_ptr(bins)) {
+        // host batch: upload tightly packed
+        OICS_TRY(ctx->in_img.ensure((size_t)n_cards * w * h));
+        for (int c = 0; c < n_cards; c++)
+            OICS_CUDA_TRY(cudaMemcpy2DAsync(ctx->in_img.as<uint8_t>() + (size_t)c * w * h, (size_t)w,
+                                            bins + (size_t)c * card_stride, (size_t)stride, (size_t)w, (size_t)h,
+                                            cudaMemcpyHostToDevice, ctx->stream));
+        dsrc = ctx->in_img.as<uint8_t>();
+        dcard = (size_t)w * h;
+        dstride = (size_t)w;
+    }
+    return sweep_to(ctx, dsrc, n_cards, dcard, w, h, dstride, M, n_angles, v_sd, h_sd, nullptr, nullptr);
+}
+
+OICS_API int32_t oics_projection_counts(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
+                                        const double M[6], int32_t *row_counts, int32_t *col_counts)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bin, w, h, stride, 1));
+    OICS_ARG(M && row_counts && col_counts);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bin, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    std::vector<int32_t> counts((size_t)h + w);
+    double v, hh;
+    OICS_TRY(sweep_to(ctx, dsrc, 1, 0, w, h, dstride, M, 1, &v, &hh, nullptr, counts.data()));
+    if (is_device_ptr(row_counts)) OICS_CUDA_TRY(cudaMemcpy(row_counts, counts.data(), sizeof(int32_t) * h, cudaMemcpyHostToDevice));
+    else memcpy(row_counts, counts.data(), sizeof(int32_t) * h);
+    if (is_device_ptr(col_counts)) OICS_CUDA_TRY(cudaMemcpy(col_counts, counts.data() + h, sizeof(int32_t) * w, cudaMemcpyHostToDevice));
+    else memcpy(col_counts, counts.data() + h, sizeof(int32_t) * w);
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_projection_standard_deviations(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h,
+                                                     int32_t stride, double *v_sd, double *h_sd)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bin, w, h, stride, 1));
+    OICS_ARG(v_sd && h_sd);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bin, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    OICS_TRY(ctx->sd.ensure(2 * sizeof(double)));
+    double *d = ctx->sd.as<double>();
+    OICS_TRY(plain_std_devs_device(ctx, dsrc, w, h, dstride, d, d + 1));
+    double out[2];
+    OICS_CUDA_TRY(cudaMemcpyAsync(out, d, sizeof(out), cudaMemcpyDeviceToHost, ctx->stream));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    *v_sd = out[0];
+    *h_sd = out[1];
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_result_from_projection(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h,
+                                             int32_t stride, uint16_t max_angle, double step, int32_t max_w,
+                                             int32_t max_h, oics_omr_result *result)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(result);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    const double scale = oics_projection_scale(w, h, max_w, max_h);
+    std::vector<double> v, hh;
+    int N = 0;
+    // the rotation re-applies the resize scale (omr.rs:159-163)
+    OICS_TRY(estimate_projection(ctx, dsrc, w, h, dstride, OICS_PRE_OMR, scale, max_angle, step, scale, &v, &hh, &N));
+    return oics_rule_a(hh.data(), v.data(), N, step, result);
+}
+
+OICS_API int32_t oics_angle_with_projections(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h,
+                                             int32_t stride, uint16_t max_angle, double step, double resize_scale,
+                                             size_t threads, double *angle)
+{
+    (void)threads;  // single-thread semantics, see header
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(angle);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    std::vector<double> v, hh;
+    int N = 0;
+    OICS_TRY(estimate_projection(ctx, dsrc, w, h, dstride, OICS_PRE_PROJECTION, resize_scale, max_angle, step, 1.0, &v,
+                                 &hh, &N));
+    if (N == 0) { set_error("empty angle range (the reference indexes vertical_vec[0] and panics)"); return OICS_ERR_INVALID_ARG; }
+    return oics_rule_b(v.data(), hh.data(), N, step, angle);
+}
+
+OICS_API int32_t oics_warp_affine(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h,
+                                  int32_t stride, const double M[6], int32_t interp, const uint8_t border[4],
+                                  uint8_t *dst, int32_t dst_w, int32_t dst_h, int32_t dst_stride)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_ARG(ch >= 1 && ch <= 4);
+    OICS_TRY(check_image(src, w, h, stride, ch));
+    OICS_ARG(M && border && dst && dst_w > 0 && dst_h > 0 && dst_stride >= dst_w * ch);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, src, (size_t)w * ch, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    if (is_device_ptr(dst)) {
+        OICS_TRY(warp_device(ctx, dsrc, ch, w, h, dstride, M, interp, border, dst, dst_w, dst_h, (size_t)dst_stride));
+    } else {
+        const size_t row = (size_t)dst_w * ch;
+        OICS_TRY(ctx->out_img.ensure(row * dst_h));
+        OICS_TRY(warp_device(ctx, dsrc, ch, w, h, dstride, M, interp, border, ctx->out_img.as<uint8_t>(), dst_w, dst_h, row));
+        OICS_TRY(stage_out(ctx, ctx->out_img.p, row, dst_h, dst, (size_t)dst_stride));
+    }
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_rotate(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                             double angle, double scale, int32_t interp, const uint8_t border[4], int32_t clip,
+                             uint8_t *dst, size_t dst_cap, int32_t *dst_w, int32_t *dst_h)
+{
+    OICS_ARG(dst_w && dst_h);
+    double M[6];
+    OICS_TRY(oics_rotate_geometry(w, h, angle, scale, clip, M, dst_w, dst_h));
+    if (*dst_w <= 0 || *dst_h <= 0) { set_error("rotated size %dx%d is empty", *dst_w, *dst_h); return OICS_ERR_INVALID_ARG; }
+    const size_t need = (size_t)*dst_w * *dst_h * ch;
+    if (need > dst_cap) {
+        set_error("rotated image needs %zu bytes, capacity %zu", need, dst_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    return oics_warp_affine(ctx, src, ch, w, h, stride, M, interp, border, dst, *dst_w, *dst_h, *dst_w * ch);
+}
+
+OICS_API int32_t oics_canny(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                            double lo, double hi, uint8_t *edges, int32_t edges_stride)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_ARG(ch == 1 || ch == 3);
+    OICS_TRY(check_image(src, w, h, stride, ch));
+    OICS_ARG(edges && edges_stride >= w);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, src, (size_t)w * ch, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    if (lo > hi) std::swap(lo, hi);
+    OICS_TRY(ctx->edges.ensure((size_t)w * h));
+    OICS_TRY(canny_device(ctx, dsrc, ch, w, h, dstride, (int)std::floor(lo), (int)std::floor(hi), ctx->edges.as<uint8_t>()));
+    OICS_TRY(stage_out(ctx, ctx->edges.p, (size_t)w, h, edges, (size_t)edges_stride));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_hough_accumulate(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h, int32_t stride,
+                                       double rho, double theta, int32_t *accum)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(edges, w, h, stride, 1));
+    OICS_ARG(accum && rho > 0 && theta > 0);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, edges, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    int na, nr;
+    hough_geometry(w, h, rho, theta, &na, &nr, nullptr);
+    const size_t bytes = (size_t)na * nr * sizeof(int32_t);
+    int32_t *dacc = is_device_ptr(accum) ? accum : nullptr;
+    if (!dacc) {
+        OICS_TRY(ctx->accum.ensure(bytes));
+        dacc = ctx->accum.as<int32_t>();
+    }
+    OICS_TRY(hough_accumulate_device(ctx, dsrc, w, h, dstride, rho, theta, dacc));
+    if (dacc != accum) OICS_TRY(copy_out(ctx, accum, dacc, bytes));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_hough_lines_p(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h, int32_t stride,
+                                    double rho, double theta, int32_t threshold, double min_line_length,
+                                    double max_line_gap, int32_t *lines, int32_t cap, int32_t *n_lines)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(edges, w, h, stride, 1));
+    OICS_ARG(n_lines && cap >= 0 && (cap == 0 || lines) && rho > 0 && theta > 0);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, edges, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    int n = 0;
+    OICS_TRY(hough_lines_p_device(ctx, dsrc, w, h, dstride, rho, theta, threshold, (int)std::lrint(min_line_length),
+                                  (int)std::lrint(max_line_gap), lines, cap, &n));
+    *n_lines = n;
+    if (n > cap) {
+        set_error("found %d segments, capacity %d", n, cap);
+        return OICS_ERR_CAPACITY;
+    }
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_result_from_edges_detection(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w,
+                                                  int32_t h, int32_t stride, double min_line_length,
+                                                  double max_line_gap, oics_omr_result *result)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_ARG(ch == 1 || ch == 3);
+    OICS_TRY(check_image(src, w, h, stride, ch));
+    OICS_ARG(result);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, src, (size_t)w * ch, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    return edges_result(ctx, dsrc, ch, w, h, dstride, 50.0, 150.0, 0, min_line_length, max_line_gap, OICS_LINES_OMR, result);
+}
+
+OICS_API int32_t oics_angle_with_hough(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
+                                       double min_line_length, double max_line_gap, double *angle)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(gray, w, h, stride, 1));
+    OICS_ARG(angle);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, gray, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    oics_omr_result r = {0, 0, 0, nullptr, 0};
+    OICS_TRY(edges_result(ctx, dsrc, 1, w, h, dstride, 50.0, 150.0, 0, min_line_length, max_line_gap, OICS_LINES_HOUGH, &r));
+    *angle = r.angle;
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_fft_image(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
+                                uint8_t *mag8, uint8_t *log8)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(gray, w, h, stride, 1));
+    OICS_ARG(log8);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, gray, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    OICS_TRY(ctx->tmp8a.ensure((size_t)w * h));
+    OICS_TRY(ctx->tmp8b.ensure((size_t)w * h));
+    OICS_TRY(fft_image_device(ctx, dsrc, w, h, dstride, mag8 ? ctx->tmp8a.as<uint8_t>() : nullptr, ctx->tmp8b.as<uint8_t>()));
+    if (mag8) OICS_TRY(copy_out(ctx, mag8, ctx->tmp8a.p, (size_t)w * h));
+    OICS_TRY(copy_out(ctx, log8, ctx->tmp8b.p, (size_t)w * h));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_angle_with_fft(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
+                                     double canny1, double canny2, double min_line_length, double max_line_gap,
+                                     double *angle)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(gray, w, h, stride, 1));
+    OICS_ARG(angle);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, gray, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    OICS_TRY(ctx->tmp8b.ensure((size_t)w * h));
+    OICS_TRY(fft_image_device(ctx, dsrc, w, h, dstride, nullptr, ctx->tmp8b.as<uint8_t>()));
+    oics_omr_result r = {0, 0, 0, nullptr, 0};
+    OICS_TRY(edges_result(ctx, ctx->tmp8b.as<uint8_t>(), 1, w, h, (size_t)w, canny1, canny2, 100, min_line_length,
+                          max_line_gap, OICS_LINES_FFT, &r));
+    *angle = r.angle;
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_result_from_fourier_transform(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h,
+                                                    int32_t stride, double canny_weak, double canny_strong,
+                                                    double min_line_length, double max_line_gap,
+                                                    oics_omr_result *result)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(result);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    OICS_TRY(ctx->gray.ensure((size_t)w * h));
+    OICS_TRY(gray_device(ctx, dsrc, w, h, dstride, ctx->gray.as<uint8_t>()));
+    OICS_TRY(ctx->tmp8b.ensure((size_t)w * h));
+    OICS_TRY(fft_image_device(ctx, ctx->gray.as<uint8_t>(), w, h, (size_t)w, nullptr, ctx->tmp8b.as<uint8_t>()));
+    // omr.rs:322-336: Canny on the log image, then get_result_from_edges_detection
+    // runs Canny(50,150) AGAIN on that edge map, threshold 0
+    OICS_TRY(ctx->tmp8a.ensure((size_t)w * h));
+    if (canny_weak > canny_strong) std::swap(canny_weak, canny_strong);
+    OICS_TRY(canny_device(ctx, ctx->tmp8b.as<uint8_t>(), 1, w, h, (size_t)w, (int)std::floor(canny_weak),
+                          (int)std::floor(canny_strong), ctx->tmp8a.as<uint8_t>()));
+    return edges_result(ctx, ctx->tmp8a.as<uint8_t>(), 1, w, h, (size_t)w, 50.0, 150.0, 0, min_line_length, max_line_gap,
+                        OICS_LINES_OMR, result);
+}
+
+// correct_default for a BGR card already on the device
+static int32_t correct_one(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint16_t max_angle,
+                           double step, int max_w, int max_h, double min_len, double max_gap, uint8_t *dst,
+                           size_t dst_cap, int32_t *dst_w, int32_t *dst_h, double *angle, int32_t *need_check)
+{
+    const double scale = oics_projection_scale(w, h, max_w, max_h);
+    std::vector<double> v, hh;
+    int N = 0;
+    OICS_TRY(estimate_projection(ctx, dbgr, w, h, stride, OICS_PRE_OMR, scale, max_angle, step, scale, &v, &hh, &N));
+    std::vector<double> cand((size_t)std::max(1, 2 * N));
+    oics_omr_result p = {0, 0, 0, cand.data(), (int32_t)cand.size()};
+    OICS_TRY(oics_rule_a(hh.data(), v.data(), N, step, &p));
+    double a;
+    int32_t need;
+    if (p.status == OICS_BELIEVED) {
+        a = p.angle;
+        need = 0;
+    } else {
+        // omr.rs:366: Canny runs on the 3-channel source
+        oics_omr_result e = {0, 0, 0, nullptr, 0};
+        OICS_TRY(edges_result(ctx, dbgr, 3, w, h, stride, 50.0, 150.0, 0, min_len, max_gap, OICS_LINES_OMR, &e));
+        OICS_TRY(oics_reconcile(&p, e.angle, &a, &need));
+    }
+    *angle = a;
+    *need_check = need;
+    double M[6];
+    int dw, dh;
+    OICS_TRY(oics_rotate_geometry(w, h, a, 1.0, OICS_CLIP_CONTAIN, M, &dw, &dh));
+    if (dst_w) *dst_w = dw;
+    if (dst_h) *dst_h = dh;
+    if (!dst) return OICS_OK;
+    const size_t row = (size_t)dw * 3, need_bytes = row * dh;
+    if (need_bytes > dst_cap) {
+        set_error("deskewed card needs %zu bytes, capacity %zu", need_bytes, dst_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    const uint8_t white[4] = {255, 255, 255, 0};
+    if (is_device_ptr(dst)) {
+        OICS_TRY(warp_device(ctx, dbgr, 3, w, h, stride, M, OICS_INTER_NEAREST, white, dst, dw, dh, row));
+    } else {
+        OICS_TRY(ctx->out_img.ensure(need_bytes));
+        OICS_TRY(warp_device(ctx, dbgr, 3, w, h, stride, M, OICS_INTER_NEAREST, white, ctx->out_img.as<uint8_t>(), dw, dh, row));
+        OICS_TRY(copy_out(ctx, dst, ctx->out_img.p, need_bytes));
+    }
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h, int32_t stride,
+                                      uint16_t max_angle, double step, int32_t max_w, int32_t max_h,
+                                      double hough_min_line_length, double hough_max_line_gap, uint8_t *dst,
+                                      size_t dst_cap, int32_t *dst_w, int32_t *dst_h, double *angle,
+                                      int32_t *need_check)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(angle && need_check);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    return correct_one(ctx, dsrc, w, h, dstride, max_angle, step, max_w, max_h, hough_min_line_length,
+                       hough_max_line_gap, dst, dst_cap, dst_w, dst_h, angle, need_check);
+}
+
+OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
+                                    int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
+                                    int32_t max_w, int32_t max_h, double hough_min_line_length,
+                                    double hough_max_line_gap, uint8_t *const *dsts, const size_t *dst_caps,
+                                    int32_t *dst_ws, int32_t *dst_hs, double *angles, int32_t *need_checks,
+                                    int32_t *statuses)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgrs, w, h, stride, 3));
+    OICS_ARG(n_cards >= 0 && angles && need_checks && statuses);
+    OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
+    OICS_ARG(!dsts || dst_caps);
+    const bool dev = is_device_ptr(bgrs);
+    // Double-buffered upload: card i+1 is copied on a side stream while card i runs.
+    cudaStream_t up = nullptr;
+    cudaEvent_t ready[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr};
+    DevBuf *slot[2] = {&ctx->in_img, &ctx->in_img2};
+    const size_t row = (size_t)w * 3;
+    if (!dev) {
+        OICS_CUDA_TRY(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            OICS_TRY(slot[i]->ensure(row * h));
+            OICS_CUDA_TRY(cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming));
+            OICS_CUDA_TRY(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming));
+        }
+        if (n_cards > 0) {
+            OICS_CUDA_TRY(cudaMemcpy2DAsync(slot[0]->p, row, bgrs, (size_t)stride, row, (size_t)h, cudaMemcpyHostToDevice, up));
+            OICS_CUDA_TRY(cudaEventRecord(ready[0], up));
+        }
+    }
+    int32_t rc = OICS_OK;
+    for (int c = 0; c < n_cards; c++) {
+        const uint8_t *dsrc = bgrs + (size_t)c * card_stride;
+        size_t dstride = (size_t)stride;
+        if (!dev) {
+            const int s = c & 1;
+            if (c + 1 < n_cards) {
+                const int ns = (c + 1) & 1;
+                if (c >= 1) cudaStreamWaitEvent(up, freed[ns], 0);
+                cudaMemcpy2DAsync(slot[ns]->p, row, bgrs + (size_t)(c + 1) * card_stride, (size_t)stride, row, (size_t)h,
+                                  cudaMemcpyHostToDevice, up);
+                cudaEventRecord(ready[ns], up);
+            }
+            cudaStreamWaitEvent(ctx->stream, ready[s], 0);
+            dsrc = slot[s]->as<uint8_t>();
+            dstride = row;
+        }
+        int32_t dw = 0, dh = 0;
+        statuses[c] = correct_one(ctx, dsrc, w, h, dstride, max_angle, step, max_w, max_h, hough_min_line_length,
+                                  hough_max_line_gap, dsts ? dsts[c] : nullptr, dsts ? dst_caps[c] : 0, &dw, &dh,
+                                  &angles[c], &need_checks[c]);
+        if (!dev) cudaEventRecord(freed[c & 1], ctx->stream);
+        if (dst_ws) dst_ws[c] = dw;
+        if (dst_hs) dst_hs[c] = dh;
+        if (statuses[c] == OICS_ERR_CUDA) { rc = OICS_ERR_CUDA; break; }
+    }
+    cudaStreamSynchronize(ctx->stream);
+    if (up) {
+        cudaStreamSynchronize(up);
+        cudaStreamDestroy(up);
+        for (int i = 0; i < 2; i++) {
+            if (ready[i]) cudaEventDestroy(ready[i]);
+            if (freed[i]) cudaEventDestroy(freed[i]);
+        }
+    }
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,133 @@
+// Internal plumbing shared by the kernels' host wrappers: context, scratch
+// buffers, error reporting, host/device pointer staging.  Not part of the ABI.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/oics_cuda.h"
+
+namespace oics {
+
+void set_error(const char *fmt, ...);
+
+#define OICS_CUDA_TRY(expr)                                                             \
+    do {                                                                                \
+        cudaError_t _e = (expr);                                                        \
+        if (_e != cudaSuccess) {                                                        \
+            ::oics::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),   \
+                              __FILE__, __LINE__);                                      \
+            return OICS_ERR_CUDA;                                                       \
+        }                                                                               \
+    } while (0)
+
+#define OICS_TRY(expr)                 \
+    do {                               \
+        int32_t _s = (expr);           \
+        if (_s != OICS_OK) return _s;  \
+    } while (0)
+
+#define OICS_ARG(cond)                                              \
+    do {                                                            \
+        if (!(cond)) {                                              \
+            ::oics::set_error("invalid argument: %s", #cond);       \
+            return OICS_ERR_INVALID_ARG;                            \
+        }                                                           \
+    } while (0)
+
+// Grow-only device scratch buffer.
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int32_t ensure(size_t bytes);
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct PinnedBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int32_t ensure(size_t bytes);
+    void release();
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+}  // namespace oics
+
+struct oics_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;      // stream all work is issued on
+    cudaStream_t own_stream = nullptr;  // created by oics_create
+    std::mutex mu;
+    int sm_count = 0;
+    int smem_optin = 0;
+    int64_t launches = 0;
+    // sweep timing evidence
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double last_sweep_ms = 0.0;
+    int last_sweep_launches = 0;
+    // scratch
+    oics::DevBuf in_img, in_img2, out_img, gray, tmp8a, tmp8b, bin, bits, mats, tabs, counts, sd,
+        sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
+    oics::PinnedBuf pin_in, pin_out, pin_small;
+};
+
+namespace oics {
+
+bool is_device_ptr(const void *p);
+
+// Makes `src` (host or device, h rows of row_bytes with `stride`) available on the
+// device; returns the device pointer and its stride.  Host data is copied tightly
+// packed into `scratch`.
+int32_t stage_in(oics_ctx *ctx, const void *src, size_t row_bytes, int h, size_t stride, DevBuf &scratch,
+                 const uint8_t **dptr, size_t *dstride);
+// Copies a tightly packed device image to `dst` (host or device) with dst_stride.
+int32_t stage_out(oics_ctx *ctx, const void *dsrc, size_t row_bytes, int h, void *dst, size_t dst_stride);
+// Flat copies that pick the direction from the pointer kinds.
+int32_t copy_out(oics_ctx *ctx, void *dst, const void *dsrc, size_t bytes);
+int32_t copy_in(oics_ctx *ctx, void *ddst, const void *src, size_t bytes);
+
+struct CtxGuard {
+    std::unique_lock<std::mutex> lk;
+    int32_t status;
+    explicit CtxGuard(oics_ctx *ctx);
+};
+
+// ---- host logic (hostlogic.cpp) ----
+void invert_affine(const double Min[6], double M[6]);
+
+// ---- kernels' host wrappers (all enqueue on ctx->stream, no sync) ----
+// sweep.cu
+int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t card_stride, int w, int h,
+                     size_t stride, const double *M_host, int n_angles, double *d_vsd, double *d_hsd,
+                     int64_t *d_sums, int32_t *d_counts_out /* nullable: [n_angles][h+w] of card 0 */);
+// warp.cu
+int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t sstride, const double Mfwd[6],
+                    int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride);
+// preprocess.cu
+int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int mode, int ow,
+                          int oh, uint8_t *dbin /* tightly packed ow x oh */);
+int32_t gray_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint8_t *dgray);
+// canny.cu
+int32_t canny_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, int low, int high,
+                     uint8_t *dedges /* tightly packed */);
+// hough.cu
+int32_t hough_accumulate_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
+                                double theta, int32_t *daccum);
+int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
+                             double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
+                             int cap, int *n_lines);
+void hough_geometry(int w, int h, double rho, double theta, int *numangle, int *numrho, std::vector<float> *ttab);
+// fft.cu
+int32_t fft_image_device(oics_ctx *ctx, const uint8_t *dgray, int w, int h, size_t stride, uint8_t *dmag8,
+                         uint8_t *dlog8);
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+}  // namespace oics

@@ -1,0 +1,562 @@
+// Fused projection-std-dev angle sweep.
+//
+// Replaces, per candidate angle, the reference's warp_affine(flags = 0) into a
+// fresh Mat (omr.rs:165-173 / projection.rs:48-57), the zero-count pass over that
+// Mat (omr.rs:8-39 / transfer.rs:305-405) and the two std-devs (calculate.rs:13-23).
+// No rotated image is ever written: every (card, angle, tile) CTA stages the
+// bit-packed source footprint of its output tile in shared memory once, samples it
+// with OpenCV's exact fixed-point nearest-neighbour coordinates, and reduces row
+// and column zero-counts on chip.
+//
+// Data layout in HBM / L2
+//   bits   : [card][h][wp] uint32, 1 bit per pixel, bit = 1 for a BLACK pixel
+//            (byte == 0), pixel x of a row in word x/32 at bit 31-(x%32)
+//            (bit-reversed so a left shift brings the wanted bit to the sign
+//            position).  1.1 MB per A4 card: L2 resident.
+//   tables : per angle, int32 adelta[w], bdelta[w] and int2 {X0,Y0}[h]: OpenCV's
+//            AB_BITS = 10 fixed-point tables, computed once per sweep call in f64
+//            with explicit round-to-nearest ops (no FMA), shared by every card.
+//   counts : [item][h + w] int32 (rows, then columns), item = (card, angle);
+//            accumulated with one coalesced RED per warp per tile.
+#include <algorithm>
+
+#include "common.h"
+
+namespace oics {
+
+static constexpr int SW_THREADS = 256;
+static constexpr int SW_WARPS = SW_THREADS / 32;
+static constexpr int SW_GROUP = 32;  // rows per warp pass
+
+// ---------------------------------------------------------------------------
+// OpenCV's warpAffine tables for every angle of the sweep.
+__global__ void sweep_tables_kernel(const double *__restrict__ Minv, int w, int h, int wpad, int hpad,
+                                    int *__restrict__ ad, int *__restrict__ bd, int2 *__restrict__ xy)
+{
+    const int a = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const double *M = Minv + 6 * (size_t)a;
+    if (i < w) {
+        // adelta[x] = saturate_cast<int>(M[0]*x*AB_SCALE): (M0*x) rounded, then *1024 (exact)
+        double x = (double)i;
+        ad[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[0], x), 1024.0));
+        bd[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[3], x), 1024.0));
+    }
+    if (i < h) {
+        double y = (double)i;
+        int X0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(M[1], y), M[2]), 1024.0)) + 512;
+        int Y0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(M[4], y), M[5]), 1024.0)) + 512;
+        xy[(size_t)a * hpad + i] = make_int2(X0, Y0);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// 8-bit card -> reversed bit plane of black pixels.  One thread per output word.
+__global__ void pack_bits_kernel(const uint8_t *__restrict__ bins, size_t card_stride, size_t stride, int w,
+                                 int h, int wp, uint32_t *__restrict__ bits, int n_cards)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;  // word in row
+    const int y = blockIdx.y;
+    const int c = blockIdx.z;
+    if (j >= wp) return;
+    const uint8_t *row = bins + (size_t)c * card_stride + (size_t)y * stride;
+    const int x0 = j * 32;
+    uint32_t word = 0;
+    if (x0 + 32 <= w && ((reinterpret_cast<uintptr_t>(row + x0) & 15) == 0)) {
+        const uint4 *p = reinterpret_cast<const uint4 *>(row + x0);
+        uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+        uint32_t v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            uint32_t t = __vcmpeq4(v[k], 0u) & 0x01010101u;  // 1 per zero byte
+            uint32_t nib = (t * 0x08040201u) >> 24;          // byte 0 -> bit 3 ... byte 3 -> bit 0
+            word |= (nib & 0xFu) << (28 - 4 * k);
+        }
+    } else {
+        for (int k = 0; k < 32; k++) {
+            int x = x0 + k;
+            if (x < w && row[x] == 0) word |= 0x80000000u >> k;
+        }
+    }
+    bits[((size_t)c * h + y) * wp + j] = word;
+}
+
+// ---------------------------------------------------------------------------
+struct SweepArgs {
+    const uint32_t *bits;
+    size_t bits_card_words;
+    int wp, w, h;
+    const int *ad, *bd;
+    const int2 *xy;
+    int wpad, hpad;
+    int *counts;  // [item][h + w]
+    int n_angles;
+    int item0;    // first (card, angle) item of this launch
+    int tiles_x;
+    int tile_h;   // rows per tile, multiple of SW_WARPS * SW_GROUP
+    int tile_cap; // staged-tile capacity in words
+};
+
+// 32x32 bit-matrix transpose across a warp: out[lane L] bit c = in[lane c] bit L.
+__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t v, int lane)
+{
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        const uint32_t lowmask = j == 16 ? 0x0000FFFFu : j == 8 ? 0x00FF00FFu : j == 4 ? 0x0F0F0F0Fu
+                                 : j == 2 ? 0x33333333u : 0x55555555u;
+        uint32_t other = __shfl_xor_sync(0xffffffffu, v, j);
+        if (lane & j) v = (v & ~lowmask) | ((other >> j) & lowmask);
+        else v = (v & lowmask) | ((other << j) & ~lowmask);
+    }
+    return v;
+}
+
+// One sample: OpenCV's NN coordinates, one LDS, shift the wanted bit into the
+// accumulator.  `tile` words are bit-reversed, so `word << (sx & 31)` puts pixel sx
+// at bit 31 and the funnel shift appends it to acc.
+template <bool CHECK>
+__device__ __forceinline__ uint32_t sample_bit(const uint32_t *__restrict__ tile, int P, int X0, int Y0, int ad,
+                                               int bd, int nrows, int nbits, uint32_t acc)
+{
+    const int a = X0 + ad;
+    const int b = Y0 + bd;
+    const int ry = b >> 10;
+    uint32_t wv;
+    if (CHECK) {
+        const int sx = a >> 10;
+        const bool in = (unsigned)ry < (unsigned)nrows && (unsigned)sx < (unsigned)nbits;
+        wv = in ? tile[ry * P + (sx >> 5)] : 0u;
+    } else {
+        wv = tile[ry * P + (a >> 15)];
+    }
+    const uint32_t top = wv << ((a >> 10) & 31);
+    return __funnelshift_l(top, acc, 1);  // (acc << 1) | (top >> 31)
+}
+
+// The sampling loop of one CTA: each warp takes 32-row groups of the tile; per group
+// every lane shifts 32 row bits into one register per column, then the warp transposes
+// those registers to turn them into row sums.
+template <int CPL, bool CHECK>
+__device__ __forceinline__ void sweep_rows(const uint32_t *__restrict__ src, int pitch, const int2 *sXY, int th,
+                                           const int (&adl)[CPL], const int (&bdl)[CPL], const bool (&valid)[CPL],
+                                           int nR, int nbits, int *rows_out, int (&colsum)[CPL], int lane, int warp)
+{
+    for (int g = warp * SW_GROUP; g < th; g += SW_WARPS * SW_GROUP) {
+        const int nr = min(SW_GROUP, th - g);
+        uint32_t cb[CPL];
+#pragma unroll
+        for (int k = 0; k < CPL; k++) cb[k] = 0;
+        if (nr == SW_GROUP) {
+#pragma unroll
+            for (int r = 0; r < SW_GROUP; r++) {
+                const int2 p = sXY[g + r];
+#pragma unroll
+                for (int k = 0; k < CPL; k++) cb[k] = sample_bit<CHECK>(src, pitch, p.x, p.y, adl[k], bdl[k], nR, nbits, cb[k]);
+            }
+        } else {
+            for (int r = 0; r < SW_GROUP; r++) {
+                if (r < nr) {
+                    const int2 p = sXY[g + r];
+#pragma unroll
+                    for (int k = 0; k < CPL; k++)
+                        cb[k] = sample_bit<CHECK>(src, pitch, p.x, p.y, adl[k], bdl[k], nR, nbits, cb[k]);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < CPL; k++) cb[k] <<= 1;
+                }
+            }
+        }
+        // row r of the group sits at bit 31-r of cb[k]
+        int rowsum = 0;
+#pragma unroll
+        for (int k = 0; k < CPL; k++) {
+            uint32_t v = valid[k] ? cb[k] : 0u;
+            colsum[k] += __popc(v);
+            rowsum += __popc(warp_bit_transpose(v, lane));
+        }
+        const int r = 31 - lane;
+        if (r < nr && rowsum) atomicAdd(rows_out + g + r, rowsum);
+    }
+}
+
+template <int CPL>
+__global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
+{
+    extern __shared__ uint32_t smem[];
+    const int TW = 32 * CPL;
+    int2 *sXY = reinterpret_cast<int2 *>(smem);              // [tile_h]
+    uint32_t *sCol = smem + 2 * A.tile_h;                    // [TW]
+    uint32_t *tile = sCol + TW;                              // [tile_cap]
+    __shared__ int sBox[6];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int item = A.item0 + blockIdx.y;
+    const int card = item / A.n_angles, ang = item - card * A.n_angles;
+    const int tx = blockIdx.x % A.tiles_x, ty = blockIdx.x / A.tiles_x;
+    const int x0 = tx * TW, y0 = ty * A.tile_h;
+    const int tw = min(TW, A.w - x0), th = min(A.tile_h, A.h - y0);
+
+    const int *ad_g = A.ad + (size_t)ang * A.wpad;
+    const int *bd_g = A.bd + (size_t)ang * A.wpad;
+    const int2 *xy_g = A.xy + (size_t)ang * A.hpad;
+    const uint32_t *bits = A.bits + (size_t)card * A.bits_card_words;
+
+    // Source footprint of the tile.  X0[y]+adelta[x] is monotone in x and in y
+    // separately, so the extremes of (sx, sy) over the tile sit at its corners.
+    if (tid == 0) {
+        int ax0 = ad_g[x0], ax1 = ad_g[x0 + tw - 1], bx0 = bd_g[x0], bx1 = bd_g[x0 + tw - 1];
+        int2 p0 = xy_g[y0], p1 = xy_g[y0 + th - 1];
+        int sx00 = (p0.x + ax0) >> 10, sx01 = (p0.x + ax1) >> 10, sx10 = (p1.x + ax0) >> 10, sx11 = (p1.x + ax1) >> 10;
+        int sy00 = (p0.y + bx0) >> 10, sy01 = (p0.y + bx1) >> 10, sy10 = (p1.y + bx0) >> 10, sy11 = (p1.y + bx1) >> 10;
+        int sxmin = min(min(sx00, sx01), min(sx10, sx11)), sxmax = max(max(sx00, sx01), max(sx10, sx11));
+        int symin = min(min(sy00, sy01), min(sy10, sy11)), symax = max(max(sy00, sy01), max(sy10, sy11));
+        const bool interior = sxmin >= 0 && sxmax < A.w && symin >= 0 && symax < A.h;
+        // clip to the image; what falls outside reads as border (white = bit 0)
+        int cx0 = max(sxmin, 0), cx1 = min(sxmax, A.w - 1), cy0 = max(symin, 0), cy1 = min(symax, A.h - 1);
+        int wx0 = cx0 >> 5, wx1 = cx1 >> 5;
+        int nW = wx1 - wx0 + 1, nR = cy1 - cy0 + 1;
+        int empty = (cx1 < cx0) || (cy1 < cy0);
+        if (empty) { nW = 0; nR = 0; wx0 = 0; cy0 = 0; }
+        sBox[0] = wx0;
+        sBox[1] = cy0;
+        sBox[2] = nW;
+        sBox[3] = nR;
+        sBox[4] = empty ? 2 : interior ? 0 : 1;
+        sBox[5] = min(cx1, A.w - 1) - wx0 * 32 + 1;  // valid bits per staged row (CHECK path)
+    }
+    for (int i = tid; i < TW; i += SW_THREADS) sCol[i] = 0;
+    __syncthreads();
+    const int wx0 = sBox[0], cy0 = sBox[1], nW = sBox[2], nR = sBox[3], kind = sBox[4], nbits = sBox[5];
+    if (kind == 2) return;  // the whole tile samples the border: no black pixels
+    const int P = nW | 1;   // odd pitch: consecutive source rows land in different banks
+    const bool staged = nR * P <= A.tile_cap;
+
+    // per-row table slice, re-based to the staged window
+    const int xoff = (wx0 * 32) << 10, yoff = cy0 << 10;
+    for (int i = tid; i < th; i += SW_THREADS) {
+        int2 p = xy_g[y0 + i];
+        sXY[i] = make_int2(p.x - xoff, p.y - yoff);
+    }
+    if (staged) {
+        for (int i = tid; i < nR * nW; i += SW_THREADS) {
+            int r = i / nW, j = i - r * nW;
+            tile[r * P + j] = __ldg(bits + (size_t)(cy0 + r) * A.wp + wx0 + j);
+        }
+    }
+    // else: footprint larger than the shared-memory budget (strong down-scaling inside
+    // the rotation): the L2-resident bit plane is sampled directly.
+    // this lane's columns
+    int adl[CPL], bdl[CPL];
+    bool valid[CPL];
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+        int x = x0 + lane + 32 * k;
+        valid[k] = x < A.w;
+        int xc = valid[k] ? x : A.w - 1;
+        adl[k] = ad_g[xc];
+        bdl[k] = bd_g[xc];
+    }
+    __syncthreads();
+
+    int colsum[CPL];
+#pragma unroll
+    for (int k = 0; k < CPL; k++) colsum[k] = 0;
+    int *rows_out = A.counts + (size_t)blockIdx.y * (A.h + A.w);
+    int *cols_out = rows_out + A.h;
+
+    // Three instantiations so the hot one reads the tile with LDS (not generic LD):
+    // staged + interior (no bounds tests), staged + edge, and un-staged (global).
+    if (staged && kind == 0)
+        sweep_rows<CPL, false>(tile, P, sXY, th, adl, bdl, valid, nR, nbits, rows_out + y0, colsum, lane, warp);
+    else if (staged)
+        sweep_rows<CPL, true>(tile, P, sXY, th, adl, bdl, valid, nR, nbits, rows_out + y0, colsum, lane, warp);
+    else
+        sweep_rows<CPL, true>(bits + (size_t)cy0 * A.wp + wx0, A.wp, sXY, th, adl, bdl, valid, nR, nbits, rows_out + y0,
+                              colsum, lane, warp);
+#pragma unroll
+    for (int k = 0; k < CPL; k++)
+        if (colsum[k]) atomicAdd(&sCol[lane + 32 * k], (uint32_t)colsum[k]);
+    __syncthreads();
+    for (int i = tid; i < tw; i += SW_THREADS) {
+        uint32_t v = sCol[i];
+        if (v) atomicAdd(cols_out + x0 + i, (int)v);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// P4: population std-dev of the count vectors in the reference's own evaluation
+// order (calculate.rs:2-23): the mean from a left-to-right f64 sum (exact for
+// integers, any order), then a strictly sequential sum of (c - mean)^2 with each
+// square rounded before the add (powf(2.0)), divided by n, square root.  One warp
+// per vector: lanes stage a chunk, lane 0 runs the dependent f64 chain.
+static constexpr int FIN_CHUNK = 1024;
+
+__device__ double seq_std_dev(const int *__restrict__ v, int n, int *stage, int lane, long long *sum_out,
+                              long long *sq_out)
+{
+    long long s = 0, q = 0;
+    for (int i = lane; i < n; i += 32) {
+        long long c = v[i];
+        s += c;
+        q += c * c;
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    *sum_out = s;
+    *sq_out = q;
+    const double mean = __ddiv_rn((double)s, (double)n);
+    double acc = 0.0;
+    for (int base = 0; base < n; base += FIN_CHUNK) {
+        const int m = min(FIN_CHUNK, n - base);
+        for (int i = lane; i < m; i += 32) stage[i] = v[base + i];
+        __syncwarp();
+        if (lane == 0) {
+            int i = 0;
+            if (base == 0) {
+                double d = __dsub_rn((double)stage[0], mean);
+                acc = __dmul_rn(d, d);
+                i = 1;
+            }
+            for (; i < m; i++) {
+                double d = __dsub_rn((double)stage[i], mean);
+                acc = __dadd_rn(acc, __dmul_rn(d, d));
+            }
+        }
+        __syncwarp();
+    }
+    return __dsqrt_rn(__ddiv_rn(acc, (double)n));
+}
+
+__global__ void __launch_bounds__(64) sweep_finalize_kernel(const int *__restrict__ counts, int w, int h,
+                                                            int item0, double *__restrict__ v_sd,
+                                                            double *__restrict__ h_sd, long long *__restrict__ sums)
+{
+    __shared__ int stage[2][FIN_CHUNK];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int *base = counts + (size_t)blockIdx.x * (h + w);
+    const size_t item = (size_t)item0 + blockIdx.x;
+    long long s, q;
+    if (warp == 0) {
+        double sd = seq_std_dev(base, h, stage[0], lane, &s, &q);
+        if (lane == 0) {
+            h_sd[item] = sd;
+            if (sums) { sums[4 * item + 0] = s; sums[4 * item + 1] = q; }
+        }
+    } else {
+        double sd = seq_std_dev(base + h, w, stage[1], lane, &s, &q);
+        if (lane == 0) {
+            v_sd[item] = sd;
+            if (sums) { sums[4 * item + 2] = s; sums[4 * item + 3] = q; }
+        }
+    }
+}
+
+// Plain zero counts of an image as is (transfer::get_projection_standard_deviations
+// on an un-rotated Mat): identity sampling of the bit plane.
+__global__ void plain_counts_kernel(const uint32_t *__restrict__ bits, int wp, int w, int h, int *__restrict__ counts)
+{
+    // one warp per row: popcounts for the row sum, bit tests for the columns
+    const int lane = threadIdx.x & 31;
+    const int y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (y >= h) return;
+    int rs = 0;
+    for (int j = lane; j < wp; j += 32) {
+        uint32_t v = bits[(size_t)y * wp + j];
+        rs += __popc(v);
+        while (v) {
+            int b = __clz(v);
+            v &= ~(0x80000000u >> b);
+            atomicAdd(counts + h + j * 32 + b, 1);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+    if (lane == 0) counts[y] = rs;
+}
+
+// ---------------------------------------------------------------------------
+static int pick_cpl(int w)
+{
+    int best = 4, best_waste = 1 << 30;
+    for (int cpl = 4; cpl >= 2; cpl--) {
+        int tw = 32 * cpl;
+        int waste = cdiv(w, tw) * tw - w;
+        if (waste < best_waste) { best_waste = waste; best = cpl; }
+    }
+    return best;
+}
+
+template <int CPL>
+static cudaError_t launch_sweep(const SweepArgs &A, dim3 grid, size_t smem, cudaStream_t st)
+{
+    static bool attr_set = false;
+    if (!attr_set || smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(sweep_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    sweep_kernel<CPL><<<grid, SW_THREADS, smem, st>>>(A);
+    return cudaGetLastError();
+}
+
+int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t card_stride, int w, int h,
+                     size_t stride, const double *M_host, int n_angles, double *d_vsd, double *d_hsd,
+                     int64_t *d_sums, int32_t *d_counts_out)
+{
+    cudaStream_t st = ctx->stream;
+    if (n_cards <= 0 || n_angles <= 0) return OICS_OK;
+    if (w > 32767 || h > 32767) {
+        set_error("image larger than 32767 px per side is not supported (OpenCV saturates coordinates to int16)");
+        return OICS_ERR_UNSUPPORTED;
+    }
+    // inverse matrices, host f64 in OpenCV's order
+    std::vector<double> inv((size_t)n_angles * 6);
+    for (int i = 0; i < n_angles; i++) invert_affine(M_host + 6 * (size_t)i, inv.data() + 6 * (size_t)i);
+    OICS_TRY(ctx->mats.ensure(inv.size() * sizeof(double)));
+    OICS_TRY(ctx->pin_small.ensure(inv.size() * sizeof(double)));
+    // pin_small may still be in flight from a previous call on this stream
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(ctx->pin_small.p, inv.data(), inv.size() * sizeof(double));
+    OICS_CUDA_TRY(cudaMemcpyAsync(ctx->mats.p, ctx->pin_small.p, inv.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+
+    const int wpad = (w + 31) & ~31, hpad = (h + 31) & ~31;
+    const size_t tab_ints = (size_t)n_angles * (2 * (size_t)wpad + 2 * (size_t)hpad);
+    OICS_TRY(ctx->tabs.ensure(tab_ints * sizeof(int)));
+    int *ad = ctx->tabs.as<int>();
+    int *bd = ad + (size_t)n_angles * wpad;
+    int2 *xy = reinterpret_cast<int2 *>(bd + (size_t)n_angles * wpad);
+    {
+        dim3 grid(cdiv(max(w, h), 256), n_angles);
+        sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
+        OICS_CUDA_TRY(cudaGetLastError());
+        ctx->launches++;
+    }
+
+    // tile shape and shared-memory budget
+    const int CPL = pick_cpl(w);
+    const int TW = 32 * CPL;
+    int tile_h = SW_WARPS * SW_GROUP * 2;  // 512 rows
+    if (h <= SW_WARPS * SW_GROUP) tile_h = SW_WARPS * SW_GROUP;
+    // worst-case footprint over the angles (one-pixel slack on each side)
+    size_t need_words = 0;
+    for (int i = 0; i < n_angles; i++) {
+        const double *m = inv.data() + 6 * (size_t)i;
+        double fw = fabs(m[0]) * TW + fabs(m[1]) * tile_h + 4.0;
+        double fh = fabs(m[3]) * TW + fabs(m[4]) * tile_h + 4.0;
+        if (fw > w + 64) fw = w + 64;
+        if (fh > h + 2) fh = h + 2;
+        size_t P = ((size_t)(fw / 32.0) + 2) | 1;
+        size_t words = P * (size_t)(fh + 1);
+        if (words > need_words) need_words = words;
+    }
+    const size_t fixed_words = 2 * (size_t)tile_h + TW;
+    size_t cap_words = need_words;
+    const size_t max_words = (size_t)(96 * 1024) / 4 - fixed_words;  // keep >= 2 CTAs per SM
+    if (cap_words > max_words) cap_words = max_words;
+    const size_t smem = (fixed_words + cap_words) * 4;
+
+    const int wp = cdiv(w, 32);
+    const int tiles_x = cdiv(w, TW), tiles_y = cdiv(h, tile_h);
+    const size_t per_item = (size_t)(h + w) * sizeof(int);
+    const long long total_items = (long long)n_cards * n_angles;
+    long long chunk_items = (long long)((size_t)64 << 20) / (long long)per_item;
+    if (chunk_items < 1) chunk_items = 1;
+    if (chunk_items > 32768) chunk_items = 32768;
+    if (chunk_items > total_items) chunk_items = total_items;
+    // whole cards per chunk when a card's angles fit, so the bit planes are packed once
+    OICS_TRY(ctx->counts.ensure((size_t)chunk_items * per_item));
+    const int cards_per_pack = (int)std::min<long long>(n_cards, std::max<long long>(1, (chunk_items + n_angles - 1) / n_angles + 1));
+    OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * h * wp * sizeof(uint32_t)));
+
+    SweepArgs A;
+    A.bits_card_words = (size_t)h * wp;
+    A.wp = wp; A.w = w; A.h = h;
+    A.ad = ad; A.bd = bd; A.xy = xy; A.wpad = wpad; A.hpad = hpad;
+    A.counts = ctx->counts.as<int>();
+    A.n_angles = n_angles;
+    A.tiles_x = tiles_x;
+    A.tile_h = tile_h;
+    A.tile_cap = (int)cap_words;
+
+    std::vector<cudaEvent_t> evs;
+    ctx->last_sweep_launches = 0;
+    int packed_first = -1, packed_n = 0;  // cards currently in ctx->bits
+    for (long long it0 = 0; it0 < total_items; it0 += chunk_items) {
+        const long long nit = min(chunk_items, total_items - it0);
+        const int c_first = (int)(it0 / n_angles), c_last = (int)((it0 + nit - 1) / n_angles);
+        if (c_first < packed_first || c_last >= packed_first + packed_n || packed_first < 0) {
+            packed_first = c_first;
+            packed_n = min(cards_per_pack, n_cards - c_first);
+            if (c_last >= packed_first + packed_n) {
+                set_error("internal: sweep chunk spans more cards than the bit-plane buffer holds");
+                return OICS_ERR_INVALID_ARG;
+            }
+            dim3 g(cdiv(wp, 128), h, packed_n);
+            pack_bits_kernel<<<g, 128, 0, st>>>(dbins + (size_t)packed_first * card_stride, card_stride, stride, w, h, wp,
+                                                ctx->bits.as<uint32_t>(), packed_n);
+            OICS_CUDA_TRY(cudaGetLastError());
+            ctx->launches++;
+        }
+        OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nit * per_item, st));
+        // item index relative to the packed window
+        A.bits = ctx->bits.as<uint32_t>() - (size_t)packed_first * A.bits_card_words;
+        A.item0 = (int)it0;
+        dim3 grid(tiles_x * tiles_y, (unsigned)nit);
+        cudaEvent_t e0, e1;
+        OICS_CUDA_TRY(cudaEventCreate(&e0));
+        OICS_CUDA_TRY(cudaEventCreate(&e1));
+        evs.push_back(e0);
+        evs.push_back(e1);
+        OICS_CUDA_TRY(cudaEventRecord(e0, st));
+        cudaError_t le = CPL == 2 ? launch_sweep<2>(A, grid, smem, st)
+                         : CPL == 3 ? launch_sweep<3>(A, grid, smem, st)
+                                    : launch_sweep<4>(A, grid, smem, st);
+        OICS_CUDA_TRY(le);
+        OICS_CUDA_TRY(cudaEventRecord(e1, st));
+        ctx->launches++;
+        ctx->last_sweep_launches++;
+        sweep_finalize_kernel<<<(unsigned)nit, 64, 0, st>>>(ctx->counts.as<int>(), w, h, (int)it0, d_vsd, d_hsd,
+                                                          reinterpret_cast<long long *>(d_sums));
+        OICS_CUDA_TRY(cudaGetLastError());
+        ctx->launches++;
+        if (d_counts_out && it0 == 0) {
+            const long long ncopy = std::min<long long>(nit, n_angles);
+            OICS_CUDA_TRY(cudaMemcpyAsync(d_counts_out, ctx->counts.p, (size_t)ncopy * per_item, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    double ms = 0.0;
+    for (size_t i = 0; i < evs.size(); i += 2) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, evs[i], evs[i + 1]);
+        ms += t;
+        cudaEventDestroy(evs[i]);
+        cudaEventDestroy(evs[i + 1]);
+    }
+    ctx->last_sweep_ms = ms;
+    return OICS_OK;
+}
+
+int32_t plain_std_devs_device(oics_ctx *ctx, const uint8_t *dbin, int w, int h, size_t stride, double *d_vsd,
+                              double *d_hsd)
+{
+    cudaStream_t st = ctx->stream;
+    const int wp = cdiv(w, 32);
+    OICS_TRY(ctx->bits.ensure((size_t)h * wp * sizeof(uint32_t)));
+    OICS_TRY(ctx->counts.ensure((size_t)(h + w) * sizeof(int)));
+    dim3 g(cdiv(wp, 128), h, 1);
+    pack_bits_kernel<<<g, 128, 0, st>>>(dbin, 0, stride, w, h, wp, ctx->bits.as<uint32_t>(), 1);
+    OICS_CUDA_TRY(cudaGetLastError());
+    OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)(h + w) * sizeof(int), st));
+    plain_counts_kernel<<<cdiv(h, 8), 256, 0, st>>>(ctx->bits.as<uint32_t>(), wp, w, h, ctx->counts.as<int>());
+    OICS_CUDA_TRY(cudaGetLastError());
+    sweep_finalize_kernel<<<1, 64, 0, st>>>(ctx->counts.as<int>(), w, h, 0, d_vsd, d_hsd, nullptr);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 3;
+    return OICS_OK;
+}
+
+}  // namespace oics

@@ -1,0 +1,224 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.  Bit-exact for counts, pixels and angles; std-devs
+within 1e-12 relative (north_star allows 1e-4)."""
+import numpy as np
+import pytest
+
+from omr_img_corrector_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+
+WHITE = (255, 255, 255, 0)
+SD_RTOL = 1e-12   # north_star tolerance is 1e-4 relative; the device follows calculate.rs's order
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = api.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def dataset_like(orc):
+    """A 1240x1150 BGR card like the reference's dataset images, skewed with the
+    reference's own input-synthesis recipe (lib.rs:156-166)."""
+    g, a = synth.base_card(3)
+    bgr = synth.to_bgr(np.ascontiguousarray(g[200:1350, 100:1340]))
+    return orc.rotate_mat(bgr, -a, 1.0, 1, WHITE, 0), a
+
+
+@pytest.fixture(scope="module")
+def a4_card(orc):
+    g, a = synth.base_card(0)
+    return orc.rotate_mat(synth.to_bgr(g), -a, 1.0, 1, WHITE, 0), a
+
+
+def _close(a, b, rtol=SD_RTOL):
+    a, b = np.asarray(a), np.asarray(b)
+    return np.all(np.abs(a - b) <= rtol * np.maximum(1.0, np.abs(b)))
+
+
+# ----------------------------------------------------------------------------- W1
+@pytest.mark.parametrize("flags", [0, 1])
+@pytest.mark.parametrize("ch", [1, 3, 4])
+def test_warp_affine_bit_exact(ctx, orc, flags, ch):
+    rng = np.random.default_rng(10 * flags + ch)
+    shape = (301, 417) if ch == 1 else (301, 417, ch)
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    h, w = shape[:2]
+    for ang in [-15.0, -3.7, 0.1, 7.3, 44.8, -90.0, 180.0]:
+        for s in [1.0, 0.2, 1.7]:
+            M = api.rotation_matrix_2d(np.float32(w) / np.float32(2), np.float32(h) / np.float32(2), ang, s)
+            for ds in [(w, h), (w + 37, h + 11), (5, 3)]:
+                ref = orc.warp_affine(img, M, ds, flags, (1, 128, 255, 77))
+                got = ctx.warp_affine(img, M, ds, flags, (1, 128, 255, 77))
+                assert np.array_equal(ref, got), (ang, s, ds)
+
+
+@pytest.mark.parametrize("clip", [0, 1])
+@pytest.mark.parametrize("flags", [0, 1])
+def test_rotate_mat_a4(ctx, orc, a4_card, clip, flags):
+    bgr, a = a4_card
+    for ang in [a, -14.9, 15.0]:
+        ref = orc.rotate_mat(bgr, ang, 1.0, flags, WHITE, clip)
+        got = ctx.rotate_mat(bgr, ang, 1.0, flags, WHITE, clip)
+        assert got.shape == ref.shape and np.array_equal(ref, got)
+
+
+def test_warp_strided_and_device_pointers(ctx, orc):
+    import torch
+    rng = np.random.default_rng(5)
+    big = rng.integers(0, 256, (120, 200, 3), dtype=np.uint8)
+    view = big[10:110, 20:180]                           # non-contiguous rows
+    M = api.rotation_matrix_2d(80.0, 50.0, 5.5, 1.0)
+    ref = orc.warp_affine(np.ascontiguousarray(view), M, (160, 100), 1, WHITE)
+    assert np.array_equal(ref, ctx.warp_affine(view, M, (160, 100), 1, WHITE))
+    t = torch.from_numpy(np.ascontiguousarray(view)).cuda()
+    out = torch.empty((100, 160, 3), dtype=torch.uint8, device="cuda")
+    ctx.warp_affine(t, M, (160, 100), 1, WHITE, out=out)
+    assert np.array_equal(ref, out.cpu().numpy())
+
+
+# ----------------------------------------------------------------------------- P0
+@pytest.mark.parametrize("size,maxwh", [((1150, 1240), (248, 230)), ((1300, 1237), (248, 230)),
+                                        ((1300, 1236), (248, 230)), ((701, 533), (0, 0)),
+                                        ((600, 400), (200, 300)), ((3508, 2480), (0, 0))])
+def test_preprocess_omr(ctx, orc, size, maxwh):
+    rng = np.random.default_rng(sum(size))
+    g, _ = synth.base_card(1)
+    crop = g[:size[0], :size[1]].copy()
+    noise = rng.integers(0, 90, crop.shape, dtype=np.uint8)
+    bgr = np.stack([np.clip(crop.astype(np.int16) - noise * (k + 1) // 3, 0, 255).astype(np.uint8) for k in range(3)],
+                   axis=2)
+    ref, s = orc.preprocess_omr(bgr, *maxwh)
+    got, gs = ctx.preprocess(bgr, api.PRE_OMR, *maxwh)
+    assert gs == s and got.shape == ref.shape and np.array_equal(ref, got)
+
+
+@pytest.mark.parametrize("scale", [1.0, 0.2, 0.5, 0.37])
+def test_preprocess_projection(ctx, orc, dataset_like, scale):
+    bgr, _ = dataset_like
+    ref = orc.preprocess_projection(bgr, scale)
+    got, _ = ctx.preprocess(bgr, api.PRE_PROJECTION, resize_scale=scale)
+    assert got.shape == ref.shape and np.array_equal(ref, got)
+
+
+# ----------------------------------------------------------------------------- P2-P4
+def _check_sweep(ctx, orc, binary, Ms, angles_to_count):
+    v, h, sums = ctx.projection_sweep(binary, Ms, want_sums=True)
+    rv, rh, rows, cols = orc.projection_sweep(binary, Ms, want_counts=True, threads=8)
+    # exact integer sums of the count vectors
+    assert np.array_equal(sums[:, 0], rows.sum(axis=1)) and np.array_equal(sums[:, 2], cols.sum(axis=1))
+    assert np.array_equal(sums[:, 1], (rows.astype(np.int64) ** 2).sum(axis=1))
+    assert np.array_equal(sums[:, 3], (cols.astype(np.int64) ** 2).sum(axis=1))
+    assert _close(v, rv) and _close(h, rh)
+    assert np.array_equal(v, rv) and np.array_equal(h, rh)          # same evaluation order -> same bits
+    for i in angles_to_count:
+        r, c = ctx.projection_counts(binary, Ms[i])
+        assert np.array_equal(r, rows[i]) and np.array_equal(c, cols[i]), i
+    return v, h
+
+
+def test_sweep_default_operating_point(ctx, orc, dataset_like):
+    """(45, 0.2, 248, 230): the reference tests' parameters (lib.rs:92-97); exercises the
+    re-applied resize scale inside the rotation (omr.rs:159-163)."""
+    bgr, a = dataset_like
+    b, s = orc.preprocess_omr(bgr, 248, 230)
+    N, angles, Ms = api.sweep_matrices(b.shape[1], b.shape[0], 45, 0.2, s)
+    v, h = _check_sweep(ctx, orc, b, Ms, range(0, 450, 37))
+    ra, rb = api.rule_a(h, v, N, 0.2), api.rule_b(v, h, N, 0.2)
+    oa = orc.get_result_from_projection(bgr, 45, 0.2, 248, 230)
+    assert (ra.angle, ra.status, ra.candidates) == (oa.angle, oa.status, oa.candidates)
+
+
+def test_sweep_scale_one_medium(ctx, orc, dataset_like):
+    bgr, a = dataset_like
+    b = orc.preprocess_projection(bgr, 1.0)
+    N, angles, Ms = api.sweep_matrices(b.shape[1], b.shape[0], 15, 0.5, 1.0)
+    _check_sweep(ctx, orc, b, Ms, [0, 17, 30, 59])
+
+
+def test_sweep_odd_sizes_and_extremes(ctx, orc):
+    rng = np.random.default_rng(9)
+    for (h, w) in [(1, 1), (3, 70), (67, 5), (255, 257), (513, 130), (300, 1031)]:
+        b = ((rng.random((h, w)) < 0.3) * 255).astype(np.uint8) ^ 255
+        Ms = np.stack([api.rotation_matrix_2d(np.float32(w) / np.float32(2), np.float32(h) / np.float32(2), a, s)
+                       for a in (-45.0, -7.3, 0.0, 0.1, 29.9, 90.0, 180.0) for s in (1.0, 0.2, 3.0)])
+        _check_sweep(ctx, orc, b, Ms, range(len(Ms)))
+    # all white / all black
+    for val in (255, 0):
+        b = np.full((120, 90), val, np.uint8)
+        N, _, Ms = api.sweep_matrices(90, 120, 5, 1.0, 1.0)
+        v, h = _check_sweep(ctx, orc, b, Ms, [0, 5])
+        r = api.rule_a(h, v, N, 1.0)
+        o = orc.rule_a(h, v, N, 1.0)
+        assert (r.angle, r.status, r.candidates) == (o.angle, o.status, o.candidates)
+
+
+def test_sweep_a4_full_resolution(ctx, orc, a4_card):
+    """BASELINE config 1 geometry: A4@300dpi, +-15 deg at 0.1 deg -- 300 candidates.  The
+    oracle is run on every 6th angle plus the neighbourhood of the optimum to bound CPU
+    time; the GPU runs all 300."""
+    bgr, a = a4_card
+    b, s = orc.preprocess_omr(bgr, 0, 0)
+    gb, gs = ctx.preprocess(bgr, api.PRE_OMR, 0, 0)
+    assert gs == s == 1.0 and np.array_equal(b, gb)
+    N, angles, Ms = api.sweep_matrices(2480, 3508, 15, 0.1, 1.0)
+    v, h, sums = ctx.projection_sweep(b, Ms, want_sums=True)
+    best = int(np.argmax(h))
+    idx = sorted(set(range(0, 300, 6)) | set(range(max(0, best - 3), min(300, best + 4))))
+    rv, rh, rows, cols = orc.projection_sweep(b, Ms[idx], want_counts=True, threads=8)
+    assert np.array_equal(v[idx], rv) and np.array_equal(h[idx], rh)
+    assert np.array_equal(sums[idx, 0], rows.sum(axis=1))
+    for k in (0, len(idx) // 2, len(idx) - 1):
+        r, c = ctx.projection_counts(b, Ms[idx[k]])
+        assert np.array_equal(r, rows[k]) and np.array_equal(c, cols[k])
+    res = api.rule_a(h, v, N, 0.1)
+    assert res.status == api.BELIEVED and abs(res.angle - a) <= 0.1 + 1e-9
+    # entry point end to end
+    got = ctx.result_from_projection(bgr, 15, 0.1, 0, 0)
+    assert (got.angle, got.status) == (res.angle, res.status)
+    assert ctx.angle_with_projections(bgr, 15, 0.1, 1.0, 1) == api.rule_b(*ctx.projection_sweep(
+        orc.preprocess_projection(bgr, 1.0), Ms), N, 0.1)
+
+
+def test_sweep_batch_equals_single(ctx, orc, dataset_like):
+    bgr, _ = dataset_like
+    b0 = orc.preprocess_projection(bgr, 0.5)
+    cards = np.stack([b0, np.ascontiguousarray(b0[::-1]), np.ascontiguousarray(b0[:, ::-1]), 255 - b0, b0])
+    h, w = b0.shape
+    N, _, Ms = api.sweep_matrices(w, h, 10, 0.5, 1.0)
+    bv, bh = ctx.projection_sweep_batch(cards, len(cards), w, h, Ms)
+    for c in range(len(cards)):
+        v, hh = ctx.projection_sweep(cards[c], Ms)
+        assert np.array_equal(bv[c], v) and np.array_equal(bh[c], hh)
+    import torch
+    t = torch.from_numpy(cards).cuda()
+    dv, dh = ctx.projection_sweep_batch(t, len(cards), w, h, Ms)
+    assert np.array_equal(dv, bv) and np.array_equal(dh, bh)
+
+
+def test_plain_projection_std_devs(ctx, orc, dataset_like):
+    bgr, _ = dataset_like
+    b = orc.preprocess_projection(bgr, 0.5)
+    assert ctx.projection_standard_deviations(b) == orc.projection_std_devs(b)
+
+
+# ----------------------------------------------------------------------------- entry points
+def test_entry_points_dataset_params(ctx, orc, dataset_like):
+    bgr, a = dataset_like
+    got = ctx.result_from_projection(bgr, 45, 0.2, 248, 230)
+    ref = orc.get_result_from_projection(bgr, 45, 0.2, 248, 230)
+    assert (got.angle, got.status, got.candidates) == (ref.angle, ref.status, ref.candidates)
+    assert ctx.angle_with_projections(bgr, 45, 0.2, 0.2, 1) == orc.get_angle_with_projections(bgr, 45, 0.2, 0.2)
+    # threads is a hint only (the reference's threads>1 branch is buggy, projection.rs:94)
+    assert ctx.angle_with_projections(bgr, 45, 0.2, 0.2, 8) == ctx.angle_with_projections(bgr, 45, 0.2, 0.2, 1)
+
+
+def test_error_reporting(ctx):
+    with pytest.raises(api.OicsError) as e:
+        ctx.warp_affine(np.zeros((4, 4, 2), np.uint8), np.array([1.0, 0, 0, 0, 1, 0]), (4, 4))
+    assert e.value.code == -6
+    with pytest.raises(api.OicsError):
+        ctx.preprocess(np.zeros((10, 10, 3), np.uint8), api.PRE_PROJECTION, resize_scale=2.0)

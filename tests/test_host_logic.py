@@ -1,0 +1,185 @@
+"""CPU tests: the C-ABI library loads, exports every symbol the header declares, and its
+host-side scalar logic (geometry, argmax rules, segment-angle rules, reconcile) agrees
+with the oracle.  No compute entry is called (no GPU here)."""
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+
+from omr_img_corrector_b200 import _lib, api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "oics_cuda.h")).read()
+    declared = set(re.findall(r"OICS_API\s+[\w\s\*]+?\b(oics_\w+)\s*\(", hdr))
+    assert len(declared) >= 35
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+def test_no_gpu_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(api.OicsError) as e:
+        api.Context(0)
+    assert e.value.code == _lib.ERR_CUDA and "no CPU fallback" in str(e.value)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "omr_img_corrector_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "oracle" not in src.lower(), f"{f} mentions the oracle"
+
+
+def test_angle_grid_is_half_open(orc):
+    for max_angle, step, expect in [(15, 0.1, 150), (45, 0.2, 225), (45, 0.01, 4500), (0, 0.1, 0), (45, 1e-9, 65535)]:
+        assert api.angle_half_range(max_angle, step) == expect
+        assert orc.sweep_angles(max_angle, step)[0] == expect
+    N, angles, M = api.sweep_matrices(2480, 3508, 15, 0.1, 1.0)
+    assert N == 150 and len(angles) == 300 and angles[0] == -15.0 and angles[153] == 3 * 0.1
+    _, _, Mo = orc.sweep_matrices(2480, 3508, 15, 0.1, 1.0)
+    assert np.array_equal(M, Mo)
+    _, _, M2 = api.sweep_matrices(248, 230, 45, 0.2, 0.2)
+    assert np.array_equal(M2, orc.sweep_matrices(248, 230, 45, 0.2, 0.2)[2])
+
+
+def test_rotate_geometry(orc):
+    for (w, h) in [(2480, 3508), (1240, 1150), (1237, 1300), (7, 5)]:
+        for ang in [-15.0, -2.8, 0.0, 0.1, 3.7, 44.9, 90.0, -135.5]:
+            for clip in (0, 1):
+                M, dw, dh = api.rotate_geometry(w, h, ang, 1.0, clip)
+                Mo, dwo, dho = orc.rotate_geometry(w, h, ang, 1.0, clip)
+                assert (dw, dh) == (dwo, dho) and np.array_equal(M, Mo)
+
+
+def test_projection_scale(orc):
+    for args in [(1240, 1150, 248, 230), (1237, 1300, 248, 230), (2480, 3508, 0, 0), (100, 100, 300, -1)]:
+        assert api.projection_scale(*args) == orc.projection_scale(*args)
+
+
+def _rand_sd(rng, n, ties):
+    v = rng.random(n) * 10
+    h = rng.random(n) * 10
+    if ties:
+        k = rng.integers(0, n, size=max(2, n // 4))
+        h[k] = h.max() if ties > 1 else h[k[0]]
+        if ties > 2:
+            v[k] = v.max()
+    return v, h
+
+
+def test_rule_a_matches_oracle(orc):
+    rng = np.random.default_rng(0)
+    for trial in range(300):
+        N = int(rng.integers(1, 40))
+        v, h = _rand_sd(rng, 2 * N, trial % 4)
+        if trial % 7 == 0:
+            h[:] = 0.0
+            v[:] = 0.0
+        got = api.rule_a(h, v, N, 0.1)
+        ref = orc.rule_a(h, v, N, 0.1)
+        assert got.status == ref.status and got.angle == ref.angle and got.candidates == ref.candidates
+
+
+def test_rule_a_literal_python(orc):
+    """omr.rs:147-221 transcribed in Python as a third opinion."""
+    rng = np.random.default_rng(1)
+    for trial in range(200):
+        N = int(rng.integers(1, 30))
+        v, h = _rand_sd(rng, 2 * N, trial % 4)
+        mh = mv = 0.0
+        ph = pv = 1
+        most = []
+        for i, deg in enumerate(range(-N, N)):
+            a = float(deg) * 0.2
+            if mh < h[i]:
+                mh, mv, ph, pv, most = h[i], v[i], 1, 1, [a]
+            elif mh == h[i]:
+                ph += 1
+                if mv < v[i]:
+                    pv, mv, most = 1, v[i], [a]
+                elif mv == v[i]:
+                    pv += 1
+                    most.append(a)
+        if ph == 1 and pv == 1:
+            exp = (most[0], 0)
+        elif len(most) == 1:
+            exp = (most[0], 1)
+        else:
+            exp = (0.0, 2)
+        got = api.rule_a(h, v, N, 0.2)
+        assert (got.angle, got.status) == exp and got.candidates == most
+
+
+def test_rule_b_matches_oracle(orc):
+    rng = np.random.default_rng(2)
+    for trial in range(300):
+        N = int(rng.integers(1, 40))
+        v, h = _rand_sd(rng, 2 * N, trial % 4)
+        if trial % 5 == 0:
+            i = int(rng.integers(0, 2 * N))
+            v[i] = 100.0
+            h[i] = 100.0
+        if trial % 11 == 0:
+            v[:] = 0
+            h[:] = 0
+        assert api.rule_b(v, h, N, 0.2) == orc.rule_b(v, h, N, 0.2)
+
+
+def _rand_lines(rng, n):
+    base = rng.uniform(-40, 40)
+    lines = []
+    for _ in range(n):
+        a = math.radians(base + rng.normal(0, 0.05) if rng.random() < 0.6 else rng.uniform(-180, 180))
+        L = rng.uniform(50, 600)
+        x1, y1 = rng.uniform(0, 1000, 2)
+        lines.append([int(x1), int(y1), int(x1 + L * math.cos(a)), int(y1 + L * math.sin(a))])
+    return np.array(lines, np.int32).reshape(-1, 4)
+
+
+def test_lines_angle_variants_match_oracle(orc):
+    rng = np.random.default_rng(3)
+    for trial in range(100):
+        lines = _rand_lines(rng, int(rng.integers(1, 60)))
+        got = api.lines_angle(lines, api.LINES_OMR)
+        ref = orc.lines_angle_omr(lines)
+        assert got.angle == ref.angle and got.status == ref.status and got.candidates == ref.candidates
+        assert api.lines_angle(lines, api.LINES_HOUGH).angle == orc.lines_angle_hough(lines)
+        assert api.lines_angle(lines, api.LINES_FFT).angle == orc.lines_angle_fft(lines)
+
+
+def test_lines_angle_empty_behaviour(orc):
+    empty = np.zeros((0, 4), np.int32)
+    for variant in (api.LINES_OMR, api.LINES_HOUGH):
+        with pytest.raises(api.OicsError) as e:
+            api.lines_angle(empty, variant)
+        assert e.value.code == _lib.ERR_NO_LINES          # the reference panics (omr.rs:272, hough.rs:74)
+    assert api.lines_angle(empty, api.LINES_FFT).angle == 0.0 == orc.lines_angle_fft(empty)
+
+
+def test_reconcile_matches_oracle(orc):
+    rng = np.random.default_rng(4)
+    for trial in range(300):
+        status = trial % 3
+        cand = [float(x) for x in np.round(rng.uniform(-5, 5, int(rng.integers(0, 5))), 1)]
+        if status != 2 and not cand:
+            cand = [1.0]
+        p = api.OmrResult(cand[0] if status != 2 else 0.0, status, cand)
+        e = float(np.round(rng.uniform(-5, 5), 2)) if trial % 4 else (cand[0] + 0.03 if cand else 0.0)
+        assert api.reconcile(p, e) == orc.reconcile(orc.OmrResult(p.angle, status, cand), e)
+
+
+def test_hough_dims(orc):
+    for (w, h) in [(2480, 3508), (1240, 1150), (310, 288)]:
+        assert api.hough_dims(w, h) == orc.hough_dims(w, h)
+    assert api.hough_dims(2480, 3508) == (180, 11977)
