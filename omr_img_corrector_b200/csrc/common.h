@@ -58,6 +58,12 @@ struct PinnedBuf {
     template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// Bluestein / radix-2 plan of one 1-D DFT length (fft.cu): device tables built on first use.
+struct FftPlan {
+    int n = 0, m = 0, direct = 0;
+    DevBuf chirp, bbr, tw;
+};
+
 }  // namespace oics
 
 struct oics_ctx {
@@ -76,6 +82,7 @@ struct oics_ctx {
     oics::DevBuf in_img, in_img2, out_img, gray, tmp8a, tmp8b, bin, bits, mats, tabs, counts, sd,
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
+    oics::FftPlan fft_row, fft_col;
 };
 
 namespace oics {

@@ -180,6 +180,11 @@ OICS_API void oics_destroy(oics_ctx *ctx)
                       &ctx->sums,   &ctx->edges,   &ctx->mag,     &ctx->dxy,   &ctx->labels, &ctx->accum,
                       &ctx->lines,  &ctx->misc,    &ctx->cplx,    &ctx->cplx2, &ctx->twid,   &ctx->fmag};
     for (DevBuf *b : bufs) b->release();
+    for (FftPlan *pl : {&ctx->fft_row, &ctx->fft_col}) {
+        pl->chirp.release();
+        pl->bbr.release();
+        pl->tw.release();
+    }
     ctx->pin_in.release();
     ctx->pin_out.release();
     ctx->pin_small.release();

@@ -1,0 +1,500 @@
+// H2: the Hough stage.
+//
+//  hough_accumulate_device   the standard (rho, theta) accumulator over ALL edge pixels
+//      with HoughLinesP's vote formula r = rint_f32(x*cos_f32 + y*sin_f32) + (numrho-1)/2.
+//      One CTA per (theta, slice of the edge list): the numrho-bin histogram of that theta
+//      lives in shared memory (privatised atomics), then is flushed once to HBM.
+//  hough_lines_p_device      cv::HoughLinesP = the progressive probabilistic transform the
+//      reference calls (hough.rs:31-42, omr.rs:245-253, fft.rs:183-191).  The algorithm is
+//      sequential by definition (RNG-ordered, each accepted segment erases pixels and votes
+//      that later points depend on), so one CTA walks one image:
+//        * the visiting order depends only on the NUMBER of edge pixels (cv::RNG seeded
+//          with (uint64)-1, swap-remove), not on the image: the host expands it from N and
+//          a gather kernel lays the points out in visiting order, so the CTA streams them
+//          and tests 256 upcoming points per L2 round trip;
+//        * a live point votes with one thread per theta (atomicAdd with return) and a block
+//          arg-max that keeps the first maximal theta, like the sequential `max_val < val`;
+//        * the two line walks test 256 steps per round trip; gap logic runs on ballots;
+//        * the erase pass clears the mask and, for accepted segments, un-votes every erased
+//          pixel with (pixel, theta) pairs spread over the CTA.
+//      Latency-bound per image (like the CPU), throughput comes from images in flight.
+#include <algorithm>
+#include <cmath>
+
+#include "common.h"
+
+namespace oics {
+
+// ---------------------------------------------------------------------------
+// ordered compaction of the edge pixels (row-major, as cv::HoughLinesP collects them)
+__global__ void edge_row_count_kernel(const uint8_t *__restrict__ edges, int w, int h, size_t stride,
+                                      int *__restrict__ rowcnt)
+{
+    const int lane = threadIdx.x & 31;
+    const int y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (y >= h) return;
+    const uint8_t *row = edges + (size_t)y * stride;
+    int c = 0;
+    for (int x = lane; x < w; x += 32) c += row[x] != 0;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) rowcnt[y] = c;
+}
+
+// exclusive scan of rowcnt[h] in place -> row offsets; total to *total.  One CTA.
+__global__ void __launch_bounds__(1024) edge_row_scan_kernel(int *__restrict__ rowcnt, int h, int *__restrict__ total)
+{
+    __shared__ int warp_sums[32];
+    __shared__ int carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < h; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = i < h ? rowcnt[i] : 0;
+        int s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) warp_sums[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            int ws = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(0xffffffffu, ws, o);
+                if (lane >= o) ws += t;
+            }
+            warp_sums[lane] = ws;
+        }
+        __syncthreads();
+        const int before = carry + (warp ? warp_sums[warp - 1] : 0) + s - v;
+        if (i < h) rowcnt[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+
+// points packed x | y << 16; mask (nullable) = edges != 0, tightly packed
+__global__ void edge_row_write_kernel(const uint8_t *__restrict__ edges, int w, int h, size_t stride,
+                                      const int *__restrict__ rowoff, uint32_t *__restrict__ pts,
+                                      uint8_t *__restrict__ mask)
+{
+    const int lane = threadIdx.x & 31;
+    const int y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (y >= h) return;
+    const uint8_t *row = edges + (size_t)y * stride;
+    int off = rowoff[y];
+    for (int x0 = 0; x0 < w; x0 += 32) {
+        const int x = x0 + lane;
+        const bool e = x < w && row[x] != 0;
+        if (mask && x < w) mask[(size_t)y * w + x] = e ? 1 : 0;
+        const uint32_t b = __ballot_sync(0xffffffffu, e);
+        if (e) pts[off + __popc(b & ((1u << lane) - 1u))] = (uint32_t)x | ((uint32_t)y << 16);
+        off += __popc(b);
+    }
+}
+
+__device__ __forceinline__ int vote_r(float x, float y, float c, float s, int half)
+{
+    return __float2int_rn(__fadd_rn(__fmul_rn(x, c), __fmul_rn(y, s))) + half;
+}
+
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hough_accumulate_kernel(const uint32_t *__restrict__ pts,
+                                                               const int *__restrict__ npts_ptr,
+                                                               const float *__restrict__ ttab, int numrho,
+                                                               int slices, int use_smem, int32_t *__restrict__ accum)
+{
+    extern __shared__ int hist[];
+    const int n = blockIdx.x, slice = blockIdx.y;
+    const int npts = *npts_ptr;
+    const float c = ttab[2 * n], s = ttab[2 * n + 1];
+    const int half = (numrho - 1) / 2;
+    int32_t *out = accum + (size_t)n * numrho;
+    const int per = (npts + slices - 1) / slices;
+    const int i0 = slice * per, i1 = min(npts, i0 + per);
+    if (use_smem) {
+        for (int i = threadIdx.x; i < numrho; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+            const uint32_t p = pts[i];
+            atomicAdd(&hist[vote_r((float)(p & 0xffffu), (float)(p >> 16), c, s, half)], 1);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < numrho; i += blockDim.x) {
+            const int v = hist[i];
+            if (v) {
+                if (slices == 1) out[i] = v;
+                else atomicAdd(out + i, v);
+            }
+        }
+    } else {
+        for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+            const uint32_t p = pts[i];
+            atomicAdd(out + vote_r((float)(p & 0xffffu), (float)(p >> 16), c, s, half), 1);
+        }
+    }
+}
+
+static int32_t compact_edges(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, bool want_mask,
+                             int **d_total, uint32_t **d_pts, uint8_t **d_mask)
+{
+    cudaStream_t st = ctx->stream;
+    if (w > 32767 || h > 32767) {
+        set_error("hough: image larger than 32767 px per side is not supported");
+        return OICS_ERR_UNSUPPORTED;
+    }
+    const size_t n = (size_t)w * h;
+    // lines: [total (16 B)][rowoff h ints] ; labels: points ; mag: mask
+    OICS_TRY(ctx->lines.ensure(16 + sizeof(int) * (size_t)h));
+    OICS_TRY(ctx->labels.ensure(sizeof(uint32_t) * n));
+    if (want_mask) OICS_TRY(ctx->mag.ensure(n));
+    int *total = ctx->lines.as<int>();
+    int *rowoff = total + 4;
+    uint32_t *pts = ctx->labels.as<uint32_t>();
+    uint8_t *mask = want_mask ? ctx->mag.as<uint8_t>() : nullptr;
+    edge_row_count_kernel<<<cdiv(h, 8), 256, 0, st>>>(dedges, w, h, stride, rowoff);
+    edge_row_scan_kernel<<<1, 1024, 0, st>>>(rowoff, h, total);
+    edge_row_write_kernel<<<cdiv(h, 8), 256, 0, st>>>(dedges, w, h, stride, rowoff, pts, mask);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 3;
+    *d_total = total;
+    *d_pts = pts;
+    if (d_mask) *d_mask = mask;
+    return OICS_OK;
+}
+
+int32_t hough_accumulate_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
+                                double theta, int32_t *daccum)
+{
+    cudaStream_t st = ctx->stream;
+    int numangle, numrho;
+    std::vector<float> ttab;
+    hough_geometry(w, h, rho, theta, &numangle, &numrho, &ttab);
+    int *d_total;
+    uint32_t *d_pts;
+    OICS_TRY(compact_edges(ctx, dedges, w, h, stride, false, &d_total, &d_pts, nullptr));
+    OICS_TRY(ctx->twid.ensure(ttab.size() * sizeof(float)));
+    OICS_CUDA_TRY(cudaMemcpyAsync(ctx->twid.p, ttab.data(), ttab.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+    const size_t acc_bytes = (size_t)numangle * numrho * sizeof(int32_t);
+    OICS_CUDA_TRY(cudaMemsetAsync(daccum, 0, acc_bytes, st));
+    const size_t smem = (size_t)numrho * sizeof(int);
+    const int use_smem = smem <= (size_t)ctx->smem_optin - 1024;
+    if (use_smem && smem > 48 * 1024)
+        OICS_CUDA_TRY(cudaFuncSetAttribute(hough_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // enough CTAs to fill the machine: numangle x slices >= ~4 waves
+    int slices = std::max(1, (4 * ctx->sm_count + numangle - 1) / numangle);
+    dim3 grid(numangle, slices);
+    hough_accumulate_kernel<<<grid, 256, use_smem ? smem : 0, st>>>(d_pts, d_total, ctx->twid.as<float>(), numrho, slices,
+                                                                    use_smem, daccum);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    // ttab is a host temporary: the async copy above must have consumed it
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    return OICS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// PPHT
+__global__ void gather_points_kernel(const uint32_t *__restrict__ pts, const int *__restrict__ order, int n,
+                                     uint32_t *__restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = pts[order[i]];
+}
+
+struct PphtArgs {
+    const uint32_t *seq;  // points in visiting order
+    int npts;
+    uint8_t *mask;        // w*h, 1 = live edge pixel
+    int w, h;
+    int32_t *accum;       // numangle * numrho, zeroed
+    const float *ttab;    // cos, sin per theta (already divided by rho)
+    const int *dirs;      // per theta: xflag, dx0, dy0, pad
+    int numangle, numrho;
+    int threshold, line_length, line_gap;
+    int32_t *lines;       // cap * 4
+    int cap;
+    int *n_lines;
+};
+
+static constexpr int PP_THREADS = 256;
+static constexpr int PP_WARPS = PP_THREADS / 32;
+
+struct PphtShared {
+    uint32_t live[PP_WARPS];   // ballots
+    uint32_t oob[PP_WARPS];
+    unsigned long long best[PP_WARPS];
+    int list[PP_THREADS];
+    int list_n;
+    int found;                 // generic broadcast slot
+    int end_step;
+};
+
+// step t of the walk from (x0, y0) with (dx, dy): pixel (j1, i1)
+__device__ __forceinline__ void walk_pixel(int xflag, int x0, int y0, int dx, int dy, int t, int *j1, int *i1)
+{
+    const int x = x0 + t * dx, y = y0 + t * dy;
+    if (xflag) { *j1 = x; *i1 = y >> 16; }
+    else { *j1 = x >> 16; *i1 = y; }
+}
+
+// First walk of one direction: returns (to every thread) the step index of line_end.
+__device__ int ppht_walk_end(const PphtArgs &A, PphtShared &S, int xflag, int x0, int y0, int dx, int dy)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int last = 0;  // step 0 is the live start point
+    for (int base = 0;; base += PP_THREADS) {
+        int j1, i1;
+        walk_pixel(xflag, x0, y0, dx, dy, base + tid, &j1, &i1);
+        const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
+        const bool m = inb && __ldcg(A.mask + (size_t)i1 * A.w + j1) != 0;
+        const uint32_t bm = __ballot_sync(0xffffffffu, m), bo = __ballot_sync(0xffffffffu, !inb);
+        if (lane == 0) { S.live[warp] = bm; S.oob[warp] = bo; }
+        __syncthreads();
+        if (tid == 0) {
+            int done = 0;
+            for (int wv = 0; wv < PP_WARPS && !done; wv++) {
+                uint32_t bits = S.live[wv];
+                const uint32_t ob = S.oob[wv];
+                const int first_oob = ob ? __ffs(ob) - 1 : 32;
+                if (first_oob < 32) bits &= (1u << first_oob) - 1u;
+                while (bits) {
+                    const int s = base + wv * 32 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    if (s - last > A.line_gap + 1) { done = 1; break; }
+                    last = s;
+                }
+                if (!done && first_oob < 32) done = 1;  // left the image: line_end = last live step
+            }
+            if (!done && (base + PP_THREADS - 1) - last > A.line_gap) done = 1;
+            S.found = done;
+            S.end_step = last;
+        }
+        __syncthreads();
+        const int done = S.found;
+        last = S.end_step;
+        __syncthreads();
+        if (done) return last;
+    }
+}
+
+// Second walk of one direction: steps 0..end; clears live pixels, un-votes them when good.
+__device__ void ppht_walk_erase(const PphtArgs &A, PphtShared &S, int xflag, int x0, int y0, int dx, int dy, int end,
+                                int good)
+{
+    const int tid = threadIdx.x;
+    const int half = (A.numrho - 1) / 2;
+    for (int base = 0; base <= end; base += PP_THREADS) {
+        if (tid == 0) S.list_n = 0;
+        __syncthreads();
+        const int t = base + tid;
+        if (t <= end) {
+            int j1, i1;
+            walk_pixel(xflag, x0, y0, dx, dy, t, &j1, &i1);
+            uint8_t *m = A.mask + (size_t)i1 * A.w + j1;
+            if (__ldcg(m)) {
+                __stcg(m, (uint8_t)0);
+                if (good) S.list[atomicAdd(&S.list_n, 1)] = j1 | (i1 << 16);
+            }
+        }
+        __syncthreads();
+        const int cnt = S.list_n;
+        if (good) {
+            const int total = cnt * A.numangle;
+            for (int k = tid; k < total; k += PP_THREADS) {
+                const int pi = k / A.numangle, n = k - pi * A.numangle;
+                const int p = S.list[pi];
+                const int r = vote_r((float)(p & 0xffff), (float)(p >> 16), A.ttab[2 * n], A.ttab[2 * n + 1], half);
+                atomicSub(A.accum + (size_t)n * A.numrho + r, 1);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(PP_THREADS) ppht_kernel(const PphtArgs A)
+{
+    __shared__ PphtShared S;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int half = (A.numrho - 1) / 2;
+    int nlines = 0;
+    for (int t0 = 0; t0 < A.npts; t0 += PP_THREADS) {
+        const int t = t0 + tid;
+        const uint32_t p = t < A.npts ? A.seq[t] : 0u;
+        const int px = (int)(p & 0xffffu), py = (int)(p >> 16);
+        int after = -1;  // chunk positions <= after are already handled
+        for (;;) {
+            const bool live = t < A.npts && tid > after && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
+            const uint32_t b = __ballot_sync(0xffffffffu, live);
+            if (lane == 0) S.live[warp] = b;
+            __syncthreads();
+            int first = -1;
+#pragma unroll
+            for (int wv = PP_WARPS - 1; wv >= 0; wv--)
+                if (S.live[wv]) first = wv * 32 + __ffs(S.live[wv]) - 1;
+            if (first < 0) { __syncthreads(); break; }
+            if (tid == first) S.found = (int)p;
+            __syncthreads();
+            const int q = S.found;
+            const int j = q & 0xffff, i = q >> 16;
+            after = first;
+            // ---- vote: one thread per theta, first maximal theta wins
+            int bv = A.threshold - 1, bn = 0;
+            for (int n = tid; n < A.numangle; n += PP_THREADS) {
+                const int r = vote_r((float)j, (float)i, A.ttab[2 * n], A.ttab[2 * n + 1], half);
+                const int val = atomicAdd(A.accum + (size_t)n * A.numrho + r, 1) + 1;
+                if (bv < val) { bv = val; bn = n; }
+            }
+            // key: larger value first, then smaller theta index
+            unsigned long long key = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) {
+                unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+                if (other > key) key = other;
+            }
+            if (lane == 0) S.best[warp] = key;
+            __syncthreads();
+            key = S.best[0];
+#pragma unroll
+            for (int wv = 1; wv < PP_WARPS; wv++)
+                if (S.best[wv] > key) key = S.best[wv];
+            const int max_val = (int)(uint32_t)(key >> 32) - 0x40000000;
+            const int max_n = 0x7fffffff - (int)(uint32_t)(key & 0xffffffffu);
+            __syncthreads();
+            if (max_val < A.threshold) continue;
+            // ---- walk
+            const int xflag = A.dirs[4 * max_n], dx0 = A.dirs[4 * max_n + 1], dy0 = A.dirs[4 * max_n + 2];
+            int x0 = j, y0 = i;
+            if (xflag) y0 = (y0 << 16) + 32768;
+            else x0 = (x0 << 16) + 32768;
+            const int e0 = ppht_walk_end(A, S, xflag, x0, y0, dx0, dy0);
+            const int e1 = ppht_walk_end(A, S, xflag, x0, y0, -dx0, -dy0);
+            int ax, ay, bx, by;
+            walk_pixel(xflag, x0, y0, dx0, dy0, e0, &ax, &ay);
+            walk_pixel(xflag, x0, y0, -dx0, -dy0, e1, &bx, &by);
+            const int good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
+            ppht_walk_erase(A, S, xflag, x0, y0, dx0, dy0, e0, good);
+            ppht_walk_erase(A, S, xflag, x0, y0, -dx0, -dy0, e1, good);
+            if (good) {
+                if (tid == 0 && nlines < A.cap) {
+                    A.lines[4 * nlines + 0] = ax;
+                    A.lines[4 * nlines + 1] = ay;
+                    A.lines[4 * nlines + 2] = bx;
+                    A.lines[4 * nlines + 3] = by;
+                }
+                nlines++;
+            }
+        }
+    }
+    if (tid == 0) *A.n_lines = nlines;
+}
+
+// The visiting order of cv::HoughLinesProbabilistic for n points: count = n..1,
+// idx = rng % count, visit arr[idx], arr[idx] = arr[count-1]; cv::RNG(-1) is the
+// multiply-with-carry generator state = lo32 * 4164903690 + hi32.
+static void ppht_order(int n, std::vector<int> &order)
+{
+    std::vector<int> arr((size_t)n);
+    for (int i = 0; i < n; i++) arr[i] = i;
+    order.resize((size_t)n);
+    uint64_t state = (uint64_t)-1;
+    int k = 0;
+    for (int count = n; count > 0; count--) {
+        state = (uint64_t)(uint32_t)state * 4164903690u + (uint32_t)(state >> 32);
+        const int idx = (int)((uint32_t)state % (uint32_t)count);
+        order[k++] = arr[idx];
+        arr[idx] = arr[count - 1];
+    }
+}
+
+int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
+                             double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
+                             int cap, int *n_lines)
+{
+    cudaStream_t st = ctx->stream;
+    int numangle, numrho;
+    std::vector<float> ttab;
+    hough_geometry(w, h, rho, theta, &numangle, &numrho, &ttab);
+    // per-theta walk direction (cv::HoughLinesProbabilistic): a = -sin, b = cos
+    std::vector<int> dirs(4 * (size_t)numangle);
+    for (int n = 0; n < numangle; n++) {
+        const float a = -ttab[2 * n + 1], b = ttab[2 * n];
+        int xflag, dx0, dy0;
+        if (std::fabs(a) > std::fabs(b)) {
+            xflag = 1;
+            dx0 = a > 0 ? 1 : -1;
+            dy0 = (int)std::lrint(b * (1 << 16) / std::fabs((double)a));
+        } else {
+            xflag = 0;
+            dy0 = b > 0 ? 1 : -1;
+            dx0 = (int)std::lrint(a * (1 << 16) / std::fabs((double)b));
+        }
+        dirs[4 * n] = xflag; dirs[4 * n + 1] = dx0; dirs[4 * n + 2] = dy0; dirs[4 * n + 3] = 0;
+    }
+    int *d_total;
+    uint32_t *d_pts;
+    uint8_t *d_mask;
+    OICS_TRY(compact_edges(ctx, dedges, w, h, stride, true, &d_total, &d_pts, &d_mask));
+    int npts = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&npts, d_total, sizeof(int), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    *n_lines = 0;
+    if (npts == 0) return OICS_OK;
+
+    std::vector<int> order;
+    ppht_order(npts, order);
+    const size_t acc_bytes = (size_t)numangle * numrho * sizeof(int32_t);
+    OICS_TRY(ctx->accum.ensure(acc_bytes));
+    // misc: [order npts][seq npts][ttab][dirs][n_lines][lines cap*4]
+    const size_t off_seq = sizeof(int) * (size_t)npts;
+    const size_t off_ttab = off_seq + sizeof(uint32_t) * (size_t)npts;
+    const size_t off_dirs = off_ttab + sizeof(float) * ttab.size();
+    const size_t off_nl = off_dirs + sizeof(int) * dirs.size();
+    const size_t off_lines = off_nl + 16;
+    const int dcap = std::max(cap, 1);
+    OICS_TRY(ctx->misc.ensure(off_lines + sizeof(int32_t) * 4 * (size_t)dcap));
+    uint8_t *base = ctx->misc.as<uint8_t>();
+    OICS_CUDA_TRY(cudaMemcpyAsync(base, order.data(), sizeof(int) * (size_t)npts, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_ttab, ttab.data(), sizeof(float) * ttab.size(), cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_dirs, dirs.data(), sizeof(int) * dirs.size(), cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(ctx->accum.p, 0, acc_bytes, st));
+    gather_points_kernel<<<cdiv(npts, 256), 256, 0, st>>>(d_pts, reinterpret_cast<const int *>(base), npts,
+                                                         reinterpret_cast<uint32_t *>(base + off_seq));
+    PphtArgs A;
+    A.seq = reinterpret_cast<const uint32_t *>(base + off_seq);
+    A.npts = npts;
+    A.mask = d_mask;
+    A.w = w; A.h = h;
+    A.accum = ctx->accum.as<int32_t>();
+    A.ttab = reinterpret_cast<const float *>(base + off_ttab);
+    A.dirs = reinterpret_cast<const int *>(base + off_dirs);
+    A.numangle = numangle; A.numrho = numrho;
+    A.threshold = threshold; A.line_length = line_length; A.line_gap = line_gap;
+    A.lines = reinterpret_cast<int32_t *>(base + off_lines);
+    A.cap = cap;
+    A.n_lines = reinterpret_cast<int *>(base + off_nl);
+    ppht_kernel<<<1, PP_THREADS, 0, st>>>(A);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 2;
+    int n = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&n, A.n_lines, sizeof(int), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    *n_lines = n;
+    const int ncopy = std::min(n, cap);
+    if (ncopy > 0) {
+        if (is_device_ptr(h_lines))
+            OICS_CUDA_TRY(cudaMemcpyAsync(h_lines, A.lines, sizeof(int32_t) * 4 * (size_t)ncopy, cudaMemcpyDeviceToDevice, st));
+        else
+            OICS_CUDA_TRY(cudaMemcpyAsync(h_lines, A.lines, sizeof(int32_t) * 4 * (size_t)ncopy, cudaMemcpyDeviceToHost, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    return OICS_OK;
+}
+
+}  // namespace oics

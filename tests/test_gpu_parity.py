@@ -222,3 +222,165 @@ def test_error_reporting(ctx):
     assert e.value.code == -6
     with pytest.raises(api.OicsError):
         ctx.preprocess(np.zeros((10, 10, 3), np.uint8), api.PRE_PROJECTION, resize_scale=2.0)
+
+
+# ----------------------------------------------------------------------------- H1
+@pytest.fixture(scope="module")
+def noisy_small(orc, dataset_like):
+    """A 460x496 crop with sensor-like noise: produces weak as well as strong Canny pixels."""
+    bgr, _ = dataset_like
+    rng = np.random.default_rng(77)
+    crop = bgr[300:760, 200:696].astype(np.int16)
+    noise = rng.normal(0, 12, crop.shape[:2] + (3,))
+    return np.clip(crop + noise, 0, 255).astype(np.uint8)
+
+
+@pytest.mark.parametrize("ch", [1, 3])
+@pytest.mark.parametrize("lohi", [(50.0, 150.0), (125.0, 150.0), (150.0, 50.0), (10.5, 40.9)])
+def test_canny_bit_exact(ctx, orc, noisy_small, dataset_like, ch, lohi):
+    for img in (noisy_small, dataset_like[0]):
+        src = img if ch == 3 else orc.gray(img)
+        ref = orc.canny(src, *lohi)
+        got = ctx.canny(src, *lohi)
+        assert ref.any() and np.array_equal(ref, got)
+
+
+def test_canny_edge_cases(ctx, orc):
+    rng = np.random.default_rng(3)
+    for shape in [(1, 1), (1, 37), (41, 1), (2, 2), (17, 65), (64, 16), (130, 67)]:
+        img = rng.integers(0, 256, shape, dtype=np.uint8)
+        assert np.array_equal(orc.canny(img, 50, 150), ctx.canny(img, 50, 150)), shape
+    # binary noise, constant image, true colour
+    b = ((rng.random((200, 300)) < 0.5) * 255).astype(np.uint8)
+    assert np.array_equal(orc.canny(b, 50, 150), ctx.canny(b, 50, 150))
+    z = np.full((50, 60), 200, np.uint8)
+    assert not ctx.canny(z, 50, 150).any()
+    col = rng.integers(0, 256, (120, 90, 3), dtype=np.uint8)
+    assert np.array_equal(orc.canny(col, 50, 150), ctx.canny(col, 50, 150))
+    # a long weak chain hanging off one strong pixel: many hysteresis levels
+    ramp = np.zeros((40, 1500), np.uint8)
+    ramp[20:, :] = 30
+    ramp[20:, :8] = 200
+    assert np.array_equal(orc.canny(ramp, 20, 300), ctx.canny(ramp, 20, 300))
+
+
+def test_canny_a4_bgr(ctx, orc, a4_card):
+    bgr, _ = a4_card
+    ref = orc.canny(bgr, 50.0, 150.0)
+    assert np.array_equal(ref, ctx.canny(bgr, 50.0, 150.0))
+
+
+# ----------------------------------------------------------------------------- H2
+def test_hough_accumulator_bit_exact(ctx, orc, dataset_like, noisy_small):
+    for img in (noisy_small, dataset_like[0]):
+        edges = orc.canny(img, 50.0, 150.0)
+        ref = orc.hough_accumulate(edges)
+        got = ctx.hough_accumulate(edges)
+        assert got.shape == ref.shape and np.array_equal(ref, got)
+        assert int(got.sum()) == 180 * int(np.count_nonzero(edges))
+    rng = np.random.default_rng(1)
+    e = ((rng.random((90, 131)) < 0.1) * 255).astype(np.uint8)
+    for rho, theta in [(1.0, np.pi / 180), (2.0, np.pi / 90), (0.5, np.pi / 360)]:
+        assert np.array_equal(orc.hough_accumulate(e, rho, theta), ctx.hough_accumulate(e, rho, theta))
+    assert not ctx.hough_accumulate(np.zeros((20, 30), np.uint8)).any()
+
+
+@pytest.mark.parametrize("args", [(0, 125.0, 15.0), (0, 150.0, 50.0), (100, 125.0, 15.0), (0, 30.0, 3.0),
+                                  (40, 20.4, 0.0), (10, 60.5, 7.5)])
+def test_hough_lines_p_line_for_line(ctx, orc, dataset_like, noisy_small, args):
+    thr, min_len, max_gap = args
+    for img in (dataset_like[0], noisy_small):
+        edges = orc.canny(img, 50.0, 150.0)
+        ref = orc.hough_lines_p(edges, thr, min_len, max_gap)
+        got = ctx.hough_lines_p(edges, thr, min_len, max_gap)
+        assert got.shape == ref.shape and np.array_equal(ref, got), (args, len(ref), len(got))
+
+
+def test_hough_lines_p_edge_cases(ctx, orc):
+    assert len(ctx.hough_lines_p(np.zeros((30, 40), np.uint8), 0, 5.0, 1.0)) == 0
+    e = np.zeros((64, 300), np.uint8)
+    e[10, 5:290] = 255            # one long horizontal line: several 256-step walk chunks
+    e[20:60, 100] = 255
+    e[63, 299] = 255
+    for thr in (0, 30):
+        assert np.array_equal(orc.hough_lines_p(e, thr, 20.0, 2.0), ctx.hough_lines_p(e, thr, 20.0, 2.0))
+    full = np.full((33, 47), 255, np.uint8)
+    assert np.array_equal(orc.hough_lines_p(full, 0, 10.0, 0.0), ctx.hough_lines_p(full, 0, 10.0, 0.0))
+
+
+def test_hough_entry_points(ctx, orc, dataset_like):
+    bgr, a = dataset_like
+    g = orc.gray(bgr)
+    n_ok = 0
+    for min_len, max_gap in [(125.0, 15.0), (150.0, 50.0), (40.0, 5.0), (20.0, 3.0)]:
+        try:
+            ref = orc.get_result_from_edges_detection(bgr, min_len, max_gap)
+        except IndexError:       # the reference panics on an empty segment list (omr.rs:272)
+            with pytest.raises(api.OicsError) as e:
+                ctx.result_from_edges_detection(bgr, min_len, max_gap)
+            assert e.value.code == -3
+        else:
+            n_ok += 1
+            got = ctx.result_from_edges_detection(bgr, min_len, max_gap)
+            assert (got.angle, got.status, got.candidates) == (ref.angle, ref.status, ref.candidates)
+        try:
+            ref = orc.get_angle_with_hough(g, min_len, max_gap)
+        except IndexError:       # hough.rs:74
+            with pytest.raises(api.OicsError) as e:
+                ctx.angle_with_hough(g, min_len, max_gap)
+            assert e.value.code == -3
+        else:
+            n_ok += 1
+            assert ctx.angle_with_hough(g, min_len, max_gap) == ref
+    assert n_ok >= 2
+
+
+# ----------------------------------------------------------------------------- F1 / F2
+def _fft_close(ref, got):
+    d = np.abs(ref.astype(np.int16) - got.astype(np.int16))
+    return d.max() <= 1 and np.count_nonzero(d) <= max(1, int(1e-4 * d.size))
+
+
+@pytest.mark.parametrize("shape", [(230, 248), (64, 128), (77, 100), (1150, 1240), (1, 9), (33, 1)])
+def test_fft_image(ctx, orc, dataset_like, shape):
+    g = orc.gray(dataset_like[0])[:shape[0], :shape[1]]
+    g = np.ascontiguousarray(g)
+    if g.shape != shape:
+        g = np.ascontiguousarray(np.resize(g, shape))
+    if g.min() == g.max():
+        g = g.copy(); g.flat[0] ^= 0x55
+    rm, rl = orc.fft_image(g)
+    gm, gl = ctx.fft_image(g, want_magnitude=True)
+    assert _fft_close(rl, gl), (shape, np.abs(rl.astype(int) - gl.astype(int)).max())
+    assert _fft_close(rm, gm)
+
+
+def test_fft_entry_points(ctx, orc, dataset_like):
+    bgr, a = dataset_like
+    g = orc.gray(bgr)
+    assert ctx.angle_with_fft(g, 125.0, 150.0, 150.0, 75.0) == orc.get_angle_with_fft(g, 125.0, 150.0, 150.0, 75.0)
+    assert ctx.angle_with_fft(g, 125.0, 150.0, 125.0, 15.0) == orc.get_angle_with_fft(g, 125.0, 150.0, 125.0, 15.0)
+    try:
+        ref = orc.get_result_from_fourier_transform(bgr, 125.0, 150.0, 125.0, 15.0)
+    except IndexError:
+        with pytest.raises(api.OicsError):
+            ctx.result_from_fourier_transform(bgr, 125.0, 150.0, 125.0, 15.0)
+    else:
+        got = ctx.result_from_fourier_transform(bgr, 125.0, 150.0, 125.0, 15.0)
+        assert (got.angle, got.status, got.candidates) == (ref.angle, ref.status, ref.candidates)
+
+
+# ----------------------------------------------------------------------------- R1: correct_default
+def test_correct_default_end_to_end(ctx, orc, dataset_like):
+    bgr, a = dataset_like
+    for params in [(45, 0.2, 248, 230, 150.0, 50.0), (15, 0.5, 0, 0, 125.0, 15.0)]:
+        ra, rneed, rout = orc.correct_default(bgr, *params)
+        ga, gneed, gout = ctx.correct_default(bgr, *params)
+        assert (ga, gneed) == (ra, rneed) and np.array_equal(rout, gout)
+    # a card whose projection sweep is ambiguous (blank) takes the Hough branch
+    blank = np.full((300, 260, 3), 255, np.uint8)
+    blank[40:43, 30:230] = 0
+    blank[45:240, 60:63] = 0
+    ra, rneed, rout = orc.correct_default(blank, 5, 1.0, 0, 0, 50.0, 5.0)
+    ga, gneed, gout = ctx.correct_default(blank, 5, 1.0, 0, 0, 50.0, 5.0)
+    assert (ga, gneed) == (ra, rneed) and np.array_equal(rout, gout)
