@@ -105,6 +105,11 @@ OICS_API int32_t oics_sweep_matrices(int32_t w, int32_t h, uint32_t max_angle, d
 /* transfer::rotate_mat geometry (transfer.rs:459-523; inlined at omr.rs:408-445). */
 OICS_API int32_t oics_rotate_geometry(int32_t cols, int32_t rows, double angle, double scale,
                                       int32_t clip, double M[6], int32_t *dst_w, int32_t *dst_h);
+/* Single-huge-image mode (BASELINE config 5): the contiguous slice of the n_angles sweep
+ * candidates that `rank` of `world` evaluates (ceil(n/world) each, the tail ranks may get
+ * fewer or none).  No reference counterpart: the reference sweeps on one CPU. */
+OICS_API int32_t oics_shard_range(int32_t n_angles, int32_t rank, int32_t world, int32_t *first,
+                                  int32_t *count);
 /* scale rule of omr.rs:60-82 */
 OICS_API double oics_projection_scale(int32_t w, int32_t h, int32_t max_w, int32_t max_h);
 

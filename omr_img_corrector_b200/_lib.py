@@ -45,6 +45,7 @@ SIGNATURES = {
     "oics_rotation_matrix_2d": (None, [C.c_float, C.c_float, _f64, _f64, _dp]),
     "oics_angle_half_range": (_i32, [C.c_uint32, _f64]),
     "oics_sweep_matrices": (_i32, [_i32, _i32, C.c_uint32, _f64, _f64, _dp, _i32, _ip]),
+    "oics_shard_range": (_i32, [_i32, _i32, _i32, _ip, _ip]),
     "oics_rotate_geometry": (_i32, [_i32, _i32, _f64, _f64, _i32, _dp, _ip, _ip]),
     "oics_projection_scale": (_f64, [_i32, _i32, _i32, _i32]),
     "oics_preprocess": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _i32, _i32, _f64, _u8p, _sz, _ip, _ip, _dp]),

@@ -114,6 +114,16 @@ OICS_API int32_t oics_sweep_matrices(int32_t w, int32_t h, uint32_t max_angle, d
     return OICS_OK;
 }
 
+OICS_API int32_t oics_shard_range(int32_t n_angles, int32_t rank, int32_t world, int32_t *first, int32_t *count)
+{
+    OICS_ARG(n_angles >= 0 && world > 0 && rank >= 0 && rank < world && first && count);
+    const int per = (n_angles + world - 1) / world;
+    const int f = std::min(n_angles, rank * per);
+    *first = f;
+    *count = std::min(per, n_angles - f);
+    return OICS_OK;
+}
+
 OICS_API int32_t oics_rotate_geometry(int32_t cols, int32_t rows, double angle, double scale, int32_t clip,
                                       double M[6], int32_t *dst_w, int32_t *dst_h)
 {
