@@ -64,6 +64,14 @@ struct FftPlan {
     DevBuf chirp, bbr, tw;
 };
 
+// What the sweep last built on the device, so that calls with the same geometry (a batch
+// run, the bench loop) skip the table / plan kernels.
+struct SweepCache {
+    int w = 0, h = 0;
+    std::vector<double> inv;        // inverse matrices the tables were built from
+    int plan_a0 = -1, plan_a1 = -1; // angle range the word-kernel plan covers
+};
+
 }  // namespace oics
 
 struct oics_ctx {
@@ -83,6 +91,8 @@ struct oics_ctx {
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;
+    oics::DevBuf wplanes, wmeta, wlists;
+    oics::SweepCache sweep_cache;
 };
 
 namespace oics {

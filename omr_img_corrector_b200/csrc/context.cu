@@ -178,7 +178,8 @@ OICS_API void oics_destroy(oics_ctx *ctx)
     DevBuf *bufs[] = {&ctx->in_img, &ctx->in_img2, &ctx->out_img, &ctx->gray,  &ctx->tmp8a, &ctx->tmp8b,
                       &ctx->bin,    &ctx->bits,    &ctx->mats,    &ctx->tabs,  &ctx->counts, &ctx->sd,
                       &ctx->sums,   &ctx->edges,   &ctx->mag,     &ctx->dxy,   &ctx->labels, &ctx->accum,
-                      &ctx->lines,  &ctx->misc,    &ctx->cplx,    &ctx->cplx2, &ctx->twid,   &ctx->fmag};
+                      &ctx->lines,  &ctx->misc,    &ctx->cplx,    &ctx->cplx2, &ctx->twid,   &ctx->fmag,
+                      &ctx->wplanes, &ctx->wmeta,  &ctx->wlists};
     for (DevBuf *b : bufs) b->release();
     for (FftPlan *pl : {&ctx->fft_row, &ctx->fft_col}) {
         pl->chirp.release();

@@ -19,8 +19,9 @@
 //   counts : [item][h + w] int32 (rows, then columns), item = (card, angle);
 //            accumulated with one coalesced RED per warp per tile.
 #include <algorithm>
+#include <cstdlib>
 
-#include "common.h"
+#include "sweep_common.h"
 
 namespace oics {
 
@@ -89,27 +90,12 @@ struct SweepArgs {
     const int *ad, *bd;
     const int2 *xy;
     int wpad, hpad;
-    int *counts;  // [item][h + w]
-    int n_angles;
-    int item0;    // first (card, angle) item of this launch
+    int *counts;  // [slot][h + w]
+    SweepItems I; // which (card, angle) items this launch covers
     int tiles_x;
     int tile_h;   // rows per tile, multiple of SW_WARPS * SW_GROUP
     int tile_cap; // staged-tile capacity in words
 };
-
-// 32x32 bit-matrix transpose across a warp: out[lane L] bit c = in[lane c] bit L.
-__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t v, int lane)
-{
-#pragma unroll
-    for (int j = 16; j >= 1; j >>= 1) {
-        const uint32_t lowmask = j == 16 ? 0x0000FFFFu : j == 8 ? 0x00FF00FFu : j == 4 ? 0x0F0F0F0Fu
-                                 : j == 2 ? 0x33333333u : 0x55555555u;
-        uint32_t other = __shfl_xor_sync(0xffffffffu, v, j);
-        if (lane & j) v = (v & ~lowmask) | ((other >> j) & lowmask);
-        else v = (v & lowmask) | ((other << j) & ~lowmask);
-    }
-    return v;
-}
 
 // One sample: OpenCV's NN coordinates, one LDS, shift the wanted bit into the
 // accumulator.  `tile` words are bit-reversed, so `word << (sx & 31)` puts pixel sx
@@ -190,8 +176,10 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
     __shared__ int sBox[6];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int item = A.item0 + blockIdx.y;
-    const int card = item / A.n_angles, ang = item - card * A.n_angles;
+    const int card_local = blockIdx.y / A.I.n_list;
+    const int ang = A.I.alist[blockIdx.y - card_local * A.I.n_list];
+    const int slot = card_local * A.I.na_chunk + (ang - A.I.a0);
+    const int card = A.I.card0 + card_local;
     const int tx = blockIdx.x % A.tiles_x, ty = blockIdx.x / A.tiles_x;
     const int x0 = tx * TW, y0 = ty * A.tile_h;
     const int tw = min(TW, A.w - x0), th = min(A.tile_h, A.h - y0);
@@ -261,7 +249,7 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
     int colsum[CPL];
 #pragma unroll
     for (int k = 0; k < CPL; k++) colsum[k] = 0;
-    int *rows_out = A.counts + (size_t)blockIdx.y * (A.h + A.w);
+    int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
     int *cols_out = rows_out + A.h;
 
     // Three instantiations so the hot one reads the tile with LDS (not generic LD):
@@ -331,7 +319,7 @@ __device__ double seq_std_dev(const int *__restrict__ v, int n, int *stage, int 
 }
 
 __global__ void __launch_bounds__(64) sweep_finalize_kernel(const int *__restrict__ counts, int w, int h,
-                                                            int item0, double *__restrict__ v_sd,
+                                                            long long item0, double *__restrict__ v_sd,
                                                             double *__restrict__ h_sd, long long *__restrict__ sums)
 {
     __shared__ int stage[2][FIN_CHUNK];
@@ -415,34 +403,68 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     // inverse matrices, host f64 in OpenCV's order
     std::vector<double> inv((size_t)n_angles * 6);
     for (int i = 0; i < n_angles; i++) invert_affine(M_host + 6 * (size_t)i, inv.data() + 6 * (size_t)i);
-    OICS_TRY(ctx->mats.ensure(inv.size() * sizeof(double)));
-    OICS_TRY(ctx->pin_small.ensure(inv.size() * sizeof(double)));
-    // pin_small may still be in flight from a previous call on this stream
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));
-    memcpy(ctx->pin_small.p, inv.data(), inv.size() * sizeof(double));
-    OICS_CUDA_TRY(cudaMemcpyAsync(ctx->mats.p, ctx->pin_small.p, inv.size() * sizeof(double), cudaMemcpyHostToDevice, st));
-
     const int wpad = (w + 31) & ~31, hpad = (h + 31) & ~31;
     const size_t tab_ints = (size_t)n_angles * (2 * (size_t)wpad + 2 * (size_t)hpad);
-    OICS_TRY(ctx->tabs.ensure(tab_ints * sizeof(int)));
+    SweepCache &cache = ctx->sweep_cache;
+    const bool same_geometry = cache.w == w && cache.h == h && cache.inv == inv && ctx->tabs.p &&
+                               ctx->tabs.cap >= tab_ints * sizeof(int);
+    if (!same_geometry) {
+        cache.w = cache.h = 0;
+        cache.plan_a0 = cache.plan_a1 = -1;
+        OICS_TRY(ctx->mats.ensure(inv.size() * sizeof(double)));
+        OICS_TRY(ctx->pin_small.ensure(inv.size() * sizeof(double)));
+        // pin_small may still be in flight from a previous call on this stream
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        memcpy(ctx->pin_small.p, inv.data(), inv.size() * sizeof(double));
+        OICS_CUDA_TRY(cudaMemcpyAsync(ctx->mats.p, ctx->pin_small.p, inv.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+        OICS_TRY(ctx->tabs.ensure(tab_ints * sizeof(int)));
+    }
     int *ad = ctx->tabs.as<int>();
     int *bd = ad + (size_t)n_angles * wpad;
     int2 *xy = reinterpret_cast<int2 *>(bd + (size_t)n_angles * wpad);
-    {
+    if (!same_geometry) {
         dim3 grid(cdiv(max(w, h), 256), n_angles);
         sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;
     }
+    SweepTables T;
+    T.ad = ad; T.bd = bd; T.xy = xy; T.wpad = wpad; T.hpad = hpad;
 
-    // tile shape and shared-memory budget
+    // ---- classify the angles: word kernel (by rho-loop length) or the general kernel
+    static const int kClassKr[5] = {0, 3, 5, 8, 11};
+    const char *force = getenv("OICS_SWEEP_KERNEL");  // "general" disables the word kernel (A/B tests)
+    const bool allow_word = !(force && force[0] == 'g');
+    std::vector<int> lists[5], kf((size_t)n_angles, -1), fast;
+    for (int i = 0; i < n_angles; i++) {
+        const int kr = allow_word ? sweepw_class(inv.data() + 6 * (size_t)i) : 0;
+        const int c = kr == 3 ? 1 : kr == 5 ? 2 : kr == 8 ? 3 : kr == 11 ? 4 : 0;
+        lists[c].push_back(i);
+        if (c) { kf[i] = (int)fast.size(); fast.push_back(i); }
+    }
+    const int n_fast = (int)fast.size(), n_general = (int)lists[0].size();
+    // device copy: [err 4 ints][kf n][fast n_fast][lists...]
+    size_t list_off[5], off = 4 + (size_t)n_angles + (size_t)n_fast;
+    for (int c = 0; c < 5; c++) { list_off[c] = off; off += lists[c].size(); }
+    if (!same_geometry || !ctx->wlists.p) {
+        std::vector<int> hostbuf(off, 0);
+        std::copy(kf.begin(), kf.end(), hostbuf.begin() + 4);
+        std::copy(fast.begin(), fast.end(), hostbuf.begin() + 4 + n_angles);
+        for (int c = 0; c < 5; c++) std::copy(lists[c].begin(), lists[c].end(), hostbuf.begin() + list_off[c]);
+        OICS_TRY(ctx->wlists.ensure(off * sizeof(int)));
+        OICS_CUDA_TRY(cudaMemcpyAsync(ctx->wlists.p, hostbuf.data(), off * sizeof(int), cudaMemcpyHostToDevice, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));  // hostbuf is a temporary
+    }
+    int *d_err = ctx->wlists.as<int>();
+    const int *d_kf = d_err + 4, *d_fast = d_kf + n_angles;
+
+    // ---- general kernel: tile shape and shared-memory budget over ITS angles
     const int CPL = pick_cpl(w);
     const int TW = 32 * CPL;
     int tile_h = SW_WARPS * SW_GROUP * 2;  // 512 rows
     if (h <= SW_WARPS * SW_GROUP) tile_h = SW_WARPS * SW_GROUP;
-    // worst-case footprint over the angles (one-pixel slack on each side)
     size_t need_words = 0;
-    for (int i = 0; i < n_angles; i++) {
+    for (int i : lists[0]) {
         const double *m = inv.data() + 6 * (size_t)i;
         double fw = fabs(m[0]) * TW + fabs(m[1]) * tile_h + 4.0;
         double fh = fabs(m[3]) * TW + fabs(m[4]) * tile_h + 4.0;
@@ -457,26 +479,39 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const size_t max_words = (size_t)(96 * 1024) / 4 - fixed_words;  // keep >= 2 CTAs per SM
     if (cap_words > max_words) cap_words = max_words;
     const size_t smem = (fixed_words + cap_words) * 4;
-
-    const int wp = cdiv(w, 32);
+    const int wp = cdiv(w, 32), wj = wp;
     const int tiles_x = cdiv(w, TW), tiles_y = cdiv(h, tile_h);
+
+    // ---- chunking: counts buffer (64 MB) and word-kernel plan (3 GB) bound a chunk
     const size_t per_item = (size_t)(h + w) * sizeof(int);
-    const long long total_items = (long long)n_cards * n_angles;
     long long chunk_items = (long long)((size_t)64 << 20) / (long long)per_item;
     if (chunk_items < 1) chunk_items = 1;
-    if (chunk_items > 32768) chunk_items = 32768;
-    if (chunk_items > total_items) chunk_items = total_items;
-    // whole cards per chunk when a card's angles fit, so the bit planes are packed once
-    OICS_TRY(ctx->counts.ensure((size_t)chunk_items * per_item));
-    const int cards_per_pack = (int)std::min<long long>(n_cards, std::max<long long>(1, (chunk_items + n_angles - 1) / n_angles + 1));
+    const size_t plan_per_angle = (size_t)wj * h * 8;
+    const long long plan_budget_angles = std::max<long long>(1, (long long)(((size_t)3 << 30) / plan_per_angle));
+    int cards_per_chunk, angles_per_chunk;
+    if (chunk_items >= n_angles && n_fast <= plan_budget_angles) {
+        angles_per_chunk = n_angles;
+        cards_per_chunk = (int)std::min<long long>(n_cards, chunk_items / n_angles);
+        cards_per_chunk = std::max(1, std::min(cards_per_chunk, 65535 / n_angles));
+    } else {
+        cards_per_chunk = 1;
+        angles_per_chunk = (int)std::max<long long>(1, std::min<long long>(std::min<long long>(n_angles, chunk_items),
+                                                                       std::min<long long>(plan_budget_angles, 65535)));
+    }
+    OICS_TRY(ctx->counts.ensure((size_t)cards_per_chunk * angles_per_chunk * per_item));
+    const int cards_per_pack = std::min(n_cards, std::max(cards_per_chunk, 8));
     OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * h * wp * sizeof(uint32_t)));
+    if (n_fast) {
+        const int max_plan = std::min<long long>(n_fast, angles_per_chunk);
+        OICS_TRY(ctx->wmeta.ensure((size_t)max_plan * wj * SWW_META * sizeof(uint32_t)));
+        OICS_TRY(ctx->wplanes.ensure((size_t)max_plan * plan_per_angle));
+    }
 
     SweepArgs A;
     A.bits_card_words = (size_t)h * wp;
     A.wp = wp; A.w = w; A.h = h;
     A.ad = ad; A.bd = bd; A.xy = xy; A.wpad = wpad; A.hpad = hpad;
     A.counts = ctx->counts.as<int>();
-    A.n_angles = n_angles;
     A.tiles_x = tiles_x;
     A.tile_h = tile_h;
     A.tile_cap = (int)cap_words;
@@ -484,49 +519,85 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     std::vector<cudaEvent_t> evs;
     ctx->last_sweep_launches = 0;
     int packed_first = -1, packed_n = 0;  // cards currently in ctx->bits
-    for (long long it0 = 0; it0 < total_items; it0 += chunk_items) {
-        const long long nit = min(chunk_items, total_items - it0);
-        const int c_first = (int)(it0 / n_angles), c_last = (int)((it0 + nit - 1) / n_angles);
-        if (c_first < packed_first || c_last >= packed_first + packed_n || packed_first < 0) {
-            packed_first = c_first;
-            packed_n = min(cards_per_pack, n_cards - c_first);
-            if (c_last >= packed_first + packed_n) {
-                set_error("internal: sweep chunk spans more cards than the bit-plane buffer holds");
-                return OICS_ERR_INVALID_ARG;
-            }
+    for (int c0 = 0; c0 < n_cards; c0 += cards_per_chunk) {
+        const int nc = std::min(cards_per_chunk, n_cards - c0);
+        if (packed_first < 0 || c0 < packed_first || c0 + nc > packed_first + packed_n) {
+            packed_first = c0;
+            packed_n = std::min(cards_per_pack, n_cards - c0);
             dim3 g(cdiv(wp, 128), h, packed_n);
             pack_bits_kernel<<<g, 128, 0, st>>>(dbins + (size_t)packed_first * card_stride, card_stride, stride, w, h, wp,
                                                 ctx->bits.as<uint32_t>(), packed_n);
             OICS_CUDA_TRY(cudaGetLastError());
             ctx->launches++;
         }
-        OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nit * per_item, st));
-        // item index relative to the packed window
-        A.bits = ctx->bits.as<uint32_t>() - (size_t)packed_first * A.bits_card_words;
-        A.item0 = (int)it0;
-        dim3 grid(tiles_x * tiles_y, (unsigned)nit);
-        cudaEvent_t e0, e1;
-        OICS_CUDA_TRY(cudaEventCreate(&e0));
-        OICS_CUDA_TRY(cudaEventCreate(&e1));
-        evs.push_back(e0);
-        evs.push_back(e1);
-        OICS_CUDA_TRY(cudaEventRecord(e0, st));
-        cudaError_t le = CPL == 2 ? launch_sweep<2>(A, grid, smem, st)
-                         : CPL == 3 ? launch_sweep<3>(A, grid, smem, st)
-                                    : launch_sweep<4>(A, grid, smem, st);
-        OICS_CUDA_TRY(le);
-        OICS_CUDA_TRY(cudaEventRecord(e1, st));
-        ctx->launches++;
-        ctx->last_sweep_launches++;
-        sweep_finalize_kernel<<<(unsigned)nit, 64, 0, st>>>(ctx->counts.as<int>(), w, h, (int)it0, d_vsd, d_hsd,
-                                                          reinterpret_cast<long long *>(d_sums));
-        OICS_CUDA_TRY(cudaGetLastError());
-        ctx->launches++;
-        if (d_counts_out && it0 == 0) {
-            const long long ncopy = std::min<long long>(nit, n_angles);
-            OICS_CUDA_TRY(cudaMemcpyAsync(d_counts_out, ctx->counts.p, (size_t)ncopy * per_item, cudaMemcpyDeviceToDevice, st));
+        // absolute card index addressing relative to the packed window
+        const uint32_t *bits_base = ctx->bits.as<uint32_t>() - (size_t)packed_first * A.bits_card_words;
+        for (int a0 = 0; a0 < n_angles; a0 += angles_per_chunk) {
+            const int a1 = std::min(n_angles, a0 + angles_per_chunk), na = a1 - a0;
+            OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nc * na * per_item, st));
+            // word-kernel plan for the fast angles of this range
+            const int f_lo = (int)(std::lower_bound(fast.begin(), fast.end(), a0) - fast.begin());
+            const int f_hi = (int)(std::lower_bound(fast.begin(), fast.end(), a1) - fast.begin());
+            uint32_t *d_pc = ctx->wplanes.as<uint32_t>();
+            uint32_t *d_pca = d_pc ? d_pc + (size_t)(f_hi - f_lo) * wj * h : nullptr;
+            if (f_hi > f_lo && !(cache.plan_a0 == a0 && cache.plan_a1 == a1)) {
+                cache.plan_a0 = cache.plan_a1 = -1;
+                OICS_TRY(sweepw_build_plan(ctx, T, d_fast + f_lo, f_hi - f_lo, w, h, ctx->wmeta.as<uint32_t>(), d_pc, d_pca, d_err));
+                cache.plan_a0 = a0;
+                cache.plan_a1 = a1;
+            }
+            cudaEvent_t e0, e1;
+            OICS_CUDA_TRY(cudaEventCreate(&e0));
+            OICS_CUDA_TRY(cudaEventCreate(&e1));
+            evs.push_back(e0);
+            evs.push_back(e1);
+            OICS_CUDA_TRY(cudaEventRecord(e0, st));
+            for (int c = 0; c < 5; c++) {
+                const std::vector<int> &L = lists[c];
+                const int l_lo = (int)(std::lower_bound(L.begin(), L.end(), a0) - L.begin());
+                const int l_hi = (int)(std::lower_bound(L.begin(), L.end(), a1) - L.begin());
+                if (l_hi == l_lo) continue;
+                SweepItems I;
+                I.alist = d_err + list_off[c] + l_lo;
+                I.n_list = l_hi - l_lo;
+                I.a0 = a0;
+                I.na_chunk = na;
+                I.card0 = c0;
+                if (c == 0) {
+                    A.bits = bits_base;
+                    A.I = I;
+                    dim3 grid(tiles_x * tiles_y, (unsigned)(nc * I.n_list));
+                    cudaError_t le = CPL == 2 ? launch_sweep<2>(A, grid, smem, st)
+                                     : CPL == 3 ? launch_sweep<3>(A, grid, smem, st)
+                                                : launch_sweep<4>(A, grid, smem, st);
+                    OICS_CUDA_TRY(le);
+                    ctx->launches++;
+                } else {
+                    SweepWPlan P;
+                    P.meta = ctx->wmeta.as<uint32_t>();
+                    P.pc = d_pc;
+                    P.pca = d_pca;
+                    P.kf = d_kf;
+                    P.kf0 = f_lo;
+                    P.err = d_err;
+                    OICS_TRY(sweepw_launch(ctx, kClassKr[c], bits_base, A.bits_card_words, wp, w, h, T, P, I, nc,
+                                           ctx->counts.as<int>()));
+                }
+                ctx->last_sweep_launches++;
+            }
+            OICS_CUDA_TRY(cudaEventRecord(e1, st));
+            const size_t item0 = (size_t)c0 * n_angles + a0;
+            sweep_finalize_kernel<<<(unsigned)(nc * na), 64, 0, st>>>(ctx->counts.as<int>(), w, h, (long long)item0, d_vsd,
+                                                                     d_hsd, reinterpret_cast<long long *>(d_sums));
+            OICS_CUDA_TRY(cudaGetLastError());
+            ctx->launches++;
+            if (d_counts_out && c0 == 0)
+                OICS_CUDA_TRY(cudaMemcpyAsync(d_counts_out + (size_t)a0 * (h + w), ctx->counts.p, (size_t)na * per_item,
+                                              cudaMemcpyDeviceToDevice, st));
         }
     }
+    int err_flag = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&err_flag, d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
     OICS_CUDA_TRY(cudaStreamSynchronize(st));
     double ms = 0.0;
     for (size_t i = 0; i < evs.size(); i += 2) {
@@ -537,6 +608,14 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         cudaEventDestroy(evs[i + 1]);
     }
     ctx->last_sweep_ms = ms;
+    if (err_flag) {
+        cache.w = cache.h = 0;
+        set_error("internal: the word sweep kernel rejected an angle its classifier accepted (flag %d)", err_flag);
+        return OICS_ERR_INVALID_ARG;
+    }
+    cache.w = w;
+    cache.h = h;
+    cache.inv.swap(inv);
     return OICS_OK;
 }
 
