@@ -69,7 +69,20 @@ struct FftPlan {
 struct SweepCache {
     int w = 0, h = 0;
     std::vector<double> inv;        // inverse matrices the tables were built from
-    int plan_a0 = -1, plan_a1 = -1; // angle range the word-kernel plan covers
+    int plan_a0 = -1, plan_a1 = -1; // angle range the word-kernel planes cover
+    int angles_per_chunk = 0;
+    // classification (meta kernel verdicts) and the launch lists derived from it
+    std::vector<int> general;       // angles the general kernel takes
+    std::vector<int> fast;          // angles the word kernel takes, ascending
+    struct WordClass {
+        int kr = 0;                 // source rows per output word
+        std::vector<int> angles;    // ascending
+        std::vector<int> gfirst;    // first angle of each group
+        std::vector<int> gstart, gcount;  // group -> index range in `angles`
+        size_t alist_off = 0, groups_off = 0;  // offsets (ints) in ctx->wlists
+    };
+    std::vector<WordClass> classes;
+    size_t general_off = 0, kf_off = 0, fast_off = 0;
 };
 
 }  // namespace oics

@@ -37,8 +37,9 @@ __global__ void sweep_tables_kernel(const double *__restrict__ Minv, int w, int 
     const int a = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const double *M = Minv + 6 * (size_t)a;
-    if (i < w) {
-        // adelta[x] = saturate_cast<int>(M[0]*x*AB_SCALE): (M0*x) rounded, then *1024 (exact)
+    if (i < wpad) {
+        // adelta[x] = saturate_cast<int>(M[0]*x*AB_SCALE): (M0*x) rounded, then *1024 (exact).
+        // Filled up to wpad: the word kernel references the last (virtual) pixel of a word.
         double x = (double)i;
         ad[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[0], x), 1024.0));
         bd[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[3], x), 1024.0));
@@ -404,10 +405,29 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     std::vector<double> inv((size_t)n_angles * 6);
     for (int i = 0; i < n_angles; i++) invert_affine(M_host + 6 * (size_t)i, inv.data() + 6 * (size_t)i);
     const int wpad = (w + 31) & ~31, hpad = (h + 31) & ~31;
+    const int wp = cdiv(w, 32), wj = wp;
     const size_t tab_ints = (size_t)n_angles * (2 * (size_t)wpad + 2 * (size_t)hpad);
     SweepCache &cache = ctx->sweep_cache;
     const bool same_geometry = cache.w == w && cache.h == h && cache.inv == inv && ctx->tabs.p &&
-                               ctx->tabs.cap >= tab_ints * sizeof(int);
+                               ctx->tabs.cap >= tab_ints * sizeof(int) && ctx->wlists.p;
+
+    // ---- chunking: counts buffer (64 MB) and word-kernel planes (3 GB) bound a chunk
+    const size_t per_item = (size_t)(h + w) * sizeof(int);
+    long long chunk_items = (long long)((size_t)64 << 20) / (long long)per_item;
+    if (chunk_items < 1) chunk_items = 1;
+    const size_t plan_per_angle = (size_t)wj * h * sizeof(uint2);
+    const long long plan_budget_angles = std::max<long long>(1, (long long)(((size_t)3 << 30) / plan_per_angle));
+    int cards_per_chunk, angles_per_chunk;
+    if (chunk_items >= n_angles && n_angles <= plan_budget_angles) {
+        angles_per_chunk = n_angles;
+        cards_per_chunk = (int)std::min<long long>(n_cards, chunk_items / n_angles);
+        cards_per_chunk = std::max(1, std::min(cards_per_chunk, 65535 / n_angles));
+    } else {
+        cards_per_chunk = 1;
+        angles_per_chunk = (int)std::max<long long>(1, std::min<long long>(std::min<long long>(n_angles, chunk_items),
+                                                                       std::min<long long>(plan_budget_angles, 65535)));
+    }
+
     if (!same_geometry) {
         cache.w = cache.h = 0;
         cache.plan_a0 = cache.plan_a1 = -1;
@@ -422,41 +442,82 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     int *ad = ctx->tabs.as<int>();
     int *bd = ad + (size_t)n_angles * wpad;
     int2 *xy = reinterpret_cast<int2 *>(bd + (size_t)n_angles * wpad);
+    SweepTables T;
+    T.ad = ad; T.bd = bd; T.xy = xy; T.wpad = wpad; T.hpad = hpad;
     if (!same_geometry) {
-        dim3 grid(cdiv(max(w, h), 256), n_angles);
+        dim3 grid(cdiv(max(wpad, h), 256), n_angles);
         sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;
-    }
-    SweepTables T;
-    T.ad = ad; T.bd = bd; T.xy = xy; T.wpad = wpad; T.hpad = hpad;
 
-    // ---- classify the angles: word kernel (by rho-loop length) or the general kernel
-    static const int kClassKr[5] = {0, 3, 5, 8, 11};
-    const char *force = getenv("OICS_SWEEP_KERNEL");  // "general" disables the word kernel (A/B tests)
-    const bool allow_word = !(force && force[0] == 'g');
-    std::vector<int> lists[5], kf((size_t)n_angles, -1), fast;
-    for (int i = 0; i < n_angles; i++) {
-        const int kr = allow_word ? sweepw_class(inv.data() + 6 * (size_t)i) : 0;
-        const int c = kr == 3 ? 1 : kr == 5 ? 2 : kr == 8 ? 3 : kr == 11 ? 4 : 0;
-        lists[c].push_back(i);
-        if (c) { kf[i] = (int)fast.size(); fast.push_back(i); }
-    }
-    const int n_fast = (int)fast.size(), n_general = (int)lists[0].size();
-    // device copy: [err 4 ints][kf n][fast n_fast][lists...]
-    size_t list_off[5], off = 4 + (size_t)n_angles + (size_t)n_fast;
-    for (int c = 0; c < 5; c++) { list_off[c] = off; off += lists[c].size(); }
-    if (!same_geometry || !ctx->wlists.p) {
+        // ---- classify the angles on the device: word kernel (by source rows per word) or general
+        const size_t meta_bytes = (size_t)n_angles * wj * SWW_META * sizeof(uint32_t);
+        const size_t cls_off = (meta_bytes + 15) & ~(size_t)15;
+        OICS_TRY(ctx->wmeta.ensure(cls_off + (size_t)n_angles * sizeof(SweepWClass)));
+        SweepWClass *d_cls = reinterpret_cast<SweepWClass *>(ctx->wmeta.as<uint8_t>() + cls_off);
+        OICS_TRY(sweepw_classify(ctx, T, n_angles, w, h, ctx->wmeta.as<uint32_t>(), d_cls));
+        std::vector<SweepWClass> cls((size_t)n_angles);
+        OICS_CUDA_TRY(cudaMemcpyAsync(cls.data(), d_cls, cls.size() * sizeof(SweepWClass), cudaMemcpyDeviceToHost, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        const char *force = getenv("OICS_SWEEP_KERNEL");  // "general" disables the word kernel (A/B tests)
+        const bool allow_word = !(force && force[0] == 'g');
+        const char *genv = getenv("OICS_SWEEP_GROUP");    // max angles per CTA (tuning)
+        const int gmax = genv ? std::max(1, std::min(SWW_GMAX, atoi(genv))) : SWW_GMAX;
+        cache.general.clear();
+        cache.fast.clear();
+        cache.classes.assign(SWW_KRMAX + 1, SweepCache::WordClass());
+        for (int i = 0; i < n_angles; i++) {
+            int kr = 0;
+            if (allow_word && !cls[i].bad && cls[i].rows >= 2 && cls[i].rows <= SWW_KRMAX &&
+                sweepw_group_fits(inv.data(), i, 1, cls[i].rows, w, h))
+                kr = cls[i].rows;
+            if (!kr) { cache.general.push_back(i); continue; }
+            cache.fast.push_back(i);
+            SweepCache::WordClass &C = cache.classes[kr];
+            C.kr = kr;
+            // extend the last group: consecutive angle, same chunk, footprints share a tile
+            bool extend = false;
+            if (!C.gstart.empty()) {
+                const int gs = C.gstart.back(), gc = C.gcount.back();
+                extend = gc < gmax && C.angles.back() == i - 1 && C.angles[gs] / angles_per_chunk == i / angles_per_chunk &&
+                         sweepw_group_fits(inv.data(), C.angles[gs], gc + 1, kr, w, h);
+            }
+            if (extend) C.gcount.back()++;
+            else { C.gstart.push_back((int)C.angles.size()); C.gcount.push_back(1); C.gfirst.push_back(i); }
+            C.angles.push_back(i);
+        }
+        // device copy: [err 4][kf n][fast][general][class lists][groups as int2]
+        const int n_fast0 = (int)cache.fast.size();
+        size_t off = 4;
+        cache.kf_off = off; off += (size_t)n_angles;
+        cache.fast_off = off; off += (size_t)n_fast0;
+        cache.general_off = off; off += cache.general.size();
+        for (auto &C : cache.classes) { C.alist_off = off; off += C.angles.size(); }
+        off = (off + 1) & ~(size_t)1;  // int2 alignment
+        for (auto &C : cache.classes) { C.groups_off = off; off += 2 * C.gstart.size(); }
         std::vector<int> hostbuf(off, 0);
-        std::copy(kf.begin(), kf.end(), hostbuf.begin() + 4);
-        std::copy(fast.begin(), fast.end(), hostbuf.begin() + 4 + n_angles);
-        for (int c = 0; c < 5; c++) std::copy(lists[c].begin(), lists[c].end(), hostbuf.begin() + list_off[c]);
+        for (int i = 0; i < n_angles; i++) hostbuf[cache.kf_off + i] = -1;
+        for (int k = 0; k < n_fast0; k++) {
+            hostbuf[cache.kf_off + cache.fast[k]] = k;
+            hostbuf[cache.fast_off + k] = cache.fast[k];
+        }
+        std::copy(cache.general.begin(), cache.general.end(), hostbuf.begin() + cache.general_off);
+        for (auto &C : cache.classes) {
+            std::copy(C.angles.begin(), C.angles.end(), hostbuf.begin() + C.alist_off);
+            for (size_t g = 0; g < C.gstart.size(); g++) {
+                hostbuf[C.groups_off + 2 * g] = C.gstart[g];
+                hostbuf[C.groups_off + 2 * g + 1] = C.gcount[g];
+            }
+        }
         OICS_TRY(ctx->wlists.ensure(off * sizeof(int)));
         OICS_CUDA_TRY(cudaMemcpyAsync(ctx->wlists.p, hostbuf.data(), off * sizeof(int), cudaMemcpyHostToDevice, st));
         OICS_CUDA_TRY(cudaStreamSynchronize(st));  // hostbuf is a temporary
+        cache.angles_per_chunk = angles_per_chunk;
     }
+    const std::vector<int> &fast = cache.fast, &general = cache.general;
+    const int n_fast = (int)fast.size();
     int *d_err = ctx->wlists.as<int>();
-    const int *d_kf = d_err + 4, *d_fast = d_kf + n_angles;
+    const int *d_kf = d_err + cache.kf_off, *d_fast = d_err + cache.fast_off;
 
     // ---- general kernel: tile shape and shared-memory budget over ITS angles
     const int CPL = pick_cpl(w);
@@ -464,7 +525,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     int tile_h = SW_WARPS * SW_GROUP * 2;  // 512 rows
     if (h <= SW_WARPS * SW_GROUP) tile_h = SW_WARPS * SW_GROUP;
     size_t need_words = 0;
-    for (int i : lists[0]) {
+    for (int i : general) {
         const double *m = inv.data() + 6 * (size_t)i;
         double fw = fabs(m[0]) * TW + fabs(m[1]) * tile_h + 4.0;
         double fh = fabs(m[3]) * TW + fabs(m[4]) * tile_h + 4.0;
@@ -479,31 +540,13 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const size_t max_words = (size_t)(96 * 1024) / 4 - fixed_words;  // keep >= 2 CTAs per SM
     if (cap_words > max_words) cap_words = max_words;
     const size_t smem = (fixed_words + cap_words) * 4;
-    const int wp = cdiv(w, 32), wj = wp;
     const int tiles_x = cdiv(w, TW), tiles_y = cdiv(h, tile_h);
 
-    // ---- chunking: counts buffer (64 MB) and word-kernel plan (3 GB) bound a chunk
-    const size_t per_item = (size_t)(h + w) * sizeof(int);
-    long long chunk_items = (long long)((size_t)64 << 20) / (long long)per_item;
-    if (chunk_items < 1) chunk_items = 1;
-    const size_t plan_per_angle = (size_t)wj * h * 8;
-    const long long plan_budget_angles = std::max<long long>(1, (long long)(((size_t)3 << 30) / plan_per_angle));
-    int cards_per_chunk, angles_per_chunk;
-    if (chunk_items >= n_angles && n_fast <= plan_budget_angles) {
-        angles_per_chunk = n_angles;
-        cards_per_chunk = (int)std::min<long long>(n_cards, chunk_items / n_angles);
-        cards_per_chunk = std::max(1, std::min(cards_per_chunk, 65535 / n_angles));
-    } else {
-        cards_per_chunk = 1;
-        angles_per_chunk = (int)std::max<long long>(1, std::min<long long>(std::min<long long>(n_angles, chunk_items),
-                                                                       std::min<long long>(plan_budget_angles, 65535)));
-    }
     OICS_TRY(ctx->counts.ensure((size_t)cards_per_chunk * angles_per_chunk * per_item));
     const int cards_per_pack = std::min(n_cards, std::max(cards_per_chunk, 8));
     OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * h * wp * sizeof(uint32_t)));
     if (n_fast) {
         const int max_plan = std::min<long long>(n_fast, angles_per_chunk);
-        OICS_TRY(ctx->wmeta.ensure((size_t)max_plan * wj * SWW_META * sizeof(uint32_t)));
         OICS_TRY(ctx->wplanes.ensure((size_t)max_plan * plan_per_angle));
     }
 
@@ -535,14 +578,13 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         for (int a0 = 0; a0 < n_angles; a0 += angles_per_chunk) {
             const int a1 = std::min(n_angles, a0 + angles_per_chunk), na = a1 - a0;
             OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nc * na * per_item, st));
-            // word-kernel plan for the fast angles of this range
+            // word-kernel planes for the fast angles of this range
             const int f_lo = (int)(std::lower_bound(fast.begin(), fast.end(), a0) - fast.begin());
             const int f_hi = (int)(std::lower_bound(fast.begin(), fast.end(), a1) - fast.begin());
-            uint32_t *d_pc = ctx->wplanes.as<uint32_t>();
-            uint32_t *d_pca = d_pc ? d_pc + (size_t)(f_hi - f_lo) * wj * h : nullptr;
             if (f_hi > f_lo && !(cache.plan_a0 == a0 && cache.plan_a1 == a1)) {
                 cache.plan_a0 = cache.plan_a1 = -1;
-                OICS_TRY(sweepw_build_plan(ctx, T, d_fast + f_lo, f_hi - f_lo, w, h, ctx->wmeta.as<uint32_t>(), d_pc, d_pca, d_err));
+                OICS_TRY(sweepw_build_planes(ctx, T, ctx->wmeta.as<uint32_t>(), d_fast + f_lo, f_hi - f_lo, w, h,
+                                             ctx->wplanes.as<uint2>()));
                 cache.plan_a0 = a0;
                 cache.plan_a1 = a1;
             }
@@ -552,18 +594,16 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
             evs.push_back(e0);
             evs.push_back(e1);
             OICS_CUDA_TRY(cudaEventRecord(e0, st));
-            for (int c = 0; c < 5; c++) {
-                const std::vector<int> &L = lists[c];
-                const int l_lo = (int)(std::lower_bound(L.begin(), L.end(), a0) - L.begin());
-                const int l_hi = (int)(std::lower_bound(L.begin(), L.end(), a1) - L.begin());
-                if (l_hi == l_lo) continue;
-                SweepItems I;
-                I.alist = d_err + list_off[c] + l_lo;
-                I.n_list = l_hi - l_lo;
-                I.a0 = a0;
-                I.na_chunk = na;
-                I.card0 = c0;
-                if (c == 0) {
+            {
+                const int l_lo = (int)(std::lower_bound(general.begin(), general.end(), a0) - general.begin());
+                const int l_hi = (int)(std::lower_bound(general.begin(), general.end(), a1) - general.begin());
+                if (l_hi > l_lo) {
+                    SweepItems I;
+                    I.alist = d_err + cache.general_off + l_lo;
+                    I.n_list = l_hi - l_lo;
+                    I.a0 = a0;
+                    I.na_chunk = na;
+                    I.card0 = c0;
                     A.bits = bits_base;
                     A.I = I;
                     dim3 grid(tiles_x * tiles_y, (unsigned)(nc * I.n_list));
@@ -572,17 +612,29 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                                                 : launch_sweep<4>(A, grid, smem, st);
                     OICS_CUDA_TRY(le);
                     ctx->launches++;
-                } else {
-                    SweepWPlan P;
-                    P.meta = ctx->wmeta.as<uint32_t>();
-                    P.pc = d_pc;
-                    P.pca = d_pca;
-                    P.kf = d_kf;
-                    P.kf0 = f_lo;
-                    P.err = d_err;
-                    OICS_TRY(sweepw_launch(ctx, kClassKr[c], bits_base, A.bits_card_words, wp, w, h, T, P, I, nc,
-                                           ctx->counts.as<int>()));
+                    ctx->last_sweep_launches++;
                 }
+            }
+            // heaviest classes first: the tail of the chunk is filled by the light ones
+            for (int kr = SWW_KRMAX; kr >= 2; kr--) {
+                const SweepCache::WordClass &C = cache.classes[kr];
+                const int g_lo = (int)(std::lower_bound(C.gfirst.begin(), C.gfirst.end(), a0) - C.gfirst.begin());
+                const int g_hi = (int)(std::lower_bound(C.gfirst.begin(), C.gfirst.end(), a1) - C.gfirst.begin());
+                if (g_hi == g_lo) continue;
+                SweepWPlan P;
+                P.meta = ctx->wmeta.as<uint32_t>();
+                P.planes = ctx->wplanes.as<uint2>();
+                P.kf = d_kf;
+                P.kf0 = f_lo;
+                P.err = d_err;
+                SweepWGroups G;
+                G.alist = d_err + C.alist_off;
+                G.groups = reinterpret_cast<const int2 *>(d_err + C.groups_off) + g_lo;
+                G.n_groups = g_hi - g_lo;
+                G.a0 = a0;
+                G.na_chunk = na;
+                G.card0 = c0;
+                OICS_TRY(sweepw_launch(ctx, kr, bits_base, A.bits_card_words, wp, w, h, T, P, G, nc, ctx->counts.as<int>()));
                 ctx->last_sweep_launches++;
             }
             OICS_CUDA_TRY(cudaEventRecord(e1, st));
@@ -610,7 +662,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     ctx->last_sweep_ms = ms;
     if (err_flag) {
         cache.w = cache.h = 0;
-        set_error("internal: the word sweep kernel rejected an angle its classifier accepted (flag %d)", err_flag);
+        set_error("internal: the word sweep kernel rejected a tile its planner accepted (flag %d)", err_flag);
         return OICS_ERR_INVALID_ARG;
     }
     cache.w = w;

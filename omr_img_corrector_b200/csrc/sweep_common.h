@@ -1,18 +1,20 @@
 // Shared between the two sweep kernels (sweep.cu: one sample per instruction group,
 // any affine map; sweepw.cu: one 32-pixel word per lane, near-unit-scale rotations).
 #pragma once
+#include <vector>
+
 #include "common.h"
 
 namespace oics {
 
 // Per-angle OpenCV warpAffine tables (AB_BITS = 10), see sweep_tables_kernel.
 struct SweepTables {
-    const int *ad, *bd;   // [angle][wpad]
+    const int *ad, *bd;   // [angle][wpad]  (filled for every x < wpad, not only x < w)
     const int2 *xy;       // [angle][hpad]  {X0, Y0} incl. the +512 rounding term
     int wpad, hpad;
 };
 
-// Which (card, angle) items one launch covers and where their counts go.
+// Which (card, angle) items one launch of the general kernel covers and where their counts go.
 //   blockIdx.y -> card_local = by / n_list, angle = alist[by % n_list]
 //   counts slot = card_local * na_chunk + (angle - a0); card = card0 + card_local
 struct SweepItems {
@@ -42,25 +44,40 @@ static constexpr int SWW_TH = 512;     // output rows per CTA
 static constexpr int SWW_TJ = 8;       // output word columns per CTA (one per warp)
 static constexpr int SWW_P = 17;       // staged-tile pitch in words (odd: rows spread over banks)
 static constexpr int SWW_TROWS = 608;  // staged-tile rows
-static constexpr int SWW_META = 16;    // uint32 per (angle, word column): Q[11], S1, S2, bj, cj, pad
+static constexpr int SWW_META = 16;    // uint32 per (angle, word column): Q[10], -, S1, -, Aref, Bref, -
+static constexpr int SWW_GMAX = 8;     // candidate angles one CTA evaluates on one staged tile
+
+// Per-angle verdict of the meta kernel: can the word kernel take this angle, and with how
+// many source rows per output word.
+struct SweepWClass {
+    int rows;   // max over word columns of (source rows one word draws from); 0 = not computed
+    int bad;    // != 0: a column map outside the supported range (scale, shear, |angle| too large)
+};
 
 struct SweepWPlan {
-    // device buffers for the fast angles of the current chunk, indexed by slot = kf[angle] - kf0
-    const uint32_t *meta;   // [slot][wj][SWW_META]
-    const uint32_t *pc;     // [slot][wj][h]  row-carry masks
-    const uint32_t *pca;    // [slot][wj][h]  column-carry masks
-    const int *kf;          // [n_angles] fast index of an angle (or -1)
+    const uint32_t *meta;   // [angle][wj][SWW_META]
+    const uint2 *planes;    // [slot][wj][h]  {row-carry mask C, column-step mask D0}
+    const int *kf;          // [n_angles] fast index of an angle (or -1); slot = kf[angle] - kf0
     int kf0;
     int *err;               // sticky device flag
 };
 
+// A run of consecutive candidate angles of one class evaluated by one CTA per tile.
+struct SweepWGroups {
+    const int *alist;       // class angle list (device)
+    const int2 *groups;     // {first index into alist, count} (device)
+    int n_groups;
+    int a0, na_chunk, card0;
+};
+
 // host side (sweepw.cu)
-// Smallest supported rho-loop length for the inverse matrix m, or 0 when the word kernel
-// cannot take this angle (scale or shear too far from a small rotation).
-int sweepw_class(const double m[6]);
-int32_t sweepw_build_plan(oics_ctx *ctx, const SweepTables &T, const int *d_fast_angles, int n_fast, int w, int h,
-                          uint32_t *d_meta, uint32_t *d_pc, uint32_t *d_pca, int *d_err);
+int32_t sweepw_classify(oics_ctx *ctx, const SweepTables &T, int n_angles, int w, int h, uint32_t *d_meta,
+                        SweepWClass *d_cls);
+// Can `cnt` consecutive angles starting at inv[6*first] share one staged tile for every tile of the image?
+bool sweepw_group_fits(const double *inv, int first, int cnt, int kr, int w, int h);
+int32_t sweepw_build_planes(oics_ctx *ctx, const SweepTables &T, const uint32_t *d_meta, const int *d_fast_angles,
+                            int n_fast, int w, int h, uint2 *d_planes);
 int32_t sweepw_launch(oics_ctx *ctx, int kr, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
-                      const SweepTables &T, const SweepWPlan &P, const SweepItems &I, int n_cards, int *counts);
+                      const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts);
 
 }  // namespace oics

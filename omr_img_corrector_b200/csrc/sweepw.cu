@@ -3,25 +3,32 @@
 // sweep.cu (OpenCV-exact nearest-neighbour sampling of omr.rs:165-173, zero counts of
 // omr.rs:8-39), but one lane produces 32 output pixels at a time.
 //
-// Exact decomposition.  With the AB_BITS = 10 tables, for output pixel x = 32 j + i of row y
-//     sx = (X0[y] + ad[x]) >> 10 = qx + qa_i + [fa_i + fx >= 1024]
-//     sy = (Y0[y] + bd[x]) >> 10 = qy + qb_i + [fb_i + fy >= 1024]
-// (q = value >> 10, f = value & 1023).  Inside one word the integer parts move little:
-//     qb_i = bmin_j + r_i,  r_i in [0, KR-2]         (a word spans <= 32 |sin| + 1 source rows)
-//     qa_i = tmin_j + i + t_i,  t_i in {0, 1, 2}     (<= 32 (1 - cos) + 1 duplicated columns)
-// so the word is assembled from KR source-row windows
-//     out = OR_rho  R_rho & pick(window(row qy + bmin_j + rho, column qx + tmin_j), t + CA)
-//     R_rho = (Q_rho & ~C) | (Q_(rho-1) & C),   Q_rho = {i : r_i = rho}
-// where Q, S1 = {t >= 1}, S2 = {t >= 2}, bmin, tmin depend on (angle, j) only ("meta") and the
-// carry masks C(y, j), CA(y, j) depend on (angle, j, y) only ("planes") -- both are
-// independent of the card, are built once per geometry and are shared by every card of a
-// batch.  The per-card work per word is then KR x (2-3 LDS, 2-5 funnel shifts, 3-5 LOP3).
+// Exact decomposition.  OpenCV samples output pixel (x, y) at
+//     sx = (X0[y] + ad[x]) >> 10,   sy = (Y0[y] + bd[x]) >> 10        (AB_BITS = 10 tables).
+// Take the 32 pixels x = 32 j + i of one output word and re-reference both sums to one pixel
+// of the word:
+//   columns, reference i = 31:   X' = X0[y] + ad[32j+31] - 31*1024
+//       sx_i = (X' >> 10) + i + d_i,   d_i = (fx' + G_i) >> 10,   G_i = ad[32j+i] - ad[32j+31] + (31-i)*1024 >= 0
+//       d_i is non-increasing in i and d_31 = 0, so the word reads exactly the 32 source
+//       bits V = [X'>>10, X'>>10 + 31] and pixel i takes bit i + d_i of V, d_i in {0, 1, 2}.
+//   rows, reference r = the end of the word where bd is smallest:   Y' = Y0[y] + bd[ref]
+//       sy_i = (Y' >> 10) + rho_i,   rho_i = (fy' + H_i) >> 10,   H_i = bd[32j+i] - bd[ref] >= 0
+//       rho_i in [0, KR-1] with KR = floor(31 |sin|) + 2 source rows per word.
+// With G_i = 1024 g_i + fg_i and H_i = 1024 h_i + fh_i the per-(angle, j) constants are the
+// masks Q_rho = {i : h_i = rho}, S1 = {i : g_i = 1} ("meta") and the carries
+//     C(y)  = {i : fh_i + fy' >= 1024},   D0(y) = S1 xor {i : fg_i + fx' >= 1024}
+// depend on (angle, j, y) only ("planes"); both are independent of the card, are built once
+// per geometry and shared by every card of a batch.  Per output word the card-dependent
+// work is then KR x (2 LDS, 1 funnel shift, 1 shift, 3 LOP3):
+//     out = OR_rho  R_rho & sel(V_rho),   R_rho = (Q_rho & ~C) | (Q_(rho-1) & C),
+//     sel(V) = D1 ? V << 2 : D0 ? V << 1 : V          (D1 = S1 & ~D0, only for |angle| > 14.6 deg)
 //
-// Layout: lane = output row, warp = one word column, CTA = 8 word columns x 512 rows whose
-// source footprint (a parallelogram of the 1-bit plane) is staged once in shared memory with
-// an odd pitch, zero outside the image (= white border), so the hot loop has no bounds tests.
-// Row counts leave the lane as popc; column counts are accumulated as bit-sliced vertical
-// counters (carry-save adders) and unpacked once per column with 5 warp bit-transposes.
+// Layout: lane = output row, warp = one word column, CTA = 8 word columns x 512 rows for up
+// to 8 CONSECUTIVE candidate angles whose source footprints (parallelograms of the 1-bit
+// plane, 0.1 degree apart) share one staged shared-memory tile (odd pitch, zero outside the
+// image = white border, so the hot loop has no bounds tests).  Row counts leave the lane as
+// popc; column counts are accumulated as bit-sliced vertical counters (carry-save adders)
+// and unpacked once per (angle, column) with warp bit-transposes.
 #include <algorithm>
 #include <cmath>
 
@@ -29,75 +36,63 @@
 
 namespace oics {
 
-int sweepw_class(const double m[6])
-{
-    // t range <= 2 and r range <= KR-2 over any 32 consecutive x (tables are rint()s of a
-    // linear function: each difference is within 1 of the real one)
-    const double tr = 31.0 * std::fabs(1.0 - m[0]) + 0.01;
-    if (!(m[0] > 0) || std::floor(tr) + 1.0 > 2.0) return 0;
-    const int rmax = (int)std::floor(31.0 * std::fabs(m[3]) + 0.01) + 1;
-    const int need = rmax + 2;
-    if (need > SWW_KRMAX) return 0;
-    // staged footprint of a 256 x 512 tile must fit SWW_P words x SWW_TROWS rows
-    const double fw = 255.0 * std::fabs(m[0]) + 511.0 * std::fabs(m[1]);
-    const double fh = 511.0 * std::fabs(m[4]) + 255.0 * std::fabs(m[3]);
-    if ((fw + 5.0) / 32.0 + 4.0 > (double)SWW_P) return 0;
-    if (fh + 4.0 + SWW_KRMAX > (double)SWW_TROWS) return 0;
-    return need <= 3 ? 3 : need <= 5 ? 5 : need <= 8 ? 8 : 11;
-}
-
 // ---------------------------------------------------------------------------
-// meta: one warp per (fast angle, word column)
-__global__ void __launch_bounds__(32) sweepw_meta_kernel(SweepTables T, const int *__restrict__ fast_angles, int w,
-                                                         int wj, uint32_t *__restrict__ meta, int *err)
+// meta + classification: one warp per (angle, word column)
+__global__ void __launch_bounds__(32) sweepw_meta_kernel(SweepTables T, int w, int wj, uint32_t *__restrict__ meta,
+                                                         SweepWClass *__restrict__ cls)
 {
-    const int j = blockIdx.x, k = blockIdx.y, lane = threadIdx.x;
-    const int ang = fast_angles[k];
-    const int x = 32 * j + lane;
+    const int j = blockIdx.x, ang = blockIdx.y, lane = threadIdx.x;
+    const int x = 32 * j + lane;  // < wpad: the tables are filled beyond w
     const bool valid = x < w;
-    const int xc = valid ? x : w - 1;
-    const int a = T.ad[(size_t)ang * T.wpad + xc], b = T.bd[(size_t)ang * T.wpad + xc];
-    int qa = (a >> 10) - lane, qb = b >> 10;
-    int tmin = valid ? qa : 0x7fffffff, bmin = valid ? qb : 0x7fffffff;
+    const int a = T.ad[(size_t)ang * T.wpad + x], b = T.bd[(size_t)ang * T.wpad + x];
+    const int a31 = __shfl_sync(0xffffffffu, a, 31);
+    const int b0 = __shfl_sync(0xffffffffu, b, 0), b31 = __shfl_sync(0xffffffffu, b, 31);
+    const int bref = min(b0, b31);
+    const int G = a - a31 + (31 - lane) * 1024;
+    const int H = b - bref;
+    // a <= a31 keeps i + d_i <= 31 (the word never reads past its 32-bit window)
+    const bool ok = G >= 0 && G < 2048 && a <= a31 && H >= 0 && (H >> 10) <= SWW_KRMAX - 2;
+    int hmax = ok ? (H >> 10) : 0;
 #pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) {
-        tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
-        bmin = min(bmin, __shfl_xor_sync(0xffffffffu, bmin, o));
-    }
-    const int t = qa - tmin, r = qb - bmin;
-    if (valid && (t > 2 || r > SWW_KRMAX - 2)) atomicExch(err, 1);
-    uint32_t *m = meta + ((size_t)k * wj + j) * SWW_META;
+    for (int o = 16; o >= 1; o >>= 1) hmax = max(hmax, __shfl_xor_sync(0xffffffffu, hmax, o));
+    const bool all_ok = __all_sync(0xffffffffu, ok);
+    uint32_t *m = meta + ((size_t)ang * wj + j) * SWW_META;
     // pixel i of the word lives at bit 31 - i
-    for (int rho = 0; rho < SWW_KRMAX; rho++) {
-        const uint32_t q = __brev(__ballot_sync(0xffffffffu, valid && r == rho));
+    for (int rho = 0; rho < SWW_KRMAX - 1; rho++) {
+        const uint32_t q = __brev(__ballot_sync(0xffffffffu, valid && ok && (H >> 10) == rho));
         if (lane == 0) m[rho] = q;
     }
-    const uint32_t s1 = __brev(__ballot_sync(0xffffffffu, valid && t >= 1));
-    const uint32_t s2 = __brev(__ballot_sync(0xffffffffu, valid && t >= 2));
+    const uint32_t s1 = __brev(__ballot_sync(0xffffffffu, ok && G >= 1024));
     if (lane == 0) {
+        m[10] = 0;
         m[11] = s1;
-        m[12] = s2;
-        m[13] = (uint32_t)bmin;
-        m[14] = (uint32_t)tmin;
+        m[12] = 0;
+        m[13] = (uint32_t)(a31 - 31 * 1024);
+        m[14] = (uint32_t)bref;
         m[15] = 0;
+        atomicMax(&cls[ang].rows, hmax + 2);
+        if (!all_ok) atomicOr(&cls[ang].bad, 1);
     }
 }
 
-// planes: one CTA per (fast angle, word column).  Phase 1 tabulates the carry mask for every
+// planes: one CTA per (fast angle, word column).  Phase 1 tabulates the two masks for every
 // possible fraction (1024 entries), phase 2 looks the rows up.
-__global__ void __launch_bounds__(1024) sweepw_planes_kernel(SweepTables T, const int *__restrict__ fast_angles, int w,
-                                                             int h, int wj, uint32_t *__restrict__ pc,
-                                                             uint32_t *__restrict__ pca)
+__global__ void __launch_bounds__(1024) sweepw_planes_kernel(SweepTables T, const uint32_t *__restrict__ meta,
+                                                             const int *__restrict__ fast_angles, int h, int wj,
+                                                             uint2 *__restrict__ planes)
 {
-    __shared__ int sfa[32], sfb[32];
-    __shared__ uint32_t tabC[1024], tabA[1024];
+    __shared__ int sfg[32], sfh[32];
+    __shared__ uint32_t tabC[1024], tabD[1024];
     const int j = blockIdx.x, k = blockIdx.y, tid = threadIdx.x;
     const int ang = fast_angles[k];
+    const uint32_t *m = meta + ((size_t)ang * wj + j) * SWW_META;
+    const uint32_t s1 = m[11];
+    const int aref = (int)m[13], bref = (int)m[14];
     if (tid < 32) {
         const int x = 32 * j + tid;
-        // beyond the image: fraction 0 never carries (and those bits are masked by Q = 0 anyway)
-        sfa[tid] = x < w ? (T.ad[(size_t)ang * T.wpad + x] & 1023) : 0;
-        sfb[tid] = x < w ? (T.bd[(size_t)ang * T.wpad + x] & 1023) : 0;
+        const int a = T.ad[(size_t)ang * T.wpad + x], b = T.bd[(size_t)ang * T.wpad + x];
+        sfg[tid] = (a - aref - tid * 1024) & 1023;   // G_i = a - a31 + (31 - i) * 1024
+        sfh[tid] = (b - bref) & 1023;
     }
     __syncthreads();
     {
@@ -105,36 +100,75 @@ __global__ void __launch_bounds__(1024) sweepw_planes_kernel(SweepTables T, cons
         uint32_t c = 0, ca = 0;
 #pragma unroll
         for (int i = 0; i < 32; i++) {
-            c |= (uint32_t)(sfb[i] + f >= 1024) << (31 - i);
-            ca |= (uint32_t)(sfa[i] + f >= 1024) << (31 - i);
+            c |= (uint32_t)(sfh[i] + f >= 1024) << (31 - i);
+            ca |= (uint32_t)(sfg[i] + f >= 1024) << (31 - i);
         }
         tabC[f] = c;
-        tabA[f] = ca;
+        tabD[f] = ca ^ s1;
     }
     __syncthreads();
     const int2 *xy = T.xy + (size_t)ang * T.hpad;
-    uint32_t *oc = pc + ((size_t)k * wj + j) * h, *oa = pca + ((size_t)k * wj + j) * h;
+    uint2 *o = planes + ((size_t)k * wj + j) * h;
     for (int y = tid; y < h; y += 1024) {
         const int2 p = xy[y];
-        oc[y] = tabC[p.y & 1023];
-        oa[y] = tabA[p.x & 1023];
+        o[y] = make_uint2(tabC[(p.y + bref) & 1023], tabD[(p.x + aref) & 1023]);
     }
 }
 
-int32_t sweepw_build_plan(oics_ctx *ctx, const SweepTables &T, const int *d_fast_angles, int n_fast, int w, int h,
-                          uint32_t *d_meta, uint32_t *d_pc, uint32_t *d_pca, int *d_err)
+int32_t sweepw_classify(oics_ctx *ctx, const SweepTables &T, int n_angles, int w, int h, uint32_t *d_meta,
+                        SweepWClass *d_cls)
 {
-    if (n_fast <= 0) return OICS_OK;
     const int wj = cdiv(w, 32);
-    dim3 grid(wj, n_fast);
-    sweepw_meta_kernel<<<grid, 32, 0, ctx->stream>>>(T, d_fast_angles, w, wj, d_meta, d_err);
+    OICS_CUDA_TRY(cudaMemsetAsync(d_cls, 0, (size_t)n_angles * sizeof(SweepWClass), ctx->stream));
+    sweepw_meta_kernel<<<dim3(wj, n_angles), 32, 0, ctx->stream>>>(T, w, wj, d_meta, d_cls);
     OICS_CUDA_TRY(cudaGetLastError());
-    sweepw_planes_kernel<<<grid, 1024, 0, ctx->stream>>>(T, d_fast_angles, w, h, wj, d_pc, d_pca);
-    OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches += 2;
+    ctx->launches++;
     return OICS_OK;
 }
 
+int32_t sweepw_build_planes(oics_ctx *ctx, const SweepTables &T, const uint32_t *d_meta, const int *d_fast_angles,
+                            int n_fast, int w, int h, uint2 *d_planes)
+{
+    if (n_fast <= 0) return OICS_OK;
+    const int wj = cdiv(w, 32);
+    sweepw_planes_kernel<<<dim3(wj, n_fast), 1024, 0, ctx->stream>>>(T, d_meta, d_fast_angles, h, wj, d_planes);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    return OICS_OK;
+}
+
+// Host-side footprint test (real-valued, with a margin over the 1/1024-pixel table rounding;
+// the kernel re-checks with the exact integers and raises the sticky flag if this was wrong).
+bool sweepw_group_fits(const double *inv, int first, int cnt, int kr, int w, int h)
+{
+    const int wj = cdiv(w, 32), tiles_x = cdiv(wj, SWW_TJ), tiles_y = cdiv(h, SWW_TH);
+    for (int ty = 0; ty < tiles_y; ty++) {
+        const double ya = ty * SWW_TH, yb = std::min(h, (ty + 1) * SWW_TH) - 1;
+        for (int tx = 0; tx < tiles_x; tx++) {
+            const int nj = std::min(SWW_TJ, wj - tx * SWW_TJ);
+            const double xa = tx * SWW_TJ * 32, xb = xa + 32 * nj - 1;
+            double cmin = 1e300, cmax = -1e300, rmin = 1e300, rmax = -1e300;
+            for (int k = first; k < first + cnt; k++) {
+                const double *m = inv + 6 * (size_t)k;
+                for (int c = 0; c < 2; c++) {
+                    const double y = c ? yb : ya;
+                    cmin = std::min(cmin, m[0] * (xa + 31) + m[1] * y + m[2] - 31.0);
+                    cmax = std::max(cmax, m[0] * xb + m[1] * y + m[2]);
+                    for (int d = 0; d < 2; d++) {
+                        const double sy = m[3] * (d ? xb : xa) + m[4] * y + m[5];
+                        rmin = std::min(rmin, sy);
+                        rmax = std::max(rmax, sy);
+                    }
+                }
+            }
+            const long long c0 = (long long)std::floor(cmin - 1.0), c1 = (long long)std::floor(cmax + 2.0);
+            const long long r0 = (long long)std::floor(rmin - 1.0), r1 = (long long)std::floor(rmax + 2.0);
+            const long long nW = (c1 >> 5) - (c0 >> 5) + 1, nR = r1 - r0 + kr;
+            if (nW > SWW_P || nR > SWW_TROWS) return false;
+        }
+    }
+    return true;
+}
 
 // ---------------------------------------------------------------------------
 struct SweepWArgs {
@@ -143,47 +177,30 @@ struct SweepWArgs {
     int wp, w, h, wj;
     SweepTables T;
     SweepWPlan P;
-    SweepItems I;
+    SweepWGroups G;
     int *counts;                // [slot][h + w]
-    int tiles_x;
+    int tiles_x, n_cards;
 };
 
 __device__ __forceinline__ uint32_t bsel(uint32_t m, uint32_t a, uint32_t b) { return (m & a) | (~m & b); }
 __device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (a & c) | (b & c); }
 
-// One output word.  NT = number of duplicated-column steps the word can contain (t range).
-template <int KR, int NT>
-__device__ __forceinline__ uint32_t assemble_word(const uint32_t *__restrict__ src, int sh, uint32_t C, uint32_t CA,
-                                                  const uint32_t (&Q)[SWW_KRMAX], uint32_t S1, uint32_t S2)
+// One output word.  NT2: the word may contain a two-column step (|angle| > 14.6 degrees).
+template <int KR, bool NT2>
+__device__ __forceinline__ uint32_t assemble_word(const uint32_t *__restrict__ src, int sh, uint32_t C, uint32_t D0,
+                                                  uint32_t D1, const uint32_t (&Q)[SWW_KRMAX - 1])
 {
     uint32_t out = 0;
-    uint32_t d0, d1;  // delta = t + CA as two bit planes
-    if (NT == 0) { d0 = CA; d1 = 0; }
-    else if (NT == 1) { d0 = S1 ^ CA; d1 = S1 & CA; }
-    else { d0 = S1 ^ S2 ^ CA; d1 = maj3(S1, S2, CA); }
 #pragma unroll
     for (int rho = 0; rho < KR; rho++) {
-        const uint32_t qa = rho < KR - 1 ? Q[rho] : 0u, qb = rho > 0 ? Q[rho - 1] : 0u;
-        const uint32_t R = (qa & ~C) | (qb & C);
-        const uint32_t *p = src + rho * SWW_P;
-        const uint32_t w0 = p[0], w1 = p[1];
-        uint32_t s;
-        if (NT == 0) {
-            const uint32_t f0 = __funnelshift_l(w1, w0, sh);
-            const uint32_t f1 = __funnelshift_lc(w1, w0, sh + 1);
-            s = bsel(d0, f1, f0);
-        } else {
-            const uint32_t w2 = p[2];
-            const uint32_t vh = __funnelshift_l(w1, w0, sh), vl = __funnelshift_l(w2, w1, sh);
-            const uint32_t f1 = __funnelshift_l(vl, vh, 1), f2 = __funnelshift_l(vl, vh, 2);
-            const uint32_t lo = bsel(d0, f1, vh);
-            if (NT == 1) {
-                s = bsel(d1, f2, lo);
-            } else {
-                const uint32_t f3 = __funnelshift_l(vl, vh, 3);
-                s = bsel(d1, bsel(d0, f3, f2), lo);
-            }
-        }
+        const uint32_t w0 = src[rho * SWW_P], w1 = src[rho * SWW_P + 1];
+        const uint32_t V = __funnelshift_l(w1, w0, sh);
+        uint32_t s = bsel(D0, V << 1, V);
+        if (NT2) s = bsel(D1, V << 2, s);
+        uint32_t R;
+        if (rho == 0) R = Q[0] & ~C;
+        else if (rho == KR - 1) R = Q[KR - 2] & C;
+        else R = (Q[rho] & ~C) | (Q[rho - 1] & C);
         out |= s & R;
     }
     return out;
@@ -193,129 +210,165 @@ template <int KR>
 __global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
 {
     extern __shared__ uint32_t smem[];
-    uint32_t *tile = smem;                                           // [SWW_TROWS][SWW_P]
-    int2 *sXY = reinterpret_cast<int2 *>(tile + SWW_TROWS * SWW_P);  // [SWW_TH]
-    uint8_t *sRow = reinterpret_cast<uint8_t *>(sXY + SWW_TH);       // [SWW_TJ][SWW_TH]
+    uint32_t *tile = smem;                                                  // [SWW_TROWS][SWW_P] + 1
+    uint8_t *sRow = reinterpret_cast<uint8_t *>(tile + SWW_TROWS * SWW_P + 1 + 3);  // [2][SWW_TJ][SWW_TH]
     __shared__ int sBox[4];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int card_local = blockIdx.y / A.I.n_list;
-    const int ang = A.I.alist[blockIdx.y - card_local * A.I.n_list];
-    const int slot = card_local * A.I.na_chunk + (ang - A.I.a0);
-    const int card = A.I.card0 + card_local;
+    const int grp = blockIdx.y / A.n_cards, card_local = blockIdx.y - grp * A.n_cards;
+    const int2 gd = A.G.groups[grp];
+    const int *alist = A.G.alist + gd.x;
+    const int n_ang = gd.y;
+    const int card = A.G.card0 + card_local;
     const int tx = blockIdx.x % A.tiles_x, ty = blockIdx.x / A.tiles_x;
     const int j0 = tx * SWW_TJ, x0 = j0 * 32, y0 = ty * SWW_TH;
-    const int tw = min(SWW_TJ * 32, A.w - x0), th = min(SWW_TH, A.h - y0);
-
-    const int *ad_g = A.T.ad + (size_t)ang * A.T.wpad;
-    const int *bd_g = A.T.bd + (size_t)ang * A.T.wpad;
-    const int2 *xy_g = A.T.xy + (size_t)ang * A.T.hpad;
+    const int nj = min(SWW_TJ, A.wj - j0), th = min(SWW_TH, A.h - y0);
     const uint32_t *bits = A.bits + (size_t)card * A.bits_card_words;
 
-    if (tid == 0) {
-        // source bounding box of the tile: the fixed-point coordinates are monotone in x and y
-        const int ax0 = ad_g[x0], ax1 = ad_g[x0 + tw - 1], bx0 = bd_g[x0], bx1 = bd_g[x0 + tw - 1];
-        const int2 p0 = xy_g[y0], p1 = xy_g[y0 + th - 1];
-        const int sxa = (p0.x + ax0) >> 10, sxb = (p0.x + ax1) >> 10, sxc = (p1.x + ax0) >> 10, sxd = (p1.x + ax1) >> 10;
-        const int sya = (p0.y + bx0) >> 10, syb = (p0.y + bx1) >> 10, syc = (p1.y + bx0) >> 10, syd = (p1.y + bx1) >> 10;
-        const int sxmin = min(min(sxa, sxb), min(sxc, sxd)), sxmax = max(max(sxa, sxb), max(sxc, sxd));
-        const int symin = min(min(sya, syb), min(syc, syd)), symax = max(max(sya, syb), max(syc, syd));
-        const int colw0 = (sxmin - 3) >> 5;                       // first staged word column
-        const int nW = (sxmax >> 5) + 2 - colw0 + 1;              // windows read 3 words
-        const int row0 = symin - 1;
-        const int nR = symax + SWW_KRMAX - row0 + 1;
-        sBox[0] = colw0;
-        sBox[1] = row0;
-        sBox[2] = nR;
-        sBox[3] = (nW > SWW_P || nR > SWW_TROWS) ? 1 : 0;
+    if (warp == 0) {
+        // Source bounding box of the tile over the angles of the group: the fixed-point
+        // coordinates are monotone in x and in y, so the extremes sit at the tile corners.
+        // lane -> (angle = lane >> 2, corner = lane & 3)
+        int cmin = 0x7fffffff, cmax = -0x7fffffff, rmin = 0x7fffffff, rmax = -0x7fffffff;
+        if ((lane >> 2) < n_ang) {
+            const int ang = alist[lane >> 2];
+            const int *ad_g = A.T.ad + (size_t)ang * A.T.wpad, *bd_g = A.T.bd + (size_t)ang * A.T.wpad;
+            const int2 p = A.T.xy[(size_t)ang * A.T.hpad + ((lane & 1) ? y0 + th - 1 : y0)];
+            const int xb = x0 + 32 * nj - 1;
+            if (lane & 2) {
+                cmax = (p.x + ad_g[xb]) >> 10;
+                rmin = rmax = (p.y + bd_g[xb]) >> 10;
+            } else {
+                cmin = ((p.x + ad_g[x0 + 31]) >> 10) - 31;
+                rmin = rmax = (p.y + bd_g[x0]) >> 10;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            cmin = min(cmin, __shfl_xor_sync(0xffffffffu, cmin, o));
+            cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+            rmin = min(rmin, __shfl_xor_sync(0xffffffffu, rmin, o));
+            rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+        }
+        if (lane == 0) {
+            const int colw0 = cmin >> 5;
+            const int nW = (cmax >> 5) - colw0 + 1;
+            const int nR = rmax - rmin + KR;
+            sBox[0] = colw0;
+            sBox[1] = rmin;
+            sBox[2] = nW;
+            sBox[3] = (nW > SWW_P || nR > SWW_TROWS) ? -1 : nR;
+        }
     }
-    for (int i = tid; i < SWW_TJ * SWW_TH; i += 256) sRow[i] = 0;
     __syncthreads();
-    const int colw0 = sBox[0], row0 = sBox[1], nR = sBox[2];
-    if (sBox[3]) {  // cannot happen for angles accepted by sweepw_class; never sample out of bounds
+    const int colw0 = sBox[0], row0 = sBox[1], nW = sBox[2], nR = sBox[3];
+    if (nR < 0) {  // cannot happen for groups accepted by sweepw_group_fits; never sample out of bounds
         if (tid == 0) atomicExch(A.P.err, 2);
         return;
     }
-    // stage the footprint, zero outside the image (white border = no black pixel)
-    for (int i = tid; i < nR * SWW_P; i += 256) {
-        const int r = i / SWW_P, c = i - r * SWW_P;
-        const int gr = row0 + r, gc = colw0 + c;
-        uint32_t v = 0;
-        if (gr >= 0 && gr < A.h && gc >= 0 && gc < A.wp) v = __ldg(bits + (size_t)gr * A.wp + gc);
-        tile[i] = v;
-    }
-    for (int i = tid; i < th; i += 256) {
-        const int2 p = xy_g[y0 + i];
-        sXY[i] = make_int2((p.x >> 10) - colw0 * 32, (p.y >> 10) - row0);
+    // stage the footprint, zero outside the image (white border = no black pixel):
+    // half a warp per source row, lane = word column
+    {
+        const int c = lane & 15, gc = colw0 + c;
+        const bool cin = gc >= 0 && gc < A.wp;
+        const uint32_t *colp = bits + gc;
+        if (nW <= 16) {
+            for (int r = warp * 2 + (lane >> 4); r < nR; r += 16) {
+                const int gr = row0 + r;
+                uint32_t v = 0;
+                if (cin && gr >= 0 && gr < A.h) v = __ldg(colp + (size_t)gr * A.wp);
+                if (c < nW) tile[r * SWW_P + c] = v;
+            }
+        } else {
+            for (int i = tid; i < nR * SWW_P; i += 256) {
+                const int r = i / SWW_P, cc = i - r * SWW_P;
+                const int gr = row0 + r, g2 = colw0 + cc;
+                uint32_t v = 0;
+                if (gr >= 0 && gr < A.h && g2 >= 0 && g2 < A.wp) v = __ldg(bits + (size_t)gr * A.wp + g2);
+                tile[i] = v;
+            }
+        }
     }
     __syncthreads();
 
     const int j = j0 + warp;
-    int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
-    int *cols_out = rows_out + A.h;
-    if (j < A.wj) {
-        const int kslot = A.P.kf[ang] - A.P.kf0;
-        const uint32_t *m = A.P.meta + ((size_t)kslot * A.wj + j) * SWW_META;
-        uint32_t Q[SWW_KRMAX];
+    const bool active = warp < nj;
+    const int xoff = (colw0 * 32) << 10, yoff = row0 << 10;
+    for (int ai = 0; ai < n_ang; ai++) {
+        const int ang = alist[ai];
+        const int slot = card_local * A.G.na_chunk + (ang - A.G.a0);
+        int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
+        int *cols_out = rows_out + A.h;
+        uint8_t *rowbuf = sRow + (ai & 1) * (SWW_TJ * SWW_TH);
+        uint8_t *myRow = rowbuf + warp * SWW_TH;
+        if (active) {
+            const uint32_t *m = A.P.meta + ((size_t)ang * A.wj + j) * SWW_META;
+            uint32_t Q[SWW_KRMAX - 1];
 #pragma unroll
-        for (int r = 0; r < SWW_KRMAX; r++) Q[r] = r < KR - 1 ? __ldg(m + r) : 0u;
-        const uint32_t S1 = __ldg(m + 11), S2 = __ldg(m + 12);
-        const int bj = (int)__ldg(m + 13), cj = (int)__ldg(m + 14);
-        const uint32_t *pc = A.P.pc + ((size_t)kslot * A.wj + j) * A.h + y0;
-        const uint32_t *pca = A.P.pca + ((size_t)kslot * A.wj + j) * A.h + y0;
-        uint8_t *myRow = sRow + warp * SWW_TH;
-        uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;  // bit-sliced column counters (<= 16 rows per lane)
-        const int ngroups = (th + 31) >> 5;
-        for (int g4 = 0; g4 < ngroups; g4 += 4) {
-            uint32_t o[4];
+            for (int r = 0; r < SWW_KRMAX - 1; r++) Q[r] = r < KR - 1 ? __ldg(m + r) : 0u;
+            const uint32_t S1 = __ldg(m + 11);
+            const int arefp = (int)__ldg(m + 13) - xoff, brefp = (int)__ldg(m + 14) - yoff;
+            const int kslot = A.P.kf[ang] - A.P.kf0;
+            const uint2 *pl = A.P.planes + ((size_t)kslot * A.wj + j) * A.h + y0;
+            const int2 *xy = A.T.xy + (size_t)ang * A.T.hpad + y0;
+            uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;  // bit-sliced column counters (<= 16 rows per lane)
+            const int ngroups = (th + 31) >> 5;
+            for (int g4 = 0; g4 < ngroups; g4 += 4) {
+                uint32_t o[4];
+                const bool full = (g4 + 4) * 32 <= th;
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int r = (g4 + u) * 32 + lane;
-                const bool valid = r < th;
-                const int rr = valid ? r : th - 1;
-                const int2 p = sXY[rr];
-                const uint32_t C = __ldg(pc + rr), CA = __ldg(pca + rr);
-                const int sc = p.x + cj;
-                const uint32_t *src = tile + (p.y + bj) * SWW_P + (sc >> 5);
-                const int sh = sc & 31;
-                uint32_t v;
-                if (S1 == 0) v = assemble_word<KR, 0>(src, sh, C, CA, Q, S1, S2);
-                else if (S2 == 0) v = assemble_word<KR, 1>(src, sh, C, CA, Q, S1, S2);
-                else v = assemble_word<KR, 2>(src, sh, C, CA, Q, S1, S2);
-                v = valid ? v : 0u;
-                if (valid) myRow[r] = (uint8_t)__popc(v);
-                o[u] = v;
+                for (int u = 0; u < 4; u++) {
+                    const int r = (g4 + u) * 32 + lane;
+                    const bool valid = full || r < th;
+                    const int rr = valid ? r : th - 1;
+                    const int2 p = __ldg(xy + rr);
+                    const uint2 cd = __ldg(pl + rr);
+                    const int xq = p.x + arefp, yq = p.y + brefp;
+                    const int cb = xq >> 10;
+                    const uint32_t *src = tile + (yq >> 10) * SWW_P + (cb >> 5);
+                    const int sh = cb & 31;
+                    uint32_t v;
+                    if (S1 == 0) v = assemble_word<KR, false>(src, sh, cd.x, cd.y, 0u, Q);
+                    else v = assemble_word<KR, true>(src, sh, cd.x, cd.y, S1 & ~cd.y, Q);
+                    v = valid ? v : 0u;
+                    if (valid) myRow[r] = (uint8_t)__popc(v);
+                    o[u] = v;
+                }
+                // carry-save accumulation of four words into the vertical counters
+                const uint32_t k0 = maj3(o[0], o[1], c0);
+                c0 ^= o[0] ^ o[1];
+                const uint32_t k1 = maj3(o[2], o[3], c0);
+                c0 ^= o[2] ^ o[3];
+                const uint32_t k2 = maj3(k0, k1, c1);
+                c1 ^= k0 ^ k1;
+                uint32_t t = c2 & k2;
+                c2 ^= k2;
+                uint32_t t2 = c3 & t;
+                c3 ^= t;
+                c4 ^= t2;
             }
-            // carry-save accumulation of four words into the vertical counters
-            const uint32_t k0 = maj3(o[0], o[1], c0);
-            c0 ^= o[0] ^ o[1];
-            const uint32_t k1 = maj3(o[2], o[3], c0);
-            c0 ^= o[2] ^ o[3];
-            const uint32_t k2 = maj3(k0, k1, c1);
-            c1 ^= k0 ^ k1;
-            uint32_t t = c2 & k2;
-            c2 ^= k2;
-            uint32_t t2 = c3 & t;
-            c3 ^= t;
-            c4 ^= t2;
+            // unpack: lane L receives bit L of every lane's plane = pixel 31 - L of the word
+            if (__any_sync(0xffffffffu, (c0 | c1 | c2 | c3 | c4) != 0)) {
+                int cnt = __popc(warp_bit_transpose(c0, lane)) + 2 * __popc(warp_bit_transpose(c1, lane));
+                if (__any_sync(0xffffffffu, (c2 | c3 | c4) != 0)) {
+                    cnt += 4 * __popc(warp_bit_transpose(c2, lane));
+                    if (__any_sync(0xffffffffu, (c3 | c4) != 0))
+                        cnt += 8 * __popc(warp_bit_transpose(c3, lane)) + 16 * __popc(warp_bit_transpose(c4, lane));
+                }
+                const int x = j * 32 + 31 - lane;
+                if (cnt && x < A.w) atomicAdd(cols_out + x, cnt);
+            }
         }
-        // unpack: lane L receives bit L of every lane's plane = pixel 31 - L of the word
-        int cnt = __popc(warp_bit_transpose(c0, lane)) + 2 * __popc(warp_bit_transpose(c1, lane)) +
-                  4 * __popc(warp_bit_transpose(c2, lane)) + 8 * __popc(warp_bit_transpose(c3, lane)) +
-                  16 * __popc(warp_bit_transpose(c4, lane));
-        const int x = j * 32 + 31 - lane;
-        if (cnt && x < A.w) atomicAdd(cols_out + x, cnt);
-    }
-    __syncthreads();
-    for (int i = tid; i < th; i += 256) {
-        int s = 0;
-#pragma unroll
-        for (int k = 0; k < SWW_TJ; k++) s += sRow[k * SWW_TH + i];
-        if (s) atomicAdd(rows_out + y0 + i, s);
+        __syncthreads();
+        for (int i = tid; i < th; i += 256) {
+            int s = 0;
+            for (int k = 0; k < nj; k++) s += rowbuf[k * SWW_TH + i];
+            if (s) atomicAdd(rows_out + y0 + i, s);
+        }
     }
 }
 
-static constexpr size_t SWW_SMEM = (size_t)SWW_TROWS * SWW_P * 4 + (size_t)SWW_TH * 8 + (size_t)SWW_TJ * SWW_TH;
+static constexpr size_t SWW_SMEM = ((size_t)SWW_TROWS * SWW_P + 4) * 4 + 2 * (size_t)SWW_TJ * SWW_TH;
 
 template <int KR>
 static cudaError_t launch_w(const SweepWArgs &A, dim3 grid, cudaStream_t st)
@@ -331,19 +384,32 @@ static cudaError_t launch_w(const SweepWArgs &A, dim3 grid, cudaStream_t st)
 }
 
 int32_t sweepw_launch(oics_ctx *ctx, int kr, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
-                      const SweepTables &T, const SweepWPlan &P, const SweepItems &I, int n_cards, int *counts)
+                      const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts)
 {
-    if (I.n_list <= 0 || n_cards <= 0) return OICS_OK;
+    if (G.n_groups <= 0 || n_cards <= 0) return OICS_OK;
     SweepWArgs A;
     A.bits = bits;
     A.bits_card_words = bits_card_words;
     A.wp = wp; A.w = w; A.h = h; A.wj = cdiv(w, 32);
-    A.T = T; A.P = P; A.I = I;
+    A.T = T; A.P = P; A.G = G;
     A.counts = counts;
     A.tiles_x = cdiv(A.wj, SWW_TJ);
-    dim3 grid(A.tiles_x * cdiv(h, SWW_TH), (unsigned)(n_cards * I.n_list));
-    cudaError_t e = kr == 3 ? launch_w<3>(A, grid, ctx->stream) : kr == 5 ? launch_w<5>(A, grid, ctx->stream)
-                    : kr == 8 ? launch_w<8>(A, grid, ctx->stream) : launch_w<11>(A, grid, ctx->stream);
+    A.n_cards = n_cards;
+    dim3 grid(A.tiles_x * cdiv(h, SWW_TH), (unsigned)(n_cards * G.n_groups));
+    cudaError_t e;
+    switch (kr) {
+    case 2: e = launch_w<2>(A, grid, ctx->stream); break;
+    case 3: e = launch_w<3>(A, grid, ctx->stream); break;
+    case 4: e = launch_w<4>(A, grid, ctx->stream); break;
+    case 5: e = launch_w<5>(A, grid, ctx->stream); break;
+    case 6: e = launch_w<6>(A, grid, ctx->stream); break;
+    case 7: e = launch_w<7>(A, grid, ctx->stream); break;
+    case 8: e = launch_w<8>(A, grid, ctx->stream); break;
+    case 9: e = launch_w<9>(A, grid, ctx->stream); break;
+    case 10: e = launch_w<10>(A, grid, ctx->stream); break;
+    case 11: e = launch_w<11>(A, grid, ctx->stream); break;
+    default: set_error("internal: unsupported word-kernel class %d", kr); return OICS_ERR_INVALID_ARG;
+    }
     OICS_CUDA_TRY(e);
     ctx->launches++;
     return OICS_OK;
