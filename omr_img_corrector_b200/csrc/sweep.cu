@@ -547,7 +547,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * h * wp * sizeof(uint32_t)));
     if (n_fast) {
         const int max_plan = std::min<long long>(n_fast, angles_per_chunk);
-        OICS_TRY(ctx->wplanes.ensure((size_t)max_plan * plan_per_angle));
+        OICS_TRY(ctx->wplanes.ensure((size_t)max_plan * plan_per_angle + SWW_PLANES_PAD));
     }
 
     SweepArgs A;

@@ -43,9 +43,11 @@ static constexpr int SWW_KRMAX = 11;   // source rows one output word may draw f
 static constexpr int SWW_TH = 512;     // output rows per CTA
 static constexpr int SWW_TJ = 8;       // output word columns per CTA (one per warp)
 static constexpr int SWW_P = 17;       // staged-tile pitch in words (odd: rows spread over banks)
-static constexpr int SWW_TROWS = 608;  // staged-tile rows
+static constexpr int SWW_TROWS = 596;  // staged-tile rows (4 CTAs of 55.6 KB per SM)
 static constexpr int SWW_META = 16;    // uint32 per (angle, word column): Q[10], -, S1, -, Aref, Bref, -
 static constexpr int SWW_GMAX = 8;     // candidate angles one CTA evaluates on one staged tile
+// the word kernel prefetches the planes one round (128 rows) past the last row of a column
+static constexpr size_t SWW_PLANES_PAD = 256 * sizeof(uint2);
 
 // Per-angle verdict of the meta kernel: can the word kernel take this angle, and with how
 // many source rows per output word.

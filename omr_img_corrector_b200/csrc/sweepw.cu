@@ -206,12 +206,87 @@ __device__ __forceinline__ uint32_t assemble_word(const uint32_t *__restrict__ s
     return out;
 }
 
+// 5 bit-sliced planes -> per-column counts.  The five 32x32 bit transposes run in lock step
+// so the lane-dependent shift and mask of a butterfly stage are computed once.
+__device__ __forceinline__ int unpack_columns(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t c4, int np,
+                                              int lane)
+{
+    uint32_t c[5] = {c0, c1, c2, c3, c4};
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        const uint32_t low = j == 16 ? 0x0000FFFFu : j == 8 ? 0x00FF00FFu : j == 4 ? 0x0F0F0F0Fu
+                             : j == 2 ? 0x33333333u : 0x55555555u;
+        const bool up = (lane & j) != 0;
+        const uint32_t keep = up ? ~low : low;   // bits of v that stay
+        const int rot = up ? 32 - j : j;         // partner bits move down (up) by j
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+            if (k < np) {
+                const uint32_t o = __shfl_xor_sync(0xffffffffu, c[k], j);
+                c[k] = (c[k] & keep) | (__funnelshift_l(o, o, rot) & ~keep);
+            }
+        }
+    }
+    int cnt = 0;
+#pragma unroll
+    for (int k = 0; k < 5; k++)
+        if (k < np) cnt += __popc(c[k]) << k;
+    return cnt;
+}
+
+// Four 32-row groups of one word column: lane = row.  `sxy`, `rowp`, `plp` already point at
+// this lane's first row; cd[] holds the planes of these four words (prefetched one round
+// ahead) and is refilled for the next round.
+template <int KR, bool CHECK>
+__device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, const int2 *__restrict__ sxy,
+                                           uint8_t *__restrict__ rowp, const uint2 *__restrict__ plp, uint2 (&cd)[4],
+                                           int arefp, int brefp, uint32_t S1, const uint32_t (&Q)[SWW_KRMAX - 1],
+                                           int rows_left, uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3,
+                                           uint32_t &c4)
+{
+    uint32_t o[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int2 p = sxy[32 * u];
+        const uint2 m = cd[u];
+        cd[u] = __ldg(plp + 128 + 32 * u);   // next round (the planes buffer is padded)
+        const int xq = p.x + arefp, yq = p.y + brefp;
+        const int cb = xq >> 10;
+        const uint32_t *src = tile + (yq >> 10) * SWW_P + (cb >> 5);
+        const int sh = cb & 31;
+        uint32_t v;
+        if (S1 == 0) v = assemble_word<KR, false>(src, sh, m.x, m.y, 0u, Q);
+        else v = assemble_word<KR, true>(src, sh, m.x, m.y, S1 & ~m.y, Q);
+        if (CHECK) {
+            const bool valid = 32 * u < rows_left;   // rows_left is relative to this lane
+            v = valid ? v : 0u;
+            if (valid) rowp[32 * u] = (uint8_t)__popc(v);
+        } else {
+            rowp[32 * u] = (uint8_t)__popc(v);
+        }
+        o[u] = v;
+    }
+    // carry-save accumulation of four words into the vertical counters
+    const uint32_t k0 = maj3(o[0], o[1], c0);
+    c0 ^= o[0] ^ o[1];
+    const uint32_t k1 = maj3(o[2], o[3], c0);
+    c0 ^= o[2] ^ o[3];
+    const uint32_t k2 = maj3(k0, k1, c1);
+    c1 ^= k0 ^ k1;
+    const uint32_t t = c2 & k2;
+    c2 ^= k2;
+    const uint32_t t2 = c3 & t;
+    c3 ^= t;
+    c4 ^= t2;
+}
+
 template <int KR>
 __global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
 {
     extern __shared__ uint32_t smem[];
-    uint32_t *tile = smem;                                                  // [SWW_TROWS][SWW_P] + 1
-    uint8_t *sRow = reinterpret_cast<uint8_t *>(tile + SWW_TROWS * SWW_P + 1 + 3);  // [2][SWW_TJ][SWW_TH]
+    uint32_t *tile = smem;                                                           // [SWW_TROWS][SWW_P] + pad
+    int2 *sXY = reinterpret_cast<int2 *>(tile + SWW_TROWS * SWW_P + 4);              // [2][SWW_TH]
+    uint8_t *sRow = reinterpret_cast<uint8_t *>(sXY + 2 * SWW_TH);                   // [2][SWW_TJ][SWW_TH]
     __shared__ int sBox[4];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -289,72 +364,63 @@ __global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
             }
         }
     }
+    // per-row {X0, Y0} of the first angle, re-based to the staged window; rows past the
+    // tile repeat its last row so every lane computes in-bounds addresses
+    const int xoff = (colw0 * 32) << 10, yoff = row0 << 10;
+    {
+        const int2 *xy = A.T.xy + (size_t)alist[0] * A.T.hpad + y0;
+        for (int i = tid; i < SWW_TH; i += 256) {
+            const int2 p = __ldg(xy + min(i, th - 1));
+            sXY[i] = make_int2(p.x - xoff, p.y - yoff);
+        }
+    }
     __syncthreads();
 
     const int j = j0 + warp;
     const bool active = warp < nj;
-    const int xoff = (colw0 * 32) << 10, yoff = row0 << 10;
     for (int ai = 0; ai < n_ang; ai++) {
         const int ang = alist[ai];
         const int slot = card_local * A.G.na_chunk + (ang - A.G.a0);
         int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
         int *cols_out = rows_out + A.h;
         uint8_t *rowbuf = sRow + (ai & 1) * (SWW_TJ * SWW_TH);
-        uint8_t *myRow = rowbuf + warp * SWW_TH;
+        if (ai + 1 < n_ang) {  // next angle's rows (read after the barrier below)
+            const int2 *xy = A.T.xy + (size_t)alist[ai + 1] * A.T.hpad + y0;
+            int2 *dst = sXY + ((ai + 1) & 1) * SWW_TH;
+            for (int i = tid; i < SWW_TH; i += 256) {
+                const int2 p = __ldg(xy + min(i, th - 1));
+                dst[i] = make_int2(p.x - xoff, p.y - yoff);
+            }
+        }
         if (active) {
             const uint32_t *m = A.P.meta + ((size_t)ang * A.wj + j) * SWW_META;
             uint32_t Q[SWW_KRMAX - 1];
 #pragma unroll
             for (int r = 0; r < SWW_KRMAX - 1; r++) Q[r] = r < KR - 1 ? __ldg(m + r) : 0u;
             const uint32_t S1 = __ldg(m + 11);
-            const int arefp = (int)__ldg(m + 13) - xoff, brefp = (int)__ldg(m + 14) - yoff;
+            const int arefp = (int)__ldg(m + 13), brefp = (int)__ldg(m + 14);
             const int kslot = A.P.kf[ang] - A.P.kf0;
-            const uint2 *pl = A.P.planes + ((size_t)kslot * A.wj + j) * A.h + y0;
-            const int2 *xy = A.T.xy + (size_t)ang * A.T.hpad + y0;
+            const uint2 *plp = A.P.planes + ((size_t)kslot * A.wj + j) * A.h + y0 + lane;
+            const int2 *sxy = sXY + (ai & 1) * SWW_TH + lane;
+            uint8_t *rowp = rowbuf + warp * SWW_TH + lane;
             uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;  // bit-sliced column counters (<= 16 rows per lane)
-            const int ngroups = (th + 31) >> 5;
-            for (int g4 = 0; g4 < ngroups; g4 += 4) {
-                uint32_t o[4];
-                const bool full = (g4 + 4) * 32 <= th;
+            uint2 cd[4];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const int r = (g4 + u) * 32 + lane;
-                    const bool valid = full || r < th;
-                    const int rr = valid ? r : th - 1;
-                    const int2 p = __ldg(xy + rr);
-                    const uint2 cd = __ldg(pl + rr);
-                    const int xq = p.x + arefp, yq = p.y + brefp;
-                    const int cb = xq >> 10;
-                    const uint32_t *src = tile + (yq >> 10) * SWW_P + (cb >> 5);
-                    const int sh = cb & 31;
-                    uint32_t v;
-                    if (S1 == 0) v = assemble_word<KR, false>(src, sh, cd.x, cd.y, 0u, Q);
-                    else v = assemble_word<KR, true>(src, sh, cd.x, cd.y, S1 & ~cd.y, Q);
-                    v = valid ? v : 0u;
-                    if (valid) myRow[r] = (uint8_t)__popc(v);
-                    o[u] = v;
-                }
-                // carry-save accumulation of four words into the vertical counters
-                const uint32_t k0 = maj3(o[0], o[1], c0);
-                c0 ^= o[0] ^ o[1];
-                const uint32_t k1 = maj3(o[2], o[3], c0);
-                c0 ^= o[2] ^ o[3];
-                const uint32_t k2 = maj3(k0, k1, c1);
-                c1 ^= k0 ^ k1;
-                uint32_t t = c2 & k2;
-                c2 ^= k2;
-                uint32_t t2 = c3 & t;
-                c3 ^= t;
-                c4 ^= t2;
+            for (int u = 0; u < 4; u++) cd[u] = __ldg(plp + 32 * u);
+            int done = 0;
+            for (; done + 128 <= th; done += 128) {  // four full 32-row groups
+                four_words<KR, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 0, c0, c1, c2, c3, c4);
+                sxy += 128; rowp += 128; plp += 128;
             }
+            if (done < th)   // the tile's last, partial round: row 32 u + lane is valid iff < th - done
+                four_words<KR, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done - lane, c0, c1, c2, c3, c4);
             // unpack: lane L receives bit L of every lane's plane = pixel 31 - L of the word
-            if (__any_sync(0xffffffffu, (c0 | c1 | c2 | c3 | c4) != 0)) {
-                int cnt = __popc(warp_bit_transpose(c0, lane)) + 2 * __popc(warp_bit_transpose(c1, lane));
-                if (__any_sync(0xffffffffu, (c2 | c3 | c4) != 0)) {
-                    cnt += 4 * __popc(warp_bit_transpose(c2, lane));
-                    if (__any_sync(0xffffffffu, (c3 | c4) != 0))
-                        cnt += 8 * __popc(warp_bit_transpose(c3, lane)) + 16 * __popc(warp_bit_transpose(c4, lane));
-                }
+            const uint32_t hi = c2 | c3 | c4;
+            if (__any_sync(0xffffffffu, (c0 | c1 | hi) != 0)) {
+                int cnt;
+                if (!__any_sync(0xffffffffu, hi != 0)) cnt = unpack_columns(c0, c1, 0, 0, 0, 2, lane);
+                else if (!__any_sync(0xffffffffu, (c3 | c4) != 0)) cnt = unpack_columns(c0, c1, c2, 0, 0, 3, lane);
+                else cnt = unpack_columns(c0, c1, c2, c3, c4, 5, lane);
                 const int x = j * 32 + 31 - lane;
                 if (cnt && x < A.w) atomicAdd(cols_out + x, cnt);
             }
@@ -368,7 +434,7 @@ __global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
     }
 }
 
-static constexpr size_t SWW_SMEM = ((size_t)SWW_TROWS * SWW_P + 4) * 4 + 2 * (size_t)SWW_TJ * SWW_TH;
+static constexpr size_t SWW_SMEM = ((size_t)SWW_TROWS * SWW_P + 4) * 4 + 2 * (size_t)SWW_TH * 8 + 2 * (size_t)SWW_TJ * SWW_TH;
 
 template <int KR>
 static cudaError_t launch_w(const SweepWArgs &A, dim3 grid, cudaStream_t st)
