@@ -74,14 +74,12 @@ struct SweepCache {
     // classification (meta kernel verdicts) and the launch lists derived from it
     std::vector<int> general;       // angles the general kernel takes
     std::vector<int> fast;          // angles the word kernel takes, ascending
-    struct WordClass {
-        int kr = 0;                 // source rows per output word
-        std::vector<int> angles;    // ascending
-        std::vector<int> gfirst;    // first angle of each group
-        std::vector<int> gstart, gcount;  // group -> index range in `angles`
-        size_t alist_off = 0, groups_off = 0;  // offsets (ints) in ctx->wlists
-    };
-    std::vector<WordClass> classes;
+    // groups of consecutive fast angles sharing a staged tile, sorted by (chunk, class
+    // descending, first angle): {index into `fast`, count, class, first angle}
+    struct Group { int start, count, kr, first; };
+    std::vector<Group> groups;
+    std::vector<int> chunk_group_begin;  // per angle chunk: first group (size n_chunks + 1)
+    size_t groups_off = 0;               // offset (ints) in ctx->wlists
     size_t general_off = 0, kf_off = 0, fast_off = 0;
 };
 

@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
 // per vector: lanes stage a chunk, lane 0 runs the dependent f64 chain.
 static constexpr int FIN_CHUNK = 1024;
 
-__device__ double seq_std_dev(const int *__restrict__ v, int n, int *stage, int lane, long long *sum_out,
+__device__ double seq_std_dev(const int *__restrict__ v, int n, double *stage, int lane, long long *sum_out,
                               long long *sq_out)
 {
     long long s = 0, q = 0;
@@ -300,19 +300,23 @@ __device__ double seq_std_dev(const int *__restrict__ v, int n, int *stage, int 
     double acc = 0.0;
     for (int base = 0; base < n; base += FIN_CHUNK) {
         const int m = min(FIN_CHUNK, n - base);
-        for (int i = lane; i < m; i += 32) stage[i] = v[base + i];
+        // every lane squares its share (each square rounded once, like powf(2.0)) ...
+        for (int i = lane; i < m; i += 32) {
+            const double d = __dsub_rn((double)v[base + i], mean);
+            stage[i] = __dmul_rn(d, d);
+        }
         __syncwarp();
+        // ... lane 0 runs the strictly sequential sum: one dependent DADD per element
         if (lane == 0) {
             int i = 0;
-            if (base == 0) {
-                double d = __dsub_rn((double)stage[0], mean);
-                acc = __dmul_rn(d, d);
-                i = 1;
+            if (base == 0) { acc = stage[0]; i = 1; }
+            for (; i + 8 <= m; i += 8) {
+                const double t0 = stage[i], t1 = stage[i + 1], t2 = stage[i + 2], t3 = stage[i + 3];
+                const double t4 = stage[i + 4], t5 = stage[i + 5], t6 = stage[i + 6], t7 = stage[i + 7];
+                acc = __dadd_rn(acc, t0); acc = __dadd_rn(acc, t1); acc = __dadd_rn(acc, t2); acc = __dadd_rn(acc, t3);
+                acc = __dadd_rn(acc, t4); acc = __dadd_rn(acc, t5); acc = __dadd_rn(acc, t6); acc = __dadd_rn(acc, t7);
             }
-            for (; i < m; i++) {
-                double d = __dsub_rn((double)stage[i], mean);
-                acc = __dadd_rn(acc, __dmul_rn(d, d));
-            }
+            for (; i < m; i++) acc = __dadd_rn(acc, stage[i]);
         }
         __syncwarp();
     }
@@ -323,7 +327,7 @@ __global__ void __launch_bounds__(64) sweep_finalize_kernel(const int *__restric
                                                             long long item0, double *__restrict__ v_sd,
                                                             double *__restrict__ h_sd, long long *__restrict__ sums)
 {
-    __shared__ int stage[2][FIN_CHUNK];
+    __shared__ double stage[2][FIN_CHUNK];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int *base = counts + (size_t)blockIdx.x * (h + w);
     const size_t item = (size_t)item0 + blockIdx.x;
@@ -411,9 +415,9 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const bool same_geometry = cache.w == w && cache.h == h && cache.inv == inv && ctx->tabs.p &&
                                ctx->tabs.cap >= tab_ints * sizeof(int) && ctx->wlists.p;
 
-    // ---- chunking: counts buffer (64 MB) and word-kernel planes (3 GB) bound a chunk
+    // ---- chunking: counts buffer (256 MB) and word-kernel planes (3 GB) bound a chunk
     const size_t per_item = (size_t)(h + w) * sizeof(int);
-    long long chunk_items = (long long)((size_t)64 << 20) / (long long)per_item;
+    long long chunk_items = (long long)((size_t)256 << 20) / (long long)per_item;
     if (chunk_items < 1) chunk_items = 1;
     const size_t plan_per_angle = (size_t)wj * h * sizeof(uint2);
     const long long plan_budget_angles = std::max<long long>(1, (long long)(((size_t)3 << 30) / plan_per_angle));
@@ -465,36 +469,45 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         const int gmax = genv ? std::max(1, std::min(SWW_GMAX, atoi(genv))) : SWW_GMAX;
         cache.general.clear();
         cache.fast.clear();
-        cache.classes.assign(SWW_KRMAX + 1, SweepCache::WordClass());
+        cache.groups.clear();
+        std::vector<int> kr_of;  // class of fast[k]
         for (int i = 0; i < n_angles; i++) {
             int kr = 0;
             if (allow_word && !cls[i].bad && cls[i].rows >= 2 && cls[i].rows <= SWW_KRMAX &&
                 sweepw_group_fits(inv.data(), i, 1, cls[i].rows, w, h))
                 kr = cls[i].rows;
             if (!kr) { cache.general.push_back(i); continue; }
-            cache.fast.push_back(i);
-            SweepCache::WordClass &C = cache.classes[kr];
-            C.kr = kr;
-            // extend the last group: consecutive angle, same chunk, footprints share a tile
+            // extend the last group: consecutive angle, same class, same chunk, footprints share a tile
             bool extend = false;
-            if (!C.gstart.empty()) {
-                const int gs = C.gstart.back(), gc = C.gcount.back();
-                extend = gc < gmax && C.angles.back() == i - 1 && C.angles[gs] / angles_per_chunk == i / angles_per_chunk &&
-                         sweepw_group_fits(inv.data(), C.angles[gs], gc + 1, kr, w, h);
+            if (!cache.groups.empty()) {
+                const SweepCache::Group &g = cache.groups.back();
+                extend = g.count < gmax && g.kr == kr && g.first + g.count == i &&
+                         g.first / angles_per_chunk == i / angles_per_chunk &&
+                         sweepw_group_fits(inv.data(), g.first, g.count + 1, kr, w, h);
             }
-            if (extend) C.gcount.back()++;
-            else { C.gstart.push_back((int)C.angles.size()); C.gcount.push_back(1); C.gfirst.push_back(i); }
-            C.angles.push_back(i);
+            if (extend) cache.groups.back().count++;
+            else cache.groups.push_back({(int)cache.fast.size(), 1, kr, i});
+            cache.fast.push_back(i);
         }
-        // device copy: [err 4][kf n][fast][general][class lists][groups as int2]
+        // heaviest classes first inside a chunk: the tail of the launch is filled by the light ones
+        std::stable_sort(cache.groups.begin(), cache.groups.end(), [&](const SweepCache::Group &a, const SweepCache::Group &b) {
+            const int ca = a.first / angles_per_chunk, cb = b.first / angles_per_chunk;
+            if (ca != cb) return ca < cb;
+            return a.kr > b.kr;
+        });
+        const int n_chunks = cdiv(n_angles, angles_per_chunk);
+        cache.chunk_group_begin.assign((size_t)n_chunks + 1, (int)cache.groups.size());
+        for (int g = (int)cache.groups.size() - 1; g >= 0; g--) cache.chunk_group_begin[cache.groups[g].first / angles_per_chunk] = g;
+        for (int c = n_chunks - 1; c >= 0; c--)
+            cache.chunk_group_begin[c] = std::min(cache.chunk_group_begin[c], cache.chunk_group_begin[c + 1]);
+        // device copy: [err 4][kf n][fast][general][groups as int4]
         const int n_fast0 = (int)cache.fast.size();
         size_t off = 4;
         cache.kf_off = off; off += (size_t)n_angles;
         cache.fast_off = off; off += (size_t)n_fast0;
         cache.general_off = off; off += cache.general.size();
-        for (auto &C : cache.classes) { C.alist_off = off; off += C.angles.size(); }
-        off = (off + 1) & ~(size_t)1;  // int2 alignment
-        for (auto &C : cache.classes) { C.groups_off = off; off += 2 * C.gstart.size(); }
+        off = (off + 3) & ~(size_t)3;  // int4 alignment
+        cache.groups_off = off; off += 4 * cache.groups.size();
         std::vector<int> hostbuf(off, 0);
         for (int i = 0; i < n_angles; i++) hostbuf[cache.kf_off + i] = -1;
         for (int k = 0; k < n_fast0; k++) {
@@ -502,12 +515,11 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
             hostbuf[cache.fast_off + k] = cache.fast[k];
         }
         std::copy(cache.general.begin(), cache.general.end(), hostbuf.begin() + cache.general_off);
-        for (auto &C : cache.classes) {
-            std::copy(C.angles.begin(), C.angles.end(), hostbuf.begin() + C.alist_off);
-            for (size_t g = 0; g < C.gstart.size(); g++) {
-                hostbuf[C.groups_off + 2 * g] = C.gstart[g];
-                hostbuf[C.groups_off + 2 * g + 1] = C.gcount[g];
-            }
+        for (size_t g = 0; g < cache.groups.size(); g++) {
+            hostbuf[cache.groups_off + 4 * g + 0] = cache.groups[g].start;
+            hostbuf[cache.groups_off + 4 * g + 1] = cache.groups[g].count;
+            hostbuf[cache.groups_off + 4 * g + 2] = cache.groups[g].kr;
+            hostbuf[cache.groups_off + 4 * g + 3] = cache.groups[g].first;
         }
         OICS_TRY(ctx->wlists.ensure(off * sizeof(int)));
         OICS_CUDA_TRY(cudaMemcpyAsync(ctx->wlists.p, hostbuf.data(), off * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -615,27 +627,26 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                     ctx->last_sweep_launches++;
                 }
             }
-            // heaviest classes first: the tail of the chunk is filled by the light ones
-            for (int kr = SWW_KRMAX; kr >= 2; kr--) {
-                const SweepCache::WordClass &C = cache.classes[kr];
-                const int g_lo = (int)(std::lower_bound(C.gfirst.begin(), C.gfirst.end(), a0) - C.gfirst.begin());
-                const int g_hi = (int)(std::lower_bound(C.gfirst.begin(), C.gfirst.end(), a1) - C.gfirst.begin());
-                if (g_hi == g_lo) continue;
-                SweepWPlan P;
-                P.meta = ctx->wmeta.as<uint32_t>();
-                P.planes = ctx->wplanes.as<uint2>();
-                P.kf = d_kf;
-                P.kf0 = f_lo;
-                P.err = d_err;
-                SweepWGroups G;
-                G.alist = d_err + C.alist_off;
-                G.groups = reinterpret_cast<const int2 *>(d_err + C.groups_off) + g_lo;
-                G.n_groups = g_hi - g_lo;
-                G.a0 = a0;
-                G.na_chunk = na;
-                G.card0 = c0;
-                OICS_TRY(sweepw_launch(ctx, kr, bits_base, A.bits_card_words, wp, w, h, T, P, G, nc, ctx->counts.as<int>()));
-                ctx->last_sweep_launches++;
+            {
+                const int ci = a0 / angles_per_chunk;
+                const int g_lo = cache.chunk_group_begin[ci], g_hi = cache.chunk_group_begin[ci + 1];
+                if (g_hi > g_lo) {
+                    SweepWPlan P;
+                    P.meta = ctx->wmeta.as<uint32_t>();
+                    P.planes = ctx->wplanes.as<uint2>();
+                    P.kf = d_kf;
+                    P.kf0 = f_lo;
+                    P.err = d_err;
+                    SweepWGroups G;
+                    G.alist = d_fast;
+                    G.groups = reinterpret_cast<const int4 *>(d_err + cache.groups_off) + g_lo;
+                    G.n_groups = g_hi - g_lo;
+                    G.a0 = a0;
+                    G.na_chunk = na;
+                    G.card0 = c0;
+                    OICS_TRY(sweepw_launch(ctx, bits_base, A.bits_card_words, wp, w, h, T, P, G, nc, ctx->counts.as<int>()));
+                    ctx->last_sweep_launches++;
+                }
             }
             OICS_CUDA_TRY(cudaEventRecord(e1, st));
             const size_t item0 = (size_t)c0 * n_angles + a0;

@@ -64,10 +64,10 @@ struct SweepWPlan {
     int *err;               // sticky device flag
 };
 
-// A run of consecutive candidate angles of one class evaluated by one CTA per tile.
+// Runs of consecutive candidate angles of one class, each evaluated by one CTA per tile.
 struct SweepWGroups {
-    const int *alist;       // class angle list (device)
-    const int2 *groups;     // {first index into alist, count} (device)
+    const int *alist;       // fast angle list (device)
+    const int4 *groups;     // {first index into alist, count, class (source rows per word), -} (device)
     int n_groups;
     int a0, na_chunk, card0;
 };
@@ -79,7 +79,7 @@ int32_t sweepw_classify(oics_ctx *ctx, const SweepTables &T, int n_angles, int w
 bool sweepw_group_fits(const double *inv, int first, int cnt, int kr, int w, int h);
 int32_t sweepw_build_planes(oics_ctx *ctx, const SweepTables &T, const uint32_t *d_meta, const int *d_fast_angles,
                             int n_fast, int w, int h, uint2 *d_planes);
-int32_t sweepw_launch(oics_ctx *ctx, int kr, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
+int32_t sweepw_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
                       const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts);
 
 }  // namespace oics

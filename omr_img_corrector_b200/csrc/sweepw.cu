@@ -281,17 +281,15 @@ __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, co
 }
 
 template <int KR>
-__global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
+__device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, const int card_local)
 {
     extern __shared__ uint32_t smem[];
     uint32_t *tile = smem;                                                           // [SWW_TROWS][SWW_P] + pad
     int2 *sXY = reinterpret_cast<int2 *>(tile + SWW_TROWS * SWW_P + 4);              // [2][SWW_TH]
     uint8_t *sRow = reinterpret_cast<uint8_t *>(sXY + 2 * SWW_TH);                   // [2][SWW_TJ][SWW_TH]
-    __shared__ int sBox[4];
+    int *sBox = reinterpret_cast<int *>(tile + SWW_TROWS * SWW_P);                   // the pad words
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int grp = blockIdx.y / A.n_cards, card_local = blockIdx.y - grp * A.n_cards;
-    const int2 gd = A.G.groups[grp];
     const int *alist = A.G.alist + gd.x;
     const int n_ang = gd.y;
     const int card = A.G.card0 + card_local;
@@ -436,23 +434,35 @@ __global__ void __launch_bounds__(256) sweepw_kernel(const SweepWArgs A)
 
 static constexpr size_t SWW_SMEM = ((size_t)SWW_TROWS * SWW_P + 4) * 4 + 2 * (size_t)SWW_TH * 8 + 2 * (size_t)SWW_TJ * SWW_TH;
 
-template <int KR>
-static cudaError_t launch_w(const SweepWArgs &A, dim3 grid, cudaStream_t st)
+// One launch covers every class: blockIdx.y -> (group, card), card fastest so that the CTAs
+// in flight share the group's planes in L2; the group descriptor carries its class.
+__global__ void __launch_bounds__(256, 4) sweepw_kernel(const SweepWArgs A)
 {
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(sweepw_kernel<KR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWW_SMEM);
-        if (e != cudaSuccess) return e;
-        attr = true;
+    const int grp = blockIdx.y / A.n_cards, card_local = blockIdx.y - grp * A.n_cards;
+    const int4 gd = A.G.groups[grp];
+    switch (gd.z) {
+    case 2: sweepw_body<2>(A, gd, card_local); break;
+    case 3: sweepw_body<3>(A, gd, card_local); break;
+    case 4: sweepw_body<4>(A, gd, card_local); break;
+    case 5: sweepw_body<5>(A, gd, card_local); break;
+    case 6: sweepw_body<6>(A, gd, card_local); break;
+    case 7: sweepw_body<7>(A, gd, card_local); break;
+    case 8: sweepw_body<8>(A, gd, card_local); break;
+    case 9: sweepw_body<9>(A, gd, card_local); break;
+    case 10: sweepw_body<10>(A, gd, card_local); break;
+    default: sweepw_body<11>(A, gd, card_local); break;
     }
-    sweepw_kernel<KR><<<grid, 256, SWW_SMEM, st>>>(A);
-    return cudaGetLastError();
 }
 
-int32_t sweepw_launch(oics_ctx *ctx, int kr, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
+int32_t sweepw_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
                       const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts)
 {
     if (G.n_groups <= 0 || n_cards <= 0) return OICS_OK;
+    static bool attr = false;
+    if (!attr) {
+        OICS_CUDA_TRY(cudaFuncSetAttribute(sweepw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWW_SMEM));
+        attr = true;
+    }
     SweepWArgs A;
     A.bits = bits;
     A.bits_card_words = bits_card_words;
@@ -462,21 +472,8 @@ int32_t sweepw_launch(oics_ctx *ctx, int kr, const uint32_t *bits, size_t bits_c
     A.tiles_x = cdiv(A.wj, SWW_TJ);
     A.n_cards = n_cards;
     dim3 grid(A.tiles_x * cdiv(h, SWW_TH), (unsigned)(n_cards * G.n_groups));
-    cudaError_t e;
-    switch (kr) {
-    case 2: e = launch_w<2>(A, grid, ctx->stream); break;
-    case 3: e = launch_w<3>(A, grid, ctx->stream); break;
-    case 4: e = launch_w<4>(A, grid, ctx->stream); break;
-    case 5: e = launch_w<5>(A, grid, ctx->stream); break;
-    case 6: e = launch_w<6>(A, grid, ctx->stream); break;
-    case 7: e = launch_w<7>(A, grid, ctx->stream); break;
-    case 8: e = launch_w<8>(A, grid, ctx->stream); break;
-    case 9: e = launch_w<9>(A, grid, ctx->stream); break;
-    case 10: e = launch_w<10>(A, grid, ctx->stream); break;
-    case 11: e = launch_w<11>(A, grid, ctx->stream); break;
-    default: set_error("internal: unsupported word-kernel class %d", kr); return OICS_ERR_INVALID_ARG;
-    }
-    OICS_CUDA_TRY(e);
+    sweepw_kernel<<<grid, 256, SWW_SMEM, ctx->stream>>>(A);
+    OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;
 }
