@@ -288,17 +288,19 @@ def run_gpu(args, rank, local_rank, world):
     traffic = None
     tp = os.path.join(ROOT, "profiles", "sweep_traffic.json")
     if os.path.exists(tp):
-        try:
-            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        try:   # ncu --set full capture: DRAM bytes per (card, angle) item x items of one launch here
+            per_item = json.load(open(tp)).get("dram_bytes_per_item")
+            traffic = float(per_item) * args.cards * args.steps * N_ANGLES / max(1, sweep_launches)
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "oics::sweep_kernel", "peak_source": peak_src,
+                "traffic": traffic, "kernel": "oics::sweepw_kernel", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_launch_s * 1000.0,
                 "launches": sweep_launches, "kernel_share_of_step": sweep_ms / elapsed_ms,
                 "note": "1 B per (angle, pixel) sample = the rotated byte image the reference writes and re-reads; "
-                        "the kernel keeps the 1.1 MB bit-packed card in L2/shared memory, so HBM is not the "
-                        "physical limiter (integer-issue bound) -- the HBM copy peak is the stated denominator"}
+                        "the kernel assembles 32 samples per lane from the 1.1 MB bit-packed card staged in shared "
+                        "memory, so HBM is not the physical limiter (issue/ALU bound, ncu in profiles/) -- the "
+                        "measured HBM copy peak is the stated denominator and frac may exceed 1"}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
