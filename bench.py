@@ -333,7 +333,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cards", type=int, default=512, help="binary cards per GPU per step (4096 / 8)")
     ap.add_argument("--distinct", type=int, default=16, help="distinct synthetic cards per GPU (cycled)")
-    ap.add_argument("--e2e-cards", dest="e2e_cards", type=int, default=24)
+    ap.add_argument("--e2e-cards", dest="e2e_cards", type=int, default=128)
     ap.add_argument("--e2e-distinct", dest="e2e_distinct", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

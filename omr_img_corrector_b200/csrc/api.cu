@@ -513,6 +513,11 @@ OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t
                        hough_max_line_gap, dst, dst_cap, dst_w, dst_h, angle, need_check);
 }
 
+// The batch driver that replaces the reference's thread pool (task.rs:19-68, thread_pool.rs):
+// cards move through a three-stage pipeline of sub-batches -- upload (side stream), estimate +
+// deskew (ctx stream: pre-processing and ONE fused sweep launch per sub-batch, exact rule A on
+// the host, one warp per card), download (side stream) -- so PCIe in both directions overlaps
+// the kernels.  Host buffers should be pinned for the copies to be asynchronous.
 OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
                                     int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
                                     int32_t max_w, int32_t max_h, double hough_min_line_length,
@@ -526,59 +531,166 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
     OICS_ARG(n_cards >= 0 && angles && need_checks && statuses);
     OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
     OICS_ARG(!dsts || dst_caps);
-    const bool dev = is_device_ptr(bgrs);
-    // Double-buffered upload: card i+1 is copied on a side stream while card i runs.
-    cudaStream_t up = nullptr;
-    cudaEvent_t ready[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr};
-    DevBuf *slot[2] = {&ctx->in_img, &ctx->in_img2};
-    const size_t row = (size_t)w * 3;
-    if (!dev) {
-        OICS_CUDA_TRY(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; i++) {
-            OICS_TRY(slot[i]->ensure(row * h));
-            OICS_CUDA_TRY(cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming));
-            OICS_CUDA_TRY(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming));
-        }
-        if (n_cards > 0) {
-            OICS_CUDA_TRY(cudaMemcpy2DAsync(slot[0]->p, row, bgrs, (size_t)stride, row, (size_t)h, cudaMemcpyHostToDevice, up));
-            OICS_CUDA_TRY(cudaEventRecord(ready[0], up));
-        }
-    }
+    if (n_cards == 0) return OICS_OK;
+    const bool dev_in = is_device_ptr(bgrs);
+    const size_t row = (size_t)w * 3, card_bytes = row * h;
+    const int B = std::min<int>(n_cards, 8);    // cards per sub-batch
+    const int n_sub = cdiv(n_cards, B);
+    cudaStream_t st = ctx->stream, up = nullptr, down = nullptr;
+    cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
+    DevBuf *in_slot[2] = {&ctx->in_img, &ctx->in_img2}, *out_slot[2] = {&ctx->out_img, &ctx->out_img2};
+
+    // geometry shared by the batch
+    const double scale = oics_projection_scale(w, h, max_w, max_h);
+    const int ow = scale == 1.0 ? w : scaled_dim(w, scale), oh = scale == 1.0 ? h : scaled_dim(h, scale);
+    if (ow <= 0 || oh <= 0) { set_error("scaled size %dx%d is empty", ow, oh); return OICS_ERR_INVALID_ARG; }
+    const int N = oics_angle_half_range(max_angle, step);
+    std::vector<double> M((size_t)std::max(1, 2 * N) * 6);
+    int n_angles = 0;
+    if (N > 0) OICS_TRY(oics_sweep_matrices(ow, oh, max_angle, step, scale, M.data(), 2 * N, &n_angles));
+    OICS_TRY(ctx->bin.ensure((size_t)B * ow * oh));
+    // CONTAIN output bound: any rotation of a w x h card fits a square of side (w + h) / sqrt(2) + 2
+    const size_t side = (size_t)std::ceil((double)(w + h) * 0.70710678118654757) + 2;
+    const size_t out_card_cap = (side * side * 3 + 255) & ~(size_t)255;
+    bool host_out = false;
+    if (dsts)
+        for (int c = 0; c < n_cards; c++) host_out = host_out || (dsts[c] && !is_device_ptr(dsts[c]));
+
     int32_t rc = OICS_OK;
-    for (int c = 0; c < n_cards; c++) {
-        const uint8_t *dsrc = bgrs + (size_t)c * card_stride;
-        size_t dstride = (size_t)stride;
-        if (!dev) {
-            const int s = c & 1;
-            if (c + 1 < n_cards) {
-                const int ns = (c + 1) & 1;
-                if (c >= 1) cudaStreamWaitEvent(up, freed[ns], 0);
-                cudaMemcpy2DAsync(slot[ns]->p, row, bgrs + (size_t)(c + 1) * card_stride, (size_t)stride, row, (size_t)h,
-                                  cudaMemcpyHostToDevice, up);
-                cudaEventRecord(ready[ns], up);
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(st);
+        if (up) { cudaStreamSynchronize(up); cudaStreamDestroy(up); }
+        if (down) { cudaStreamSynchronize(down); cudaStreamDestroy(down); }
+        for (int i = 0; i < 2; i++)
+            for (cudaEvent_t e : {in_ready[i], in_free[i], out_ready[i], out_free[i]})
+                if (e) cudaEventDestroy(e);
+    };
+#define OICS_BATCH_TRY(expr)                                   \
+    do {                                                       \
+        int32_t _s = (expr);                                   \
+        if (_s != OICS_OK) { cleanup(); return _s; }           \
+    } while (0)
+#define OICS_BATCH_CUDA(expr)                                                                     \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            cleanup();                                                                            \
+            return OICS_ERR_CUDA;                                                                 \
+        }                                                                                         \
+    } while (0)
+
+    for (int i = 0; i < 2; i++) {
+        for (cudaEvent_t *e : {&in_ready[i], &in_free[i], &out_ready[i], &out_free[i]})
+            OICS_BATCH_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        if (!dev_in && i < n_sub) OICS_BATCH_TRY(in_slot[i]->ensure((size_t)B * card_bytes));
+        if (host_out && i < n_sub) OICS_BATCH_TRY(out_slot[i]->ensure((size_t)B * out_card_cap));
+    }
+    if (!dev_in) OICS_BATCH_CUDA(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
+    if (host_out) OICS_BATCH_CUDA(cudaStreamCreateWithFlags(&down, cudaStreamNonBlocking));
+
+    auto upload = [&](int k) -> cudaError_t {   // sub-batch k -> in_slot[k & 1]
+        const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
+        cudaError_t e = cudaSuccess;
+        if (k >= 2) e = cudaStreamWaitEvent(up, in_free[s], 0);
+        const uint8_t *src = bgrs + (size_t)c0 * card_stride;
+        uint8_t *dst = in_slot[s]->as<uint8_t>();
+        if (e == cudaSuccess) {
+            if ((size_t)stride == row && card_stride == card_bytes)
+                e = cudaMemcpyAsync(dst, src, (size_t)nb * card_bytes, cudaMemcpyHostToDevice, up);
+            else
+                for (int i = 0; i < nb && e == cudaSuccess; i++)
+                    e = cudaMemcpy2DAsync(dst + (size_t)i * card_bytes, row, src + (size_t)i * card_stride, (size_t)stride,
+                                          row, (size_t)h, cudaMemcpyHostToDevice, up);
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(in_ready[s], up);
+        return e;
+    };
+    if (!dev_in) {
+        OICS_BATCH_CUDA(upload(0));
+        if (n_sub > 1) OICS_BATCH_CUDA(upload(1));
+    }
+
+    std::vector<double> v((size_t)B * std::max(1, 2 * N)), hh((size_t)B * std::max(1, 2 * N)), cand((size_t)std::max(1, 2 * N));
+    const uint8_t white[4] = {255, 255, 255, 0};
+    for (int k = 0; k < n_sub && rc == OICS_OK; k++) {
+        const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
+        const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
+        const size_t dcard = dev_in ? card_stride : card_bytes, dstride = dev_in ? (size_t)stride : row;
+        if (!dev_in) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, in_ready[s], 0));
+        // P0 for every card of the sub-batch, then one fused sweep over all of them
+        for (int i = 0; i < nb; i++)
+            OICS_BATCH_TRY(preprocess_device(ctx, dsrc + (size_t)i * dcard, w, h, dstride, OICS_PRE_OMR, ow, oh,
+                                             ctx->bin.as<uint8_t>() + (size_t)i * ow * oh));
+        if (N > 0)
+            OICS_BATCH_TRY(sweep_to(ctx, ctx->bin.as<uint8_t>(), nb, (size_t)ow * oh, ow, oh, (size_t)ow, M.data(), n_angles,
+                                    v.data(), hh.data(), nullptr, nullptr));
+        // exact rule A (+ Hough fallback and reconcile, omr.rs:352-403) per card on the host
+        if (host_out && k >= 2) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, out_free[s], 0));
+        std::vector<size_t> out_off((size_t)nb, 0), out_bytes((size_t)nb, 0);
+        for (int i = 0; i < nb; i++) {
+            const int c = c0 + i;
+            const uint8_t *card = dsrc + (size_t)i * dcard;
+            oics_omr_result p = {0, 0, 0, cand.data(), (int32_t)cand.size()};
+            int32_t stc = oics_rule_a(hh.data() + (size_t)i * 2 * N, v.data() + (size_t)i * 2 * N, N, step, &p);
+            double a = 0.0;
+            int32_t need = 0;
+            if (stc == OICS_OK) {
+                if (p.status == OICS_BELIEVED) {
+                    a = p.angle;
+                } else {
+                    oics_omr_result e = {0, 0, 0, nullptr, 0};   // omr.rs:366: Canny runs on the 3-channel source
+                    stc = edges_result(ctx, card, 3, w, h, dstride, 50.0, 150.0, 0, hough_min_line_length,
+                                       hough_max_line_gap, OICS_LINES_OMR, &e);
+                    if (stc == OICS_OK) stc = oics_reconcile(&p, e.angle, &a, &need);
+                }
             }
-            cudaStreamWaitEvent(ctx->stream, ready[s], 0);
-            dsrc = slot[s]->as<uint8_t>();
-            dstride = row;
+            double Mw[6];
+            int dw = 0, dh = 0;
+            if (stc == OICS_OK) stc = oics_rotate_geometry(w, h, a, 1.0, OICS_CLIP_CONTAIN, Mw, &dw, &dh);
+            angles[c] = a;
+            need_checks[c] = need;
+            if (dst_ws) dst_ws[c] = dw;
+            if (dst_hs) dst_hs[c] = dh;
+            uint8_t *dst = dsts ? dsts[c] : nullptr;
+            if (stc == OICS_OK && dst) {
+                const size_t need_bytes = (size_t)dw * 3 * dh;
+                if (need_bytes > dst_caps[c]) {
+                    set_error("deskewed card needs %zu bytes, capacity %zu", need_bytes, dst_caps[c]);
+                    stc = OICS_ERR_CAPACITY;
+                } else if (is_device_ptr(dst)) {
+                    stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white, dst, dw, dh, (size_t)dw * 3);
+                } else if (need_bytes > out_card_cap) {
+                    set_error("internal: CONTAIN bound %zu < %zu", out_card_cap, need_bytes);
+                    stc = OICS_ERR_CAPACITY;
+                } else {
+                    out_off[i] = (size_t)i * out_card_cap;
+                    out_bytes[i] = need_bytes;
+                    stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white,
+                                      out_slot[s]->as<uint8_t>() + out_off[i], dw, dh, (size_t)dw * 3);
+                }
+            }
+            statuses[c] = stc;
+            if (stc == OICS_ERR_CUDA) rc = OICS_ERR_CUDA;
         }
-        int32_t dw = 0, dh = 0;
-        statuses[c] = correct_one(ctx, dsrc, w, h, dstride, max_angle, step, max_w, max_h, hough_min_line_length,
-                                  hough_max_line_gap, dsts ? dsts[c] : nullptr, dsts ? dst_caps[c] : 0, &dw, &dh,
-                                  &angles[c], &need_checks[c]);
-        if (!dev) cudaEventRecord(freed[c & 1], ctx->stream);
-        if (dst_ws) dst_ws[c] = dw;
-        if (dst_hs) dst_hs[c] = dh;
-        if (statuses[c] == OICS_ERR_CUDA) { rc = OICS_ERR_CUDA; break; }
-    }
-    cudaStreamSynchronize(ctx->stream);
-    if (up) {
-        cudaStreamSynchronize(up);
-        cudaStreamDestroy(up);
-        for (int i = 0; i < 2; i++) {
-            if (ready[i]) cudaEventDestroy(ready[i]);
-            if (freed[i]) cudaEventDestroy(freed[i]);
+        if (rc != OICS_OK) break;
+        if (!dev_in) {
+            OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
+            if (k + 2 < n_sub) OICS_BATCH_CUDA(upload(k + 2));
+        }
+        if (host_out) {
+            OICS_BATCH_CUDA(cudaEventRecord(out_ready[s], st));
+            OICS_BATCH_CUDA(cudaStreamWaitEvent(down, out_ready[s], 0));
+            for (int i = 0; i < nb; i++)
+                if (out_bytes[i])
+                    OICS_BATCH_CUDA(cudaMemcpyAsync(dsts[c0 + i], out_slot[s]->as<uint8_t>() + out_off[i], out_bytes[i],
+                                                    cudaMemcpyDeviceToHost, down));
+            OICS_BATCH_CUDA(cudaEventRecord(out_free[s], down));
         }
     }
+    cleanup();
+#undef OICS_BATCH_TRY
+#undef OICS_BATCH_CUDA
     return rc;
 }
 

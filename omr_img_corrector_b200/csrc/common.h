@@ -98,7 +98,7 @@ struct oics_ctx {
     double last_sweep_ms = 0.0;
     int last_sweep_launches = 0;
     // scratch
-    oics::DevBuf in_img, in_img2, out_img, gray, tmp8a, tmp8b, bin, bits, mats, tabs, counts, sd,
+    oics::DevBuf in_img, in_img2, out_img, out_img2, gray, tmp8a, tmp8b, bin, bits, mats, tabs, counts, sd,
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;

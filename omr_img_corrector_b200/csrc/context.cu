@@ -175,7 +175,7 @@ OICS_API void oics_destroy(oics_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf *bufs[] = {&ctx->in_img, &ctx->in_img2, &ctx->out_img, &ctx->gray,  &ctx->tmp8a, &ctx->tmp8b,
+    DevBuf *bufs[] = {&ctx->in_img, &ctx->in_img2, &ctx->out_img, &ctx->out_img2, &ctx->gray,  &ctx->tmp8a, &ctx->tmp8b,
                       &ctx->bin,    &ctx->bits,    &ctx->mats,    &ctx->tabs,  &ctx->counts, &ctx->sd,
                       &ctx->sums,   &ctx->edges,   &ctx->mag,     &ctx->dxy,   &ctx->labels, &ctx->accum,
                       &ctx->lines,  &ctx->misc,    &ctx->cplx,    &ctx->cplx2, &ctx->twid,   &ctx->fmag,

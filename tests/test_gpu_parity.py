@@ -384,3 +384,50 @@ def test_correct_default_end_to_end(ctx, orc, dataset_like):
     ra, rneed, rout = orc.correct_default(blank, 5, 1.0, 0, 0, 50.0, 5.0)
     ga, gneed, gout = ctx.correct_default(blank, 5, 1.0, 0, 0, 50.0, 5.0)
     assert (ga, gneed) == (ra, rneed) and np.array_equal(rout, gout)
+
+
+def test_correct_batch_pipeline_equals_one_by_one(ctx, orc, dataset_like):
+    """oics_correct_batch (upload / estimate + deskew / download pipeline, 16 cards per
+    sub-batch) must return exactly what omr::correct_default returns card by card; 37 cards
+    make three sub-batches so both buffer slots are reused."""
+    bgr, _ = dataset_like
+    base = np.ascontiguousarray(bgr[100:400, 200:460])               # 300 x 260 crop
+    blank = np.full((300, 260, 3), 255, np.uint8)                    # ambiguous sweep -> Hough branch
+    blank[40:43, 30:230] = 0
+    blank[45:240, 60:63] = 0
+    cards = []
+    for i in range(37):
+        if i % 9 == 4:
+            cards.append(blank)
+        else:
+            a = -4.0 + 0.25 * i
+            cards.append(orc.rotate_mat(base, a, 1.0, 1, orc.WHITE, 0))
+    cards = np.stack(cards)
+    params = (5, 0.5, 0, 0, 50.0, 5.0)
+    outs = [np.zeros(520 * 520 * 3, np.uint8) for _ in cards]
+    ang, need, stat, sizes = ctx.correct_batch(cards, *params, outs=outs)
+    assert not stat.any()
+    for i in range(len(cards)):
+        ga, gneed, gout = ctx.correct_default(cards[i], *params)
+        assert (ang[i], bool(need[i])) == (ga, gneed), i
+        dw, dh = sizes[i]
+        assert (dh, dw) == gout.shape[:2]
+        assert np.array_equal(outs[i][:dw * dh * 3].reshape(dh, dw, 3), gout), i
+    for i in (0, 4, 36):                                              # and the oracle on a few
+        ra, rneed, rout = orc.correct_default(cards[i], *params)
+        dw, dh = sizes[i]
+        assert (ang[i], bool(need[i])) == (ra, rneed) and np.array_equal(outs[i][:dw * dh * 3].reshape(dh, dw, 3), rout)
+    # device-resident input and output
+    import torch
+    t = torch.from_numpy(cards[:3]).cuda()
+    douts = [torch.zeros(520 * 520 * 3, dtype=torch.uint8, device="cuda") for _ in range(3)]
+
+    class _P:                                                         # minimal buffer facade for api.correct_batch
+        def __init__(self, t):
+            self.ctypes = type("c", (), {"data": t.data_ptr()})()
+            self.size = t.numel()
+    a2, n2, s2, z2 = ctx.correct_batch(t, *params, outs=[_P(d) for d in douts])
+    assert np.array_equal(a2, ang[:3]) and not s2.any()
+    for i in range(3):
+        dw, dh = z2[i]
+        assert np.array_equal(douts[i][:dw * dh * 3].cpu().numpy(), outs[i][:dw * dh * 3])

@@ -2,9 +2,9 @@
 # Quick GPU iteration: sweep parity tests + bench (no CPU baseline).
 set -u
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q -k "sweep or entry or smoke or correct" > gpurun_out/pytest_quick.log 2>&1; echo "pytest rc=$?"
+python -m pytest tests -m gpu -x -q -k "sweep or entry or correct" > gpurun_out/pytest_quick.log 2>&1; echo "pytest rc=$?"
 tail -15 gpurun_out/pytest_quick.log
-python bench.py --no-cpu-baseline "$@" > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo "bench rc=$?"
+python bench.py --no-cpu-baseline --e2e-cards 128 "$@" > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo "bench rc=$?"
 tail -3 gpurun_out/bench_quick.err
 python - <<'PY'
 import json
