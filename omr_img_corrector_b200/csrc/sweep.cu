@@ -44,8 +44,9 @@ __global__ void sweep_tables_kernel(const double *__restrict__ Minv, int w, int 
         ad[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[0], x), 1024.0));
         bd[(size_t)a * wpad + i] = __double2int_rn(__dmul_rn(__dmul_rn(M[3], x), 1024.0));
     }
-    if (i < h) {
-        double y = (double)i;
+    if (i < hpad) {
+        // rows past the image (hpad is a whole number of word-kernel tiles) repeat the last row
+        double y = (double)min(i, h - 1);
         int X0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(M[1], y), M[2]), 1024.0)) + 512;
         int Y0 = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(M[4], y), M[5]), 1024.0)) + 512;
         xy[(size_t)a * hpad + i] = make_int2(X0, Y0);
@@ -408,7 +409,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     // inverse matrices, host f64 in OpenCV's order
     std::vector<double> inv((size_t)n_angles * 6);
     for (int i = 0; i < n_angles; i++) invert_affine(M_host + 6 * (size_t)i, inv.data() + 6 * (size_t)i);
-    const int wpad = (w + 31) & ~31, hpad = (h + 31) & ~31;
+    const int wpad = (w + 31) & ~31, hpad = cdiv(h, SWW_TH) * SWW_TH;
     const int wp = cdiv(w, 32), wj = wp;
     const size_t tab_ints = (size_t)n_angles * (2 * (size_t)wpad + 2 * (size_t)hpad);
     SweepCache &cache = ctx->sweep_cache;
@@ -449,7 +450,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     SweepTables T;
     T.ad = ad; T.bd = bd; T.xy = xy; T.wpad = wpad; T.hpad = hpad;
     if (!same_geometry) {
-        dim3 grid(cdiv(max(wpad, h), 256), n_angles);
+        dim3 grid(cdiv(max(wpad, hpad), 256), n_angles);
         sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;

@@ -206,6 +206,14 @@ __device__ __forceinline__ uint32_t assemble_word(const uint32_t *__restrict__ s
     return out;
 }
 
+// 4 KB of {X0, Y0} rows -> shared memory, 16 bytes per thread, asynchronously
+__device__ __forceinline__ void copy_rows_async(int2 *dst, const int2 *src, int tid)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst + 2 * tid);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src + 2 * tid) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
 // 5 bit-sliced planes -> per-column counts.  The five 32x32 bit transposes run in lock step
 // so the lane-dependent shift and mask of a butterfly stage are computed once.
 __device__ __forceinline__ int unpack_columns(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t c4, int np,
@@ -241,12 +249,16 @@ template <int KR, bool CHECK>
 __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, const int2 *__restrict__ sxy,
                                            uint8_t *__restrict__ rowp, const uint2 *__restrict__ plp, uint2 (&cd)[4],
                                            int arefp, int brefp, uint32_t S1, const uint32_t (&Q)[SWW_KRMAX - 1],
-                                           int rows_left, uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3,
+                                           int rows_total, int lane, uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3,
                                            uint32_t &c4)
 {
     uint32_t o[4];
 #pragma unroll
     for (int u = 0; u < 4; u++) {
+        if (CHECK && 32 * u >= rows_total) {   // whole group past the tile (warp-uniform)
+            o[u] = 0;
+            continue;
+        }
         const int2 p = sxy[32 * u];
         const uint2 m = cd[u];
         cd[u] = __ldg(plp + 128 + 32 * u);   // next round (the planes buffer is padded)
@@ -258,7 +270,7 @@ __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, co
         if (S1 == 0) v = assemble_word<KR, false>(src, sh, m.x, m.y, 0u, Q);
         else v = assemble_word<KR, true>(src, sh, m.x, m.y, S1 & ~m.y, Q);
         if (CHECK) {
-            const bool valid = 32 * u < rows_left;   // rows_left is relative to this lane
+            const bool valid = 32 * u + lane < rows_total;
             v = valid ? v : 0u;
             if (valid) rowp[32 * u] = (uint8_t)__popc(v);
         } else {
@@ -362,16 +374,11 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
             }
         }
     }
-    // per-row {X0, Y0} of the first angle, re-based to the staged window; rows past the
-    // tile repeat its last row so every lane computes in-bounds addresses
+    // per-row {X0, Y0} of the first angle: a 4 KB copy (the tables are padded to whole tiles,
+    // rows past the image repeat its last row, so every lane computes in-bounds addresses)
     const int xoff = (colw0 * 32) << 10, yoff = row0 << 10;
-    {
-        const int2 *xy = A.T.xy + (size_t)alist[0] * A.T.hpad + y0;
-        for (int i = tid; i < SWW_TH; i += 256) {
-            const int2 p = __ldg(xy + min(i, th - 1));
-            sXY[i] = make_int2(p.x - xoff, p.y - yoff);
-        }
-    }
+    copy_rows_async(sXY, A.T.xy + (size_t)alist[0] * A.T.hpad + y0, tid);
+    cp_async_wait_all();
     __syncthreads();
 
     const int j = j0 + warp;
@@ -382,21 +389,18 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
         int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
         int *cols_out = rows_out + A.h;
         uint8_t *rowbuf = sRow + (ai & 1) * (SWW_TJ * SWW_TH);
-        if (ai + 1 < n_ang) {  // next angle's rows (read after the barrier below)
-            const int2 *xy = A.T.xy + (size_t)alist[ai + 1] * A.T.hpad + y0;
-            int2 *dst = sXY + ((ai + 1) & 1) * SWW_TH;
-            for (int i = tid; i < SWW_TH; i += 256) {
-                const int2 p = __ldg(xy + min(i, th - 1));
-                dst[i] = make_int2(p.x - xoff, p.y - yoff);
-            }
-        }
+        if (ai + 1 < n_ang)  // next angle's rows, in flight during this angle's loop
+            copy_rows_async(sXY + ((ai + 1) & 1) * SWW_TH, A.T.xy + (size_t)alist[ai + 1] * A.T.hpad + y0, tid);
         if (active) {
-            const uint32_t *m = A.P.meta + ((size_t)ang * A.wj + j) * SWW_META;
+            const uint4 *m4 = reinterpret_cast<const uint4 *>(A.P.meta + ((size_t)ang * A.wj + j) * SWW_META);
+            const uint4 ma = __ldg(m4), mb = KR > 5 ? __ldg(m4 + 1) : make_uint4(0, 0, 0, 0);
+            const uint4 mc = __ldg(m4 + 2), md = __ldg(m4 + 3);
+            const uint32_t Qall[SWW_KRMAX - 1] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w, mc.x, mc.y};
             uint32_t Q[SWW_KRMAX - 1];
 #pragma unroll
-            for (int r = 0; r < SWW_KRMAX - 1; r++) Q[r] = r < KR - 1 ? __ldg(m + r) : 0u;
-            const uint32_t S1 = __ldg(m + 11);
-            const int arefp = (int)__ldg(m + 13), brefp = (int)__ldg(m + 14);
+            for (int r = 0; r < SWW_KRMAX - 1; r++) Q[r] = r < KR - 1 ? Qall[r] : 0u;
+            const uint32_t S1 = mc.w;
+            const int arefp = (int)md.y - xoff, brefp = (int)md.z - yoff;
             const int kslot = A.P.kf[ang] - A.P.kf0;
             const uint2 *plp = A.P.planes + ((size_t)kslot * A.wj + j) * A.h + y0 + lane;
             const int2 *sxy = sXY + (ai & 1) * SWW_TH + lane;
@@ -407,11 +411,11 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
             for (int u = 0; u < 4; u++) cd[u] = __ldg(plp + 32 * u);
             int done = 0;
             for (; done + 128 <= th; done += 128) {  // four full 32-row groups
-                four_words<KR, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 0, c0, c1, c2, c3, c4);
+                four_words<KR, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2, c3, c4);
                 sxy += 128; rowp += 128; plp += 128;
             }
             if (done < th)   // the tile's last, partial round: row 32 u + lane is valid iff < th - done
-                four_words<KR, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done - lane, c0, c1, c2, c3, c4);
+                four_words<KR, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done, lane, c0, c1, c2, c3, c4);
             // unpack: lane L receives bit L of every lane's plane = pixel 31 - L of the word
             const uint32_t hi = c2 | c3 | c4;
             if (__any_sync(0xffffffffu, (c0 | c1 | hi) != 0)) {
@@ -423,11 +427,23 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
                 if (cnt && x < A.w) atomicAdd(cols_out + x, cnt);
             }
         }
+        cp_async_wait_all();
         __syncthreads();
-        for (int i = tid; i < th; i += 256) {
-            int s = 0;
-            for (int k = 0; k < nj; k++) s += rowbuf[k * SWW_TH + i];
-            if (s) atomicAdd(rows_out + y0 + i, s);
+        // rows: thread t sums the 8 per-column bytes of rows 4t..4t+3 as packed 16-bit lanes
+        if (tid < SWW_TH / 4 && 4 * tid < th) {
+            const uint32_t *rb = reinterpret_cast<const uint32_t *>(rowbuf) + tid;
+            uint32_t lo = 0, hi = 0;
+            for (int k = 0; k < nj; k++) {
+                const uint32_t v = rb[k * (SWW_TH / 4)];
+                lo += v & 0x00FF00FFu;
+                hi += (v >> 8) & 0x00FF00FFu;
+            }
+            int *ro = rows_out + y0 + 4 * tid;
+            const int n = th - 4 * tid;   // rows of this quad inside the tile (bytes past it are stale)
+            if (lo & 0xFFFFu) atomicAdd(ro, (int)(lo & 0xFFFFu));
+            if (n > 1 && (hi & 0xFFFFu)) atomicAdd(ro + 1, (int)(hi & 0xFFFFu));
+            if (n > 2 && (lo >> 16)) atomicAdd(ro + 2, (int)(lo >> 16));
+            if (n > 3 && (hi >> 16)) atomicAdd(ro + 3, (int)(hi >> 16));
         }
     }
 }
