@@ -195,8 +195,7 @@ def run_gpu(args, rank, local_rank, world):
 
     def step():
         v, h = ctx.projection_sweep_batch(cards.data_ptr(), args.cards, W, H, M, out=(out_v, out_h))
-        res = [api.rule_a(h[c], v[c], N, STEP) for c in range(args.cards)]
-        return res
+        return api.rule_a_batch(h, v, N, STEP)     # exact rule A (omr.rs:147-221) per card, host
 
     def barrier():
         if world > 1:
@@ -206,8 +205,8 @@ def run_gpu(args, rank, local_rank, world):
     for _ in range(max(3, args.warmup)):
         res = step()
     # parity sanity on the distinct cards: the sweep must recover the known skew
-    bad = [(skews[c % D], res[c].angle, res[c].status) for c in range(args.cards)
-           if res[c].status != api.BELIEVED or abs(res[c].angle - skews[c % D]) > 0.1 + 1e-9]
+    bad = [(skews[c % D], float(res[0][c]), int(res[1][c])) for c in range(args.cards)
+           if res[1][c] != api.BELIEVED or abs(res[0][c] - skews[c % D]) > 0.1 + 1e-9]
 
     sampler = ClockSampler(local_rank)
     sampler.start()

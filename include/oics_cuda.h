@@ -150,6 +150,10 @@ OICS_API int32_t oics_projection_standard_deviations(oics_ctx *ctx, const uint8_
 /* rule A: omr.rs:147-221 */
 OICS_API int32_t oics_rule_a(const double *h_sd, const double *v_sd, int32_t N, double step,
                              oics_omr_result *result);
+/* rule A for every card of a batch: h_sd, v_sd are [n_cards][2N]; per card the selected angle,
+ * the status (OICS_BELIEVED / NEED_CHECK / NOT_A_RESULT) and the number of candidates. */
+OICS_API int32_t oics_rule_a_batch(const double *h_sd, const double *v_sd, int32_t n_cards, int32_t N,
+                                   double step, double *angles, int32_t *statuses, int32_t *n_candidates);
 /* rule B: projection.rs:125-190 -> angle */
 OICS_API int32_t oics_rule_b(const double *v_sd, const double *h_sd, int32_t N, double step, double *angle);
 

@@ -124,6 +124,20 @@ def rule_a(h_sd, v_sd, N, step) -> OmrResult:
     return _unpack(r, buf)
 
 
+def rule_a_batch(h_sd, v_sd, N, step):
+    """h_sd, v_sd: [n_cards, 2N] -> (angles, statuses, n_candidates) arrays."""
+    h_sd = np.ascontiguousarray(h_sd, np.float64)
+    v_sd = np.ascontiguousarray(v_sd, np.float64)
+    n = h_sd.shape[0] if h_sd.ndim == 2 else 1
+    angles = np.zeros(n, np.float64)
+    stats = np.zeros(n, np.int32)
+    ncand = np.zeros(n, np.int32)
+    ip = C.POINTER(C.c_int32)
+    check(_lib.load().oics_rule_a_batch(_dptr(h_sd), _dptr(v_sd), n, N, float(step), _dptr(angles),
+                                        stats.ctypes.data_as(ip), ncand.ctypes.data_as(ip)))
+    return angles, stats, ncand
+
+
 def rule_b(v_sd, h_sd, N, step) -> float:
     v_sd = np.ascontiguousarray(v_sd, np.float64)
     h_sd = np.ascontiguousarray(h_sd, np.float64)

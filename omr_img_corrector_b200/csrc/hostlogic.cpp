@@ -191,6 +191,21 @@ OICS_API int32_t oics_rule_a(const double *h_sd, const double *v_sd, int32_t N, 
     return OICS_OK;
 }
 
+OICS_API int32_t oics_rule_a_batch(const double *h_sd, const double *v_sd, int32_t n_cards, int32_t N,
+                                   double step, double *angles, int32_t *statuses, int32_t *n_candidates)
+{
+    OICS_ARG(n_cards >= 0 && N >= 0 && angles && statuses);
+    std::vector<double> cand((size_t)std::max(1, 2 * N));
+    for (int c = 0; c < n_cards; c++) {
+        oics_omr_result r = {0, 0, 0, cand.data(), (int32_t)cand.size()};
+        OICS_TRY(oics_rule_a(h_sd + (size_t)c * 2 * N, v_sd + (size_t)c * 2 * N, N, step, &r));
+        angles[c] = r.angle;
+        statuses[c] = r.status;
+        if (n_candidates) n_candidates[c] = r.n_candidates;
+    }
+    return OICS_OK;
+}
+
 OICS_API int32_t oics_rule_b(const double *v_sd, const double *h_sd, int32_t N, double step, double *angle)
 {
     OICS_ARG(angle && N > 0 && v_sd && h_sd);

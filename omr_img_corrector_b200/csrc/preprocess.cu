@@ -56,6 +56,129 @@ __global__ void __launch_bounds__(256) gray_erode_kernel(const uint8_t *__restri
     }
 }
 
+// ---------------------------------------------------------------------------
+// Fast path of the same operation for radius 0 or 3 (the two
+// the reference uses): HBM-bound.  A CTA produces a 128 x 64 tile; the BGR rows of the tile
+// and its halo are fetched as whole 32-bit words (coalesced), converted to gray once, and the
+// L1 diamond is taken four pixels at a time with byte-SIMD minima:
+//     H_k[r] = min over |dx| <= k of gray[r][x + dx]            (k = 1, 2, 3; 2 shifts + 2 vmin each)
+//     out[r] = min(H3[r], H2[r +- 1], H1[r +- 2], gray[r +- 3])
+static constexpr int GF_TW = 128, GF_TH = 64, GF_WW = GF_TW / 4;   // tile in pixels / words
+static constexpr int GF_RAWW = (GF_TW + 8) * 3 / 4 + 1;            // aligned words covering a staged BGR row (136 px)
+
+template <int R>   // R = 0 (gray [+ threshold]) or 3
+__global__ void __launch_bounds__(256) gray_erode_fast_kernel(const uint8_t *__restrict__ src, int w, int h,
+                                                              size_t stride, int do_threshold,
+                                                              uint8_t *__restrict__ dst, size_t dstride)
+{
+    constexpr int ROWS = GF_TH + 2 * R;
+    __shared__ uint32_t raw[ROWS * GF_RAWW];          // BGR words; re-used for H1..H3 after the conversion
+    __shared__ uint32_t G[ROWS][GF_WW + 2];           // gray, one halo word per side
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bx = blockIdx.x * GF_TW, by = blockIdx.y * GF_TH;
+    __shared__ int sMis[ROWS];                        // byte misalignment of each staged row segment
+    // phase 0: the aligned 32-bit words that cover each row segment, a warp per row.  A word is
+    // read iff it overlaps the valid bytes of its row (same page as a valid byte: never faults).
+    const int seg0 = (bx - 4) * 3, row_bytes = w * 3;
+    for (int r = warp; r < ROWS; r += 8) {
+        const int gy = by - R + r;
+        const bool rin = gy >= 0 && gy < h;
+        const uint8_t *a0 = src + (size_t)(rin ? gy : 0) * stride + seg0;
+        const int mis = (int)(reinterpret_cast<uintptr_t>(a0) & 3);
+        const uint32_t *ab = reinterpret_cast<const uint32_t *>(a0 - mis);
+        if (lane == 0) sMis[r] = mis;
+#pragma unroll
+        for (int k = lane; k < GF_RAWW; k += 32) {
+            const int off = seg0 - mis + 4 * k;       // first byte of the word, relative to the row
+            const bool in = rin && off + 4 > 0 && off < row_bytes;
+            // asynchronous 4-byte copy, zero-filled when the word is outside the image: every
+            // row of the tile is in flight at once (no register round trip between rows)
+            const unsigned d = (unsigned)__cvta_generic_to_shared(&raw[r * GF_RAWW + k]);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(in ? ab + k : ab),
+                         "r"(in ? 4 : 0)
+                         : "memory");
+        }
+    }
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+    __syncthreads();
+    // phase 1: gray, four pixels per thread; outside the image = 255 (never the minimum)
+    for (int i = tid; i < ROWS * (GF_WW + 2); i += 256) {
+        const int r = i / (GF_WW + 2), wc = i - r * (GF_WW + 2);
+        const int gy = by - R + r, gx = bx - 4 + 4 * wc;
+        const uint32_t *rw = raw + r * GF_RAWW + 3 * wc;
+        const int sh = 8 * sMis[r];
+        const uint32_t a = __funnelshift_r(rw[0], rw[1], sh), b = __funnelshift_r(rw[1], rw[2], sh),
+                       c = __funnelshift_r(rw[2], rw[3], sh);
+        uint32_t g0 = ((a & 255) * 9798 + ((a >> 8) & 255) * 19235 + ((a >> 16) & 255) * 3735 + 16384) >> 15;
+        uint32_t g1 = ((a >> 24) * 9798 + (b & 255) * 19235 + ((b >> 8) & 255) * 3735 + 16384) >> 15;
+        uint32_t g2 = (((b >> 16) & 255) * 9798 + (b >> 24) * 19235 + (c & 255) * 3735 + 16384) >> 15;
+        uint32_t g3 = (((c >> 8) & 255) * 9798 + ((c >> 16) & 255) * 19235 + (c >> 24) * 3735 + 16384) >> 15;
+        const bool rin = gy >= 0 && gy < h;
+        if (!(rin && gx >= 0 && gx < w)) g0 = 255;
+        if (!(rin && gx + 1 >= 0 && gx + 1 < w)) g1 = 255;
+        if (!(rin && gx + 2 >= 0 && gx + 2 < w)) g2 = 255;
+        if (!(rin && gx + 3 >= 0 && gx + 3 < w)) g3 = 255;
+        G[r][wc] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+    }
+    __syncthreads();
+    uint32_t *H1 = raw, *H2 = raw + ROWS * GF_WW, *H3 = raw + 2 * ROWS * GF_WW;
+    if (R == 3) {
+        // phase 2a: horizontal minima of every staged row
+        for (int i = tid; i < ROWS * GF_WW; i += 256) {
+            const int r = i >> 5, wc = (i & 31) + 1;
+            const uint32_t p = G[r][wc - 1], c = G[r][wc], n = G[r][wc + 1];
+            uint32_t m = __vminu4(__vminu4(c, __funnelshift_l(p, c, 8)), __funnelshift_r(c, n, 8));
+            H1[i] = m;
+            m = __vminu4(__vminu4(m, __funnelshift_l(p, c, 16)), __funnelshift_r(c, n, 16));
+            H2[i] = m;
+            m = __vminu4(__vminu4(m, __funnelshift_l(p, c, 24)), __funnelshift_r(c, n, 24));
+            H3[i] = m;
+        }
+        __syncthreads();
+    }
+    // phase 2b: vertical combination, threshold, store
+    const bool word_ok = ((reinterpret_cast<uintptr_t>(dst) | dstride) & 3) == 0;
+    for (int i = tid; i < GF_TH * GF_WW; i += 256) {
+        const int r = i >> 5, wc = i & 31;
+        const int gy = by + r, gx = bx + 4 * wc;
+        if (gy >= h || gx >= w) continue;
+        uint32_t m;
+        if (R == 3) {
+            const int q = r + 3;   // staged row of this output row
+            m = __vminu4(H3[q * GF_WW + wc], __vminu4(H2[(q - 1) * GF_WW + wc], H2[(q + 1) * GF_WW + wc]));
+            m = __vminu4(m, __vminu4(H1[(q - 2) * GF_WW + wc], H1[(q + 2) * GF_WW + wc]));
+            m = __vminu4(m, __vminu4(G[q - 3][wc + 1], G[q + 3][wc + 1]));
+        } else {
+            m = G[r][wc + 1];
+        }
+        if (do_threshold) m = __vcmpgtu4(m, 0x7f7f7f7fu);
+        uint8_t *o = dst + (size_t)gy * dstride + gx;
+        if (word_ok && gx + 3 < w) {
+            *reinterpret_cast<uint32_t *>(o) = m;
+        } else {
+            for (int k = 0; k < 4 && gx + k < w; k++) o[k] = (uint8_t)(m >> (8 * k));
+        }
+    }
+}
+
+// gray (+ erode radius) (+ threshold) of a BGR image: the fast kernel when the radius is one
+// the reference uses (0 or 3), the generic one otherwise.
+static int32_t launch_gray_erode(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int radius,
+                                 int do_threshold, uint8_t *dst, size_t dstride)
+{
+    if (radius == 0 || radius == 3) {
+        dim3 grid(cdiv(w, GF_TW), cdiv(h, GF_TH));
+        if (radius == 3) gray_erode_fast_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, do_threshold, dst, dstride);
+        else gray_erode_fast_kernel<0><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, do_threshold, dst, dstride);
+    } else {
+        dim3 grid(cdiv(w, GE_TX), cdiv(h, GE_TY));
+        gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, radius, do_threshold, dst, dstride);
+    }
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    return OICS_OK;
+}
+
 // One axis of computeResizeAreaTab for destination index d: up to `*n` taps.
 struct AreaTaps {
     int s0;        // first source index
@@ -159,11 +282,7 @@ static int32_t launch_resize(oics_ctx *ctx, const uint8_t *src, int ch, int w, i
 
 int32_t gray_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint8_t *dgray)
 {
-    dim3 grid(cdiv(w, GE_TX), cdiv(h, GE_TY));
-    gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, 0, 0, dgray, (size_t)w);
-    OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches++;
-    return OICS_OK;
+    return launch_gray_erode(ctx, dbgr, w, h, stride, 0, 0, dgray, (size_t)w);
 }
 
 int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int mode, int ow, int oh,
@@ -175,17 +294,9 @@ int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size
         return OICS_ERR_INVALID_ARG;
     }
     if (mode == OICS_PRE_OMR) {
-        dim3 grid(cdiv(w, GE_TX), cdiv(h, GE_TY));
-        if (identity) {
-            gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, 3, 1, dbin, (size_t)w);
-            OICS_CUDA_TRY(cudaGetLastError());
-            ctx->launches++;
-            return OICS_OK;
-        }
+        if (identity) return launch_gray_erode(ctx, dbgr, w, h, stride, 3, 1, dbin, (size_t)w);
         OICS_TRY(ctx->tmp8a.ensure((size_t)w * h));
-        gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, 3, 0, ctx->tmp8a.as<uint8_t>(), (size_t)w);
-        OICS_CUDA_TRY(cudaGetLastError());
-        ctx->launches++;
+        OICS_TRY(launch_gray_erode(ctx, dbgr, w, h, stride, 3, 0, ctx->tmp8a.as<uint8_t>(), (size_t)w));
         return launch_resize(ctx, ctx->tmp8a.as<uint8_t>(), 1, w, h, (size_t)w, dbin, ow, oh, 1);
     }
     if (mode == OICS_PRE_PROJECTION) {
@@ -197,11 +308,7 @@ int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size
             col = ctx->tmp8a.as<uint8_t>();
             cstride = (size_t)ow * 3;
         }
-        dim3 grid(cdiv(ow, GE_TX), cdiv(oh, GE_TY));
-        gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(col, ow, oh, cstride, 0, 1, dbin, (size_t)ow);
-        OICS_CUDA_TRY(cudaGetLastError());
-        ctx->launches++;
-        return OICS_OK;
+        return launch_gray_erode(ctx, col, ow, oh, cstride, 0, 1, dbin, (size_t)ow);
     }
     set_error("unknown pre-processing mode %d", mode);
     return OICS_ERR_INVALID_ARG;

@@ -183,3 +183,15 @@ def test_hough_dims(orc):
     for (w, h) in [(2480, 3508), (1240, 1150), (310, 288)]:
         assert api.hough_dims(w, h) == orc.hough_dims(w, h)
     assert api.hough_dims(2480, 3508) == (180, 11977)
+
+
+def test_rule_a_batch_matches_rule_a():
+    from omr_img_corrector_b200 import api
+    rng = np.random.default_rng(5)
+    N = 20
+    h = rng.integers(0, 6, (7, 2 * N)).astype(np.float64)       # small alphabet -> exact ties
+    v = rng.integers(0, 6, (7, 2 * N)).astype(np.float64)
+    ang, stat, ncand = api.rule_a_batch(h, v, N, 0.5)
+    for c in range(7):
+        r = api.rule_a(h[c], v[c], N, 0.5)
+        assert (ang[c], stat[c], ncand[c]) == (r.angle, r.status, len(r.candidates))
