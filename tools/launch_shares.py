@@ -21,4 +21,6 @@ tot = sum(v['gpu__time_duration.sum'] for v in t.values())
 for k, v in sorted(t.items(), key=lambda kv: -kv[1]['gpu__time_duration.sum']):
     us = v['gpu__time_duration.sum']
     mb = v.get('dram__bytes_read.sum', 0) + v.get('dram__bytes_write.sum', 0)
-    print(f"{k:44s} n={n[k]:4d} total {us/1e3:8.3f} ms {100*us/tot:5.1f}%  per launch {us/n[k]:8.1f} us  dram {mb/n[k]:8.1f} MB/launch  {mb/us*1e-3 if us else 0:6.2f} TB/s")
+    cyc = v.get('sm__cycles_elapsed.max', 0)
+    ghz = f" {cyc/us*1e-3:5.2f} GHz" if cyc else ""
+    print(f"{k:44s} n={n[k]:4d}{ghz} total {us/1e3:8.3f} ms {100*us/tot:5.1f}%  per launch {us/n[k]:8.1f} us  dram {mb/n[k]:8.1f} MB/launch  {mb/us*1e-3 if us else 0:6.2f} TB/s")
