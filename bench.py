@@ -158,6 +158,30 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_numa(local_rank):
+    """Runs this rank (and so its pinned host buffers, first-touch) on the NUMA node of its GPU."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(local_rank), "pci_domain_id", 0)
+        dev_id = getattr(torch.cuda.get_device_properties(local_rank), "pci_device_id", 0)
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev_id:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 # --------------------------------------------------------------------------- GPU arm
 def run_gpu(args, rank, local_rank, world):
     import torch
@@ -168,6 +192,7 @@ def run_gpu(args, rank, local_rank, world):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     ctx = api.Context(local_rank)
@@ -268,7 +293,7 @@ def run_gpu(args, rank, local_rank, world):
         d2h = int(sum(int(sizes[i][0]) * int(sizes[i][1]) * 3 for i in range(E)))
         e2e = {"value": world * E * ksteps / (float(t_e2e.item()) / 1000.0), "unit": UNIT,
                "h2d_bytes_per_step": int(E * W * H * 3), "d2h_bytes_per_step": d2h + E * 16,
-               "cards_per_gpu_per_step": E, "steps": ksteps, "mismatches": len(e2e_bad)}
+               "cards_per_gpu_per_step": E, "steps": ksteps, "mismatches": len(e2e_bad), "numa_node": numa}
 
     if rank != 0:
         if world > 1:

@@ -618,10 +618,8 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
         const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
         const size_t dcard = dev_in ? card_stride : card_bytes, dstride = dev_in ? (size_t)stride : row;
         if (!dev_in) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, in_ready[s], 0));
-        // P0 for every card of the sub-batch, then one fused sweep over all of them
-        for (int i = 0; i < nb; i++)
-            OICS_BATCH_TRY(preprocess_device(ctx, dsrc + (size_t)i * dcard, w, h, dstride, OICS_PRE_OMR, ow, oh,
-                                             ctx->bin.as<uint8_t>() + (size_t)i * ow * oh));
+        // P0 for every card of the sub-batch (one launch), then one fused sweep over all of them
+        OICS_BATCH_TRY(preprocess_batch_device(ctx, dsrc, nb, dcard, w, h, dstride, OICS_PRE_OMR, ow, oh, ctx->bin.as<uint8_t>()));
         if (N > 0)
             OICS_BATCH_TRY(sweep_to(ctx, ctx->bin.as<uint8_t>(), nb, (size_t)ow * oh, ow, oh, (size_t)ow, M.data(), n_angles,
                                     v.data(), hh.data(), nullptr, nullptr));

@@ -141,6 +141,8 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
 // preprocess.cu
 int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int mode, int ow,
                           int oh, uint8_t *dbin /* tightly packed ow x oh */);
+int32_t preprocess_batch_device(oics_ctx *ctx, const uint8_t *dbgrs, int n_cards, size_t card_stride, int w, int h,
+                                size_t stride, int mode, int ow, int oh, uint8_t *dbins /* n x ow x oh */);
 int32_t gray_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint8_t *dgray);
 // canny.cu
 int32_t canny_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, int low, int high,

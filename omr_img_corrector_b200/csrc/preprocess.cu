@@ -57,68 +57,83 @@ __global__ void __launch_bounds__(256) gray_erode_kernel(const uint8_t *__restri
 }
 
 // ---------------------------------------------------------------------------
-// Fast path of the same operation for radius 0 or 3 (the two
-// the reference uses): HBM-bound.  A CTA produces a 128 x 64 tile; the BGR rows of the tile
-// and its halo are fetched as whole 32-bit words (coalesced), converted to gray once, and the
-// L1 diamond is taken four pixels at a time with byte-SIMD minima:
+// Fast path of the same operation for radius 0 or 3 (the two the reference uses): a CTA
+// produces a 128 x 64 tile of one card of a batch.  The BGR rows of the tile and its halo are
+// fetched as aligned 16-byte chunks straight into shared memory (cp.async, every row in
+// flight at once, any row alignment), converted to gray once with two dp4a per pixel
+// (weights split into 8-bit halves: 9798 = 38*256 + 70, 19235 = 75*256 + 35, 3735 = 14*256 + 151),
+// and the L1 diamond is taken four pixels at a time with byte-SIMD minima:
 //     H_k[r] = min over |dx| <= k of gray[r][x + dx]            (k = 1, 2, 3; 2 shifts + 2 vmin each)
 //     out[r] = min(H3[r], H2[r +- 1], H1[r +- 2], gray[r +- 3])
 static constexpr int GF_TW = 128, GF_TH = 64, GF_WW = GF_TW / 4;   // tile in pixels / words
-static constexpr int GF_RAWW = (GF_TW + 8) * 3 / 4 + 1;            // aligned words covering a staged BGR row (136 px)
+static constexpr int GF_CHUNKS = 27;                               // 16-byte chunks covering 15 + 412 bytes
+static constexpr int GF_RAWW = GF_CHUNKS * 4;                      // words per staged BGR row
+
+__device__ __forceinline__ uint32_t gray4(uint32_t a, uint32_t b, uint32_t c)
+{
+    // a, b, c: 12 BGR bytes of four pixels; the 4th byte of each dp4a operand has weight 0
+    const uint32_t HI = 0x000E4B26u, LO = 0x00972346u;
+    const uint32_t p1 = __byte_perm(a, b, 0x0543), p2 = __byte_perm(b, c, 0x0432), p3 = c >> 8;
+    const uint32_t g0 = (__dp4a(a, LO, 16384u) + (__dp4a(a, HI, 0u) << 8)) >> 15;
+    const uint32_t g1 = (__dp4a(p1, LO, 16384u) + (__dp4a(p1, HI, 0u) << 8)) >> 15;
+    const uint32_t g2 = (__dp4a(p2, LO, 16384u) + (__dp4a(p2, HI, 0u) << 8)) >> 15;
+    const uint32_t g3 = (__dp4a(p3, LO, 16384u) + (__dp4a(p3, HI, 0u) << 8)) >> 15;
+    return g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+}
 
 template <int R>   // R = 0 (gray [+ threshold]) or 3
-__global__ void __launch_bounds__(256) gray_erode_fast_kernel(const uint8_t *__restrict__ src, int w, int h,
-                                                              size_t stride, int do_threshold,
-                                                              uint8_t *__restrict__ dst, size_t dstride)
+__global__ void __launch_bounds__(256) gray_erode_fast_kernel(const uint8_t *__restrict__ src0, size_t src_card, int w,
+                                                              int h, size_t stride, int do_threshold,
+                                                              uint8_t *__restrict__ dst0, size_t dst_card,
+                                                              size_t dstride)
 {
     constexpr int ROWS = GF_TH + 2 * R;
-    __shared__ uint32_t raw[ROWS * GF_RAWW];          // BGR words; re-used for H1..H3 after the conversion
-    __shared__ uint32_t G[ROWS][GF_WW + 2];           // gray, one halo word per side
+    __shared__ __align__(16) uint32_t raw[ROWS * GF_RAWW];   // BGR chunks; re-used for H1..H3 after the conversion
+    __shared__ uint32_t G[ROWS][GF_WW + 2];                   // gray, one halo word per side
+    __shared__ int sMis[ROWS];                                // byte offset of each row segment in its first chunk
+    const uint8_t *src = src0 + (size_t)blockIdx.z * src_card;
+    uint8_t *dst = dst0 + (size_t)blockIdx.z * dst_card;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int bx = blockIdx.x * GF_TW, by = blockIdx.y * GF_TH;
-    __shared__ int sMis[ROWS];                        // byte misalignment of each staged row segment
-    // phase 0: the aligned 32-bit words that cover each row segment, a warp per row.  A word is
-    // read iff it overlaps the valid bytes of its row (same page as a valid byte: never faults).
+    // phase 0: the aligned 16-byte chunks that cover each row segment, a warp per row.  A chunk
+    // is read iff it overlaps the valid bytes of its row (same page as a valid byte: never faults).
     const int seg0 = (bx - 4) * 3, row_bytes = w * 3;
     for (int r = warp; r < ROWS; r += 8) {
         const int gy = by - R + r;
         const bool rin = gy >= 0 && gy < h;
         const uint8_t *a0 = src + (size_t)(rin ? gy : 0) * stride + seg0;
-        const int mis = (int)(reinterpret_cast<uintptr_t>(a0) & 3);
-        const uint32_t *ab = reinterpret_cast<const uint32_t *>(a0 - mis);
+        const int mis = (int)(reinterpret_cast<uintptr_t>(a0) & 15);
         if (lane == 0) sMis[r] = mis;
-#pragma unroll
-        for (int k = lane; k < GF_RAWW; k += 32) {
-            const int off = seg0 - mis + 4 * k;       // first byte of the word, relative to the row
-            const bool in = rin && off + 4 > 0 && off < row_bytes;
-            // asynchronous 4-byte copy, zero-filled when the word is outside the image: every
-            // row of the tile is in flight at once (no register round trip between rows)
-            const unsigned d = (unsigned)__cvta_generic_to_shared(&raw[r * GF_RAWW + k]);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(in ? ab + k : ab),
-                         "r"(in ? 4 : 0)
-                         : "memory");
+        if (lane < GF_CHUNKS) {
+            const int off = seg0 - mis + 16 * lane;    // first byte of the chunk, relative to the row
+            const bool in = rin && off + 16 > 0 && off < row_bytes;
+            const unsigned d = (unsigned)__cvta_generic_to_shared(&raw[r * GF_RAWW + 4 * lane]);
+            const uint8_t *g = a0 - mis + (in ? 16 * lane : 0);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(g), "r"(in ? 16 : 0) : "memory");
         }
     }
     asm volatile("cp.async.wait_all;\n" ::: "memory");
     __syncthreads();
     // phase 1: gray, four pixels per thread; outside the image = 255 (never the minimum)
+    const bool interior = bx >= 4 && bx + GF_TW + 4 <= w && by >= R && by + GF_TH + R <= h;
     for (int i = tid; i < ROWS * (GF_WW + 2); i += 256) {
         const int r = i / (GF_WW + 2), wc = i - r * (GF_WW + 2);
-        const int gy = by - R + r, gx = bx - 4 + 4 * wc;
-        const uint32_t *rw = raw + r * GF_RAWW + 3 * wc;
-        const int sh = 8 * sMis[r];
-        const uint32_t a = __funnelshift_r(rw[0], rw[1], sh), b = __funnelshift_r(rw[1], rw[2], sh),
-                       c = __funnelshift_r(rw[2], rw[3], sh);
-        uint32_t g0 = ((a & 255) * 9798 + ((a >> 8) & 255) * 19235 + ((a >> 16) & 255) * 3735 + 16384) >> 15;
-        uint32_t g1 = ((a >> 24) * 9798 + (b & 255) * 19235 + ((b >> 8) & 255) * 3735 + 16384) >> 15;
-        uint32_t g2 = (((b >> 16) & 255) * 9798 + (b >> 24) * 19235 + (c & 255) * 3735 + 16384) >> 15;
-        uint32_t g3 = (((c >> 8) & 255) * 9798 + ((c >> 16) & 255) * 19235 + (c >> 24) * 3735 + 16384) >> 15;
-        const bool rin = gy >= 0 && gy < h;
-        if (!(rin && gx >= 0 && gx < w)) g0 = 255;
-        if (!(rin && gx + 1 >= 0 && gx + 1 < w)) g1 = 255;
-        if (!(rin && gx + 2 >= 0 && gx + 2 < w)) g2 = 255;
-        if (!(rin && gx + 3 >= 0 && gx + 3 < w)) g3 = 255;
-        G[r][wc] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+        const int mis = sMis[r];
+        const uint32_t *rw = raw + r * GF_RAWW + (mis >> 2) + 3 * wc;
+        const int sh = 8 * (mis & 3);
+        uint32_t g = gray4(__funnelshift_r(rw[0], rw[1], sh), __funnelshift_r(rw[1], rw[2], sh),
+                           __funnelshift_r(rw[2], rw[3], sh));
+        if (!interior) {
+            const int gy = by - R + r, gx = bx - 4 + 4 * wc;
+            const bool rin = gy >= 0 && gy < h;
+            uint32_t keep = 0;
+            if (rin && gx >= 0 && gx < w) keep |= 0x000000FFu;
+            if (rin && gx + 1 >= 0 && gx + 1 < w) keep |= 0x0000FF00u;
+            if (rin && gx + 2 >= 0 && gx + 2 < w) keep |= 0x00FF0000u;
+            if (rin && gx + 3 >= 0 && gx + 3 < w) keep |= 0xFF000000u;
+            g |= ~keep;
+        }
+        G[r][wc] = g;
     }
     __syncthreads();
     uint32_t *H1 = raw, *H2 = raw + ROWS * GF_WW, *H3 = raw + 2 * ROWS * GF_WW;
@@ -161,21 +176,152 @@ __global__ void __launch_bounds__(256) gray_erode_fast_kernel(const uint8_t *__r
     }
 }
 
+// ---------------------------------------------------------------------------
+// gray -> erode -> threshold when nothing follows the threshold (the BASELINE operating point:
+// no resize).  threshold(min(...)) = min(threshold(...)), so the diamond minimum is taken on
+// ONE BIT per pixel (gray > 127): a warp converts one 128-pixel row segment (4 pixels per
+// lane, two dp4a each), four ballots turn it into four interleaved bit words (bit l of word k
+// = pixel 4 l + k), the horizontal partial ANDs A1..A3 of the L1 diamond cost 12 LOP3 per row
+// and the vertical combination 3 LOP3 per word.  A CTA produces 120 x 64 output pixels (the
+// 128 staged pixels include a 4-pixel halo per side).
+static constexpr int GB_TW = 120, GB_TH = 64;
+static constexpr int GB_CHUNKS = 25, GB_RAWW = GB_CHUNKS * 4;   // 15 + 384 bytes of a staged BGR row
+
+template <int R>   // R = 0 (gray + threshold) or 3
+__global__ void __launch_bounds__(256) gray_erode_bits_kernel(const uint8_t *__restrict__ src0, size_t src_card, int w,
+                                                              int h, size_t stride, uint8_t *__restrict__ dst0,
+                                                              size_t dst_card, size_t dstride)
+{
+    constexpr int ROWS = GB_TH + 2 * R;
+    __shared__ __align__(16) uint32_t raw[ROWS * GB_RAWW];
+    __shared__ __align__(16) uint32_t Bw[ROWS][4], A1[ROWS][4], A2[ROWS][4], A3[ROWS][4];
+    __shared__ uint32_t O[GB_TH][4];
+    const uint8_t *src = src0 + (size_t)blockIdx.z * src_card;
+    uint8_t *dst = dst0 + (size_t)blockIdx.z * dst_card;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bx = blockIdx.x * GB_TW, by = blockIdx.y * GB_TH;
+    const int seg0 = (bx - 4) * 3, row_bytes = w * 3;
+    // phase 0: aligned 16-byte chunks covering each row segment, a warp per row, all in flight
+    for (int r = warp; r < ROWS; r += 8) {
+        const int gy = by - R + r;
+        const bool rin = gy >= 0 && gy < h;
+        const uint8_t *a0 = src + (size_t)(rin ? gy : 0) * stride + seg0;
+        const int mis = (int)(reinterpret_cast<uintptr_t>(a0) & 15);
+        if (lane < GB_CHUNKS) {
+            const int off = seg0 - mis + 16 * lane;
+            const bool in = rin && off + 16 > 0 && off < row_bytes;
+            const unsigned d = (unsigned)__cvta_generic_to_shared(&raw[r * GB_RAWW + 4 * lane]);
+            const uint8_t *g = a0 - mis + (in ? 16 * lane : 0);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(g), "r"(in ? 16 : 0) : "memory");
+        }
+    }
+    asm volatile("cp.async.wait_all;\n" ::: "memory");
+    __syncthreads();
+    // phase 1: gray > 127 as interleaved bit words + horizontal partial ANDs, a warp per row
+    const bool interior = bx >= 4 && bx + GB_TW + 4 <= w && by >= R && by + GB_TH + R <= h;
+    for (int r = warp; r < ROWS; r += 8) {
+        const int gy = by - R + r;
+        const bool rin = gy >= 0 && gy < h;
+        const int mis = (int)(reinterpret_cast<uintptr_t>(src + (size_t)(rin ? gy : 0) * stride + seg0) & 15);
+        const uint32_t *rw = raw + r * GB_RAWW + (mis >> 2) + 3 * lane;
+        const int sh = 8 * (mis & 3);
+        // gray > 127  <=>  c0*9798 + c1*19235 + c2*3735 + 16384 >= 128 << 15: compare the dot
+        // product, the gray byte itself is never needed
+        const uint32_t a = __funnelshift_r(rw[0], rw[1], sh), b = __funnelshift_r(rw[1], rw[2], sh),
+                       c = __funnelshift_r(rw[2], rw[3], sh);
+        const uint32_t HI = 0x000E4B26u, LO = 0x00972346u, T = (128u << 15) - 16384u;
+        const uint32_t q1 = __byte_perm(a, b, 0x0543), q2 = __byte_perm(b, c, 0x0432), q3 = c >> 8;
+        bool p0 = __dp4a(a, LO, 0u) + (__dp4a(a, HI, 0u) << 8) >= T;
+        bool p1 = __dp4a(q1, LO, 0u) + (__dp4a(q1, HI, 0u) << 8) >= T;
+        bool p2 = __dp4a(q2, LO, 0u) + (__dp4a(q2, HI, 0u) << 8) >= T;
+        bool p3 = __dp4a(q3, LO, 0u) + (__dp4a(q3, HI, 0u) << 8) >= T;
+        if (!interior) {                               // outside the image: never the minimum
+            const int gx = bx - 4 + 4 * lane;
+            p0 = p0 || !(rin && gx >= 0 && gx < w);
+            p1 = p1 || !(rin && gx + 1 >= 0 && gx + 1 < w);
+            p2 = p2 || !(rin && gx + 2 >= 0 && gx + 2 < w);
+            p3 = p3 || !(rin && gx + 3 >= 0 && gx + 3 < w);
+        }
+        const uint32_t w0 = __ballot_sync(0xffffffffu, p0), w1 = __ballot_sync(0xffffffffu, p1);
+        const uint32_t w2 = __ballot_sync(0xffffffffu, p2), w3 = __ballot_sync(0xffffffffu, p3);
+        if (R == 0) {
+            if (lane == 0) *reinterpret_cast<uint4 *>(&Bw[r][0]) = make_uint4(w0, w1, w2, w3);
+        } else {
+            // pixel x + s lives in word (k + s) mod 4, lane shifted by floor((k + s) / 4)
+            const uint32_t u0 = w0 >> 1, u1 = w1 >> 1, u2 = w2 >> 1;   // next lane's pixels 0..2
+            const uint32_t d1 = w1 << 1, d2 = w2 << 1, d3 = w3 << 1;   // previous lane's pixels 1..3
+            const uint32_t a10 = w0 & w1 & d3, a11 = w1 & w2 & w0, a12 = w2 & w3 & w1, a13 = w3 & u0 & w2;
+            const uint32_t a20 = a10 & w2 & d2, a21 = a11 & w3 & d3, a22 = a12 & u0 & w0, a23 = a13 & u1 & w1;
+            const uint32_t a30 = a20 & w3 & d1, a31 = a21 & u0 & d2, a32 = a22 & u1 & d3, a33 = a23 & u2 & w0;
+            if (lane == 0) {
+                *reinterpret_cast<uint4 *>(&Bw[r][0]) = make_uint4(w0, w1, w2, w3);
+                *reinterpret_cast<uint4 *>(&A1[r][0]) = make_uint4(a10, a11, a12, a13);
+                *reinterpret_cast<uint4 *>(&A2[r][0]) = make_uint4(a20, a21, a22, a23);
+                *reinterpret_cast<uint4 *>(&A3[r][0]) = make_uint4(a30, a31, a32, a33);
+            }
+        }
+    }
+    __syncthreads();
+    // phase 2: vertical combination, one thread per (row, word)
+    {
+        const int r = tid >> 2, k = tid & 3;
+        uint32_t o;
+        if (R == 3) {
+            const int q = r + 3;
+            o = A3[q][k] & A2[q - 1][k] & A2[q + 1][k] & A1[q - 2][k] & A1[q + 2][k] & Bw[q - 3][k] & Bw[q + 3][k];
+        } else {
+            o = Bw[r][k];
+        }
+        O[r][k] = o;
+    }
+    __syncthreads();
+    // phase 3: bits -> 0/255 bytes, a warp per row, lane l = staged pixels 4l..4l+3 (lanes 1..30 are the tile)
+    const bool word_ok = ((reinterpret_cast<uintptr_t>(dst) | dstride) & 3) == 0;
+    for (int r = warp; r < GB_TH; r += 8) {
+        const int gy = by + r, gx = bx + 4 * (lane - 1);
+        if (gy >= h) break;
+        const uint4 o = *reinterpret_cast<const uint4 *>(&O[r][0]);
+        if (lane < 1 || lane > 30 || gx >= w) continue;
+        const uint32_t m = (((o.x >> lane) & 1u) * 0x000000FFu) | (((o.y >> lane) & 1u) * 0x0000FF00u) |
+                           (((o.z >> lane) & 1u) * 0x00FF0000u) | (((o.w >> lane) & 1u) * 0xFF000000u);
+        uint8_t *p = dst + (size_t)gy * dstride + gx;
+        if (word_ok && gx + 3 < w) {
+            *reinterpret_cast<uint32_t *>(p) = m;
+        } else {
+            for (int k = 0; k < 4 && gx + k < w; k++) p[k] = (uint8_t)(m >> (8 * k));
+        }
+    }
+}
+
 // gray (+ erode radius) (+ threshold) of a BGR image: the fast kernel when the radius is one
 // the reference uses (0 or 3), the generic one otherwise.
 static int32_t launch_gray_erode(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int radius,
-                                 int do_threshold, uint8_t *dst, size_t dstride)
+                                 int do_threshold, uint8_t *dst, size_t dstride, int n_cards = 1, size_t src_card = 0,
+                                 size_t dst_card = 0)
 {
-    if (radius == 0 || radius == 3) {
-        dim3 grid(cdiv(w, GF_TW), cdiv(h, GF_TH));
-        if (radius == 3) gray_erode_fast_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, do_threshold, dst, dstride);
-        else gray_erode_fast_kernel<0><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, do_threshold, dst, dstride);
+    if ((radius == 0 || radius == 3) && do_threshold) {
+        dim3 grid(cdiv(w, GB_TW), cdiv(h, GB_TH), n_cards);
+        if (radius == 3) gray_erode_bits_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, dst, dst_card, dstride);
+        else gray_erode_bits_kernel<0><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, dst, dst_card, dstride);
+        OICS_CUDA_TRY(cudaGetLastError());
+        ctx->launches++;
+    } else if (radius == 0 || radius == 3) {
+        dim3 grid(cdiv(w, GF_TW), cdiv(h, GF_TH), n_cards);
+        if (radius == 3)
+            gray_erode_fast_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, do_threshold, dst, dst_card, dstride);
+        else
+            gray_erode_fast_kernel<0><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, do_threshold, dst, dst_card, dstride);
+        OICS_CUDA_TRY(cudaGetLastError());
+        ctx->launches++;
     } else {
         dim3 grid(cdiv(w, GE_TX), cdiv(h, GE_TY));
-        gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, w, h, stride, radius, do_threshold, dst, dstride);
+        for (int c = 0; c < n_cards; c++) {
+            gray_erode_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr + (size_t)c * src_card, w, h, stride, radius, do_threshold,
+                                                               dst + (size_t)c * dst_card, dstride);
+            OICS_CUDA_TRY(cudaGetLastError());
+            ctx->launches++;
+        }
     }
-    OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches++;
     return OICS_OK;
 }
 
@@ -312,6 +458,18 @@ int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size
     }
     set_error("unknown pre-processing mode %d", mode);
     return OICS_ERR_INVALID_ARG;
+}
+
+// P0 for n cards of one geometry (the batch driver): one launch when no resize follows.
+int32_t preprocess_batch_device(oics_ctx *ctx, const uint8_t *dbgrs, int n_cards, size_t card_stride, int w, int h,
+                                size_t stride, int mode, int ow, int oh, uint8_t *dbins)
+{
+    if (mode == OICS_PRE_OMR && ow == w && oh == h)
+        return launch_gray_erode(ctx, dbgrs, w, h, stride, 3, 1, dbins, (size_t)w, n_cards, card_stride, (size_t)w * h);
+    for (int c = 0; c < n_cards; c++)
+        OICS_TRY(preprocess_device(ctx, dbgrs + (size_t)c * card_stride, w, h, stride, mode, ow, oh,
+                                   dbins + (size_t)c * ow * oh));
+    return OICS_OK;
 }
 
 }  // namespace oics

@@ -88,6 +88,109 @@ __global__ void __launch_bounds__(256) warp_kernel(const uint8_t *__restrict__ s
     }
 }
 
+// ---------------------------------------------------------------------------
+// Flat variant for tightly packed destinations (dstride == dw * CH, the layout of every image
+// this library returns): thread t produces destination pixels 4t .. 4t+3 in flat (row-major)
+// order = CH aligned 32-bit words whatever the row alignment.  Source pixels are fetched as
+// two aligned words + funnel shift (CH = 3, 4) instead of CH byte loads, and the CH words of
+// a thread are transposed through shared memory so a warp stores CH x 128 contiguous bytes.
+template <int CH>
+__device__ __forceinline__ uint32_t fetch_px(const uint32_t *__restrict__ src32, size_t byte_addr, uint32_t last_word)
+{
+    if (CH == 1) return reinterpret_cast<const uint8_t *>(src32)[byte_addr];
+    const uint32_t i0 = (uint32_t)(byte_addr >> 2), i1 = min(i0 + 1u, last_word);
+    const uint32_t v = __funnelshift_r(__ldg(src32 + i0), __ldg(src32 + i1), 8 * (int)(byte_addr & 3));
+    return CH == 3 ? (v & 0x00FFFFFFu) : v;
+}
+
+template <int CH, bool LINEAR>
+__global__ void __launch_bounds__(256) warp_flat_kernel(const uint32_t *__restrict__ src32, int w, int h, size_t sstride,
+                                                        uint32_t *__restrict__ dst32, int dw, long long npix,
+                                                        const int *__restrict__ ad, const int *__restrict__ bd,
+                                                        const int2 *__restrict__ xy, uint32_t border, uint32_t last_word)
+{
+    __shared__ uint32_t sT[8][32 * CH + 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    const long long p0 = 4 * t;
+    uint32_t px[4];
+    if (p0 < npix) {
+        int y = (int)(p0 / dw), x = (int)(p0 - (long long)y * dw);
+        int2 p = xy[y];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (p0 + i < npix) {
+                const int a = p.x + __ldg(ad + x), b = p.y + __ldg(bd + x);
+                if (!LINEAR) {
+                    const int sx = sat16(a >> 10), sy = sat16(b >> 10);
+                    px[i] = ((unsigned)sx < (unsigned)w && (unsigned)sy < (unsigned)h)
+                                ? fetch_px<CH>(src32, (size_t)sy * sstride + (size_t)sx * CH, last_word)
+                                : border;
+                } else {
+                    const int X = a >> 5, Y = b >> 5;
+                    const int sx = sat16(X >> 5), sy = sat16(Y >> 5), fx = X & 31, fy = Y & 31;
+                    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
+                    const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+                    const bool x0in = (unsigned)sx < (unsigned)w, x1in = (unsigned)(sx + 1) < (unsigned)w;
+                    const bool y0in = (unsigned)sy < (unsigned)h, y1in = (unsigned)(sy + 1) < (unsigned)h;
+                    const long long base = (long long)sy * (long long)sstride + (long long)sx * CH;
+                    const uint32_t q00 = (x0in && y0in) ? fetch_px<CH>(src32, (size_t)base, last_word) : border;
+                    const uint32_t q01 = (x1in && y0in) ? fetch_px<CH>(src32, (size_t)(base + CH), last_word) : border;
+                    const uint32_t q10 = (x0in && y1in) ? fetch_px<CH>(src32, (size_t)(base + (long long)sstride), last_word) : border;
+                    const uint32_t q11 = (x1in && y1in) ? fetch_px<CH>(src32, (size_t)(base + (long long)sstride + CH), last_word) : border;
+                    uint32_t o = 0;
+#pragma unroll
+                    for (int c = 0; c < CH; c++) {
+                        const int v = (int)((q00 >> (8 * c)) & 255) * w00 + (int)((q01 >> (8 * c)) & 255) * w01 +
+                                      (int)((q10 >> (8 * c)) & 255) * w10 + (int)((q11 >> (8 * c)) & 255) * w11 + 16384;
+                        o |= (uint32_t)min(255, max(0, v >> 15)) << (8 * c);
+                    }
+                    px[i] = o;
+                }
+                if (++x == dw) {  // next destination row
+                    x = 0;
+                    y++;
+                    if (p0 + i + 1 < npix) p = xy[y];
+                }
+            } else {
+                px[i] = 0;
+            }
+        }
+    } else {
+        px[0] = px[1] = px[2] = px[3] = 0;
+    }
+    // pack 4 pixels -> CH words, transpose through shared memory, store coalesced
+    uint32_t wv[CH];
+    if (CH == 1) wv[0] = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+    if (CH == 3) {
+        wv[0] = px[0] | (px[1] << 24);
+        wv[CH > 1 ? 1 : 0] = (px[1] >> 8) | (px[2] << 16);
+        wv[CH > 2 ? 2 : 0] = (px[2] >> 16) | (px[3] << 8);
+    }
+    if (CH == 4) {
+#pragma unroll
+        for (int k = 0; k < CH; k++) wv[k] = px[k & 3];
+    }
+    const long long nwords = (npix * CH + 3) >> 2;
+    const long long wbase = ((long long)blockIdx.x * 256 + warp * 32) * CH;   // first word of this warp
+#pragma unroll
+    for (int k = 0; k < CH; k++) sT[warp][CH * lane + k] = wv[k];
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < CH; k++) {
+        const long long wi = wbase + 32 * k + lane;
+        if (wi < nwords) {
+            const uint32_t v = sT[warp][32 * k + lane];
+            const long long tail = npix * CH - 4 * wi;   // valid bytes of this word (>= 4 except at the very end)
+            if (tail >= 4) dst32[wi] = v;
+            else {
+                uint8_t *d8 = reinterpret_cast<uint8_t *>(dst32 + wi);
+                for (int q = 0; q < (int)tail; q++) d8[q] = (uint8_t)(v >> (8 * q));
+            }
+        }
+    }
+}
+
 int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t sstride, const double Mfwd[6],
                     int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride)
 {
@@ -115,15 +218,34 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
                                                                bd, xy);
     OICS_CUDA_TRY(cudaGetLastError());
     const uchar4 bv = make_uchar4(border[0], border[1], border[2], border[3]);
-    const int aligned = ((reinterpret_cast<uintptr_t>(ddst) | dstride) & 3) == 0;
-    dim3 grid(cdiv(cdiv(dw, 4), 256), dh);
+    const bool lin = interp == OICS_INTER_LINEAR;
+    const bool flat = dstride == (size_t)dw * ch && ((reinterpret_cast<uintptr_t>(ddst) | reinterpret_cast<uintptr_t>(dsrc)) & 3) == 0 &&
+                      (size_t)(h - 1) * sstride + (size_t)w * ch < ((size_t)1 << 34);
+    if (flat) {
+        const long long npix = (long long)dw * dh;
+        const size_t src_bytes = (size_t)(h - 1) * sstride + (size_t)w * ch;
+        const uint32_t last_word = (uint32_t)((src_bytes - 1) >> 2);
+        uint32_t bcol = 0;
+        for (int c = 0; c < ch; c++) bcol |= (uint32_t)border[c] << (8 * c);
+        const unsigned blocks = (unsigned)((npix + 1023) / 1024);
+        const uint32_t *s32 = reinterpret_cast<const uint32_t *>(dsrc);
+        uint32_t *d32 = reinterpret_cast<uint32_t *>(ddst);
+#define OICS_WARPF(CH, LIN) \
+    warp_flat_kernel<CH, LIN><<<blocks, 256, 0, st>>>(s32, w, h, sstride, d32, dw, npix, ad, bd, xy, bcol, last_word)
+        if (ch == 1) { if (lin) OICS_WARPF(1, true); else OICS_WARPF(1, false); }
+        else if (ch == 3) { if (lin) OICS_WARPF(3, true); else OICS_WARPF(3, false); }
+        else { if (lin) OICS_WARPF(4, true); else OICS_WARPF(4, false); }
+#undef OICS_WARPF
+    } else {
+        const int aligned = ((reinterpret_cast<uintptr_t>(ddst) | dstride) & 3) == 0;
+        dim3 grid(cdiv(cdiv(dw, 4), 256), dh);
 #define OICS_WARP(CH, LIN) \
     warp_kernel<CH, LIN><<<grid, 256, 0, st>>>(dsrc, w, h, sstride, ddst, dw, dh, dstride, ad, bd, xy, bv, aligned)
-    const bool lin = interp == OICS_INTER_LINEAR;
-    if (ch == 1) { if (lin) OICS_WARP(1, true); else OICS_WARP(1, false); }
-    else if (ch == 3) { if (lin) OICS_WARP(3, true); else OICS_WARP(3, false); }
-    else { if (lin) OICS_WARP(4, true); else OICS_WARP(4, false); }
+        if (ch == 1) { if (lin) OICS_WARP(1, true); else OICS_WARP(1, false); }
+        else if (ch == 3) { if (lin) OICS_WARP(3, true); else OICS_WARP(3, false); }
+        else { if (lin) OICS_WARP(4, true); else OICS_WARP(4, false); }
 #undef OICS_WARP
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     return OICS_OK;
