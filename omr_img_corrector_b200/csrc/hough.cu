@@ -221,19 +221,7 @@ struct PphtArgs {
     int32_t *lines;       // cap * 4
     int cap;
     int *n_lines;
-};
-
-static constexpr int PP_THREADS = 256;
-static constexpr int PP_WARPS = PP_THREADS / 32;
-
-struct PphtShared {
-    uint32_t live[PP_WARPS];   // ballots
-    uint32_t oob[PP_WARPS];
-    unsigned long long best[PP_WARPS];
-    int list[PP_THREADS];
-    int list_n;
-    int found;                 // generic broadcast slot
-    int end_step;
+    uint32_t *list;       // accepted pixels of the current segment: 2 * max(w, h) + 2 entries
 };
 
 // step t of the walk from (x0, y0) with (dx, dy): pixel (j1, i1)
@@ -244,145 +232,144 @@ __device__ __forceinline__ void walk_pixel(int xflag, int x0, int y0, int dx, in
     else { *j1 = x >> 16; *i1 = y; }
 }
 
-// First walk of one direction: returns (to every thread) the step index of line_end.
-__device__ int ppht_walk_end(const PphtArgs &A, PphtShared &S, int xflag, int x0, int y0, int dx, int dy)
+// cv::HoughLinesProbabilistic, one WARP per image.  The algorithm is sequential by definition
+// (RNG visiting order; every accepted segment erases pixels and votes later points see), so the
+// kernel is latency-bound per image and is built to keep the critical path of one live point
+// short: no block barriers (warp-synchronous), one L2 round trip for the 180 vote atomics (6 per
+// lane, in flight together), both walk directions in the same round trips (16 steps each),
+// pixels cleared as the walk accepts them (plain stores, nothing waits on them), and the
+// still-pending candidates of the 32-point window are re-tested against the accepted segment
+// arithmetically instead of re-reading the mask.
+__global__ void __launch_bounds__(32) ppht_kernel(const PphtArgs A)
 {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int last = 0;  // step 0 is the live start point
-    for (int base = 0;; base += PP_THREADS) {
-        int j1, i1;
-        walk_pixel(xflag, x0, y0, dx, dy, base + tid, &j1, &i1);
-        const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
-        const bool m = inb && __ldcg(A.mask + (size_t)i1 * A.w + j1) != 0;
-        const uint32_t bm = __ballot_sync(0xffffffffu, m), bo = __ballot_sync(0xffffffffu, !inb);
-        if (lane == 0) { S.live[warp] = bm; S.oob[warp] = bo; }
-        __syncthreads();
-        if (tid == 0) {
-            int done = 0;
-            for (int wv = 0; wv < PP_WARPS && !done; wv++) {
-                uint32_t bits = S.live[wv];
-                const uint32_t ob = S.oob[wv];
-                const int first_oob = ob ? __ffs(ob) - 1 : 32;
-                if (first_oob < 32) bits &= (1u << first_oob) - 1u;
-                while (bits) {
-                    const int s = base + wv * 32 + __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    if (s - last > A.line_gap + 1) { done = 1; break; }
-                    last = s;
-                }
-                if (!done && first_oob < 32) done = 1;  // left the image: line_end = last live step
-            }
-            if (!done && (base + PP_THREADS - 1) - last > A.line_gap) done = 1;
-            S.found = done;
-            S.end_step = last;
-        }
-        __syncthreads();
-        const int done = S.found;
-        last = S.end_step;
-        __syncthreads();
-        if (done) return last;
-    }
-}
-
-// Second walk of one direction: steps 0..end; clears live pixels, un-votes them when good.
-__device__ void ppht_walk_erase(const PphtArgs &A, PphtShared &S, int xflag, int x0, int y0, int dx, int dy, int end,
-                                int good)
-{
-    const int tid = threadIdx.x;
+    const int lane = threadIdx.x;
     const int half = (A.numrho - 1) / 2;
-    for (int base = 0; base <= end; base += PP_THREADS) {
-        if (tid == 0) S.list_n = 0;
-        __syncthreads();
-        const int t = base + tid;
-        if (t <= end) {
-            int j1, i1;
-            walk_pixel(xflag, x0, y0, dx, dy, t, &j1, &i1);
-            uint8_t *m = A.mask + (size_t)i1 * A.w + j1;
-            if (__ldcg(m)) {
-                __stcg(m, (uint8_t)0);
-                if (good) S.list[atomicAdd(&S.list_n, 1)] = j1 | (i1 << 16);
-            }
-        }
-        __syncthreads();
-        const int cnt = S.list_n;
-        if (good) {
-            const int total = cnt * A.numangle;
-            for (int k = tid; k < total; k += PP_THREADS) {
-                const int pi = k / A.numangle, n = k - pi * A.numangle;
-                const int p = S.list[pi];
-                const int r = vote_r((float)(p & 0xffff), (float)(p >> 16), A.ttab[2 * n], A.ttab[2 * n + 1], half);
-                atomicSub(A.accum + (size_t)n * A.numrho + r, 1);
-            }
-        }
-        __syncthreads();
+    const int d = lane >> 4, s16 = lane & 15;            // walk direction and step slot of this lane
+    // this lane's thetas: n = lane + 32 k
+    float tc[6], ts[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        const int n = lane + 32 * k;
+        tc[k] = n < A.numangle ? A.ttab[2 * n] : 0.f;
+        ts[k] = n < A.numangle ? A.ttab[2 * n + 1] : 0.f;
     }
-}
-
-__global__ void __launch_bounds__(PP_THREADS) ppht_kernel(const PphtArgs A)
-{
-    __shared__ PphtShared S;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int half = (A.numrho - 1) / 2;
     int nlines = 0;
-    for (int t0 = 0; t0 < A.npts; t0 += PP_THREADS) {
-        const int t = t0 + tid;
+    for (int t0 = 0; t0 < A.npts; t0 += 32) {
+        const int t = t0 + lane;
         const uint32_t p = t < A.npts ? A.seq[t] : 0u;
         const int px = (int)(p & 0xffffu), py = (int)(p >> 16);
-        int after = -1;  // chunk positions <= after are already handled
-        for (;;) {
-            const bool live = t < A.npts && tid > after && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
-            const uint32_t b = __ballot_sync(0xffffffffu, live);
-            if (lane == 0) S.live[warp] = b;
-            __syncthreads();
-            int first = -1;
-#pragma unroll
-            for (int wv = PP_WARPS - 1; wv >= 0; wv--)
-                if (S.live[wv]) first = wv * 32 + __ffs(S.live[wv]) - 1;
-            if (first < 0) { __syncthreads(); break; }
-            if (tid == first) S.found = (int)p;
-            __syncthreads();
-            const int q = S.found;
-            const int j = q & 0xffff, i = q >> 16;
-            after = first;
-            // ---- vote: one thread per theta, first maximal theta wins
+        const bool live0 = t < A.npts && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
+        uint32_t pending = __ballot_sync(0xffffffffu, live0);
+        while (pending) {
+            const int first = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const int j = __shfl_sync(0xffffffffu, px, first), i = __shfl_sync(0xffffffffu, py, first);
+            // ---- vote: first maximal theta wins
             int bv = A.threshold - 1, bn = 0;
-            for (int n = tid; n < A.numangle; n += PP_THREADS) {
-                const int r = vote_r((float)j, (float)i, A.ttab[2 * n], A.ttab[2 * n + 1], half);
-                const int val = atomicAdd(A.accum + (size_t)n * A.numrho + r, 1) + 1;
-                if (bv < val) { bv = val; bn = n; }
+            const float fj = (float)j, fi = (float)i;
+            if (A.numangle <= 192) {
+                // six atomics per lane, all in flight before the first result is consumed
+                // (asm keeps the compiler from funnelling them through one register)
+                int val[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) {
+                    const int n = min(lane + 32 * k, A.numangle - 1);
+                    int32_t *bin = A.accum + (size_t)n * A.numrho + vote_r(fj, fi, tc[k], ts[k], half);
+                    val[k] = -0x40000000;
+                    if (lane + 32 * k < A.numangle)
+                        asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(val[k]) : "l"(bin) : "memory");
+                }
+#pragma unroll
+                for (int k = 0; k < 6; k++)
+                    if (lane + 32 * k < A.numangle && bv < val[k] + 1) { bv = val[k] + 1; bn = lane + 32 * k; }
+            } else {
+                for (int n = lane; n < A.numangle; n += 32) {
+                    const int v = atomicAdd(A.accum + (size_t)n * A.numrho + vote_r(fj, fi, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1) + 1;
+                    if (bv < v) { bv = v; bn = n; }
+                }
             }
             // key: larger value first, then smaller theta index
             unsigned long long key = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) {
-                unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
                 if (other > key) key = other;
             }
-            if (lane == 0) S.best[warp] = key;
-            __syncthreads();
-            key = S.best[0];
-#pragma unroll
-            for (int wv = 1; wv < PP_WARPS; wv++)
-                if (S.best[wv] > key) key = S.best[wv];
             const int max_val = (int)(uint32_t)(key >> 32) - 0x40000000;
             const int max_n = 0x7fffffff - (int)(uint32_t)(key & 0xffffffffu);
-            __syncthreads();
             if (max_val < A.threshold) continue;
-            // ---- walk
-            const int xflag = A.dirs[4 * max_n], dx0 = A.dirs[4 * max_n + 1], dy0 = A.dirs[4 * max_n + 2];
+            // ---- walk both directions at once: lanes 0-15 forwards, 16-31 backwards, 16 steps a round
+            const int xflag = A.dirs[4 * max_n];
+            const int dx = d ? -A.dirs[4 * max_n + 1] : A.dirs[4 * max_n + 1];
+            const int dy = d ? -A.dirs[4 * max_n + 2] : A.dirs[4 * max_n + 2];
             int x0 = j, y0 = i;
             if (xflag) y0 = (y0 << 16) + 32768;
             else x0 = (x0 << 16) + 32768;
-            const int e0 = ppht_walk_end(A, S, xflag, x0, y0, dx0, dy0);
-            const int e1 = ppht_walk_end(A, S, xflag, x0, y0, -dx0, -dy0);
+            int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
+            bool done = false;     // uniform inside each half-warp
+            int nlist = 1;         // accepted pixels recorded so far (uniform); entry 0 = the start pixel
+            if (lane == 0) {
+                __stcg(A.mask + (size_t)i * A.w + j, (uint8_t)0);
+                __stcg(A.list, (uint32_t)j | ((uint32_t)i << 16));
+            }
+            for (int base = 1; __any_sync(0xffffffffu, !done); base += 16) {   // a round = steps base .. base + 15
+                const int st = base + s16;
+                int j1, i1;
+                walk_pixel(xflag, x0, y0, dx, dy, st, &j1, &i1);
+                const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
+                uint8_t *mp = A.mask + (size_t)i1 * A.w + j1;
+                const bool m = !done && inb && __ldcg(mp) != 0;
+                const uint32_t bm_all = __ballot_sync(0xffffffffu, m), bo_all = __ballot_sync(0xffffffffu, !inb);
+                if (!done) {
+                    uint32_t bits = (bm_all >> (16 * d)) & 0xffffu;
+                    const uint32_t ob = (bo_all >> (16 * d)) & 0xffffu;
+                    const int first_oob = ob ? __ffs(ob) - 1 : 16;
+                    if (first_oob < 16) bits &= (1u << first_oob) - 1u;
+                    while (bits) {
+                        const int sb = base + __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        if (sb - last > A.line_gap + 1) { done = true; break; }
+                        last = sb;
+                    }
+                    if (!done && first_oob < 16) done = true;      // left the image: line_end = last live step
+                    if (!done && (base + 15) - last > A.line_gap) done = true;
+                }
+                // clear what this round accepted (cv clears every live pixel of [0, line_end])
+                const bool acc = m && st <= last;
+                if (acc) __stcg(mp, (uint8_t)0);
+                const uint32_t ba = __ballot_sync(0xffffffffu, acc);
+                if (acc) __stcg(A.list + nlist + __popc(ba & ((1u << lane) - 1u)), (uint32_t)j1 | ((uint32_t)i1 << 16));
+                nlist += __popc(ba);
+            }
+            const int e0 = __shfl_sync(0xffffffffu, last, 0), e1 = __shfl_sync(0xffffffffu, last, 16);
+            const int dxf = __shfl_sync(0xffffffffu, dx, 0), dyf = __shfl_sync(0xffffffffu, dy, 0);
             int ax, ay, bx, by;
-            walk_pixel(xflag, x0, y0, dx0, dy0, e0, &ax, &ay);
-            walk_pixel(xflag, x0, y0, -dx0, -dy0, e1, &bx, &by);
-            const int good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
-            ppht_walk_erase(A, S, xflag, x0, y0, dx0, dy0, e0, good);
-            ppht_walk_erase(A, S, xflag, x0, y0, -dx0, -dy0, e1, good);
+            walk_pixel(xflag, x0, y0, dxf, dyf, e0, &ax, &ay);
+            walk_pixel(xflag, x0, y0, -dxf, -dyf, e1, &bx, &by);
+            const bool good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
+            // pending candidates of this window that sat on the accepted segment are dead now
+            {
+                bool dead = false;
+                if ((pending >> lane) & 1u) {
+                    const int tt = xflag ? (px - j) * dxf : (py - i) * dyf;   // dxf (dyf) is +-1 on the major axis
+                    int cj, ci;
+                    walk_pixel(xflag, x0, y0, dxf, dyf, tt, &cj, &ci);
+                    dead = cj == px && ci == py && tt <= e0 && -tt <= e1;
+                }
+                pending &= ~__ballot_sync(0xffffffffu, dead);
+            }
             if (good) {
-                if (tid == 0 && nlines < A.cap) {
+                __syncwarp();
+                __threadfence();   // the list writes above are read back by other lanes
+                const int total = nlist * A.numangle;
+                for (int k = lane; k < total; k += 32) {
+                    const int pi = k / A.numangle, n = k - pi * A.numangle;
+                    const uint32_t q = __ldcg(A.list + pi);
+                    const int r = vote_r((float)(q & 0xffffu), (float)(q >> 16), A.ttab[2 * n], A.ttab[2 * n + 1], half);
+                    atomicSub(A.accum + (size_t)n * A.numrho + r, 1);
+                }
+                __threadfence();
+                if (lane == 0 && nlines < A.cap) {
                     A.lines[4 * nlines + 0] = ax;
                     A.lines[4 * nlines + 1] = ay;
                     A.lines[4 * nlines + 2] = bx;
@@ -390,9 +377,10 @@ __global__ void __launch_bounds__(PP_THREADS) ppht_kernel(const PphtArgs A)
                 }
                 nlines++;
             }
+            __syncwarp();
         }
     }
-    if (tid == 0) *A.n_lines = nlines;
+    if (lane == 0) *A.n_lines = nlines;
 }
 
 // The visiting order of cv::HoughLinesProbabilistic for n points: count = n..1,
@@ -458,7 +446,8 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     const size_t off_nl = off_dirs + sizeof(int) * dirs.size();
     const size_t off_lines = off_nl + 16;
     const int dcap = std::max(cap, 1);
-    OICS_TRY(ctx->misc.ensure(off_lines + sizeof(int32_t) * 4 * (size_t)dcap));
+    const size_t off_list = off_lines + sizeof(int32_t) * 4 * (size_t)dcap;
+    OICS_TRY(ctx->misc.ensure(off_list + sizeof(uint32_t) * (2 * (size_t)std::max(w, h) + 2)));
     uint8_t *base = ctx->misc.as<uint8_t>();
     OICS_CUDA_TRY(cudaMemcpyAsync(base, order.data(), sizeof(int) * (size_t)npts, cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(base + off_ttab, ttab.data(), sizeof(float) * ttab.size(), cudaMemcpyHostToDevice, st));
@@ -479,7 +468,8 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     A.lines = reinterpret_cast<int32_t *>(base + off_lines);
     A.cap = cap;
     A.n_lines = reinterpret_cast<int *>(base + off_nl);
-    ppht_kernel<<<1, PP_THREADS, 0, st>>>(A);
+    A.list = reinterpret_cast<uint32_t *>(base + off_list);
+    ppht_kernel<<<1, 32, 0, st>>>(A);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     int n = 0;
