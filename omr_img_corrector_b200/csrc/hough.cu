@@ -12,11 +12,14 @@
 //          with (uint64)-1, swap-remove), not on the image: the host expands it from N and
 //          a gather kernel lays the points out in visiting order, so the CTA streams them
 //          and tests 256 upcoming points per L2 round trip;
-//        * a live point votes with one thread per theta (atomicAdd with return) and a block
-//          arg-max that keeps the first maximal theta, like the sequential `max_val < val`;
-//        * the two line walks test 256 steps per round trip; gap logic runs on ballots;
-//        * the erase pass clears the mask and, for accepted segments, un-votes every erased
-//          pixel with (pixel, theta) pairs spread over the CTA.
+//        * the next four live points are processed speculatively at once: all vote in one L2
+//          round trip (one thread per theta, atomics issued in visiting order, so each point
+//          sees exactly the sequential counts), one warp walks each point read-only, and the
+//          results commit in visiting order; a point that an earlier commit could have
+//          influenced is rolled back (its votes subtracted) and retried;
+//        * the arg-max keeps the first maximal theta, like the sequential `max_val < val`;
+//        * the two line walks test 16 steps each per round trip; gap logic runs on ballots;
+//        * a commit clears the step range and, for accepted segments, un-votes its live pixels.
 //      Latency-bound per image (like the CPU), throughput comes from images in flight.
 #include <algorithm>
 #include <cmath>
@@ -232,155 +235,308 @@ __device__ __forceinline__ void walk_pixel(int xflag, int x0, int y0, int dx, in
     else { *j1 = x >> 16; *i1 = y; }
 }
 
-// cv::HoughLinesProbabilistic, one WARP per image.  The algorithm is sequential by definition
-// (RNG visiting order; every accepted segment erases pixels and votes later points see), so the
-// kernel is latency-bound per image and is built to keep the critical path of one live point
-// short: no block barriers (warp-synchronous), one L2 round trip for the 180 vote atomics (6 per
-// lane, in flight together), both walk directions in the same round trips (16 steps each),
-// pixels cleared as the walk accepts them (plain stores, nothing waits on them), and the
-// still-pending candidates of the 32-point window are re-tested against the accepted segment
-// arithmetically instead of re-reading the mask.
-__global__ void __launch_bounds__(32) ppht_kernel(const PphtArgs A)
+// cv::HoughLinesProbabilistic, one CTA of PPHT_K warps per image, PPHT_K points in flight.
+//
+// The algorithm is sequential by definition (RNG visiting order; every accepted segment erases
+// pixels and votes that later points see), so one image is latency-bound: a live point costs one
+// L2 round trip for its 180 vote atomics plus one per 16 walk steps.  The kernel keeps the exact
+// sequential semantics and hides that latency by SPECULATING on the next PPHT_K live points:
+//   vote    all points of the group vote in one round trip.  Theta n is always voted (and later
+//           un-voted) by the same thread, and a thread issues its atomics in visiting order, so
+//           same-address ordering gives every point exactly the counts the sequential loop
+//           would have seen (the earlier points of the group included, the later ones not);
+//   walk    warp q walks point q in both directions, READ-ONLY (no pixel is cleared while any
+//           walk of the group is in flight);
+//   commit  in visiting order, uniformly on every warp: a point commits if no earlier segment
+//           of the group erased it and its scanned path cannot meet an earlier erased range
+//           (bounding boxes); committing clears the whole step range [-e1, e0] (cv clears the
+//           live pixels of it, the others are zero already) and kills the pending candidates
+//           that sat on it.  The first point that fails, and everything after it, is rolled
+//           back: speculative state is votes only, they are subtracted by the threads that added
+//           them, and the points return to the pending set.  An accepted ("good") segment
+//           un-votes its pixels, so it also ends the group.  The first point of a group always
+//           commits, so every group makes progress.
+constexpr int PPHT_K = 4;
+constexpr int PPHT_THREADS = 32 * PPHT_K;
+constexpr int PPHT_NT = 2;    // thetas per thread held in registers (numangle <= 256)
+
+struct PphtSeg { int xflag, x0, y0, dx, dy, e0, e1; };   // (dx, dy) = forward direction
+
+__device__ __forceinline__ void seg_box(const PphtSeg &s, int a, int b, int *bx0, int *by0, int *bx1, int *by1)
 {
-    const int lane = threadIdx.x;
+    int ax, ay, cx, cy;
+    walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, a, &ax, &ay);
+    walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, -b, &cx, &cy);
+    *bx0 = min(ax, cx) - 1; *bx1 = max(ax, cx) + 1;
+    *by0 = min(ay, cy) - 1; *by1 = max(ay, cy) + 1;
+}
+
+__global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
+{
+    __shared__ unsigned long long sKey[PPHT_K][PPHT_K];   // [warp][point] partial arg-max keys
+    __shared__ int sRes[PPHT_K][2];                       // [point] last accepted step forwards / backwards
+    __shared__ uint32_t sList[2 * PPHT_THREADS];          // accepted-segment pixels, one chunk
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int half = (A.numrho - 1) / 2;
     const int d = lane >> 4, s16 = lane & 15;            // walk direction and step slot of this lane
-    // this lane's thetas: n = lane + 32 k
-    float tc[6], ts[6];
+    const int nth = (A.numangle + PPHT_THREADS - 1) / PPHT_THREADS;   // thetas per thread: n = tid + 128 k
+    float tc[PPHT_NT], ts[PPHT_NT];
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
-        const int n = lane + 32 * k;
+    for (int k = 0; k < PPHT_NT; k++) {
+        const int n = tid + PPHT_THREADS * k;
         tc[k] = n < A.numangle ? A.ttab[2 * n] : 0.f;
         ts[k] = n < A.numangle ? A.ttab[2 * n + 1] : 0.f;
     }
     int nlines = 0;
+    uint32_t pnext = lane < A.npts ? A.seq[lane] : 0u;
     for (int t0 = 0; t0 < A.npts; t0 += 32) {
+        // every warp holds the same 32-point window (lane = point); the next one is prefetched
         const int t = t0 + lane;
-        const uint32_t p = t < A.npts ? A.seq[t] : 0u;
+        const uint32_t p = pnext;
+        pnext = t + 32 < A.npts ? A.seq[t + 32] : 0u;
         const int px = (int)(p & 0xffffu), py = (int)(p >> 16);
         const bool live0 = t < A.npts && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
         uint32_t pending = __ballot_sync(0xffffffffu, live0);
         while (pending) {
-            const int first = __ffs(pending) - 1;
-            pending &= pending - 1;
-            const int j = __shfl_sync(0xffffffffu, px, first), i = __shfl_sync(0xffffffffu, py, first);
-            // ---- vote: first maximal theta wins
-            int bv = A.threshold - 1, bn = 0;
-            const float fj = (float)j, fi = (float)i;
-            if (A.numangle <= 192) {
-                // six atomics per lane, all in flight before the first result is consumed
-                // (asm keeps the compiler from funnelling them through one register)
-                int val[6];
+            // ---- the group: the next PPHT_K pending points in visiting order
+            int gi[PPHT_K], gx[PPHT_K], gy[PPHT_K], gn = 0;
+            {
+                uint32_t rest = pending;
 #pragma unroll
-                for (int k = 0; k < 6; k++) {
-                    const int n = min(lane + 32 * k, A.numangle - 1);
-                    int32_t *bin = A.accum + (size_t)n * A.numrho + vote_r(fj, fi, tc[k], ts[k], half);
-                    val[k] = -0x40000000;
-                    if (lane + 32 * k < A.numangle)
-                        asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(val[k]) : "l"(bin) : "memory");
+                for (int q = 0; q < PPHT_K; q++) {
+                    gi[q] = rest ? __ffs(rest) - 1 : 0;
+                    if (rest) gn = q + 1;
+                    rest &= rest - 1;
+                    gx[q] = __shfl_sync(0xffffffffu, px, gi[q]);
+                    gy[q] = __shfl_sync(0xffffffffu, py, gi[q]);
+                }
+            }
+            // ---- vote: first maximal theta wins
+            unsigned long long key[PPHT_K];
+            if (nth <= PPHT_NT) {
+                int val[PPHT_K][PPHT_NT];
+#pragma unroll
+                for (int q = 0; q < PPHT_K; q++) {
+#pragma unroll
+                    for (int k = 0; k < PPHT_NT; k++) {
+                        const int n = tid + PPHT_THREADS * k;
+                        val[q][k] = -0x40000000;
+                        if (q < gn && n < A.numangle) {
+                            int32_t *bin = A.accum + (size_t)n * A.numrho + vote_r((float)gx[q], (float)gy[q], tc[k], ts[k], half);
+                            asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(val[q][k]) : "l"(bin) : "memory");
+                        }
+                    }
                 }
 #pragma unroll
-                for (int k = 0; k < 6; k++)
-                    if (lane + 32 * k < A.numangle && bv < val[k] + 1) { bv = val[k] + 1; bn = lane + 32 * k; }
+                for (int q = 0; q < PPHT_K; q++) {
+                    int bv = A.threshold - 1, bn = 0;
+#pragma unroll
+                    for (int k = 0; k < PPHT_NT; k++) {
+                        const int n = tid + PPHT_THREADS * k;
+                        if (n < A.numangle && bv < val[q][k] + 1) { bv = val[q][k] + 1; bn = n; }
+                    }
+                    key[q] = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
+                }
             } else {
-                for (int n = lane; n < A.numangle; n += 32) {
-                    const int v = atomicAdd(A.accum + (size_t)n * A.numrho + vote_r(fj, fi, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1) + 1;
-                    if (bv < v) { bv = v; bn = n; }
+#pragma unroll
+                for (int q = 0; q < PPHT_K; q++) {
+                    int bv = A.threshold - 1, bn = 0;
+                    if (q < gn)
+                        for (int n = tid; n < A.numangle; n += PPHT_THREADS) {
+                            const int v = atomicAdd(A.accum + (size_t)n * A.numrho +
+                                                    vote_r((float)gx[q], (float)gy[q], A.ttab[2 * n], A.ttab[2 * n + 1], half), 1) + 1;
+                            if (bv < v) { bv = v; bn = n; }
+                        }
+                    key[q] = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
                 }
             }
             // key: larger value first, then smaller theta index
-            unsigned long long key = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) {
-                const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
-                if (other > key) key = other;
+#pragma unroll
+                for (int q = 0; q < PPHT_K; q++) {
+                    const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[q], o);
+                    if (other > key[q]) key[q] = other;
+                }
             }
-            const int max_val = (int)(uint32_t)(key >> 32) - 0x40000000;
-            const int max_n = 0x7fffffff - (int)(uint32_t)(key & 0xffffffffu);
-            if (max_val < A.threshold) continue;
-            // ---- walk both directions at once: lanes 0-15 forwards, 16-31 backwards, 16 steps a round
-            const int xflag = A.dirs[4 * max_n];
-            const int dx = d ? -A.dirs[4 * max_n + 1] : A.dirs[4 * max_n + 1];
-            const int dy = d ? -A.dirs[4 * max_n + 2] : A.dirs[4 * max_n + 2];
-            int x0 = j, y0 = i;
-            if (xflag) y0 = (y0 << 16) + 32768;
-            else x0 = (x0 << 16) + 32768;
-            int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
-            bool done = false;     // uniform inside each half-warp
-            int nlist = 1;         // accepted pixels recorded so far (uniform); entry 0 = the start pixel
             if (lane == 0) {
-                __stcg(A.mask + (size_t)i * A.w + j, (uint8_t)0);
-                __stcg(A.list, (uint32_t)j | ((uint32_t)i << 16));
+#pragma unroll
+                for (int q = 0; q < PPHT_K; q++) sKey[warp][q] = key[q];
             }
-            for (int base = 1; __any_sync(0xffffffffu, !done); base += 16) {   // a round = steps base .. base + 15
-                const int st = base + s16;
-                int j1, i1;
-                walk_pixel(xflag, x0, y0, dx, dy, st, &j1, &i1);
-                const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
-                uint8_t *mp = A.mask + (size_t)i1 * A.w + j1;
-                const bool m = !done && inb && __ldcg(mp) != 0;
-                const uint32_t bm_all = __ballot_sync(0xffffffffu, m), bo_all = __ballot_sync(0xffffffffu, !inb);
-                if (!done) {
-                    uint32_t bits = (bm_all >> (16 * d)) & 0xffffu;
-                    const uint32_t ob = (bo_all >> (16 * d)) & 0xffffu;
-                    const int first_oob = ob ? __ffs(ob) - 1 : 16;
-                    if (first_oob < 16) bits &= (1u << first_oob) - 1u;
-                    while (bits) {
-                        const int sb = base + __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        if (sb - last > A.line_gap + 1) { done = true; break; }
-                        last = sb;
+            __syncthreads();
+            int mval[PPHT_K], mn[PPHT_K];
+#pragma unroll
+            for (int q = 0; q < PPHT_K; q++) {
+                unsigned long long kq = sKey[0][q];
+#pragma unroll
+                for (int w2 = 1; w2 < PPHT_K; w2++) kq = sKey[w2][q] > kq ? sKey[w2][q] : kq;
+                mval[q] = (int)(uint32_t)(kq >> 32) - 0x40000000;
+                mn[q] = 0x7fffffff - (int)(uint32_t)(kq & 0xffffffffu);
+            }
+            // ---- walk: warp q walks point q, both directions at once (lanes 0-15 forwards,
+            // 16-31 backwards, 16 steps a round), reading only
+            PphtSeg seg[PPHT_K];
+#pragma unroll
+            for (int q = 0; q < PPHT_K; q++) {
+                const int4 dr = *reinterpret_cast<const int4 *>(A.dirs + 4 * mn[q]);
+                seg[q].xflag = dr.x; seg[q].dx = dr.y; seg[q].dy = dr.z;
+                seg[q].x0 = dr.x ? gx[q] : (gx[q] << 16) + 32768;
+                seg[q].y0 = dr.x ? (gy[q] << 16) + 32768 : gy[q];
+                seg[q].e0 = seg[q].e1 = 0;
+            }
+#pragma unroll
+            for (int q = 0; q < PPHT_K; q++) {
+                if (q == warp && q < gn && mval[q] >= A.threshold) {
+                    const int dx = d ? -seg[q].dx : seg[q].dx, dy = d ? -seg[q].dy : seg[q].dy;
+                    int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
+                    bool done = false;     // uniform inside each half-warp
+                    for (int base = 1; __any_sync(0xffffffffu, !done); base += 16) {   // a round = steps base .. base + 15
+                        const int st = base + s16;
+                        int j1, i1;
+                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, st, &j1, &i1);
+                        const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
+                        const bool m = !done && inb && __ldcg(A.mask + (size_t)i1 * A.w + j1) != 0;
+                        const uint32_t bm_all = __ballot_sync(0xffffffffu, m), bo_all = __ballot_sync(0xffffffffu, !inb);
+                        if (!done) {
+                            uint32_t bits = (bm_all >> (16 * d)) & 0xffffu;
+                            const uint32_t ob = (bo_all >> (16 * d)) & 0xffffu;
+                            const int first_oob = ob ? __ffs(ob) - 1 : 16;
+                            if (first_oob < 16) bits &= (1u << first_oob) - 1u;
+                            while (bits) {
+                                const int sb = base + __ffs(bits) - 1;
+                                bits &= bits - 1;
+                                if (sb - last > A.line_gap + 1) { done = true; break; }
+                                last = sb;
+                            }
+                            if (!done && first_oob < 16) done = true;      // left the image: line_end = last live step
+                            if (!done && (base + 15) - last > A.line_gap) done = true;
+                        }
                     }
-                    if (!done && first_oob < 16) done = true;      // left the image: line_end = last live step
-                    if (!done && (base + 15) - last > A.line_gap) done = true;
+                    if (s16 == 0) sRes[q][d] = last;
                 }
-                // clear what this round accepted (cv clears every live pixel of [0, line_end])
-                const bool acc = m && st <= last;
-                if (acc) __stcg(mp, (uint8_t)0);
-                const uint32_t ba = __ballot_sync(0xffffffffu, acc);
-                if (acc) __stcg(A.list + nlist + __popc(ba & ((1u << lane) - 1u)), (uint32_t)j1 | ((uint32_t)i1 << 16));
-                nlist += __popc(ba);
             }
-            const int e0 = __shfl_sync(0xffffffffu, last, 0), e1 = __shfl_sync(0xffffffffu, last, 16);
-            const int dxf = __shfl_sync(0xffffffffu, dx, 0), dyf = __shfl_sync(0xffffffffu, dy, 0);
-            int ax, ay, bx, by;
-            walk_pixel(xflag, x0, y0, dxf, dyf, e0, &ax, &ay);
-            walk_pixel(xflag, x0, y0, -dxf, -dyf, e1, &bx, &by);
-            const bool good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
-            // pending candidates of this window that sat on the accepted segment are dead now
-            {
-                bool dead = false;
-                if ((pending >> lane) & 1u) {
-                    const int tt = xflag ? (px - j) * dxf : (py - i) * dyf;   // dxf (dyf) is +-1 on the major axis
-                    int cj, ci;
-                    walk_pixel(xflag, x0, y0, dxf, dyf, tt, &cj, &ci);
-                    dead = cj == px && ci == py && tt <= e0 && -tt <= e1;
+            __syncthreads();
+            // ---- commit in visiting order (every warp runs this identically)
+            int cbox[PPHT_K][4], ncommit = 0;    // erased ranges of the segments committed in this group
+            int undo_from = gn;
+#pragma unroll
+            for (int q = 0; q < PPHT_K; q++) {
+                if (q < gn && q < undo_from) {
+                    const uint32_t bit = 1u << gi[q];
+                    const bool walked = mval[q] >= A.threshold;
+                    bool ok = (pending & bit) != 0;          // else an earlier segment of the group erased it
+                    if (ok && walked) {
+                        seg[q].e0 = sRes[q][0];
+                        seg[q].e1 = sRes[q][1];
+                        // every pixel the walk looked at lies within line_gap + 1 steps of its ends
+                        int bx0, by0, bx1, by1;
+                        seg_box(seg[q], seg[q].e0 + A.line_gap + 1, seg[q].e1 + A.line_gap + 1, &bx0, &by0, &bx1, &by1);
+#pragma unroll
+                        for (int c = 0; c < PPHT_K; c++)
+                            if (c < ncommit && bx0 <= cbox[c][2] && cbox[c][0] <= bx1 && by0 <= cbox[c][3] && cbox[c][1] <= by1)
+                                ok = false;                  // may have read a pixel erased since: walk again
+                    }
+                    if (!ok) {
+                        undo_from = q;
+                    } else {
+                        pending &= ~bit;
+                        if (walked) {
+                            const PphtSeg s = seg[q];
+                            int ax, ay, bx, by;
+                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, s.e0, &ax, &ay);
+                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, -s.e1, &bx, &by);
+                            const bool good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
+                            const int len = s.e0 + s.e1 + 1;
+                            if (good) {
+                                // un-vote the live pixels of [-e1, e0]; theta n stays with its thread
+                                for (int c0 = 0; c0 < len; c0 += 2 * PPHT_THREADS) {
+#pragma unroll
+                                    for (int u = 0; u < 2; u++) {
+                                        const int idx = c0 + tid + PPHT_THREADS * u;
+                                        uint32_t e = 0xffffffffu;
+                                        if (idx < len) {
+                                            int j1, i1;
+                                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, idx - s.e1, &j1, &i1);
+                                            if (__ldcg(A.mask + (size_t)i1 * A.w + j1) != 0) e = (uint32_t)j1 | ((uint32_t)i1 << 16);
+                                        }
+                                        sList[tid + PPHT_THREADS * u] = e;
+                                    }
+                                    __syncthreads();
+                                    const int cn = min(2 * PPHT_THREADS, len - c0);
+                                    for (int i = 0; i < cn; i++) {
+                                        const uint32_t e = sList[i];
+                                        if (e == 0xffffffffu) continue;
+                                        const float fx = (float)(e & 0xffffu), fy = (float)(e >> 16);
+                                        if (nth <= PPHT_NT) {
+#pragma unroll
+                                            for (int k = 0; k < PPHT_NT; k++) {
+                                                const int n = tid + PPHT_THREADS * k;
+                                                if (n < A.numangle)
+                                                    atomicSub(A.accum + (size_t)n * A.numrho + vote_r(fx, fy, tc[k], ts[k], half), 1);
+                                            }
+                                        } else {
+                                            for (int n = tid; n < A.numangle; n += PPHT_THREADS)
+                                                atomicSub(A.accum + (size_t)n * A.numrho + vote_r(fx, fy, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
+                                        }
+                                    }
+                                    __syncthreads();
+                                }
+                                if (tid == 0 && nlines < A.cap) {
+                                    A.lines[4 * nlines + 0] = ax;
+                                    A.lines[4 * nlines + 1] = ay;
+                                    A.lines[4 * nlines + 2] = bx;
+                                    A.lines[4 * nlines + 3] = by;
+                                }
+                                nlines++;
+                                undo_from = q + 1;           // the counts later points saw are stale now
+                            }
+                            // erase the range (cv clears its live pixels; the others are zero already)
+                            for (int idx = tid; idx < len; idx += PPHT_THREADS) {
+                                int j1, i1;
+                                walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, idx - s.e1, &j1, &i1);
+                                __stcg(A.mask + (size_t)i1 * A.w + j1, (uint8_t)0);
+                            }
+                            // pending candidates of this window that sat on the range are dead now
+                            {
+                                bool dead = false;
+                                if ((pending >> lane) & 1u) {
+                                    const int tt = s.xflag ? (px - gx[q]) * s.dx : (py - gy[q]) * s.dy;   // +-1 on the major axis
+                                    int cj, ci;
+                                    walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, tt, &cj, &ci);
+                                    dead = cj == px && ci == py && tt <= s.e0 && -tt <= s.e1;
+                                }
+                                pending &= ~__ballot_sync(0xffffffffu, dead);
+                            }
+                            seg_box(s, s.e0, s.e1, &cbox[ncommit][0], &cbox[ncommit][1], &cbox[ncommit][2], &cbox[ncommit][3]);
+                            ncommit++;
+                        }
+                    }
                 }
-                pending &= ~__ballot_sync(0xffffffffu, dead);
             }
-            if (good) {
-                __syncwarp();
-                __threadfence();   // the list writes above are read back by other lanes
-                const int total = nlist * A.numangle;
-                for (int k = lane; k < total; k += 32) {
-                    const int pi = k / A.numangle, n = k - pi * A.numangle;
-                    const uint32_t q = __ldcg(A.list + pi);
-                    const int r = vote_r((float)(q & 0xffffu), (float)(q >> 16), A.ttab[2 * n], A.ttab[2 * n + 1], half);
-                    atomicSub(A.accum + (size_t)n * A.numrho + r, 1);
+            // ---- roll back the votes of the points that did not commit (same thread, same bins)
+#pragma unroll
+            for (int q = 0; q < PPHT_K; q++) {
+                if (q >= undo_from && q < gn) {
+                    if (nth <= PPHT_NT) {
+#pragma unroll
+                        for (int k = 0; k < PPHT_NT; k++) {
+                            const int n = tid + PPHT_THREADS * k;
+                            if (n < A.numangle)
+                                atomicSub(A.accum + (size_t)n * A.numrho + vote_r((float)gx[q], (float)gy[q], tc[k], ts[k], half), 1);
+                        }
+                    } else {
+                        for (int n = tid; n < A.numangle; n += PPHT_THREADS)
+                            atomicSub(A.accum + (size_t)n * A.numrho +
+                                      vote_r((float)gx[q], (float)gy[q], A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
+                    }
                 }
-                __threadfence();
-                if (lane == 0 && nlines < A.cap) {
-                    A.lines[4 * nlines + 0] = ax;
-                    A.lines[4 * nlines + 1] = ay;
-                    A.lines[4 * nlines + 2] = bx;
-                    A.lines[4 * nlines + 3] = by;
-                }
-                nlines++;
             }
-            __syncwarp();
         }
+        // bar.sync orders this window's erasing stores (st.cg) before the next window's liveness loads (ld.cg)
+        __syncthreads();
     }
-    if (lane == 0) *A.n_lines = nlines;
+    if (tid == 0) *A.n_lines = nlines;
 }
 
 // The visiting order of cv::HoughLinesProbabilistic for n points: count = n..1,
@@ -441,8 +597,8 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     OICS_TRY(ctx->accum.ensure(acc_bytes));
     // misc: [order npts][seq npts][ttab][dirs][n_lines][lines cap*4]
     const size_t off_seq = sizeof(int) * (size_t)npts;
-    const size_t off_ttab = off_seq + sizeof(uint32_t) * (size_t)npts;
-    const size_t off_dirs = off_ttab + sizeof(float) * ttab.size();
+    const size_t off_ttab = (off_seq + sizeof(uint32_t) * (size_t)npts + 15) & ~(size_t)15;
+    const size_t off_dirs = (off_ttab + sizeof(float) * ttab.size() + 15) & ~(size_t)15;   // int4 loads
     const size_t off_nl = off_dirs + sizeof(int) * dirs.size();
     const size_t off_lines = off_nl + 16;
     const int dcap = std::max(cap, 1);
@@ -469,7 +625,7 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     A.cap = cap;
     A.n_lines = reinterpret_cast<int *>(base + off_nl);
     A.list = reinterpret_cast<uint32_t *>(base + off_list);
-    ppht_kernel<<<1, 32, 0, st>>>(A);
+    ppht_kernel<<<1, PPHT_THREADS, 0, st>>>(A);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     int n = 0;
