@@ -18,7 +18,7 @@
 //          results commit in visiting order; a point that an earlier commit could have
 //          influenced is rolled back (its votes subtracted) and retried;
 //        * the arg-max keeps the first maximal theta, like the sequential `max_val < val`;
-//        * the two line walks test 16 steps each per round trip; gap logic runs on ballots;
+//        * the two line walks test 32 steps each per round trip; gap logic runs on ballots;
 //        * a commit clears the step range and, for accepted segments, un-votes its live pixels.
 //      Latency-bound per image (like the CPU), throughput comes from images in flight.
 #include <algorithm>
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
                 mn[q] = 0x7fffffff - (int)(uint32_t)(kq & 0xffffffffu);
             }
             // ---- walk: warp q walks point q, both directions at once (lanes 0-15 forwards,
-            // 16-31 backwards, 16 steps a round), reading only
+            // 16-31 backwards, 32 steps a round), reading only
             PphtSeg seg[PPHT_K];
 #pragma unroll
             for (int q = 0; q < PPHT_K; q++) {
@@ -391,26 +391,31 @@ __global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
                     const int dx = d ? -seg[q].dx : seg[q].dx, dy = d ? -seg[q].dy : seg[q].dy;
                     int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
                     bool done = false;     // uniform inside each half-warp
-                    for (int base = 1; __any_sync(0xffffffffu, !done); base += 16) {   // a round = steps base .. base + 15
-                        const int st = base + s16;
-                        int j1, i1;
-                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, st, &j1, &i1);
-                        const bool inb = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
-                        const bool m = !done && inb && __ldcg(A.mask + (size_t)i1 * A.w + j1) != 0;
-                        const uint32_t bm_all = __ballot_sync(0xffffffffu, m), bo_all = __ballot_sync(0xffffffffu, !inb);
+                    for (int base = 1; __any_sync(0xffffffffu, !done); base += 32) {   // a round = steps base .. base + 31
+                        // two loads per lane in flight: steps base + s16 and base + 16 + s16
+                        int ja, ia, jb, ib;
+                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, base + s16, &ja, &ia);
+                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, base + 16 + s16, &jb, &ib);
+                        const bool inba = ja >= 0 && ja < A.w && ia >= 0 && ia < A.h;
+                        const bool inbb = jb >= 0 && jb < A.w && ib >= 0 && ib < A.h;
+                        uint8_t va = 0, vb = 0;
+                        if (!done && inba) va = __ldcg(A.mask + (size_t)ia * A.w + ja);
+                        if (!done && inbb) vb = __ldcg(A.mask + (size_t)ib * A.w + jb);
+                        const uint32_t bma = __ballot_sync(0xffffffffu, va != 0), bmb = __ballot_sync(0xffffffffu, vb != 0);
+                        const uint32_t boa = __ballot_sync(0xffffffffu, !inba), bob = __ballot_sync(0xffffffffu, !inbb);
                         if (!done) {
-                            uint32_t bits = (bm_all >> (16 * d)) & 0xffffu;
-                            const uint32_t ob = (bo_all >> (16 * d)) & 0xffffu;
-                            const int first_oob = ob ? __ffs(ob) - 1 : 16;
-                            if (first_oob < 16) bits &= (1u << first_oob) - 1u;
+                            uint32_t bits = ((bma >> (16 * d)) & 0xffffu) | (((bmb >> (16 * d)) & 0xffffu) << 16);
+                            const uint32_t ob = ((boa >> (16 * d)) & 0xffffu) | (((bob >> (16 * d)) & 0xffffu) << 16);
+                            const int first_oob = ob ? __ffs(ob) - 1 : 32;
+                            if (first_oob < 32) bits &= (1u << first_oob) - 1u;
                             while (bits) {
                                 const int sb = base + __ffs(bits) - 1;
                                 bits &= bits - 1;
                                 if (sb - last > A.line_gap + 1) { done = true; break; }
                                 last = sb;
                             }
-                            if (!done && first_oob < 16) done = true;      // left the image: line_end = last live step
-                            if (!done && (base + 15) - last > A.line_gap) done = true;
+                            if (!done && first_oob < 32) done = true;      // left the image: line_end = last live step
+                            if (!done && (base + 31) - last > A.line_gap) done = true;
                         }
                     }
                     if (s16 == 0) sRes[q][d] = last;
