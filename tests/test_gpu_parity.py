@@ -431,3 +431,23 @@ def test_correct_batch_pipeline_equals_one_by_one(ctx, orc, dataset_like):
     for i in range(3):
         dw, dh = z2[i]
         assert np.array_equal(douts[i][:dw * dh * 3].cpu().numpy(), outs[i][:dw * dh * 3])
+
+
+# ----------------------------------------------------------------------------- N4: the reference's acceptance run
+def test_accuracy_regression_operating_point(ctx, orc):
+    """lib.rs:131-245 in miniature: skews over +-45 degrees, correct_default with the test's parameter
+    tuple (45, 0.2, 248, 230, 150, 50) through the batch driver; (angle, need_check) must equal the
+    oracle's on every input and most inputs must land in the test's SUCCESS class (< 0.4 degrees)."""
+    g, _ = synth.base_card(100)
+    base = synth.to_bgr(np.ascontiguousarray(g[200:1350, 100:1340]))
+    skews = [-44.0 + 5.5 * i for i in range(17)]
+    cards = np.stack([orc.rotate_mat(base, -a, 1.0, 1, orc.WHITE, 0) for a in skews])
+    params = (45, 0.2, 248, 230, 150.0, 50.0)
+    ang, need, stat, _ = ctx.correct_batch(cards, *params)
+    assert not stat.any()
+    ok = 0
+    for i, a in enumerate(skews):
+        ra, rneed, _ = orc.correct_default(cards[i], *params)
+        assert (float(ang[i]), bool(need[i])) == (ra, bool(rneed)), (a, ang[i], need[i], ra, rneed)
+        ok += (not need[i]) and abs(a - ang[i]) <= 0.4
+    assert ok >= 13
