@@ -6,3 +6,4 @@ timeout 600 python tools/configs_bench.py > gpurun_out/configs.json 2> gpurun_ou
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__cycles_elapsed.max --clock-control none -c 3000 --csv --log-file gpurun_out/launches_configs.csv python tools/configs_bench.py > gpurun_out/ncu_cfg.log 2>&1
 echo "ncu rc=$?"
 python tools/launch_shares.py gpurun_out/launches_configs.csv
+python tools/kernel_rooflines.py gpurun_out/launches_configs.csv gpurun_out/kernel_rooflines.json
