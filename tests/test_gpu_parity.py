@@ -451,3 +451,21 @@ def test_accuracy_regression_operating_point(ctx, orc):
         assert (float(ang[i]), bool(need[i])) == (ra, bool(rneed)), (a, ang[i], need[i], ra, rneed)
         ok += (not need[i]) and abs(a - ang[i]) <= 0.4
     assert ok >= 13
+
+
+# ----------------------------------------------------------------------------- config 5 at full size
+def test_sweep_config5_full_size(ctx, orc, a4_card):
+    """BASELINE config 5 geometry: the 9921 x 14032 scan (A4 card scaled x4, INTER_NEAREST).  Six of
+    the 9000 candidate angles -- both ends of +-45 degrees, the word kernel's range and the general
+    kernel's -- are checked against the oracle bit for bit (std-devs, exact sums, count vectors)."""
+    bgr, a = a4_card
+    b, _ = orc.preprocess_omr(bgr, 0, 0)
+    big = np.repeat(np.repeat(b, 4, axis=0), 4, axis=1)
+    big = np.ascontiguousarray(big[:14032, :9920])
+    big = np.ascontiguousarray(np.concatenate([big, big[:, -1:]], axis=1))
+    h, w = big.shape
+    assert (w, h) == (9921, 14032)
+    N, angles, M = api.sweep_matrices(w, h, 45, 0.01, 1.0)
+    assert len(M) == 9000
+    idx = [0, 2500, 4500 + int(round(a * 100)), 4501, 6230, 8999]
+    _check_sweep(ctx, orc, big, M[idx], [2, 5])
