@@ -12,17 +12,20 @@
 //          with (uint64)-1, swap-remove), not on the image: the host expands it from N and
 //          a gather kernel lays the points out in visiting order, so the CTA streams them
 //          and tests 256 upcoming points per L2 round trip;
-//        * the next four live points are processed speculatively at once: all vote in one L2
-//          round trip (one thread per theta, atomics issued in visiting order, so each point
-//          sees exactly the sequential counts), one warp walks each point read-only, and the
-//          results commit in visiting order; a point that an earlier commit could have
-//          influenced is rolled back (its votes subtracted) and retried;
+//        * the next sixteen live points are processed speculatively at once on a cluster of
+//          four CTAs: all vote in one L2 round trip (one thread per theta, thetas spread over
+//          the four SMs, atomics issued in visiting order, so each point sees exactly the
+//          sequential counts), one warp walks each point read-only, and the results commit in
+//          visiting order; a point that an earlier commit could have influenced is rolled
+//          back (its votes subtracted) and retried;
 //        * the arg-max keeps the first maximal theta, like the sequential `max_val < val`;
 //        * the two line walks test 32 steps each per round trip; gap logic runs on ballots;
 //        * a commit clears the step range and, for accepted segments, un-votes its live pixels.
 //      Latency-bound per image (like the CPU), throughput comes from images in flight.
 #include <algorithm>
 #include <cmath>
+
+#include <cooperative_groups.h>
 
 #include "common.h"
 
@@ -235,30 +238,39 @@ __device__ __forceinline__ void walk_pixel(int xflag, int x0, int y0, int dx, in
     else { *j1 = x >> 16; *i1 = y; }
 }
 
-// cv::HoughLinesProbabilistic, one CTA of PPHT_K warps per image, PPHT_K points in flight.
+// cv::HoughLinesProbabilistic, one thread-block CLUSTER per image, PPHT_K points in flight.
 //
 // The algorithm is sequential by definition (RNG visiting order; every accepted segment erases
 // pixels and votes that later points see), so one image is latency-bound: a live point costs one
-// L2 round trip for its 180 vote atomics plus one per 16 walk steps.  The kernel keeps the exact
-// sequential semantics and hides that latency by SPECULATING on the next PPHT_K live points:
-//   vote    all points of the group vote in one round trip.  Theta n is always voted (and later
-//           un-voted) by the same thread, and a thread issues its atomics in visiting order, so
-//           same-address ordering gives every point exactly the counts the sequential loop
-//           would have seen (the earlier points of the group included, the later ones not);
-//   walk    warp q walks point q in both directions, READ-ONLY (no pixel is cleared while any
-//           walk of the group is in flight);
-//   commit  in visiting order, uniformly on every warp: a point commits if no earlier segment
-//           of the group erased it and its scanned path cannot meet an earlier erased range
-//           (bounding boxes); committing clears the whole step range [-e1, e0] (cv clears the
-//           live pixels of it, the others are zero already) and kills the pending candidates
-//           that sat on it.  The first point that fails, and everything after it, is rolled
-//           back: speculative state is votes only, they are subtracted by the threads that added
-//           them, and the points return to the pending set.  An accepted ("good") segment
-//           un-votes its pixels, so it also ends the group.  The first point of a group always
-//           commits, so every group makes progress.
-constexpr int PPHT_K = 4;
-constexpr int PPHT_THREADS = 32 * PPHT_K;
-constexpr int PPHT_NT = 2;    // thetas per thread held in registers (numangle <= 256)
+// L2 round trip for its 180 vote atomics plus one per 32 walk steps, and ONE SM can only issue a
+// scattered returning atomic every ~4 cycles.  The kernel keeps the exact sequential semantics and
+// hides both by SPECULATING on the next PPHT_K live points with the work spread over the
+// PPHT_C SMs of a cluster:
+//   vote    theta n belongs to ONE thread of ONE CTA (n mod PPHT_C picks the CTA) for every vote,
+//           un-vote and roll-back, and that thread issues its atomics in visiting order, so
+//           same-address program order gives every point exactly the counts the sequential loop
+//           would have seen (the earlier points of the group included, the later ones not).  Each
+//           CTA reduces its thetas' arg-max per point (REDUX on a packed 32-bit key) and writes it
+//           into every CTA's shared memory (DSMEM); barrier.cluster #1;
+//   walk    point q is walked by warp q / PPHT_C of CTA q mod PPHT_C, both directions, 32 steps
+//           each per round trip, READ-ONLY (no pixel is cleared while any walk of the group is in
+//           flight); the two end steps go to every CTA's shared memory; barrier.cluster #2;
+//   commit  in visiting order, identically on every warp of every CTA, resolved with ballots (lane
+//           q prepares point q, every lane tests its points against all segments of the group): a
+//           point commits if no earlier segment of the group erased it and its scanned path cannot
+//           meet an earlier erased range (bounding boxes); committing clears the whole step range [-e1, e0] (cv
+//           clears the live pixels of it, the others are zero already; the stores are shared out
+//           over the cluster) and kills the pending candidates that sat on it.  The first point
+//           that fails, and everything after it, is rolled back: speculative state is votes only,
+//           they are subtracted by the threads that added them, and the points return to the
+//           pending set.  An accepted ("good") segment un-votes its pixels, so it also ends the
+//           group.  The first point of a group always commits, so every group makes progress.
+// barrier.cluster (release/acquire at cluster scope) orders a group's erasing stores before the
+// next group's walk loads; the accumulator needs no fence at all (one thread per theta).
+constexpr int PPHT_C = 4;                     // CTAs (SMs) per image
+constexpr int PPHT_W = 4;                     // warps per CTA
+constexpr int PPHT_T = 32 * PPHT_W;           // threads per CTA
+constexpr int PPHT_K = PPHT_C * PPHT_W;       // points in flight
 
 struct PphtSeg { int xflag, x0, y0, dx, dy, e0, e1; };   // (dx, dy) = forward direction
 
@@ -271,27 +283,40 @@ __device__ __forceinline__ void seg_box(const PphtSeg &s, int a, int b, int *bx0
     *by0 = min(ay, cy) - 1; *by1 = max(ay, cy) + 1;
 }
 
-__global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
+__device__ __forceinline__ unsigned long long ppht_key(int bv, int bn)   // larger value first, then smaller theta
 {
-    __shared__ unsigned long long sKey[PPHT_K][PPHT_K];   // [warp][point] partial arg-max keys
-    __shared__ int sRes[PPHT_K][2];                       // [point] last accepted step forwards / backwards
-    __shared__ uint32_t sList[2 * PPHT_THREADS];          // accepted-segment pixels, one chunk
+    return ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
+}
+
+__global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_kernel(const PphtArgs A)
+{
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    __shared__ unsigned long long sKey[2][PPHT_C][PPHT_K];   // [group parity][source CTA][point] arg-max keys
+    __shared__ unsigned long long sPart[PPHT_W][PPHT_K];     // [warp][point] partial keys of this CTA
+    __shared__ int sRes[PPHT_K][2];                          // [point] last accepted step forwards / backwards
+    __shared__ uint32_t sList[2 * PPHT_T];                   // accepted-segment pixels, one chunk
+    __shared__ int4 sDirs[PPHT_C * PPHT_T];                  // per-theta walk direction (fast path: numangle <= 512)
+    __shared__ int4 sSeg[PPHT_W][PPHT_K][3];                 // [warp][point] walk geometry, ends, erased box (per-warp copy)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = (int)cluster.block_rank();
     const int half = (A.numrho - 1) / 2;
-    const int d = lane >> 4, s16 = lane & 15;            // walk direction and step slot of this lane
-    const int nth = (A.numangle + PPHT_THREADS - 1) / PPHT_THREADS;   // thetas per thread: n = tid + 128 k
-    float tc[PPHT_NT], ts[PPHT_NT];
-#pragma unroll
-    for (int k = 0; k < PPHT_NT; k++) {
-        const int n = tid + PPHT_THREADS * k;
-        tc[k] = n < A.numangle ? A.ttab[2 * n] : 0.f;
-        ts[k] = n < A.numangle ? A.ttab[2 * n + 1] : 0.f;
+    const int d = lane >> 4, s16 = lane & 15;                // walk direction and step slot of this lane
+    // thetas of this thread: n = cta + PPHT_C * (tid + PPHT_T * k)
+    const int n0 = cta + PPHT_C * tid;
+    const bool fast = A.numangle <= PPHT_C * PPHT_T && A.numangle <= 1024 && A.threshold >= 0;
+    const bool voter = n0 < A.numangle;
+    const bool warp_votes = cta + PPHT_C * (warp * 32) < A.numangle;   // any voter in this warp
+    const float tc0 = voter ? A.ttab[2 * n0] : 0.f, ts0 = voter ? A.ttab[2 * n0 + 1] : 0.f;
+    if (fast) {
+        for (int n = tid; n < A.numangle; n += PPHT_T) sDirs[n] = *reinterpret_cast<const int4 *>(A.dirs + 4 * n);
+        __syncthreads();
     }
-    int nlines = 0;
+    int nlines = 0, parity = 0;
     uint32_t pnext = lane < A.npts ? A.seq[lane] : 0u;
     for (int t0 = 0; t0 < A.npts; t0 += 32) {
-        // every warp holds the same 32-point window (lane = point); the next one is prefetched
+        // every warp of every CTA holds the same 32-point window (lane = point); the next one is prefetched
         const int t = t0 + lane;
         const uint32_t p = pnext;
         pnext = t + 32 < A.npts ? A.seq[t + 32] : 0u;
@@ -299,103 +324,93 @@ __global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
         const bool live0 = t < A.npts && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
         uint32_t pending = __ballot_sync(0xffffffffu, live0);
         while (pending) {
-            // ---- the group: the next PPHT_K pending points in visiting order
-            int gi[PPHT_K], gx[PPHT_K], gy[PPHT_K], gn = 0;
-            {
-                uint32_t rest = pending;
-#pragma unroll
-                for (int q = 0; q < PPHT_K; q++) {
-                    gi[q] = rest ? __ffs(rest) - 1 : 0;
-                    if (rest) gn = q + 1;
-                    rest &= rest - 1;
-                    gx[q] = __shfl_sync(0xffffffffu, px, gi[q]);
-                    gy[q] = __shfl_sync(0xffffffffu, py, gi[q]);
-                }
-            }
+            // ---- the group: the next PPHT_K pending points in visiting order; lane q keeps point q
+            const int gn = min(PPHT_K, __popc(pending));
+            const int my_i = lane < gn ? (int)__fns(pending, 0, lane + 1) : 0;     // the (lane + 1)-th pending point
+            const int my_x = __shfl_sync(0xffffffffu, px, my_i), my_y = __shfl_sync(0xffffffffu, py, my_i);
             // ---- vote: first maximal theta wins
-            unsigned long long key[PPHT_K];
-            if (nth <= PPHT_NT) {
-                int val[PPHT_K][PPHT_NT];
+            if (fast) {
+                int val[PPHT_K];
 #pragma unroll
                 for (int q = 0; q < PPHT_K; q++) {
-#pragma unroll
-                    for (int k = 0; k < PPHT_NT; k++) {
-                        const int n = tid + PPHT_THREADS * k;
-                        val[q][k] = -0x40000000;
-                        if (q < gn && n < A.numangle) {
-                            int32_t *bin = A.accum + (size_t)n * A.numrho + vote_r((float)gx[q], (float)gy[q], tc[k], ts[k], half);
-                            asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(val[q][k]) : "l"(bin) : "memory");
-                        }
+                    const int x = __shfl_sync(0xffffffffu, my_x, q), y = __shfl_sync(0xffffffffu, my_y, q);
+                    val[q] = -1;
+                    if (q < gn && voter) {
+                        int32_t *bin = A.accum + (size_t)n0 * A.numrho + vote_r((float)x, (float)y, tc0, ts0, half);
+                        asm volatile("atom.global.add.s32 %0, [%1], 1;" : "=r"(val[q]) : "l"(bin) : "memory");
                     }
                 }
+                if (warp_votes) {
 #pragma unroll
-                for (int q = 0; q < PPHT_K; q++) {
-                    int bv = A.threshold - 1, bn = 0;
-#pragma unroll
-                    for (int k = 0; k < PPHT_NT; k++) {
-                        const int n = tid + PPHT_THREADS * k;
-                        if (n < A.numangle && bv < val[q][k] + 1) { bv = val[q][k] + 1; bn = n; }
+                    for (int q = 0; q < PPHT_K; q++) {
+                        // packed key: count << 10 | (1023 - theta); "no vote reaches the threshold" packs below every real one
+                        uint32_t k32 = ((uint32_t)A.threshold << 10) | 1023u;    // (threshold - 1) + 1, theta 0
+                        if (voter && q < gn && val[q] + 1 >= A.threshold) k32 = ((uint32_t)(val[q] + 2) << 10) | (uint32_t)(1023 - n0);
+                        k32 = __reduce_max_sync(0xffffffffu, k32);
+                        if (lane == q) sPart[warp][q] = ppht_key((int)(k32 >> 10) - 1, 1023 - (int)(k32 & 1023u));
                     }
-                    key[q] = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
+                } else if (lane < PPHT_K) {
+                    sPart[warp][lane] = ppht_key(A.threshold - 1, 0);
                 }
             } else {
-#pragma unroll
                 for (int q = 0; q < PPHT_K; q++) {
+                    const int x = __shfl_sync(0xffffffffu, my_x, q), y = __shfl_sync(0xffffffffu, my_y, q);
                     int bv = A.threshold - 1, bn = 0;
                     if (q < gn)
-                        for (int n = tid; n < A.numangle; n += PPHT_THREADS) {
+                        for (int n = n0; n < A.numangle; n += PPHT_C * PPHT_T) {
                             const int v = atomicAdd(A.accum + (size_t)n * A.numrho +
-                                                    vote_r((float)gx[q], (float)gy[q], A.ttab[2 * n], A.ttab[2 * n + 1], half), 1) + 1;
+                                                    vote_r((float)x, (float)y, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1) + 1;
                             if (bv < v) { bv = v; bn = n; }
                         }
-                    key[q] = ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
+                    unsigned long long key = ppht_key(bv, bn);
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) {
+                        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+                        if (other > key) key = other;
+                    }
+                    if (lane == q) sPart[warp][q] = key;
                 }
-            }
-            // key: larger value first, then smaller theta index
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) {
-#pragma unroll
-                for (int q = 0; q < PPHT_K; q++) {
-                    const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[q], o);
-                    if (other > key[q]) key[q] = other;
-                }
-            }
-            if (lane == 0) {
-#pragma unroll
-                for (int q = 0; q < PPHT_K; q++) sKey[warp][q] = key[q];
             }
             __syncthreads();
-            int mval[PPHT_K], mn[PPHT_K];
+            if (tid < PPHT_K) {   // this CTA's arg-max per point -> every CTA of the cluster
+                unsigned long long kq = sPart[0][tid];
 #pragma unroll
-            for (int q = 0; q < PPHT_K; q++) {
-                unsigned long long kq = sKey[0][q];
+                for (int w2 = 1; w2 < PPHT_W; w2++) kq = sPart[w2][tid] > kq ? sPart[w2][tid] : kq;
 #pragma unroll
-                for (int w2 = 1; w2 < PPHT_K; w2++) kq = sKey[w2][q] > kq ? sKey[w2][q] : kq;
-                mval[q] = (int)(uint32_t)(kq >> 32) - 0x40000000;
-                mn[q] = 0x7fffffff - (int)(uint32_t)(kq & 0xffffffffu);
+                for (int c = 0; c < PPHT_C; c++) *cluster.map_shared_rank(&sKey[parity][cta][tid], c) = kq;
             }
-            // ---- walk: warp q walks point q, both directions at once (lanes 0-15 forwards,
-            // 16-31 backwards, 32 steps a round), reading only
-            PphtSeg seg[PPHT_K];
+            cluster.sync();
+            // lane q: arg-max of point q over the cluster, and its walk geometry
+            int my_val = A.threshold - 1, my_n = 0;
+            PphtSeg ms = {0, 0, 0, 0, 0, 0, 0};
+            if (lane < gn) {
+                unsigned long long kq = sKey[parity][0][lane];
 #pragma unroll
-            for (int q = 0; q < PPHT_K; q++) {
-                const int4 dr = *reinterpret_cast<const int4 *>(A.dirs + 4 * mn[q]);
-                seg[q].xflag = dr.x; seg[q].dx = dr.y; seg[q].dy = dr.z;
-                seg[q].x0 = dr.x ? gx[q] : (gx[q] << 16) + 32768;
-                seg[q].y0 = dr.x ? (gy[q] << 16) + 32768 : gy[q];
-                seg[q].e0 = seg[q].e1 = 0;
+                for (int c = 1; c < PPHT_C; c++) kq = sKey[parity][c][lane] > kq ? sKey[parity][c][lane] : kq;
+                my_val = (int)(uint32_t)(kq >> 32) - 0x40000000;
+                my_n = 0x7fffffff - (int)(uint32_t)(kq & 0xffffffffu);
+                const int4 dr = fast ? sDirs[my_n] : *reinterpret_cast<const int4 *>(A.dirs + 4 * my_n);
+                ms.xflag = dr.x; ms.dx = dr.y; ms.dy = dr.z;
+                ms.x0 = dr.x ? my_x : (my_x << 16) + 32768;
+                ms.y0 = dr.x ? (my_y << 16) + 32768 : my_y;
             }
-#pragma unroll
-            for (int q = 0; q < PPHT_K; q++) {
-                if (q == warp && q < gn && mval[q] >= A.threshold) {
-                    const int dx = d ? -seg[q].dx : seg[q].dx, dy = d ? -seg[q].dy : seg[q].dy;
+            const uint32_t walked_mask = __ballot_sync(0xffffffffu, lane < gn && my_val >= A.threshold);
+            // ---- walk: point q on warp q / PPHT_C of CTA q % PPHT_C, both directions at once (lanes 0-15
+            // forwards, 16-31 backwards, 32 steps a round), reading only
+            {
+                const int q = warp * PPHT_C + cta;
+                if (q < gn && ((walked_mask >> q) & 1u)) {
+                    const int xflag = __shfl_sync(0xffffffffu, ms.xflag, q), x0 = __shfl_sync(0xffffffffu, ms.x0, q);
+                    const int y0 = __shfl_sync(0xffffffffu, ms.y0, q);
+                    const int dxf = __shfl_sync(0xffffffffu, ms.dx, q), dyf = __shfl_sync(0xffffffffu, ms.dy, q);
+                    const int dx = d ? -dxf : dxf, dy = d ? -dyf : dyf;
                     int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
                     bool done = false;     // uniform inside each half-warp
                     for (int base = 1; __any_sync(0xffffffffu, !done); base += 32) {   // a round = steps base .. base + 31
                         // two loads per lane in flight: steps base + s16 and base + 16 + s16
                         int ja, ia, jb, ib;
-                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, base + s16, &ja, &ia);
-                        walk_pixel(seg[q].xflag, seg[q].x0, seg[q].y0, dx, dy, base + 16 + s16, &jb, &ib);
+                        walk_pixel(xflag, x0, y0, dx, dy, base + s16, &ja, &ia);
+                        walk_pixel(xflag, x0, y0, dx, dy, base + 16 + s16, &jb, &ib);
                         const bool inba = ja >= 0 && ja < A.w && ia >= 0 && ia < A.h;
                         const bool inbb = jb >= 0 && jb < A.w && ib >= 0 && ib < A.h;
                         uint8_t va = 0, vb = 0;
@@ -418,130 +433,146 @@ __global__ void __launch_bounds__(PPHT_THREADS) ppht_kernel(const PphtArgs A)
                             if (!done && (base + 31) - last > A.line_gap) done = true;
                         }
                     }
-                    if (s16 == 0) sRes[q][d] = last;
+                    if (s16 == 0) {
+#pragma unroll
+                        for (int c = 0; c < PPHT_C; c++) *cluster.map_shared_rank(&sRes[q][d], c) = last;
+                    }
                 }
             }
-            __syncthreads();
-            // ---- commit in visiting order (every warp runs this identically)
-            int cbox[PPHT_K][4], ncommit = 0;    // erased ranges of the segments committed in this group
-            int undo_from = gn;
+            if (walked_mask) cluster.sync();     // uniform over the cluster
+            // ---- commit in visiting order, resolved in parallel (every warp of every CTA runs this
+            // identically).  Lane q prepares point q; then every lane tests its points against all
+            // walked segments of the group; the first point that fails is found with ballots.
+            const bool walked_me = (walked_mask >> lane) & 1u;
+            int ax = 0, ay = 0, bx = 0, by = 0, len = 0;
+            bool good_me = false;
+            int sb0 = 0, sb1 = 0, sb2 = 0, sb3 = 0;        // what this point's walk looked at
+            if (walked_me) {
+                ms.e0 = sRes[lane][0];
+                ms.e1 = sRes[lane][1];
+                walk_pixel(ms.xflag, ms.x0, ms.y0, ms.dx, ms.dy, ms.e0, &ax, &ay);
+                walk_pixel(ms.xflag, ms.x0, ms.y0, ms.dx, ms.dy, -ms.e1, &bx, &by);
+                good_me = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
+                len = ms.e0 + ms.e1 + 1;
+                // every pixel the walk looked at lies within line_gap + 1 steps of its ends
+                seg_box(ms, ms.e0 + A.line_gap + 1, ms.e1 + A.line_gap + 1, &sb0, &sb1, &sb2, &sb3);
+                int4 *o = sSeg[warp][lane];
+                o[0] = make_int4(ms.xflag, ms.x0, ms.y0, ms.dx);
+                o[1] = make_int4(ms.dy, ms.e0, ms.e1, len);
+                o[2] = make_int4(min(ax, bx) - 1, min(ay, by) - 1, max(ax, bx) + 1, max(ay, by) + 1);   // erased range
+            }
+            __syncwarp();
+            uint32_t deadW = 0, failG = 0;     // bit c: segment c erases my window point / defeats my group point
+            const bool pendW = (pending >> lane) & 1u;
+            for (uint32_t rest = walked_mask; rest; rest &= rest - 1) {
+                const int c = __ffs(rest) - 1;
+                const int4 *sp = sSeg[warp][c];
+                const int4 s2 = sp[2];                           // erased range of segment c, as a box
+                const bool member = lane < gn && c < lane;
+                if (member && walked_me && sb0 <= s2.z && s2.x <= sb2 && sb1 <= s2.w && s2.y <= sb3)
+                    failG |= 1u << c;                            // may have read an erased pixel: walk again
+                const bool nearW = pendW && px >= s2.x && px <= s2.z && py >= s2.y && py <= s2.w;
+                const bool nearG = member && my_x >= s2.x && my_x <= s2.z && my_y >= s2.y && my_y <= s2.w;
+                if (!__any_sync(0xffffffffu, nearW || nearG)) continue;      // nobody near it: the usual case
+                const int4 s0 = sp[0], s1 = sp[1];
+                const int xflag = s0.x, x0 = s0.y, y0 = s0.z, dx = s0.w, dy = s1.x, e0 = s1.y, e1 = s1.z;
+                const int gxc = xflag ? x0 : x0 >> 16, gyc = xflag ? y0 >> 16 : y0;
+                int cj, ci;
+                if (nearW) {
+                    const int tt = xflag ? (px - gxc) * dx : (py - gyc) * dy;      // +-1 on the major axis
+                    walk_pixel(xflag, x0, y0, dx, dy, tt, &cj, &ci);
+                    if (cj == px && ci == py && tt <= e0 && -tt <= e1) deadW |= 1u << c;
+                }
+                if (nearG) {
+                    const int tt = xflag ? (my_x - gxc) * dx : (my_y - gyc) * dy;
+                    walk_pixel(xflag, x0, y0, dx, dy, tt, &cj, &ci);
+                    if (cj == my_x && ci == my_y && tt <= e0 && -tt <= e1) failG |= 1u << c;      // erased before its turn
+                }
+            }
+            const uint32_t failmask = __ballot_sync(0xffffffffu, failG != 0);
+            const uint32_t goodmask = __ballot_sync(0xffffffffu, walked_me && good_me);
+            int F = failmask ? __ffs(failmask) - 1 : gn;          // first point that does not commit
+            const int G = goodmask ? __ffs(goodmask) - 1 : 32;    // first accepted segment
+            const bool has_good = G < F;
+            if (has_good) F = G + 1;                              // the counts later points saw are stale
+            const uint32_t committed = F >= 32 ? 0xffffffffu : (1u << F) - 1u;
+            const uint32_t commit_walked = walked_mask & committed;
+            pending &= ~__reduce_or_sync(0xffffffffu, lane < F ? 1u << my_i : 0u);
+            pending &= ~__ballot_sync(0xffffffffu, (deadW & commit_walked) != 0);
+            if (has_good) {
+                // un-vote the live pixels of [-e1, e0] of segment G; theta n stays with its thread
+                const int4 *sp = sSeg[warp][G];
+                const int4 s0 = sp[0], s1 = sp[1];
+                const int glen = s1.w;
+                for (int c0 = 0; c0 < glen; c0 += 2 * PPHT_T) {
 #pragma unroll
-            for (int q = 0; q < PPHT_K; q++) {
-                if (q < gn && q < undo_from) {
-                    const uint32_t bit = 1u << gi[q];
-                    const bool walked = mval[q] >= A.threshold;
-                    bool ok = (pending & bit) != 0;          // else an earlier segment of the group erased it
-                    if (ok && walked) {
-                        seg[q].e0 = sRes[q][0];
-                        seg[q].e1 = sRes[q][1];
-                        // every pixel the walk looked at lies within line_gap + 1 steps of its ends
-                        int bx0, by0, bx1, by1;
-                        seg_box(seg[q], seg[q].e0 + A.line_gap + 1, seg[q].e1 + A.line_gap + 1, &bx0, &by0, &bx1, &by1);
-#pragma unroll
-                        for (int c = 0; c < PPHT_K; c++)
-                            if (c < ncommit && bx0 <= cbox[c][2] && cbox[c][0] <= bx1 && by0 <= cbox[c][3] && cbox[c][1] <= by1)
-                                ok = false;                  // may have read a pixel erased since: walk again
+                    for (int u = 0; u < 2; u++) {
+                        const int idx = c0 + tid + PPHT_T * u;
+                        uint32_t e = 0xffffffffu;
+                        if (idx < glen) {
+                            int j1, i1;
+                            walk_pixel(s0.x, s0.y, s0.z, s0.w, s1.x, idx - s1.z, &j1, &i1);
+                            if (__ldcg(A.mask + (size_t)i1 * A.w + j1) != 0) e = (uint32_t)j1 | ((uint32_t)i1 << 16);
+                        }
+                        sList[tid + PPHT_T * u] = e;
                     }
-                    if (!ok) {
-                        undo_from = q;
-                    } else {
-                        pending &= ~bit;
-                        if (walked) {
-                            const PphtSeg s = seg[q];
-                            int ax, ay, bx, by;
-                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, s.e0, &ax, &ay);
-                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, -s.e1, &bx, &by);
-                            const bool good = abs(bx - ax) >= A.line_length || abs(by - ay) >= A.line_length;
-                            const int len = s.e0 + s.e1 + 1;
-                            if (good) {
-                                // un-vote the live pixels of [-e1, e0]; theta n stays with its thread
-                                for (int c0 = 0; c0 < len; c0 += 2 * PPHT_THREADS) {
-#pragma unroll
-                                    for (int u = 0; u < 2; u++) {
-                                        const int idx = c0 + tid + PPHT_THREADS * u;
-                                        uint32_t e = 0xffffffffu;
-                                        if (idx < len) {
-                                            int j1, i1;
-                                            walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, idx - s.e1, &j1, &i1);
-                                            if (__ldcg(A.mask + (size_t)i1 * A.w + j1) != 0) e = (uint32_t)j1 | ((uint32_t)i1 << 16);
-                                        }
-                                        sList[tid + PPHT_THREADS * u] = e;
-                                    }
-                                    __syncthreads();
-                                    const int cn = min(2 * PPHT_THREADS, len - c0);
-                                    for (int i = 0; i < cn; i++) {
-                                        const uint32_t e = sList[i];
-                                        if (e == 0xffffffffu) continue;
-                                        const float fx = (float)(e & 0xffffu), fy = (float)(e >> 16);
-                                        if (nth <= PPHT_NT) {
-#pragma unroll
-                                            for (int k = 0; k < PPHT_NT; k++) {
-                                                const int n = tid + PPHT_THREADS * k;
-                                                if (n < A.numangle)
-                                                    atomicSub(A.accum + (size_t)n * A.numrho + vote_r(fx, fy, tc[k], ts[k], half), 1);
-                                            }
-                                        } else {
-                                            for (int n = tid; n < A.numangle; n += PPHT_THREADS)
-                                                atomicSub(A.accum + (size_t)n * A.numrho + vote_r(fx, fy, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
-                                        }
-                                    }
-                                    __syncthreads();
-                                }
-                                if (tid == 0 && nlines < A.cap) {
-                                    A.lines[4 * nlines + 0] = ax;
-                                    A.lines[4 * nlines + 1] = ay;
-                                    A.lines[4 * nlines + 2] = bx;
-                                    A.lines[4 * nlines + 3] = by;
-                                }
-                                nlines++;
-                                undo_from = q + 1;           // the counts later points saw are stale now
-                            }
-                            // erase the range (cv clears its live pixels; the others are zero already)
-                            for (int idx = tid; idx < len; idx += PPHT_THREADS) {
-                                int j1, i1;
-                                walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, idx - s.e1, &j1, &i1);
-                                __stcg(A.mask + (size_t)i1 * A.w + j1, (uint8_t)0);
-                            }
-                            // pending candidates of this window that sat on the range are dead now
-                            {
-                                bool dead = false;
-                                if ((pending >> lane) & 1u) {
-                                    const int tt = s.xflag ? (px - gx[q]) * s.dx : (py - gy[q]) * s.dy;   // +-1 on the major axis
-                                    int cj, ci;
-                                    walk_pixel(s.xflag, s.x0, s.y0, s.dx, s.dy, tt, &cj, &ci);
-                                    dead = cj == px && ci == py && tt <= s.e0 && -tt <= s.e1;
-                                }
-                                pending &= ~__ballot_sync(0xffffffffu, dead);
-                            }
-                            seg_box(s, s.e0, s.e1, &cbox[ncommit][0], &cbox[ncommit][1], &cbox[ncommit][2], &cbox[ncommit][3]);
-                            ncommit++;
+                    __syncthreads();
+                    const int cn = min(2 * PPHT_T, glen - c0);
+                    for (int i = 0; i < cn; i++) {
+                        const uint32_t e = sList[i];
+                        if (e == 0xffffffffu) continue;
+                        const float fx = (float)(e & 0xffffu), fy = (float)(e >> 16);
+                        if (fast) {
+                            if (voter) atomicSub(A.accum + (size_t)n0 * A.numrho + vote_r(fx, fy, tc0, ts0, half), 1);
+                        } else {
+                            for (int n = n0; n < A.numangle; n += PPHT_C * PPHT_T)
+                                atomicSub(A.accum + (size_t)n * A.numrho + vote_r(fx, fy, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
                         }
                     }
+                    __syncthreads();
+                }
+                cluster.sync();     // no CTA may erase while another still reads the segment's pixels
+                const int lx0 = __shfl_sync(0xffffffffu, ax, G), ly0 = __shfl_sync(0xffffffffu, ay, G);
+                const int lx1 = __shfl_sync(0xffffffffu, bx, G), ly1 = __shfl_sync(0xffffffffu, by, G);
+                if (cta == 0 && tid == 0 && nlines < A.cap) {
+                    A.lines[4 * nlines + 0] = lx0;
+                    A.lines[4 * nlines + 1] = ly0;
+                    A.lines[4 * nlines + 2] = lx1;
+                    A.lines[4 * nlines + 3] = ly1;
+                }
+                nlines++;
+            }
+            // erase the committed ranges (cv clears their live pixels; the others are zero already).
+            // Every CTA stores the same zeros, so each one's later loads are ordered behind its own stores.
+            for (uint32_t rest = commit_walked; rest; rest &= rest - 1) {
+                const int c = __ffs(rest) - 1;
+                const int4 *sp = sSeg[warp][c];
+                const int4 s1 = sp[1];
+                if (s1.w <= 32 && (c % PPHT_W) != warp) continue;    // short ranges: one warp each
+                const int4 s0 = sp[0];
+                const int first = s1.w <= 32 ? lane : tid, step = s1.w <= 32 ? 32 : PPHT_T;
+                for (int idx = first; idx < s1.w; idx += step) {
+                    int j1, i1;
+                    walk_pixel(s0.x, s0.y, s0.z, s0.w, s1.x, idx - s1.z, &j1, &i1);
+                    __stcg(A.mask + (size_t)i1 * A.w + j1, (uint8_t)0);
                 }
             }
             // ---- roll back the votes of the points that did not commit (same thread, same bins)
-#pragma unroll
-            for (int q = 0; q < PPHT_K; q++) {
-                if (q >= undo_from && q < gn) {
-                    if (nth <= PPHT_NT) {
-#pragma unroll
-                        for (int k = 0; k < PPHT_NT; k++) {
-                            const int n = tid + PPHT_THREADS * k;
-                            if (n < A.numangle)
-                                atomicSub(A.accum + (size_t)n * A.numrho + vote_r((float)gx[q], (float)gy[q], tc[k], ts[k], half), 1);
-                        }
-                    } else {
-                        for (int n = tid; n < A.numangle; n += PPHT_THREADS)
-                            atomicSub(A.accum + (size_t)n * A.numrho +
-                                      vote_r((float)gx[q], (float)gy[q], A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
-                    }
+            for (int q = F; q < gn; q++) {
+                const int x = __shfl_sync(0xffffffffu, my_x, q), y = __shfl_sync(0xffffffffu, my_y, q);
+                if (fast) {
+                    if (voter) atomicSub(A.accum + (size_t)n0 * A.numrho + vote_r((float)x, (float)y, tc0, ts0, half), 1);
+                } else {
+                    for (int n = n0; n < A.numangle; n += PPHT_C * PPHT_T)
+                        atomicSub(A.accum + (size_t)n * A.numrho + vote_r((float)x, (float)y, A.ttab[2 * n], A.ttab[2 * n + 1], half), 1);
                 }
             }
+            parity ^= 1;
         }
         // bar.sync orders this window's erasing stores (st.cg) before the next window's liveness loads (ld.cg)
         __syncthreads();
     }
-    if (tid == 0) *A.n_lines = nlines;
+    if (cta == 0 && tid == 0) *A.n_lines = nlines;
 }
 
 // The visiting order of cv::HoughLinesProbabilistic for n points: count = n..1,
@@ -630,7 +661,7 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     A.cap = cap;
     A.n_lines = reinterpret_cast<int *>(base + off_nl);
     A.list = reinterpret_cast<uint32_t *>(base + off_list);
-    ppht_kernel<<<1, PPHT_THREADS, 0, st>>>(A);
+    ppht_kernel<<<PPHT_C, PPHT_T, 0, st>>>(A);   // one cluster (__cluster_dims__)
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     int n = 0;
