@@ -127,9 +127,18 @@ __global__ void __launch_bounds__(256) hough_accumulate_kernel(const uint32_t *_
     if (use_smem) {
         for (int i = threadIdx.x; i < numrho; i += blockDim.x) hist[i] = 0;
         __syncthreads();
-        for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-            const uint32_t p = pts[i];
-            atomicAdd(&hist[vote_r((float)(p & 0xffffu), (float)(p >> 16), c, s, half)], 1);
+        // eight independent point loads in flight per thread before their votes (the loop is
+        // latency-bound otherwise: one L2 round trip per vote)
+        for (int base = i0 + threadIdx.x; base < i1; base += 8 * blockDim.x) {
+            uint32_t p[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int i = base + u * blockDim.x;
+                p[u] = i < i1 ? __ldg(pts + i) : 0xffffffffu;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (p[u] != 0xffffffffu) atomicAdd(&hist[vote_r((float)(p[u] & 0xffffu), (float)(p[u] >> 16), c, s, half)], 1);
         }
         __syncthreads();
         for (int i = threadIdx.x; i < numrho; i += blockDim.x) {
@@ -193,8 +202,8 @@ int32_t hough_accumulate_device(oics_ctx *ctx, const uint8_t *dedges, int w, int
     const int use_smem = smem <= (size_t)ctx->smem_optin - 1024;
     if (use_smem && smem > 48 * 1024)
         OICS_CUDA_TRY(cudaFuncSetAttribute(hough_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // enough CTAs to fill the machine: numangle x slices >= ~4 waves
-    int slices = std::max(1, (4 * ctx->sm_count + numangle - 1) / numangle);
+    // one full wave, no tail: 4 CTAs fit an SM (48 KB histogram each), numangle x slices <= 4 x SMs
+    int slices = std::max(1, (4 * ctx->sm_count) / numangle);
     dim3 grid(numangle, slices);
     hough_accumulate_kernel<<<grid, 256, use_smem ? smem : 0, st>>>(d_pts, d_total, ctx->twid.as<float>(), numrho, slices,
                                                                     use_smem, daccum);

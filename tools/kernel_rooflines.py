@@ -78,6 +78,12 @@ def main():
             gbs = b / (us * 1e-6) / 1e9
             row.update({"algorithmic_bytes": b, "what": what, "achieved_gbs": round(gbs, 1), "peak_gbs": peak,
                         "frac_of_hbm_peak": round(gbs / peak, 3)})
+        if name == "hough_accumulate_kernel":
+            cfg = os.path.join(os.path.dirname(os.path.abspath(sys.argv[1])), "configs.json")
+            if os.path.exists(cfg):
+                votes = json.load(open(cfg)).get("hough_accumulate", {}).get("votes")
+                if votes:
+                    row.update({"votes": votes, "gvotes_per_s": round(votes / (us * 1e-6) / 1e9, 3)})
         out.append(row)
     out.sort(key=lambda r: -r["median_us"] * r["launches"])
     txt = json.dumps({"card": f"{W}x{H} A4, skew {SKEW}", "note": "ncu per-launch times: cold cache, serialised", "kernels": out}, indent=1)
@@ -85,7 +91,8 @@ def main():
         open(sys.argv[2], "w").write(txt)
     for r in out:
         print(f"{r['kernel']:34s} n={r['launches']:3d} {r['median_us']:10.1f} us"
-              + (f"  {r['achieved_gbs']:8.1f} GB/s  {100 * r['frac_of_hbm_peak']:5.1f}% of HBM peak" if "achieved_gbs" in r else ""))
+              + (f"  {r['achieved_gbs']:8.1f} GB/s  {100 * r['frac_of_hbm_peak']:5.1f}% of HBM peak" if "achieved_gbs" in r else "")
+              + (f"  {r['gvotes_per_s']:6.3f} G votes/s" if "gvotes_per_s" in r else ""))
 
 
 if __name__ == "__main__":
