@@ -308,6 +308,27 @@ def test_hough_lines_p_edge_cases(ctx, orc):
     assert np.array_equal(orc.hough_lines_p(full, 0, 10.0, 0.0), ctx.hough_lines_p(full, 0, 10.0, 0.0))
 
 
+@pytest.mark.parametrize("rho,theta", [(1.0, np.pi / 720), (2.0, np.pi / 180), (1.0, np.pi / 90), (0.5, np.pi / 360)])
+def test_hough_lines_p_other_resolutions(ctx, orc, dataset_like, rho, theta):
+    """Accumulator resolutions other than the reference's (1, pi/180): 720 thetas take the kernel's
+    general path (more thetas than the cluster has voting threads)."""
+    edges = orc.canny(dataset_like[0], 50.0, 150.0)
+    for thr in (0, 60):
+        ref = orc.hough_lines_p(edges, thr, 40.0, 5.0, rho, theta)
+        got = ctx.hough_lines_p(edges, thr, 40.0, 5.0, rho, theta)
+        assert got.shape == ref.shape and np.array_equal(ref, got), (rho, theta, thr, len(ref), len(got))
+
+
+def test_hough_lines_p_a4(ctx, orc, a4_card):
+    """BASELINE configs 2 and 3 geometry: the A4 card's 4.6e5 edge pixels, threshold 0 (omr.rs:245-253)
+    and threshold 100 (fft.rs:183-191), line for line."""
+    edges = orc.canny(a4_card[0], 50.0, 150.0)
+    for thr in (0, 100):
+        ref = orc.hough_lines_p(edges, thr, 125.0, 15.0)
+        got = ctx.hough_lines_p(edges, thr, 125.0, 15.0)
+        assert got.shape == ref.shape and np.array_equal(ref, got), (thr, len(ref), len(got))
+
+
 def test_hough_entry_points(ctx, orc, dataset_like):
     bgr, a = dataset_like
     g = orc.gray(bgr)
