@@ -375,15 +375,20 @@ class Context:
         return out
 
     # -- pipeline
-    def correct_default(self, bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, want_image=True):
-        """omr::correct_default on memory buffers -> (angle, need_check, deskewed BGR or None)."""
+    def correct_default(self, bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, want_image=True,
+                        out=None):
+        """omr::correct_default on memory buffers -> (angle, need_check, deskewed BGR or None).
+        `out`: optional flat uint8 buffer for the deskewed card (numpy, e.g. a view of pinned memory,
+        or anything api._describe-like with .ctypes.data/.size); the returned image is a view of it.
+        A caller that deskews card after card should pass one: a fresh pageable 30 MB array costs
+        more in page faults than the whole GPU path."""
         p, w, h, ch, stride, keep = _describe(bgr)
-        out = None
         cap = 0
         if want_image:
             # CONTAIN output is at most (w+h) x (w+h)
             side = int(math.ceil(math.hypot(w, h))) + 2
-            out = np.empty(side * side * 3, np.uint8)
+            if out is None:
+                out = np.empty(side * side * 3, np.uint8)
             cap = out.size
         dw, dh, a, need = C.c_int32(), C.c_int32(), C.c_double(), C.c_int32()
         check(self._lib.oics_correct_default(self._h, p, w, h, stride, int(max_angle), float(step), max_w, max_h,

@@ -29,6 +29,16 @@ out = {"skew": a}
 # config 1: projection method end to end (correct_default)
 tg, rg = t(lambda: ctx.correct_default(bgr, 15, 0.1, 0, 0, 125.0, 15.0))
 out["config1_correct_default"] = {"gpu_s": tg, "angle": rg[0]}
+# the same with the caller's buffers pinned and reused (a fresh pageable 30 MB output array costs
+# more in page faults than the whole GPU path)
+import torch
+pin_in = torch.from_numpy(bgr.copy()).pin_memory().numpy()
+pin_out = torch.empty(int(np.hypot(*bgr.shape[:2]) + 3) ** 2 * 3, dtype=torch.uint8).pin_memory().numpy()
+tg, rp = t(lambda: ctx.correct_default(pin_in, 15, 0.1, 0, 0, 125.0, 15.0, out=pin_out))
+assert rp[0] == rg[0] and np.array_equal(rp[2], rg[2])
+out["config1_correct_default"]["gpu_s_pinned_buffers"] = tg
+tg, _ = t(lambda: ctx.correct_default(pin_in, 15, 0.1, 0, 0, 125.0, 15.0, want_image=False))
+out["config1_correct_default"]["gpu_s_estimate_only"] = tg
 # config 2: Hough method (Canny on BGR + HoughLinesP thr 0 + segment-angle mode)
 tg, rg = t(lambda: ctx.result_from_edges_detection(bgr, 125.0, 15.0))
 tc, rc = t(lambda: orc.get_result_from_edges_detection(bgr, 125.0, 15.0), n=1)
