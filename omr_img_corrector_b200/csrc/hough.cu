@@ -323,20 +323,28 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
         __syncthreads();
     }
     int nlines = 0, parity = 0;
-    uint32_t pnext = lane < A.npts ? A.seq[lane] : 0u;
-    for (int t0 = 0; t0 < A.npts; t0 += 32) {
-        // every warp of every CTA holds the same 32-point window (lane = point); the next one is prefetched
+    // every warp of every CTA holds the same 64-point window: lane l keeps points l (half A) and
+    // 32 + l (half B) of it; the next window is prefetched
+    uint32_t pnextA = lane < A.npts ? A.seq[lane] : 0u, pnextB = lane + 32 < A.npts ? A.seq[lane + 32] : 0u;
+    for (int t0 = 0; t0 < A.npts; t0 += 64) {
         const int t = t0 + lane;
-        const uint32_t p = pnext;
-        pnext = t + 32 < A.npts ? A.seq[t + 32] : 0u;
-        const int px = (int)(p & 0xffffu), py = (int)(p >> 16);
-        const bool live0 = t < A.npts && __ldcg(A.mask + (size_t)py * A.w + px) != 0;
-        uint32_t pending = __ballot_sync(0xffffffffu, live0);
-        while (pending) {
-            // ---- the group: the next PPHT_K pending points in visiting order; lane q keeps point q
-            const int gn = min(PPHT_K, __popc(pending));
-            const int my_i = lane < gn ? (int)__fns(pending, 0, lane + 1) : 0;     // the (lane + 1)-th pending point
-            const int my_x = __shfl_sync(0xffffffffu, px, my_i), my_y = __shfl_sync(0xffffffffu, py, my_i);
+        const uint32_t pA = pnextA, pB = pnextB;
+        pnextA = t + 64 < A.npts ? A.seq[t + 64] : 0u;
+        pnextB = t + 96 < A.npts ? A.seq[t + 96] : 0u;
+        const int pxA = (int)(pA & 0xffffu), pyA = (int)(pA >> 16), pxB = (int)(pB & 0xffffu), pyB = (int)(pB >> 16);
+        const bool liveA = t < A.npts && __ldcg(A.mask + (size_t)pyA * A.w + pxA) != 0;
+        const bool liveB = t + 32 < A.npts && __ldcg(A.mask + (size_t)pyB * A.w + pxB) != 0;
+        uint32_t pendA = __ballot_sync(0xffffffffu, liveA), pendB = __ballot_sync(0xffffffffu, liveB);
+        while (pendA | pendB) {
+            // ---- the group: the next PPHT_K pending points in visiting order (half A before half B);
+            // lane q keeps point q: my_i in [0, 64) is its place in the window
+            const int nA = __popc(pendA);
+            const int gn = min(PPHT_K, nA + __popc(pendB));
+            int my_i = 0;
+            if (lane < gn) my_i = lane < nA ? (int)__fns(pendA, 0, lane + 1) : 32 + (int)__fns(pendB, 0, lane - nA + 1);
+            const int xa = __shfl_sync(0xffffffffu, pxA, my_i & 31), ya = __shfl_sync(0xffffffffu, pyA, my_i & 31);
+            const int xb = __shfl_sync(0xffffffffu, pxB, my_i & 31), yb = __shfl_sync(0xffffffffu, pyB, my_i & 31);
+            const int my_x = my_i < 32 ? xa : xb, my_y = my_i < 32 ? ya : yb;
             // ---- vote: first maximal theta wins
             if (fast) {
                 int val[PPHT_K];
@@ -471,8 +479,8 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
                 o[2] = make_int4(min(ax, bx) - 1, min(ay, by) - 1, max(ax, bx) + 1, max(ay, by) + 1);   // erased range
             }
             __syncwarp();
-            uint32_t deadW = 0, failG = 0;     // bit c: segment c erases my window point / defeats my group point
-            const bool pendW = (pending >> lane) & 1u;
+            uint32_t deadA = 0, deadB = 0, failG = 0;     // bit c: segment c erases my window points / defeats my group point
+            const bool pendWA = (pendA >> lane) & 1u, pendWB = (pendB >> lane) & 1u;
             for (uint32_t rest = walked_mask; rest; rest &= rest - 1) {
                 const int c = __ffs(rest) - 1;
                 const int4 *sp = sSeg[warp][c];
@@ -480,17 +488,23 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
                 const bool member = lane < gn && c < lane;
                 if (member && walked_me && sb0 <= s2.z && s2.x <= sb2 && sb1 <= s2.w && s2.y <= sb3)
                     failG |= 1u << c;                            // may have read an erased pixel: walk again
-                const bool nearW = pendW && px >= s2.x && px <= s2.z && py >= s2.y && py <= s2.w;
+                const bool nearA = pendWA && pxA >= s2.x && pxA <= s2.z && pyA >= s2.y && pyA <= s2.w;
+                const bool nearB = pendWB && pxB >= s2.x && pxB <= s2.z && pyB >= s2.y && pyB <= s2.w;
                 const bool nearG = member && my_x >= s2.x && my_x <= s2.z && my_y >= s2.y && my_y <= s2.w;
-                if (!__any_sync(0xffffffffu, nearW || nearG)) continue;      // nobody near it: the usual case
+                if (!__any_sync(0xffffffffu, nearA || nearB || nearG)) continue;      // nobody near it: the usual case
                 const int4 s0 = sp[0], s1 = sp[1];
                 const int xflag = s0.x, x0 = s0.y, y0 = s0.z, dx = s0.w, dy = s1.x, e0 = s1.y, e1 = s1.z;
                 const int gxc = xflag ? x0 : x0 >> 16, gyc = xflag ? y0 >> 16 : y0;
                 int cj, ci;
-                if (nearW) {
-                    const int tt = xflag ? (px - gxc) * dx : (py - gyc) * dy;      // +-1 on the major axis
+                if (nearA) {
+                    const int tt = xflag ? (pxA - gxc) * dx : (pyA - gyc) * dy;      // +-1 on the major axis
                     walk_pixel(xflag, x0, y0, dx, dy, tt, &cj, &ci);
-                    if (cj == px && ci == py && tt <= e0 && -tt <= e1) deadW |= 1u << c;
+                    if (cj == pxA && ci == pyA && tt <= e0 && -tt <= e1) deadA |= 1u << c;
+                }
+                if (nearB) {
+                    const int tt = xflag ? (pxB - gxc) * dx : (pyB - gyc) * dy;
+                    walk_pixel(xflag, x0, y0, dx, dy, tt, &cj, &ci);
+                    if (cj == pxB && ci == pyB && tt <= e0 && -tt <= e1) deadB |= 1u << c;
                 }
                 if (nearG) {
                     const int tt = xflag ? (my_x - gxc) * dx : (my_y - gyc) * dy;
@@ -506,8 +520,10 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
             if (has_good) F = G + 1;                              // the counts later points saw are stale
             const uint32_t committed = F >= 32 ? 0xffffffffu : (1u << F) - 1u;
             const uint32_t commit_walked = walked_mask & committed;
-            pending &= ~__reduce_or_sync(0xffffffffu, lane < F ? 1u << my_i : 0u);
-            pending &= ~__ballot_sync(0xffffffffu, (deadW & commit_walked) != 0);
+            pendA &= ~__reduce_or_sync(0xffffffffu, lane < F && my_i < 32 ? 1u << my_i : 0u);
+            pendB &= ~__reduce_or_sync(0xffffffffu, lane < F && my_i >= 32 ? 1u << (my_i - 32) : 0u);
+            pendA &= ~__ballot_sync(0xffffffffu, (deadA & commit_walked) != 0);
+            pendB &= ~__ballot_sync(0xffffffffu, (deadB & commit_walked) != 0);
             if (has_good) {
                 // un-vote the live pixels of [-e1, e0] of segment G; theta n stays with its thread
                 const int4 *sp = sSeg[warp][G];
@@ -587,11 +603,9 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
 // The visiting order of cv::HoughLinesProbabilistic for n points: count = n..1,
 // idx = rng % count, visit arr[idx], arr[idx] = arr[count-1]; cv::RNG(-1) is the
 // multiply-with-carry generator state = lo32 * 4164903690 + hi32.
-static void ppht_order(int n, std::vector<int> &order)
+static void ppht_order(int n, int *order, int *arr)
 {
-    std::vector<int> arr((size_t)n);
     for (int i = 0; i < n; i++) arr[i] = i;
-    order.resize((size_t)n);
     uint64_t state = (uint64_t)-1;
     int k = 0;
     for (int count = n; count > 0; count--) {
@@ -636,8 +650,11 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     *n_lines = 0;
     if (npts == 0) return OICS_OK;
 
-    std::vector<int> order;
-    ppht_order(npts, order);
+    // the order is expanded in pinned memory the context keeps (no page faults, asynchronous upload);
+    // the stream is idle here, so nothing else is reading pin_small
+    OICS_TRY(ctx->pin_small.ensure(2 * sizeof(int) * (size_t)npts));
+    int *order = ctx->pin_small.as<int>();
+    ppht_order(npts, order, order + npts);
     const size_t acc_bytes = (size_t)numangle * numrho * sizeof(int32_t);
     OICS_TRY(ctx->accum.ensure(acc_bytes));
     // misc: [order npts][seq npts][ttab][dirs][n_lines][lines cap*4]
@@ -650,7 +667,7 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     const size_t off_list = off_lines + sizeof(int32_t) * 4 * (size_t)dcap;
     OICS_TRY(ctx->misc.ensure(off_list + sizeof(uint32_t) * (2 * (size_t)std::max(w, h) + 2)));
     uint8_t *base = ctx->misc.as<uint8_t>();
-    OICS_CUDA_TRY(cudaMemcpyAsync(base, order.data(), sizeof(int) * (size_t)npts, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(base, order, sizeof(int) * (size_t)npts, cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(base + off_ttab, ttab.data(), sizeof(float) * ttab.size(), cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(base + off_dirs, dirs.data(), sizeof(int) * dirs.size(), cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemsetAsync(ctx->accum.p, 0, acc_bytes, st));
