@@ -3,7 +3,7 @@
 The package holds only what the path needs: `csrc/` (hand-written sm_100a CUDA
 kernels + the C ABI of include/oics_cuda.h, built into liboics_cuda.so) and a
 host-side mirror of the reference's module layout -- `omr`, `projection`,
-`hough`, `fft`, `transfer`, `calculate`, `types` -- whose functions keep the
+`hough`, `fft`, `transfer`, `calculate`, `types` (and `task`, the Tauri batch path) -- whose functions keep the
 reference's names, argument meaning and error behaviour and call the C ABI.
 Importing the package does not need a GPU; calling a compute function does.
 """
@@ -13,4 +13,4 @@ from .api import (BELIEVED, CLIP_CONTAIN, CLIP_DEFAULT, INTER_LINEAR, INTER_NEAR
                   default_context)
 
 __all__ = ["Context", "DeviceImage", "OmrResult", "OicsError", "default_context", "omr", "projection", "hough",
-           "fft", "transfer", "calculate", "types"]
+           "fft", "transfer", "calculate", "types", "task"]

@@ -490,3 +490,26 @@ def test_sweep_config5_full_size(ctx, orc, a4_card):
     assert len(M) == 9000
     idx = [0, 2500, 4500 + int(round(a * 100)), 4501, 6230, 8999]
     _check_sweep(ctx, orc, big, M[idx], [2, 5])
+
+
+# ----------------------------------------------------------------------------- N1: the Tauri batch path
+def test_task_runner_matches_correct_default(ctx, orc, dataset_like):
+    """task.rs:19-68 through oics_correct_batch: event vocabulary, and the written cards equal the
+    oracle's correct_default output."""
+    from omr_img_corrector_b200 import task
+    bgr, _ = dataset_like
+    base = np.ascontiguousarray(bgr[100:400, 200:460])
+    blank = np.full((300, 260, 3), 255, np.uint8)
+    blank[40:43, 30:230] = 0
+    blank[45:240, 60:63] = 0
+    cards = [orc.rotate_mat(base, -2.0, 1.0, 1, orc.WHITE, 0), blank, orc.rotate_mat(base, 3.5, 1.0, 1, orc.WHITE, 0)]
+    tasks = [task.Task(i, c, f"o{i}") for i, c in enumerate(cards)]
+    events, written = [], {}
+    params = (5, 0.5, 0, 0, 50.0, 5.0)
+    task.run_tasks(ctx, tasks, *params, emit=lambda e, p: events.append((e, p)),
+                   write=lambda path, img: written.__setitem__(path, img.copy()))
+    done = {p["task_id"]: p["result"] for e, p in events if e == "task_completed"}
+    for i, c in enumerate(cards):
+        ra, rneed, rout = orc.correct_default(c, *params)
+        assert done[i] == ("debatable" if rneed else "finished")
+        assert np.array_equal(written[f"o{i}"], rout)

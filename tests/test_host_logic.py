@@ -195,3 +195,36 @@ def test_rule_a_batch_matches_rule_a():
     for c in range(7):
         r = api.rule_a(h[c], v[c], N, 0.5)
         assert (ang[c], stat[c], ncand[c]) == (r.angle, r.status, len(r.candidates))
+
+
+def test_task_events_follow_the_reference_vocabulary():
+    """task.rs:19-68: start_running_task, then task_completed with finished | debatable | error."""
+    from omr_img_corrector_b200 import task
+
+    class FakeCtx:
+        def correct_batch(self, cards, *params, outs=None):
+            n = len(cards)
+            ang = np.arange(n, dtype=np.float64)
+            need = np.array([i % 3 == 1 for i in range(n)])
+            stat = np.array([-3 if i % 3 == 2 else 0 for i in range(n)], np.int32)
+            sizes = np.tile(np.array([[4, 2]], np.int32), (n, 1))
+            if outs is not None:
+                for i, o in enumerate(outs):
+                    o[:24] = i
+            return ang, need, stat, sizes
+
+    tasks = [task.Task(10 + i, np.zeros((5, 6, 3), np.uint8), f"out{i}.jpg") for i in range(4)]
+    tasks.append(task.Task(99, np.zeros((5, 6), np.uint8), "gray.jpg"))           # not a BGR card -> error
+    events, written = [], {}
+    task.run_tasks(FakeCtx(), tasks, 45, 0.2, 248, 230, 150.0, 50.0, lambda e, p: events.append((e, p)),
+                   write=lambda path, img: written.__setitem__(path, img.copy()))
+    done = {p["task_id"]: p for e, p in events if e == "task_completed"}
+    started = [p["task_id"] for e, p in events if e == "start_running_task"]
+    assert sorted(started) == [10, 11, 12, 13, 99]
+    assert [done[k]["result"] for k in (10, 11, 12, 13, 99)] == ["finished", "debatable", "error", "finished", "error"]
+    assert done[11]["output_path"] == "out1.jpg"
+    assert set(written) == {"out0.jpg", "out1.jpg", "out3.jpg"} and written["out3.jpg"].shape == (2, 4, 3)
+    for tid in (10, 11, 12, 13, 99):                       # a task starts before it completes
+        i0 = next(i for i, (e, p) in enumerate(events) if e == "start_running_task" and p["task_id"] == tid)
+        i1 = next(i for i, (e, p) in enumerate(events) if e == "task_completed" and p["task_id"] == tid)
+        assert i0 < i1
