@@ -43,35 +43,81 @@ __device__ __forceinline__ double2 cmul_conj(double2 a, double2 b)  // a * conj(
     return make_double2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
 }
 
-// forward DIF, natural in -> bit-reversed out
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+
+// Two consecutive radix-2 DIF stages (spans 2h and h) on the four elements i0 + {0, h, 2h, 3h}:
+// the same operations in the same order as the two separate stages, one pass over shared memory.
+__device__ __forceinline__ void dif_pair(double2 *a, int g, int h, int tstep1, const double2 *__restrict__ tw)
+{
+    const int pos = g & (h - 1);
+    const int i0 = ((g - pos) << 2) + pos;
+    const double2 a0 = a[i0], a1 = a[i0 + h], a2 = a[i0 + 2 * h], a3 = a[i0 + 3 * h];
+    const double2 w1a = __ldg(tw + pos * tstep1), w1b = __ldg(tw + (pos + h) * tstep1), w2 = __ldg(tw + pos * 2 * tstep1);
+    const double2 b0 = cadd(a0, a2), b2 = cmul(csub(a0, a2), w1a);
+    const double2 b1 = cadd(a1, a3), b3 = cmul(csub(a1, a3), w1b);
+    a[i0] = cadd(b0, b1);
+    a[i0 + h] = cmul(csub(b0, b1), w2);
+    a[i0 + 2 * h] = cadd(b2, b3);
+    a[i0 + 3 * h] = cmul(csub(b2, b3), w2);
+}
+
+// forward DIF, natural in -> bit-reversed out: stages fused in pairs (one barrier per pair)
 __device__ void fft_dif(double2 *a, int m, const double2 *__restrict__ tw)
 {
-    for (int s = m >> 1; s >= 1; s >>= 1) {
-        const int tstep = (m >> 1) / s;
+    int s = m >> 1;
+    int lg = 0;
+    while ((1 << lg) < m) lg++;
+    if (lg & 1) {   // odd number of stages: the first one alone
         for (int t = threadIdx.x; t < (m >> 1); t += blockDim.x) {
-            const int pos = t & (s - 1);
-            const int i = ((t - pos) << 1) + pos, j = i + s;
+            const int i = t, j = t + s;           // s = m / 2: pos = t
             const double2 u = a[i], v = a[j];
-            a[i] = make_double2(u.x + v.x, u.y + v.y);
-            const double2 d = make_double2(u.x - v.x, u.y - v.y);
-            a[j] = cmul(d, __ldg(tw + pos * tstep));
+            a[i] = cadd(u, v);
+            a[j] = cmul(csub(u, v), __ldg(tw + t));
         }
         __syncthreads();
+        s >>= 1;
     }
+    for (; s >= 2; s >>= 2) {
+        const int h = s >> 1, tstep1 = (m >> 1) / s;
+        for (int g = threadIdx.x; g < (m >> 2); g += blockDim.x) dif_pair(a, g, h, tstep1, tw);
+        __syncthreads();
+    }
+}
+
+// Two consecutive radix-2 DIT stages (spans s and 2s) with conjugated twiddles on i0 + {0, s, 2s, 3s}
+__device__ __forceinline__ void dit_pair(double2 *a, int g, int s, int tstepA, const double2 *__restrict__ tw)
+{
+    const int pos = g & (s - 1);
+    const int i0 = ((g - pos) << 2) + pos;
+    const double2 a0 = a[i0], a1 = a[i0 + s], a2 = a[i0 + 2 * s], a3 = a[i0 + 3 * s];
+    const int tstepB = tstepA >> 1;
+    const double2 wa = __ldg(tw + pos * tstepA), wb0 = __ldg(tw + pos * tstepB), wb1 = __ldg(tw + (pos + s) * tstepB);
+    const double2 v01 = cmul_conj(a1, wa), v23 = cmul_conj(a3, wa);
+    const double2 b0 = cadd(a0, v01), b1 = csub(a0, v01), b2 = cadd(a2, v23), b3 = csub(a2, v23);
+    const double2 v02 = cmul_conj(b2, wb0), v13 = cmul_conj(b3, wb1);
+    a[i0] = cadd(b0, v02);
+    a[i0 + 2 * s] = csub(b0, v02);
+    a[i0 + s] = cadd(b1, v13);
+    a[i0 + 3 * s] = csub(b1, v13);
 }
 
 // inverse DIT with conjugated twiddles, bit-reversed in -> natural out (unscaled)
 __device__ void ifft_dit(double2 *a, int m, const double2 *__restrict__ tw)
 {
-    for (int s = 1; s <= (m >> 1); s <<= 1) {
-        const int tstep = (m >> 1) / s;
+    int s = 1;
+    for (; (s << 1) <= (m >> 1); s <<= 2) {
+        const int tstepA = (m >> 1) / s;
+        for (int g = threadIdx.x; g < (m >> 2); g += blockDim.x) dit_pair(a, g, s, tstepA, tw);
+        __syncthreads();
+    }
+    if (s <= (m >> 1)) {   // odd number of stages: the last one (span m / 2) alone
         for (int t = threadIdx.x; t < (m >> 1); t += blockDim.x) {
-            const int pos = t & (s - 1);
-            const int i = ((t - pos) << 1) + pos, j = i + s;
+            const int i = t, j = t + s;
             const double2 u = a[i];
-            const double2 v = cmul_conj(a[j], __ldg(tw + pos * tstep));
-            a[i] = make_double2(u.x + v.x, u.y + v.y);
-            a[j] = make_double2(u.x - v.x, u.y - v.y);
+            const double2 v = cmul_conj(a[j], __ldg(tw + t));
+            a[i] = cadd(u, v);
+            a[j] = csub(u, v);
         }
         __syncthreads();
     }
