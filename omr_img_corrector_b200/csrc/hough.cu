@@ -261,7 +261,7 @@ __device__ __forceinline__ void walk_pixel(int xflag, int x0, int y0, int dx, in
 //           would have seen (the earlier points of the group included, the later ones not).  Each
 //           CTA reduces its thetas' arg-max per point (REDUX on a packed 32-bit key) and writes it
 //           into every CTA's shared memory (DSMEM); barrier.cluster #1;
-//   walk    point q is walked by warp q / PPHT_C of CTA q mod PPHT_C, both directions, 32 steps
+//   walk    point q is walked by warp q / PPHT_C of CTA q mod PPHT_C, both directions, 64 steps
 //           each per round trip, READ-ONLY (no pixel is cleared while any walk of the group is in
 //           flight); the two end steps go to every CTA's shared memory; barrier.cluster #2;
 //   commit  in visiting order, identically on every warp of every CTA, resolved with ballots (lane
@@ -413,7 +413,7 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
             }
             const uint32_t walked_mask = __ballot_sync(0xffffffffu, lane < gn && my_val >= A.threshold);
             // ---- walk: point q on warp q / PPHT_C of CTA q % PPHT_C, both directions at once (lanes 0-15
-            // forwards, 16-31 backwards, 32 steps a round), reading only
+            // forwards, 16-31 backwards, 64 steps a round), reading only
             {
                 const int q = warp * PPHT_C + cta;
                 if (q < gn && ((walked_mask >> q) & 1u)) {
@@ -423,31 +423,36 @@ __global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_ke
                     const int dx = d ? -dxf : dxf, dy = d ? -dyf : dyf;
                     int last = 0;          // last accepted step of this lane's direction (step 0 = the point itself)
                     bool done = false;     // uniform inside each half-warp
-                    for (int base = 1; __any_sync(0xffffffffu, !done); base += 32) {   // a round = steps base .. base + 31
-                        // two loads per lane in flight: steps base + s16 and base + 16 + s16
-                        int ja, ia, jb, ib;
-                        walk_pixel(xflag, x0, y0, dx, dy, base + s16, &ja, &ia);
-                        walk_pixel(xflag, x0, y0, dx, dy, base + 16 + s16, &jb, &ib);
-                        const bool inba = ja >= 0 && ja < A.w && ia >= 0 && ia < A.h;
-                        const bool inbb = jb >= 0 && jb < A.w && ib >= 0 && ib < A.h;
-                        uint8_t va = 0, vb = 0;
-                        if (!done && inba) va = __ldcg(A.mask + (size_t)ia * A.w + ja);
-                        if (!done && inbb) vb = __ldcg(A.mask + (size_t)ib * A.w + jb);
-                        const uint32_t bma = __ballot_sync(0xffffffffu, va != 0), bmb = __ballot_sync(0xffffffffu, vb != 0);
-                        const uint32_t boa = __ballot_sync(0xffffffffu, !inba), bob = __ballot_sync(0xffffffffu, !inbb);
+                    for (int base = 1; __any_sync(0xffffffffu, !done); base += 64) {   // a round = steps base .. base + 63
+                        // four loads per lane in flight: steps base + 16 u + s16
+                        unsigned long long bits = 0, ob = 0;
+                        uint8_t v[4];
+                        bool inb[4];
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            int j1, i1;
+                            walk_pixel(xflag, x0, y0, dx, dy, base + 16 * u + s16, &j1, &i1);
+                            inb[u] = j1 >= 0 && j1 < A.w && i1 >= 0 && i1 < A.h;
+                            v[u] = 0;
+                            if (!done && inb[u]) v[u] = __ldcg(A.mask + (size_t)i1 * A.w + j1);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const uint32_t bm = __ballot_sync(0xffffffffu, v[u] != 0), bo = __ballot_sync(0xffffffffu, !inb[u]);
+                            bits |= (unsigned long long)((bm >> (16 * d)) & 0xffffu) << (16 * u);
+                            ob |= (unsigned long long)((bo >> (16 * d)) & 0xffffu) << (16 * u);
+                        }
                         if (!done) {
-                            uint32_t bits = ((bma >> (16 * d)) & 0xffffu) | (((bmb >> (16 * d)) & 0xffffu) << 16);
-                            const uint32_t ob = ((boa >> (16 * d)) & 0xffffu) | (((bob >> (16 * d)) & 0xffffu) << 16);
-                            const int first_oob = ob ? __ffs(ob) - 1 : 32;
-                            if (first_oob < 32) bits &= (1u << first_oob) - 1u;
+                            const int first_oob = ob ? __ffsll((long long)ob) - 1 : 64;
+                            if (first_oob < 64) bits &= (1ull << first_oob) - 1ull;
                             while (bits) {
-                                const int sb = base + __ffs(bits) - 1;
+                                const int sb = base + __ffsll((long long)bits) - 1;
                                 bits &= bits - 1;
                                 if (sb - last > A.line_gap + 1) { done = true; break; }
                                 last = sb;
                             }
-                            if (!done && first_oob < 32) done = true;      // left the image: line_end = last live step
-                            if (!done && (base + 31) - last > A.line_gap) done = true;
+                            if (!done && first_oob < 64) done = true;      // left the image: line_end = last live step
+                            if (!done && (base + 63) - last > A.line_gap) done = true;
                         }
                     }
                     if (s16 == 0) {
