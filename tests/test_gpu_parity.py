@@ -329,6 +329,19 @@ def test_hough_lines_p_a4(ctx, orc, a4_card):
         assert got.shape == ref.shape and np.array_equal(ref, got), (thr, len(ref), len(got))
 
 
+def test_hough_lines_p_repeatable(ctx, orc, a4_card, dataset_like):
+    """The cluster kernel speculates on 16 points at once and relies on barrier ordering between its
+    erasing stores and later loads: a latent race would show up as run-to-run differences.  Repeated
+    runs must return the oracle's list every time."""
+    for img, reps, args in ((a4_card[0], 8, (0, 125.0, 15.0)), (dataset_like[0], 25, (0, 150.0, 50.0)),
+                            (dataset_like[0], 25, (30, 20.0, 2.0))):
+        edges = orc.canny(img, 50.0, 150.0)
+        ref = orc.hough_lines_p(edges, *args)
+        for _ in range(reps):
+            got = ctx.hough_lines_p(edges, *args)
+            assert got.shape == ref.shape and np.array_equal(ref, got)
+
+
 def test_hough_entry_points(ctx, orc, dataset_like):
     bgr, a = dataset_like
     g = orc.gray(bgr)
