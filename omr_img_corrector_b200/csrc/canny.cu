@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(256) canny_nms_kernel(const uint8_t *__restric
                                                         int low, int high, uint8_t *__restrict__ map,
                                                         int *__restrict__ queue, int *__restrict__ qtail)
 {
-    __shared__ uint8_t s[CH][CN_SH][CN_SW];
+    __shared__ uint8_t s[CN_SH][CN_SW * CH + 4];      // interleaved channels, as in the source
     __shared__ uint16_t smag[CN_MH][CN_MW];
     __shared__ short2 sgrad[CN_MH][CN_MW];
     __shared__ int s_cnt, s_base;
@@ -49,30 +49,48 @@ __global__ void __launch_bounds__(256) canny_nms_kernel(const uint8_t *__restric
         const int gx = min(max(bx + lx - 2, 0), w - 1), gy = min(max(by + ly - 2, 0), h - 1);  // BORDER_REPLICATE
         const uint8_t *p = src + (size_t)gy * stride + (size_t)gx * CH;
 #pragma unroll
-        for (int c = 0; c < CH; c++) s[c][ly][lx] = p[c];
+        for (int c = 0; c < CH; c++) s[ly][lx * CH + c] = p[c];
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < CN_MW * CN_MH; i += blockDim.x) {
-        const int ly = i / CN_MW, lx = i - ly * CN_MW;
-        const int gx = bx + lx - 1, gy = by + ly - 1;
-        int bm = 0, bdx = 0, bdy = 0;
-        if (gx >= 0 && gx < w && gy >= 0 && gy < h) {
-            bm = -1;
+    // Sobel + L1 magnitude, the channel with the largest magnitude wins (first on ties).  A thread
+    // walks CN_SEG consecutive rows of one column with a three-row window of the horizontal
+    // difference d = right - left and the horizontal smooth sm = left + 2 mid + right, so a
+    // magnitude costs (CN_SEG + 2) / CN_SEG row reads of three bytes per channel instead of eight taps.
+    constexpr int CN_SEG = CN_MH / 3;                 // 18 rows = 3 segments of 6
+    static_assert(CN_SEG * 3 == CN_MH && CN_MW * 3 <= 256, "canny tile / thread mapping");
+    if (threadIdx.x < CN_MW * 3) {
+        const int seg = threadIdx.x / CN_MW, lx = threadIdx.x - seg * CN_MW, ly0 = seg * CN_SEG;
+        const int gx = bx + lx - 1;
+        int bm[CN_SEG], bdx[CN_SEG], bdy[CN_SEG];
 #pragma unroll
-            for (int c = 0; c < CH; c++) {
-                // source tile coordinates of (gx, gy) are (lx + 1, ly + 1)
-                const int a00 = s[c][ly][lx], a01 = s[c][ly][lx + 1], a02 = s[c][ly][lx + 2];
-                const int a10 = s[c][ly + 1][lx], a12 = s[c][ly + 1][lx + 2];
-                const int a20 = s[c][ly + 2][lx], a21 = s[c][ly + 2][lx + 1], a22 = s[c][ly + 2][lx + 2];
-                const int gxv = (a02 + 2 * a12 + a22) - (a00 + 2 * a10 + a20);
-                const int gyv = (a20 + 2 * a21 + a22) - (a00 + 2 * a01 + a02);
+        for (int r = 0; r < CN_SEG; r++) { bm[r] = -1; bdx[r] = 0; bdy[r] = 0; }
+#pragma unroll
+        for (int c = 0; c < CH; c++) {
+            int d[CN_SEG + 2], sm[CN_SEG + 2];
+#pragma unroll
+            for (int r = 0; r < CN_SEG + 2; r++) {
+                // source tile coordinates of magnitude (lx, ly) are (lx + 1, ly + 1): rows ly .. ly + 2
+                const uint8_t *row = &s[ly0 + r][lx * CH + c];
+                const int l = row[0], m = row[CH], rr = row[2 * CH];
+                d[r] = rr - l;
+                sm[r] = l + 2 * m + rr;
+            }
+#pragma unroll
+            for (int r = 0; r < CN_SEG; r++) {
+                const int gxv = d[r] + 2 * d[r + 1] + d[r + 2];
+                const int gyv = sm[r + 2] - sm[r];
                 const int m = abs(gxv) + abs(gyv);
-                if (m > bm) { bm = m; bdx = gxv; bdy = gyv; }
+                if (m > bm[r]) { bm[r] = m; bdx[r] = gxv; bdy[r] = gyv; }
             }
         }
-        // outside the image the magnitude is the zero padding
-        smag[ly][lx] = (uint16_t)bm;
-        sgrad[ly][lx] = make_short2((short)bdx, (short)bdy);
+#pragma unroll
+        for (int r = 0; r < CN_SEG; r++) {
+            const int gy = by + ly0 + r - 1;
+            const bool in = gx >= 0 && gx < w && gy >= 0 && gy < h;
+            // outside the image the magnitude is the zero padding
+            smag[ly0 + r][lx] = (uint16_t)(in ? bm[r] : 0);
+            sgrad[ly0 + r][lx] = in ? make_short2((short)bdx[r], (short)bdy[r]) : make_short2(0, 0);
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < CN_TX * CN_TY; i += blockDim.x) {
