@@ -31,7 +31,7 @@ WHITE = (255, 255, 255, 0)
 
 def build(force: bool = False) -> str:
     """Compile the C restatement into oracle/_ref/ (recipe: oracle/Makefile)."""
-    srcs = [os.path.join(_HERE, f) for f in ("oics_oracle.c", "oics_oracle_lines.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("oics_oracle.c", "oics_oracle_lines.c", "oics_oracle_jpeg.c", "Makefile")]
     if (not force and os.path.exists(_SO)
             and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in srcs)):
         return _SO
@@ -418,3 +418,17 @@ def correct_default(bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max
         angle, need = reconcile(p, e.angle)
     out = rotate_mat(bgr, angle, 1.0, INTER_NEAREST, WHITE, CLIP_CONTAIN)            # omr.rs:408-445
     return angle, need, out
+
+
+# --------------------------------------------------------------------------- N2: imwrite(JPEG, q)
+def jpeg_encode(bgr, quality=100) -> bytes:
+    """TransformableMatrix::im_write(path, JPEG, 100) (transfer.rs:162-179, omr.rs:447-448) ->
+    the bytes cv::imwrite / cv::imencode produce for a BGR image."""
+    bgr, w, h, ch = _img(bgr)
+    assert ch == 3
+    lib().orc_jpeg_encode.restype = C.c_long
+    cap = 4096 + 4 * w * h
+    out = np.empty(cap, np.uint8)
+    n = lib().orc_jpeg_encode(_p(bgr), w, h, w * 3, int(quality), _p(out), C.c_long(cap))
+    assert n <= cap
+    return out[:n].tobytes()

@@ -209,3 +209,18 @@ def test_fft_image_within_one_lsb(orc, small_card):
     diff = np.abs(log8.astype(np.int32) - got.astype(np.int32))
     assert diff.max() <= 1
     assert (diff != 0).mean() <= 1e-3
+
+
+# ----------------------------------------------------------------------------- N2: imwrite(JPEG, q)
+@pytest.mark.parametrize("shape", [(37, 53), (64, 48), (16, 16), (95, 130), (1, 1), (9, 7), (24, 40), (33, 17), (230, 248)])
+def test_jpeg_encode_bytes_equal_cv2(orc, shape):
+    """omr.rs:447-448: the deskewed card is written with imwrite(JPEG, quality 100).  The restatement
+    must produce cv2's file byte for byte (also at a few other qualities)."""
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    img = (rng.random(shape + (3,)) * 255).astype(np.uint8)
+    img[shape[0] // 4:shape[0] // 2, shape[1] // 5:shape[1] // 2] = (10, 200, 90)
+    smooth = cv2.GaussianBlur(img, (7, 7), 2.0)
+    for im in (img, smooth, np.full(shape + (3,), 255, np.uint8)):
+        for q in (100, 95, 75, 30):
+            ref = bytes(cv2.imencode(".jpg", im, [cv2.IMWRITE_JPEG_QUALITY, q])[1])
+            assert orc.jpeg_encode(im, q) == ref, (shape, q)
