@@ -226,6 +226,14 @@ OICS_API int32_t oics_rotate(oics_ctx *ctx, const uint8_t *src, int32_t ch, int3
                              const uint8_t border[4], int32_t clip, uint8_t *dst, size_t dst_cap,
                              int32_t *dst_w, int32_t *dst_h);
 
+/* ---- N2: the file written at the end of omr::correct_default ---------------- */
+/* TransformableMatrix::im_write(path, ImageFormat::JPEG, quality) (transfer.rs:162-179, called with
+ * quality 100 at omr.rs:447-448) = cv::imwrite: the bytes of the JPEG file OpenCV writes for a BGR
+ * image (JFIF, 4:2:0, standard Huffman tables), byte for byte.  bgr and out may be host or device
+ * pointers.  *out_size = file size; OICS_ERR_CAPACITY (with the needed size) if out_cap is too small. */
+OICS_API int32_t oics_jpeg_encode(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h, int32_t stride,
+                                  int32_t quality, uint8_t *out, size_t out_cap, size_t *out_size);
+
 /* ---- one-call pipeline ---------------------------------------------------- */
 /* reconcile rule of omr::correct_default (omr.rs:352-403), host */
 OICS_API int32_t oics_reconcile(const oics_omr_result *projection, double edges_angle, double *angle,

@@ -374,6 +374,18 @@ class Context:
                                     out.ctypes.data, out.size, C.byref(rw), C.byref(rh)))
         return out
 
+    # -- N2: imwrite
+    def jpeg_encode(self, bgr, quality=100, out=None) -> bytes:
+        """TransformableMatrix::im_write(path, JPEG, quality) (transfer.rs:162-179) -> the file's bytes."""
+        p, w, h, ch, stride, keep = _describe(bgr)
+        if ch != 3:
+            raise ValueError("jpeg_encode expects a BGR image")
+        if out is None:
+            out = np.empty(4096 + 4 * w * h, np.uint8)
+        n = C.c_size_t()
+        check(self._lib.oics_jpeg_encode(self._h, p, w, h, stride, int(quality), out.ctypes.data, out.size, C.byref(n)))
+        return out[:n.value].tobytes()
+
     # -- pipeline
     def correct_default(self, bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, want_image=True,
                         out=None):

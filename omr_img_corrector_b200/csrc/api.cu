@@ -448,6 +448,27 @@ OICS_API int32_t oics_result_from_fourier_transform(oics_ctx *ctx, const uint8_t
                         OICS_LINES_OMR, result);
 }
 
+OICS_API int32_t oics_jpeg_encode(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h, int32_t stride,
+                                  int32_t quality, uint8_t *out, size_t out_cap, size_t *out_size)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bgr, w, h, stride, 3));
+    OICS_ARG(out && out_size);
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bgr, (size_t)w * 3, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    if (is_device_ptr(out)) return jpeg_encode_device(ctx, dsrc, w, h, dstride, quality, out, out_cap, out_size);
+    // a file is never larger than a few bytes per pixel; the device copy is sized like the caller's buffer
+    const size_t dcap = std::min(out_cap, (size_t)4096 + (size_t)w * h * 6);
+    OICS_TRY(ctx->out_img2.ensure(dcap));
+    int32_t rc = jpeg_encode_device(ctx, dsrc, w, h, dstride, quality, ctx->out_img2.as<uint8_t>(), dcap, out_size);
+    if (rc != OICS_OK) return rc;
+    OICS_TRY(copy_out(ctx, out, ctx->out_img2.p, *out_size));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
 // correct_default for a BGR card already on the device
 static int32_t correct_one(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint16_t max_angle,
                            double step, int max_w, int max_h, double min_len, double max_gap, uint8_t *dst,

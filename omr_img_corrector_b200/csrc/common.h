@@ -157,6 +157,9 @@ void hough_geometry(int w, int h, double rho, double theta, int *numangle, int *
 // fft.cu
 int32_t fft_image_device(oics_ctx *ctx, const uint8_t *dgray, int w, int h, size_t stride, uint8_t *dmag8,
                          uint8_t *dlog8);
+// N2: imwrite(JPEG, quality) of a BGR image on the device -> file bytes on the device (jpeg.cu)
+int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                           size_t d_cap, size_t *size);
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 

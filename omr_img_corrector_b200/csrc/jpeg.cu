@@ -1,0 +1,541 @@
+// N2 (output side): TransformableMatrix::im_write(path, JPEG, 100) (transfer.rs:162-179,
+// omr.rs:447-448) = cv::imwrite = libjpeg's baseline encoder with OpenCV's defaults (JFIF, 4:2:0,
+// standard Huffman tables, one scan), byte for byte, on the GPU -- so a deskewed card leaves the
+// device as the few-MB file the reference writes instead of 30 MB of pixels.
+//
+//   jpeg_dct_kernel    8 threads per 8x8 block (a thread = a row, then a column): BGR -> Y / Cb / Cr
+//                      (jccolor.c fixed point), h2v2 chroma box average with the alternating bias
+//                      (jcsample.c), edge replication (jcprepct.c), jfdctint.c forward DCT and the
+//                      jcdctmgr.c quantiser; coefficients are stored zigzag-major [k][block] so the
+//                      entropy kernels read them coalesced (lane = block).
+//   jpeg_bits_kernel   one thread per block: resolves the dummy blocks of the right / bottom edge
+//                      (jccoefct.c: AC zero, DC of the previous block), the DC prediction of its
+//                      component, and counts the bits of jchuff.c's encode_one_block.
+//   scan               exclusive prefix sum of the bit counts -> bit offset of every block.
+//   jpeg_emit_kernel   one thread per block: the same walk again, now OR-ing the codes into the
+//                      (zeroed) unstuffed bit stream at the block's offset.
+//   jpeg_stuff_*       0xFF -> 0xFF 0x00: count per 32-byte chunk, scan, scatter behind the header.
+// The header (markers, quantisation and Huffman tables) is built on the host.
+#include <algorithm>
+
+#include "common.h"
+
+namespace oics {
+
+__constant__ uint8_t c_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48,
+                                 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+__constant__ uint8_t c_izz[64];        // natural index -> zigzag position
+__constant__ uint8_t c_quant[2][64];   // natural order: luma, chroma
+__constant__ uint16_t c_hcode[4][256]; // DC luma, AC luma, DC chroma, AC chroma
+__constant__ uint8_t c_hlen[4][256];
+
+static const uint8_t h_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48,
+                                 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+static const uint8_t h_ql[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57,
+                                 69, 56, 14, 17, 22, 29, 51, 87, 80, 62, 18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64,
+                                 81, 104, 113, 92, 49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+static const uint8_t h_qc[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99, 24, 26, 56, 99, 99, 99,
+                                 99, 99, 47, 66, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99,
+                                 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99};
+static const uint8_t h_dc_l_bits[16] = {0, 1, 5, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0};
+static const uint8_t h_dc_c_bits[16] = {0, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0};
+static const uint8_t h_dc_vals[12] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11};
+static const uint8_t h_ac_l_bits[16] = {0, 2, 1, 3, 3, 2, 4, 3, 5, 5, 4, 4, 0, 0, 1, 0x7d};
+static const uint8_t h_ac_l_vals[162] = {
+    0x01, 0x02, 0x03, 0x00, 0x04, 0x11, 0x05, 0x12, 0x21, 0x31, 0x41, 0x06, 0x13, 0x51, 0x61, 0x07, 0x22, 0x71, 0x14, 0x32,
+    0x81, 0x91, 0xa1, 0x08, 0x23, 0x42, 0xb1, 0xc1, 0x15, 0x52, 0xd1, 0xf0, 0x24, 0x33, 0x62, 0x72, 0x82, 0x09, 0x0a, 0x16,
+    0x17, 0x18, 0x19, 0x1a, 0x25, 0x26, 0x27, 0x28, 0x29, 0x2a, 0x34, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44, 0x45,
+    0x46, 0x47, 0x48, 0x49, 0x4a, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68, 0x69,
+    0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7a, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89, 0x8a, 0x92, 0x93, 0x94,
+    0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3, 0xa4, 0xa5, 0xa6, 0xa7, 0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4, 0xb5, 0xb6,
+    0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3, 0xc4, 0xc5, 0xc6, 0xc7, 0xc8, 0xc9, 0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6, 0xd7, 0xd8,
+    0xd9, 0xda, 0xe1, 0xe2, 0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf1, 0xf2, 0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8,
+    0xf9, 0xfa};
+static const uint8_t h_ac_c_bits[16] = {0, 2, 1, 2, 4, 4, 3, 4, 7, 5, 4, 4, 0, 1, 2, 0x77};
+static const uint8_t h_ac_c_vals[162] = {
+    0x00, 0x01, 0x02, 0x03, 0x11, 0x04, 0x05, 0x21, 0x31, 0x06, 0x12, 0x41, 0x51, 0x07, 0x61, 0x71, 0x13, 0x22, 0x32, 0x81,
+    0x08, 0x14, 0x42, 0x91, 0xa1, 0xb1, 0xc1, 0x09, 0x23, 0x33, 0x52, 0xf0, 0x15, 0x62, 0x72, 0xd1, 0x0a, 0x16, 0x24, 0x34,
+    0xe1, 0x25, 0xf1, 0x17, 0x18, 0x19, 0x1a, 0x26, 0x27, 0x28, 0x29, 0x2a, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44,
+    0x45, 0x46, 0x47, 0x48, 0x49, 0x4a, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68,
+    0x69, 0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7a, 0x82, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89, 0x8a, 0x92,
+    0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3, 0xa4, 0xa5, 0xa6, 0xa7, 0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4,
+    0xb5, 0xb6, 0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3, 0xc4, 0xc5, 0xc6, 0xc7, 0xc8, 0xc9, 0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6,
+    0xd7, 0xd8, 0xd9, 0xda, 0xe2, 0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf2, 0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8,
+    0xf9, 0xfa};
+
+struct JpegGeom {
+    int w, h, mcux, mcuy, wibY, hibY, nblocks;   // nblocks = 6 * mcux * mcuy, MCU order: Y00 Y01 Y10 Y11 Cb Cr
+    size_t cstride;                                // blocks per coefficient plane (padded)
+};
+
+#define JFIX13(x) ((int)((x) * 8192.0 + 0.5))
+#define JFIX16(x) ((int)((x) * 65536.0 + 0.5))
+
+// jfdctint.c, one row (first pass) or column (second pass)
+__device__ __forceinline__ void fdct_1d(const int (&x)[8], int (&o)[8], bool first)
+{
+    const int t0 = x[0] + x[7], t7 = x[0] - x[7], t1 = x[1] + x[6], t6 = x[1] - x[6];
+    const int t2 = x[2] + x[5], t5 = x[2] - x[5], t3 = x[3] + x[4], t4 = x[3] - x[4];
+    const int t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+    const int sh = first ? 13 - 2 : 13 + 2;
+    const int rnd = 1 << (sh - 1);
+    if (first) {
+        o[0] = (t10 + t11) * 4;
+        o[4] = (t10 - t11) * 4;
+    } else {
+        o[0] = (t10 + t11 + 2) >> 2;
+        o[4] = (t10 - t11 + 2) >> 2;
+    }
+    int z1 = (t12 + t13) * JFIX13(0.541196100);
+    o[2] = (z1 + t13 * JFIX13(0.765366865) + rnd) >> sh;
+    o[6] = (z1 + t12 * (-JFIX13(1.847759065)) + rnd) >> sh;
+    z1 = t4 + t7;
+    int z2 = t5 + t6, z3 = t4 + t6, z4 = t5 + t7;
+    const int z5 = (z3 + z4) * JFIX13(1.175875602);
+    const int u4 = t4 * JFIX13(0.298631336), u5 = t5 * JFIX13(2.053119869);
+    const int u6 = t6 * JFIX13(3.072711026), u7 = t7 * JFIX13(1.501321110);
+    z1 *= -JFIX13(0.899976223);
+    z2 *= -JFIX13(2.562915447);
+    z3 = z3 * (-JFIX13(1.961570560)) + z5;
+    z4 = z4 * (-JFIX13(0.390180644)) + z5;
+    o[7] = (u4 + z1 + z3 + rnd) >> sh;
+    o[5] = (u5 + z2 + z4 + rnd) >> sh;
+    o[3] = (u6 + z2 + z3 + rnd) >> sh;
+    o[1] = (u7 + z1 + z4 + rnd) >> sh;
+}
+
+// 256 threads = 32 blocks; thread = (block in CTA, row r), then column r
+__global__ void __launch_bounds__(256) jpeg_dct_kernel(const uint8_t *__restrict__ bgr, size_t stride, JpegGeom G,
+                                                       int16_t *__restrict__ coef)
+{
+    __shared__ int sm[32][8][9];
+    const int lb = threadIdx.x >> 3, r = threadIdx.x & 7;
+    const int g = blockIdx.x * 32 + lb;
+    const bool valid = g < G.nblocks;
+    const int mcu = valid ? g / 6 : 0, b = valid ? g - mcu * 6 : 0;
+    const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
+    int x[8], o[8];
+    bool real = valid;
+    if (b < 4) {
+        const int br = my * 2 + (b >> 1), bc = mx * 2 + (b & 1);
+        real = valid && br < G.hibY && bc < G.wibY;        // else a dummy block (resolved by the entropy kernels)
+        const int yy = min(br * 8 + r, G.h - 1);
+        const uint8_t *row = bgr + (size_t)yy * stride;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint8_t *p = row + 3 * min(bc * 8 + i, G.w - 1);
+            x[i] = ((JFIX16(0.29900) * p[2] + JFIX16(0.58700) * p[1] + JFIX16(0.11400) * p[0] + 32768) >> 16) - 128;
+        }
+    } else {
+        const int cy = min(my * 8 + r, (G.h + 1) / 2 - 1);
+        const uint8_t *row0 = bgr + (size_t)min(2 * cy, G.h - 1) * stride, *row1 = bgr + (size_t)min(2 * cy + 1, G.h - 1) * stride;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int cx = mx * 8 + i;
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint8_t *p = ((k & 2) ? row1 : row0) + 3 * min(2 * cx + (k & 1), G.w - 1);
+                const int R = p[2], Gc = p[1], B = p[0];
+                s += b == 4 ? (-JFIX16(0.16874) * R - JFIX16(0.33126) * Gc + JFIX16(0.50000) * B + (128 << 16) + 32767) >> 16
+                            : (JFIX16(0.50000) * R - JFIX16(0.41869) * Gc - JFIX16(0.08131) * B + (128 << 16) + 32767) >> 16;
+            }
+            x[i] = ((s + ((cx & 1) ? 2 : 1)) >> 2) - 128;
+        }
+    }
+    fdct_1d(x, o, true);
+#pragma unroll
+    for (int i = 0; i < 8; i++) sm[lb][r][i] = o[i];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = sm[lb][i][r];      // column r
+    fdct_1d(x, o, false);
+    if (!valid) return;
+    const uint8_t *q = c_quant[b < 4 ? 0 : 1];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {                          // coefficient (row i, column r)
+        const int n = 8 * i + r, d = (int)q[n] << 3, v = o[i];
+        const int qv = real ? (v < 0 ? -((-v + (d >> 1)) / d) : (v + (d >> 1)) / d) : 0;
+        coef[(size_t)c_izz[n] * G.cstride + g] = (int16_t)qv;
+    }
+}
+
+// The resolved DC of block (mcu, b): jccoefct.c fills whole blocks past the right / bottom edge of the
+// luma plane with zero AC and the DC of the previous block of the MCU buffer.
+__device__ __forceinline__ int resolved_dc(const int16_t *__restrict__ coef, const JpegGeom &G, int mcu, int b)
+{
+    if (b < 4) {
+        const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
+        const bool row1_dummy = my * 2 + 1 >= G.hibY, col1_dummy = mx * 2 + 1 >= G.wibY;
+        if ((b >> 1) && row1_dummy) b = 1;                 // dummy row: the last block of the row above
+        if ((b & 1) && col1_dummy) b -= 1;                 // dummy at the right edge: its left neighbour
+    }
+    return coef[(size_t)mcu * 6 + b];                      // zigzag position 0 plane
+}
+
+__device__ __forceinline__ int bit_length(int v) { return 32 - __clz(v); }
+
+// jchuff.c encode_one_block of block g; SINK(code, size) receives every Huffman code and value field
+template <typename SINK>
+__device__ __forceinline__ void walk_block(const int16_t *__restrict__ coef, const JpegGeom &G, int g, SINK &sink)
+{
+    const int mcu = g / 6, b = g - mcu * 6;
+    bool dummy = false;
+    if (b < 4) {
+        const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
+        dummy = my * 2 + (b >> 1) >= G.hibY || mx * 2 + (b & 1) >= G.wibY;
+    }
+    // DC prediction: the previous block of the same component in scan order
+    int pred = 0;
+    if (b < 4) {
+        if (b > 0) pred = resolved_dc(coef, G, mcu, b - 1);
+        else if (mcu > 0) pred = resolved_dc(coef, G, mcu - 1, 3);
+    } else if (mcu > 0) {
+        pred = resolved_dc(coef, G, mcu - 1, b);
+    }
+    const int tdc = b < 4 ? 0 : 2, tac = tdc + 1;
+    int t = resolved_dc(coef, G, mcu, b) - pred, t2 = t;
+    if (t < 0) { t = -t; t2--; }
+    int nb = bit_length(t);
+    sink(c_hcode[tdc][nb], c_hlen[tdc][nb]);
+    sink((unsigned)t2, nb);
+    if (dummy) {                                            // all AC zero
+        sink(c_hcode[tac][0], c_hlen[tac][0]);
+        return;
+    }
+    int r = 0;
+    for (int k = 1; k < 64; k++) {
+        int v = coef[(size_t)k * G.cstride + g];
+        if (v == 0) { r++; continue; }
+        while (r > 15) { sink(c_hcode[tac][0xF0], c_hlen[tac][0xF0]); r -= 16; }
+        t2 = v;
+        if (v < 0) { v = -v; t2--; }
+        nb = bit_length(v);
+        sink(c_hcode[tac][(r << 4) + nb], c_hlen[tac][(r << 4) + nb]);
+        sink((unsigned)t2, nb);
+        r = 0;
+    }
+    if (r > 0) sink(c_hcode[tac][0], c_hlen[tac][0]);
+}
+
+struct CountSink {
+    unsigned n = 0;
+    __device__ __forceinline__ void operator()(unsigned, int size) { n += size; }
+};
+
+__global__ void __launch_bounds__(256) jpeg_bits_kernel(const int16_t *__restrict__ coef, JpegGeom G,
+                                                        unsigned long long *__restrict__ bits)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G.nblocks) return;
+    CountSink s;
+    walk_block(coef, G, g, s);
+    bits[g] = s.n;
+}
+
+// MSB-first bit stream in 32-bit words (word i holds stream bits 32 i .. 32 i + 31, bit 31 first)
+struct EmitSink {
+    uint32_t *words;
+    unsigned long long pos;     // next stream bit
+    unsigned long long acc = 0; // pending bits, right-aligned
+    int n = 0;
+    __device__ __forceinline__ void flush_word()
+    {
+        // the top (32 - pos % 32) pending bits complete word pos / 32
+        const int room = 32 - (int)(pos & 31);
+        const int take = min(room, n);
+        const uint32_t chunk = (uint32_t)((acc >> (n - take)) & ((1ull << take) - 1ull));
+        atomicOr(words + (pos >> 5), chunk << (room - take));
+        pos += take;
+        n -= take;
+    }
+    __device__ __forceinline__ void operator()(unsigned code, int size)
+    {
+        if (!size) return;
+        acc = (acc << size) | (code & ((1u << size) - 1u));
+        n += size;
+        while (n >= 32) flush_word();
+    }
+    __device__ __forceinline__ void finish()
+    {
+        while (n > 0) flush_word();
+    }
+};
+
+__global__ void __launch_bounds__(256) jpeg_emit_kernel(const int16_t *__restrict__ coef, JpegGeom G,
+                                                        const unsigned long long *__restrict__ offs,
+                                                        uint32_t *__restrict__ words)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G.nblocks) return;
+    EmitSink s;
+    s.words = words;
+    s.pos = offs[g];
+    walk_block(coef, G, g, s);
+    s.finish();
+}
+
+// ---------------------------------------------------------------------------
+// exclusive prefix sum of n 64-bit values (in place), total to *total: 1024 values per CTA
+__global__ void __launch_bounds__(1024) scan_block_kernel(unsigned long long *__restrict__ v, size_t n,
+                                                          unsigned long long *__restrict__ sums)
+{
+    __shared__ unsigned long long ws[32];
+    const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long x = i < n ? v[i] : 0ull;
+    unsigned long long s = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += t;
+    }
+    if (lane == 31) ws[warp] = s;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = ws[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        ws[lane] = w;
+    }
+    __syncthreads();
+    const unsigned long long before = (warp ? ws[warp - 1] : 0ull) + s - x;
+    if (i < n) v[i] = before;
+    if (threadIdx.x == 1023) sums[blockIdx.x] = before + x;
+}
+
+// one CTA: exclusive scan of the per-CTA sums (any count), total out
+__global__ void __launch_bounds__(1024) scan_sums_kernel(unsigned long long *__restrict__ sums, int m,
+                                                         unsigned long long *__restrict__ total)
+{
+    __shared__ unsigned long long ws[32];
+    __shared__ unsigned long long carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < m; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned long long x = i < m ? sums[i] : 0ull;
+        unsigned long long s = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) ws[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long w = ws[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            ws[lane] = w;
+        }
+        __syncthreads();
+        const unsigned long long before = carry + (warp ? ws[warp - 1] : 0ull) + s - x;
+        if (i < m) sums[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void __launch_bounds__(1024) scan_add_kernel(unsigned long long *__restrict__ v, size_t n,
+                                                        const unsigned long long *__restrict__ sums)
+{
+    const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
+    if (i < n) v[i] += sums[blockIdx.x];
+}
+
+static int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums,
+                              unsigned long long *total)
+{
+    const int m = (int)((n + 1023) / 1024);
+    scan_block_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums);
+    scan_sums_kernel<<<1, 1024, 0, ctx->stream>>>(sums, m, total);
+    scan_add_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 3;
+    return OICS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// byte stuffing: stream byte j of the MSB-first words; the last byte is padded with ones
+__device__ __forceinline__ uint32_t stream_byte(const uint32_t *__restrict__ words, unsigned long long j,
+                                                unsigned long long nbytes, int pad_bits)
+{
+    uint32_t b = (words[j >> 2] >> (24 - 8 * (int)(j & 3))) & 0xFFu;
+    if (j == nbytes - 1) b |= (1u << pad_bits) - 1u;
+    return b;
+}
+
+__global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *__restrict__ words,
+                                                               const unsigned long long *__restrict__ total_bits,
+                                                               unsigned long long *__restrict__ cnt, size_t nchunks)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nchunks) return;
+    const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
+    const int pad = (int)(8 * nbytes - T);
+    unsigned c = 0;
+    for (unsigned long long j = 32ull * i; j < min(nbytes, 32ull * i + 32ull); j++) c += stream_byte(words, j, nbytes, pad) == 0xFFu;
+    cnt[i] = c;
+}
+
+__global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *__restrict__ words,
+                                                               const unsigned long long *__restrict__ total_bits,
+                                                               const unsigned long long *__restrict__ off, size_t nchunks,
+                                                               uint8_t *__restrict__ out, size_t cap)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nchunks) return;
+    const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
+    const int pad = (int)(8 * nbytes - T);
+    size_t o = 32 * i + (size_t)off[i];
+    const unsigned long long j1 = min(nbytes, 32ull * i + 32ull);
+    for (unsigned long long j = 32ull * i; j < j1; j++) {
+        const uint32_t b = stream_byte(words, j, nbytes, pad);
+        if (o < cap) out[o] = (uint8_t)b;
+        o++;
+        if (b == 0xFFu) {
+            if (o < cap) out[o] = 0;
+            o++;
+        }
+    }
+    if (j1 == nbytes) {   // EOI behind the last data byte
+        if (o < cap) out[o] = 0xFF;
+        if (o + 1 < cap) out[o + 1] = 0xD9;
+    }
+}
+
+// ---------------------------------------------------------------------------
+static void host_quant(const uint8_t *base, int quality, uint8_t *out)   // jcparam.c, force_baseline
+{
+    quality = std::min(100, std::max(1, quality));
+    const int scale = quality < 50 ? 5000 / quality : 200 - quality * 2;
+    for (int i = 0; i < 64; i++) out[i] = (uint8_t)std::min(255L, std::max(1L, ((long)base[i] * scale + 50L) / 100L));
+}
+
+static void host_huff(const uint8_t *bits, const uint8_t *vals, uint16_t *code, uint8_t *len)
+{
+    memset(code, 0, 256 * sizeof(uint16_t));
+    memset(len, 0, 256);
+    unsigned c = 0;
+    int k = 0;
+    for (int l = 1; l <= 16; l++) {
+        for (int i = 0; i < bits[l - 1]; i++, k++) {
+            code[vals[k]] = (uint16_t)c++;
+            len[vals[k]] = (uint8_t)l;
+        }
+        c <<= 1;
+    }
+}
+
+static size_t host_header(int w, int h, const uint8_t *ql, const uint8_t *qc, uint8_t *o)
+{
+    size_t n = 0;
+    auto put = [&](std::initializer_list<int> b) { for (int v : b) o[n++] = (uint8_t)v; };
+    put({0xFF, 0xD8, 0xFF, 0xE0, 0, 16, 'J', 'F', 'I', 'F', 0, 1, 1, 0, 0, 1, 0, 1, 0, 0});
+    for (int t = 0; t < 2; t++) {
+        put({0xFF, 0xDB, 0, 67, t});
+        for (int k = 0; k < 64; k++) o[n++] = (t ? qc : ql)[h_zz[k]];
+    }
+    put({0xFF, 0xC0, 0, 17, 8, h >> 8, h & 255, w >> 8, w & 255, 3, 1, 0x22, 0, 2, 0x11, 1, 3, 0x11, 1});
+    const struct { int id; const uint8_t *bits, *vals; int nv; } dht[4] = {
+        {0x00, h_dc_l_bits, h_dc_vals, 12}, {0x10, h_ac_l_bits, h_ac_l_vals, 162},
+        {0x01, h_dc_c_bits, h_dc_vals, 12}, {0x11, h_ac_c_bits, h_ac_c_vals, 162}};
+    for (const auto &d : dht) {
+        const int L = 2 + 1 + 16 + d.nv;
+        put({0xFF, 0xC4, L >> 8, L & 255, d.id});
+        for (int i = 0; i < 16; i++) o[n++] = d.bits[i];
+        for (int i = 0; i < d.nv; i++) o[n++] = d.vals[i];
+    }
+    put({0xFF, 0xDA, 0, 12, 3, 1, 0x00, 2, 0x11, 3, 0x11, 0, 0x3F, 0});
+    return n;
+}
+
+// BGR image on the device -> JPEG file bytes on the device (d_out, capacity d_cap); *size = file size
+// (OICS_ERR_CAPACITY with the needed size if it does not fit).
+int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                           size_t d_cap, size_t *size)
+{
+    cudaStream_t st = ctx->stream;
+    if (w <= 0 || h <= 0 || w > 65535 || h > 65535) {
+        set_error("jpeg: image size %dx%d is outside 1..65535", w, h);
+        return OICS_ERR_INVALID_ARG;
+    }
+    JpegGeom G;
+    G.w = w; G.h = h;
+    G.mcux = cdiv(w, 16); G.mcuy = cdiv(h, 16);
+    G.wibY = cdiv(w, 8); G.hibY = cdiv(h, 8);
+    G.nblocks = 6 * G.mcux * G.mcuy;
+    G.cstride = ((size_t)G.nblocks + 63) & ~(size_t)63;
+    // tables
+    uint8_t q[2][64], izz[64], hlen[4][256], header[1024];
+    uint16_t hcode[4][256];
+    host_quant(h_ql, quality, q[0]);
+    host_quant(h_qc, quality, q[1]);
+    for (int k = 0; k < 64; k++) izz[h_zz[k]] = (uint8_t)k;
+    host_huff(h_dc_l_bits, h_dc_vals, hcode[0], hlen[0]);
+    host_huff(h_ac_l_bits, h_ac_l_vals, hcode[1], hlen[1]);
+    host_huff(h_dc_c_bits, h_dc_vals, hcode[2], hlen[2]);
+    host_huff(h_ac_c_bits, h_ac_c_vals, hcode[3], hlen[3]);
+    const size_t hdr = host_header(w, h, q[0], q[1], header);
+    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_quant, q, sizeof(q), 0, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_izz, izz, sizeof(izz), 0, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_hcode, hcode, sizeof(hcode), 0, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_hlen, hlen, sizeof(hlen), 0, cudaMemcpyHostToDevice, st));
+    if (hdr + 2 > d_cap) { *size = hdr + 2; set_error("jpeg: output capacity %zu is below the header", d_cap); return OICS_ERR_CAPACITY; }
+    OICS_CUDA_TRY(cudaMemcpyAsync(d_out, header, hdr, cudaMemcpyHostToDevice, st));
+    // scratch: cplx = coefficients, labels = bit counts / offsets + scan sums + totals, cplx2 = bit stream
+    const size_t nb = (size_t)G.nblocks;
+    OICS_TRY(ctx->cplx.ensure(64 * G.cstride * sizeof(int16_t)));
+    const size_t nsums = (nb + 1023) / 1024 + 8;
+    OICS_TRY(ctx->labels.ensure((nb + nsums + 8) * sizeof(unsigned long long)));
+    int16_t *coef = ctx->cplx.as<int16_t>();
+    unsigned long long *bits = ctx->labels.as<unsigned long long>(), *sums = bits + nb, *totals = sums + nsums;
+    jpeg_dct_kernel<<<cdiv(G.nblocks, 32), 256, 0, st>>>(dbgr, stride, G, coef);
+    jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 2;
+    OICS_TRY(exclusive_scan(ctx, bits, nb, sums, totals));
+    unsigned long long total_bits = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&total_bits, totals, sizeof(total_bits), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));   // also: the host tables above have been consumed
+    const size_t nbytes = (size_t)((total_bits + 7) >> 3), nwords = (nbytes + 3) / 4 + 2;
+    OICS_TRY(ctx->cplx2.ensure(nwords * sizeof(uint32_t)));
+    uint32_t *words = ctx->cplx2.as<uint32_t>();
+    OICS_CUDA_TRY(cudaMemsetAsync(words, 0, nwords * sizeof(uint32_t), st));
+    jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, words);
+    const size_t nchunks = (nbytes + 31) / 32;
+    const size_t nsums2 = (nchunks + 1023) / 1024 + 8;
+    OICS_TRY(ctx->mag.ensure((nchunks + nsums2 + 8) * sizeof(unsigned long long)));
+    unsigned long long *cnt = ctx->mag.as<unsigned long long>(), *sums2 = cnt + nchunks, *total_ff = sums2 + nsums2;
+    jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, totals, cnt, nchunks);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 2;
+    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums2, total_ff));
+    jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, totals, cnt, nchunks, d_out + hdr,
+                                                                                    d_cap - hdr);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    unsigned long long nff = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&nff, total_ff, sizeof(nff), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    *size = hdr + nbytes + (size_t)nff + 2;
+    if (*size > d_cap) {
+        set_error("jpeg: the file needs %zu bytes, capacity %zu", *size, d_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    return OICS_OK;
+}
+
+}  // namespace oics

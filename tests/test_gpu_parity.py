@@ -526,3 +526,26 @@ def test_task_runner_matches_correct_default(ctx, orc, dataset_like):
         ra, rneed, rout = orc.correct_default(c, *params)
         assert done[i] == ("debatable" if rneed else "finished")
         assert np.array_equal(written[f"o{i}"], rout)
+
+
+# ----------------------------------------------------------------------------- N2: imwrite(JPEG, q)
+@pytest.mark.parametrize("shape", [(37, 53), (64, 48), (16, 16), (95, 130), (1, 1), (9, 7), (24, 40), (33, 17), (230, 248)])
+def test_jpeg_encode_bytes(ctx, orc, shape):
+    """omr.rs:447-448 imwrite(JPEG, 100): the CUDA encoder returns the oracle's (= cv2's) file byte for byte."""
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    img = (rng.random(shape + (3,)) * 255).astype(np.uint8)
+    img[shape[0] // 4:shape[0] // 2, shape[1] // 5:shape[1] // 2] = (10, 200, 90)
+    for im in (img, np.full(shape + (3,), 255, np.uint8), np.zeros(shape + (3,), np.uint8)):
+        for q in (100, 95, 75, 30):
+            assert ctx.jpeg_encode(im, q) == orc.jpeg_encode(im, q), (shape, q)
+
+
+def test_jpeg_encode_deskewed_a4_card(ctx, orc, a4_card):
+    """The file correct_default writes for the A4 card (CONTAIN-deskewed, odd size), quality 100."""
+    bgr, a = a4_card
+    out = ctx.rotate_mat(bgr, a, 1.0, api.INTER_NEAREST, api.WHITE, api.CLIP_CONTAIN)
+    ref = orc.jpeg_encode(out, 100)
+    got = ctx.jpeg_encode(out, 100)
+    assert len(got) == len(ref) and got == ref
+    import torch                                            # device-resident input
+    assert ctx.jpeg_encode(torch.from_numpy(out).cuda(), 100) == ref
