@@ -295,6 +295,30 @@ def run_gpu(args, rank, local_rank, world):
                "h2d_bytes_per_step": int(E * W * H * 3), "d2h_bytes_per_step": d2h + E * 16,
                "cards_per_gpu_per_step": E, "steps": ksteps, "mismatches": len(e2e_bad), "numa_node": numa}
 
+        # the same call with the reference's own output format: correct_default ends by writing the deskewed
+        # card as a JPEG of quality 100 (omr.rs:447-448); the file bytes come back instead of the pixels
+        def e2e_jpeg_step():
+            return ctx.correct_batch(hin, MAX_ANGLE, STEP, 0, 0, 125.0, 15.0, outs=outs, jpeg_quality=100)
+
+        for _ in range(2):
+            ang2, need2, stat2, sizes2, fsz = e2e_jpeg_step()
+        jbad = int(sum(1 for i in range(E) if stat2[i] != 0 or ang2[i] != ang[i]))
+        barrier()
+        j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        j0.record(stream)
+        for _ in range(ksteps):
+            e2e_jpeg_step()
+        j1.record(stream)
+        j1.synchronize()
+        barrier()
+        t_j = torch.tensor([j0.elapsed_time(j1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_j, op=dist.ReduceOp.MAX)
+        e2e["jpeg_out"] = {"value": world * E * ksteps / (float(t_j.item()) / 1000.0), "unit": UNIT,
+                           "what": "same call, deskewed cards returned as the JPEG (quality 100) files omr::correct_default writes",
+                           "h2d_bytes_per_step": int(E * W * H * 3), "d2h_bytes_per_step": int(fsz.sum()) + E * 16,
+                           "mismatches": jbad}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

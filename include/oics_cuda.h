@@ -257,6 +257,15 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
                                     uint8_t *const *dsts, const size_t *dst_caps, int32_t *dst_ws,
                                     int32_t *dst_hs, double *angles, int32_t *need_checks,
                                     int32_t *statuses);
+/* The same with the output side of omr::correct_default included (omr.rs:447-448): dsts[c] receives the
+ * JPEG file imwrite(JPEG, jpeg_quality) would write for card c (the reference uses 100), dst_sizes[c]
+ * its size -- a few MB cross PCIe instead of the 30 MB of pixels. */
+OICS_API int32_t oics_correct_batch_jpeg(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
+                                         int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
+                                         int32_t max_w, int32_t max_h, double hough_min_line_length,
+                                         double hough_max_line_gap, int32_t jpeg_quality, uint8_t *const *dsts,
+                                         const size_t *dst_caps, size_t *dst_sizes, int32_t *dst_ws, int32_t *dst_hs,
+                                         double *angles, int32_t *need_checks, int32_t *statuses);
 
 #ifdef __cplusplus
 }

@@ -410,10 +410,13 @@ class Context:
         img = out[:dw.value * dh.value * 3].reshape(dh.value, dw.value, 3) if want_image else None
         return a.value, bool(need.value), img
 
-    def correct_batch(self, bgrs, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, outs=None):
+    def correct_batch(self, bgrs, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, outs=None,
+                      jpeg_quality=None):
         """bgrs: numpy [n, h, w, 3] (host) or CUDA tensor of that shape.
         outs: optional list of n writable uint8 numpy buffers for the deskewed cards.
-        -> (angles, need_checks, statuses, dst sizes [n, 2])"""
+        jpeg_quality: None -> the buffers receive BGR pixels; 1..100 -> the JPEG file imwrite would write
+        (omr.rs:447-448 uses 100) and a fifth return value holds the file sizes.
+        -> (angles, need_checks, statuses, dst sizes [n, 2][, file sizes])"""
         if isinstance(bgrs, np.ndarray):
             bgrs = np.ascontiguousarray(bgrs, np.uint8)
             ptr = bgrs.ctypes.data
@@ -429,11 +432,18 @@ class Context:
             dsts = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
             caps = (C.c_size_t * n)(*[o.size for o in outs])
         ip = C.POINTER(C.c_int32)
-        check(self._lib.oics_correct_batch(self._h, ptr, n, w * h * 3, w, h, w * 3, int(max_angle), float(step), max_w,
-                                           max_h, float(hough_min_len), float(hough_max_gap), dsts, caps,
-                                           sizes[0].ctypes.data_as(ip), sizes[1].ctypes.data_as(ip), _dptr(angles),
-                                           needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
-        return angles, needs.astype(bool), stats, sizes.T.copy()
+        if jpeg_quality is None:
+            check(self._lib.oics_correct_batch(self._h, ptr, n, w * h * 3, w, h, w * 3, int(max_angle), float(step), max_w,
+                                               max_h, float(hough_min_len), float(hough_max_gap), dsts, caps,
+                                               sizes[0].ctypes.data_as(ip), sizes[1].ctypes.data_as(ip), _dptr(angles),
+                                               needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
+            return angles, needs.astype(bool), stats, sizes.T.copy()
+        fsz = (C.c_size_t * n)()
+        check(self._lib.oics_correct_batch_jpeg(self._h, ptr, n, w * h * 3, w, h, w * 3, int(max_angle), float(step), max_w,
+                                                max_h, float(hough_min_len), float(hough_max_gap), int(jpeg_quality), dsts,
+                                                caps, fsz, sizes[0].ctypes.data_as(ip), sizes[1].ctypes.data_as(ip),
+                                                _dptr(angles), needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
+        return angles, needs.astype(bool), stats, sizes.T.copy(), np.array(list(fsz), np.int64)
 
 
 _default = {}

@@ -539,17 +539,20 @@ OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t
 // deskew (ctx stream: pre-processing and ONE fused sweep launch per sub-batch, exact rule A on
 // the host, one warp per card), download (side stream) -- so PCIe in both directions overlaps
 // the kernels.  Host buffers should be pinned for the copies to be asynchronous.
-OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
-                                    int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
-                                    int32_t max_w, int32_t max_h, double hough_min_line_length,
-                                    double hough_max_line_gap, uint8_t *const *dsts, const size_t *dst_caps,
-                                    int32_t *dst_ws, int32_t *dst_hs, double *angles, int32_t *need_checks,
-                                    int32_t *statuses)
+// jpeg_quality == 0: dsts receive the deskewed BGR pixels; 1..100: the JPEG file imwrite would produce
+// (omr.rs:447-448 writes quality 100), its size in dst_sizes.
+static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride, int32_t w,
+                                  int32_t h, int32_t stride, uint16_t max_angle, double step, int32_t max_w,
+                                  int32_t max_h, double hough_min_line_length, double hough_max_line_gap,
+                                  int32_t jpeg_quality, uint8_t *const *dsts, const size_t *dst_caps, size_t *dst_sizes,
+                                  int32_t *dst_ws, int32_t *dst_hs, double *angles, int32_t *need_checks,
+                                  int32_t *statuses)
 {
     CtxGuard g(ctx);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgrs, w, h, stride, 3));
     OICS_ARG(n_cards >= 0 && angles && need_checks && statuses);
+    OICS_ARG(jpeg_quality >= 0 && jpeg_quality <= 100 && (!jpeg_quality || !dsts || dst_sizes));
     OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
     OICS_ARG(!dsts || dst_caps);
     if (n_cards == 0) return OICS_OK;
@@ -576,6 +579,7 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
     bool host_out = false;
     if (dsts)
         for (int c = 0; c < n_cards; c++) host_out = host_out || (dsts[c] && !is_device_ptr(dsts[c]));
+    if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_raw.ensure(out_card_cap));   // the deskewed pixels of the card being encoded
 
     int32_t rc = OICS_OK;
     auto cleanup = [&]() {
@@ -672,8 +676,33 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
             if (dst_ws) dst_ws[c] = dw;
             if (dst_hs) dst_hs[c] = dh;
             uint8_t *dst = dsts ? dsts[c] : nullptr;
-            if (stc == OICS_OK && dst) {
+            if (dst_sizes) dst_sizes[c] = 0;
+            if (stc == OICS_OK && dst && jpeg_quality) {
+                // deskew into the raw scratch, encode into the caller's device buffer or the download slot
                 const size_t need_bytes = (size_t)dw * 3 * dh;
+                size_t fsz = 0;
+                if (need_bytes > out_card_cap) {
+                    set_error("internal: CONTAIN bound %zu < %zu", out_card_cap, need_bytes);
+                    stc = OICS_ERR_CAPACITY;
+                } else {
+                    stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white, ctx->jpeg_raw.as<uint8_t>(), dw, dh,
+                                      (size_t)dw * 3);
+                    if (stc == OICS_OK) {
+                        if (is_device_ptr(dst)) {
+                            stc = jpeg_encode_device(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality, dst,
+                                                     dst_caps[c], &fsz);
+                        } else {
+                            out_off[i] = (size_t)i * out_card_cap;
+                            stc = jpeg_encode_device(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality,
+                                                     out_slot[s]->as<uint8_t>() + out_off[i], std::min(out_card_cap, dst_caps[c]), &fsz);
+                            if (stc == OICS_OK) out_bytes[i] = fsz;
+                        }
+                    }
+                }
+                dst_sizes[c] = fsz;
+            } else if (stc == OICS_OK && dst) {
+                const size_t need_bytes = (size_t)dw * 3 * dh;
+                if (dst_sizes) dst_sizes[c] = need_bytes;
                 if (need_bytes > dst_caps[c]) {
                     set_error("deskewed card needs %zu bytes, capacity %zu", need_bytes, dst_caps[c]);
                     stc = OICS_ERR_CAPACITY;
@@ -711,6 +740,31 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
 #undef OICS_BATCH_TRY
 #undef OICS_BATCH_CUDA
     return rc;
+}
+
+OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
+                                    int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
+                                    int32_t max_w, int32_t max_h, double hough_min_line_length,
+                                    double hough_max_line_gap, uint8_t *const *dsts, const size_t *dst_caps,
+                                    int32_t *dst_ws, int32_t *dst_hs, double *angles, int32_t *need_checks,
+                                    int32_t *statuses)
+{
+    return correct_batch_impl(ctx, bgrs, n_cards, card_stride, w, h, stride, max_angle, step, max_w, max_h,
+                              hough_min_line_length, hough_max_line_gap, 0, dsts, dst_caps, nullptr, dst_ws, dst_hs, angles,
+                              need_checks, statuses);
+}
+
+OICS_API int32_t oics_correct_batch_jpeg(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,
+                                         int32_t w, int32_t h, int32_t stride, uint16_t max_angle, double step,
+                                         int32_t max_w, int32_t max_h, double hough_min_line_length,
+                                         double hough_max_line_gap, int32_t jpeg_quality, uint8_t *const *dsts,
+                                         const size_t *dst_caps, size_t *dst_sizes, int32_t *dst_ws, int32_t *dst_hs,
+                                         double *angles, int32_t *need_checks, int32_t *statuses)
+{
+    OICS_ARG(jpeg_quality >= 1 && jpeg_quality <= 100);
+    return correct_batch_impl(ctx, bgrs, n_cards, card_stride, w, h, stride, max_angle, step, max_w, max_h,
+                              hough_min_line_length, hough_max_line_gap, jpeg_quality, dsts, dst_caps, dst_sizes, dst_ws,
+                              dst_hs, angles, need_checks, statuses);
 }
 
 }  // extern "C"

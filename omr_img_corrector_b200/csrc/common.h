@@ -102,7 +102,7 @@ struct oics_ctx {
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;
-    oics::DevBuf wplanes, wmeta, wlists;
+    oics::DevBuf wplanes, wmeta, wlists, jpeg_raw;
     oics::SweepCache sweep_cache;
 };
 

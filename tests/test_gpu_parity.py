@@ -549,3 +549,23 @@ def test_jpeg_encode_deskewed_a4_card(ctx, orc, a4_card):
     assert len(got) == len(ref) and got == ref
     import torch                                            # device-resident input
     assert ctx.jpeg_encode(torch.from_numpy(out).cuda(), 100) == ref
+
+
+def test_correct_batch_jpeg_files(ctx, orc, dataset_like):
+    """oics_correct_batch_jpeg: the whole of omr::correct_default including its imwrite(JPEG, 100)
+    (omr.rs:339-452) -- every returned file equals the oracle's encoding of the oracle's deskewed card."""
+    bgr, _ = dataset_like
+    base = np.ascontiguousarray(bgr[100:400, 200:460])
+    blank = np.full((300, 260, 3), 255, np.uint8)
+    blank[40:43, 30:230] = 0
+    blank[45:240, 60:63] = 0
+    cards = [orc.rotate_mat(base, -4.0 + 0.75 * i, 1.0, 1, orc.WHITE, 0) if i % 5 != 3 else blank for i in range(11)]
+    params = (5, 0.5, 0, 0, 50.0, 5.0)
+    outs = [np.zeros(520 * 520 * 3, np.uint8) for _ in cards]
+    ang, need, stat, sizes, fsz = ctx.correct_batch(np.stack(cards), *params, outs=outs, jpeg_quality=100)
+    assert not stat.any()
+    for i, c in enumerate(cards):
+        ra, rneed, rout = orc.correct_default(c, *params)
+        assert (ang[i], bool(need[i])) == (ra, bool(rneed))
+        assert tuple(sizes[i]) == (rout.shape[1], rout.shape[0])
+        assert outs[i][:fsz[i]].tobytes() == orc.jpeg_encode(rout, 100), i
