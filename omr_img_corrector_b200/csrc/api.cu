@@ -579,6 +579,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     bool host_out = false;
     if (dsts)
         for (int c = 0; c < n_cards; c++) host_out = host_out || (dsts[c] && !is_device_ptr(dsts[c]));
+    if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_totals.ensure((size_t)B * 2 * sizeof(unsigned long long)));
     if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_raw.ensure(out_card_cap));   // the deskewed pixels of the card being encoded
 
     int32_t rc = OICS_OK;
@@ -650,7 +651,8 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                                     v.data(), hh.data(), nullptr, nullptr));
         // exact rule A (+ Hough fallback and reconcile, omr.rs:352-403) per card on the host
         if (host_out && k >= 2) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, out_free[s], 0));
-        std::vector<size_t> out_off((size_t)nb, 0), out_bytes((size_t)nb, 0);
+        std::vector<size_t> out_off((size_t)nb, 0), out_bytes((size_t)nb, 0), jpeg_cap((size_t)nb, 0);
+        size_t jpeg_hdr = 0;
         for (int i = 0; i < nb; i++) {
             const int c = c0 + i;
             const uint8_t *card = dsrc + (size_t)i * dcard;
@@ -680,7 +682,6 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             if (stc == OICS_OK && dst && jpeg_quality) {
                 // deskew into the raw scratch, encode into the caller's device buffer or the download slot
                 const size_t need_bytes = (size_t)dw * 3 * dh;
-                size_t fsz = 0;
                 if (need_bytes > out_card_cap) {
                     set_error("internal: CONTAIN bound %zu < %zu", out_card_cap, need_bytes);
                     stc = OICS_ERR_CAPACITY;
@@ -688,18 +689,19 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                     stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white, ctx->jpeg_raw.as<uint8_t>(), dw, dh,
                                       (size_t)dw * 3);
                     if (stc == OICS_OK) {
-                        if (is_device_ptr(dst)) {
-                            stc = jpeg_encode_device(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality, dst,
-                                                     dst_caps[c], &fsz);
-                        } else {
+                        // no host round trip here: the sizes of the sub-batch are read back together below
+                        uint8_t *file = dst;
+                        size_t cap = dst_caps[c];
+                        if (!is_device_ptr(dst)) {
                             out_off[i] = (size_t)i * out_card_cap;
-                            stc = jpeg_encode_device(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality,
-                                                     out_slot[s]->as<uint8_t>() + out_off[i], std::min(out_card_cap, dst_caps[c]), &fsz);
-                            if (stc == OICS_OK) out_bytes[i] = fsz;
+                            file = out_slot[s]->as<uint8_t>() + out_off[i];
+                            cap = std::min(out_card_cap, dst_caps[c]);
                         }
+                        stc = jpeg_encode_enqueue(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality, file, cap,
+                                                  ctx->jpeg_totals.as<unsigned long long>() + 2 * i, &jpeg_hdr);
+                        if (stc == OICS_OK) jpeg_cap[i] = cap;
                     }
                 }
-                dst_sizes[c] = fsz;
             } else if (stc == OICS_OK && dst) {
                 const size_t need_bytes = (size_t)dw * 3 * dh;
                 if (dst_sizes) dst_sizes[c] = need_bytes;
@@ -725,6 +727,23 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (!dev_in) {
             OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
             if (k + 2 < n_sub) OICS_BATCH_CUDA(upload(k + 2));
+        }
+        if (jpeg_quality && dsts) {   // file sizes of the sub-batch: one read-back
+            std::vector<unsigned long long> totals((size_t)2 * nb, 0ull);
+            OICS_BATCH_CUDA(cudaMemcpyAsync(totals.data(), ctx->jpeg_totals.p, totals.size() * sizeof(unsigned long long),
+                                            cudaMemcpyDeviceToHost, st));
+            OICS_BATCH_CUDA(cudaStreamSynchronize(st));
+            for (int i = 0; i < nb; i++) {
+                if (!jpeg_cap[i]) continue;
+                const size_t fsz = jpeg_file_size(jpeg_hdr, &totals[(size_t)2 * i]);
+                dst_sizes[c0 + i] = fsz;
+                if (fsz > jpeg_cap[i]) {
+                    set_error("jpeg: the file needs %zu bytes, capacity %zu", fsz, jpeg_cap[i]);
+                    statuses[c0 + i] = OICS_ERR_CAPACITY;
+                } else if (!is_device_ptr(dsts[c0 + i])) {
+                    out_bytes[i] = fsz;
+                }
+            }
         }
         if (host_out) {
             OICS_BATCH_CUDA(cudaEventRecord(out_ready[s], st));

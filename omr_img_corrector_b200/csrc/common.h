@@ -102,7 +102,11 @@ struct oics_ctx {
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;
-    oics::DevBuf wplanes, wmeta, wlists, jpeg_raw;
+    oics::DevBuf wplanes, wmeta, wlists, jpeg_raw, jpeg_hdr, jpeg_totals;
+    // jpeg.cu: the file header of the last quality used (host copy and its device cache)
+    int jpeg_hdr_quality = 0, jpeg_hdr_sof = 0;
+    size_t jpeg_hdr_len = 0;
+    uint8_t jpeg_hdr_host[1024];
     oics::SweepCache sweep_cache;
 };
 
@@ -160,6 +164,10 @@ int32_t fft_image_device(oics_ctx *ctx, const uint8_t *dgray, int w, int h, size
 // N2: imwrite(JPEG, quality) of a BGR image on the device -> file bytes on the device (jpeg.cu)
 int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
                            size_t d_cap, size_t *size);
+
+int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len);
+size_t jpeg_file_size(size_t hdr_len, const unsigned long long *totals);
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 

@@ -17,16 +17,13 @@
 //   jpeg_stuff_*       0xFF -> 0xFF 0x00: count per 32-byte chunk, scan, scatter behind the header.
 // The header (markers, quantisation and Huffman tables) is built on the host.
 #include <algorithm>
+#include <mutex>
 
 #include "common.h"
 
 namespace oics {
 
-__constant__ uint8_t c_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48,
-                                 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
-                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 __constant__ uint8_t c_izz[64];        // natural index -> zigzag position
-__constant__ uint8_t c_quant[2][64];   // natural order: luma, chroma
 __constant__ uint16_t c_hcode[4][256]; // DC luma, AC luma, DC chroma, AC chroma
 __constant__ uint8_t c_hlen[4][256];
 
@@ -106,59 +103,141 @@ __device__ __forceinline__ void fdct_1d(const int (&x)[8], int (&o)[8], bool fir
     o[1] = (u7 + z1 + z4 + rnd) >> sh;
 }
 
-// 256 threads = 32 blocks; thread = (block in CTA, row r), then column r
-__global__ void __launch_bounds__(256) jpeg_dct_kernel(const uint8_t *__restrict__ bgr, size_t stride, JpegGeom G,
-                                                       int16_t *__restrict__ coef)
+// One CTA = JD_MCU consecutive MCUs of one MCU row (16 rows x 128 pixels), 8 threads per 8x8 block.
+//   1. the 16 source rows are staged with aligned 32-bit loads (every pixel is read from HBM once);
+//   2. one thread per 2x2 pixel quad: four Y samples and the box-averaged Cb / Cr sample -> int8 planes;
+//   3. thread = a row of its block, then a column (jfdctint.c), quantiser, zigzag;
+//   4. the CTA's coefficients leave as 32-bit stores, 96 contiguous bytes per zigzag plane.
+#define JD_MCU 8
+#define JD_BLOCKS (JD_MCU * 6)
+#define JD_T (JD_BLOCKS * 8)
+#define JD_ROWW (JD_MCU * 12 + 1)   // words per staged row: 384 bytes + up to 3 bytes of misalignment
+
+struct JpegQuant {
+    uint8_t q[2][64];     // natural order: luma, chroma
+    float rcp[2][64];     // 1 / (8 q)
+};
+
+__global__ void __launch_bounds__(JD_T) jpeg_dct_kernel(const uint8_t *__restrict__ bgr, size_t stride, JpegGeom G,
+                                                        JpegQuant Q, int strips, int16_t *__restrict__ coef)
 {
-    __shared__ int sm[32][8][9];
-    const int lb = threadIdx.x >> 3, r = threadIdx.x & 7;
-    const int g = blockIdx.x * 32 + lb;
-    const bool valid = g < G.nblocks;
-    const int mcu = valid ? g / 6 : 0, b = valid ? g - mcu * 6 : 0;
-    const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
-    int x[8], o[8];
-    bool real = valid;
-    if (b < 4) {
-        const int br = my * 2 + (b >> 1), bc = mx * 2 + (b & 1);
-        real = valid && br < G.hibY && bc < G.wibY;        // else a dummy block (resolved by the entropy kernels)
-        const int yy = min(br * 8 + r, G.h - 1);
-        const uint8_t *row = bgr + (size_t)yy * stride;
+    __shared__ uint32_t sraw[16][JD_ROWW];
+    __shared__ int smis[16];
+    // row pitches chosen so that the 8 rows a block's threads read fall into different banks
+    __shared__ __align__(8) int8_t sY[16][JD_MCU * 16 + 16];
+    __shared__ __align__(8) int8_t sC[2][8][JD_MCU * 8 + 8];
+    __shared__ int sT[JD_BLOCKS][8][9];
+    __shared__ __align__(4) int16_t sO[64][JD_BLOCKS + 2];
+    __shared__ float sRcp[2][64];
+    __shared__ uint16_t sD[2][64];
+    __shared__ uint8_t sIzz[64];
+    const int tid = threadIdx.x;
+    if (tid < 128) {
+        sRcp[tid >> 6][tid & 63] = Q.rcp[tid >> 6][tid & 63];
+        sD[tid >> 6][tid & 63] = (uint16_t)((int)Q.q[tid >> 6][tid & 63] << 3);
+        if (tid < 64) sIzz[tid] = c_izz[tid];
+    }
+    const int my = blockIdx.x / strips, mx0 = (blockIdx.x - my * strips) * JD_MCU;
+    const int nm = min(JD_MCU, G.mcux - mx0);
+    // 1. stage
+    {
+        const uintptr_t last_word = ((uintptr_t)bgr + (size_t)(G.h - 1) * stride + 3 * (size_t)G.w - 1) & ~(uintptr_t)3;
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const uint8_t *p = row + 3 * min(bc * 8 + i, G.w - 1);
-            x[i] = ((JFIX16(0.29900) * p[2] + JFIX16(0.58700) * p[1] + JFIX16(0.11400) * p[0] + 32768) >> 16) - 128;
+        for (int it = 0; it < (16 * JD_ROWW + JD_T - 1) / JD_T; it++) {
+            const int t = tid + it * JD_T;
+            if (t >= 16 * JD_ROWW) break;
+            const int rr = t / JD_ROWW, j = t - rr * JD_ROWW;
+            const uintptr_t a = (uintptr_t)bgr + (size_t)min(my * 16 + rr, G.h - 1) * stride + (size_t)mx0 * 48;
+            if (j == 0) smis[rr] = (int)(a & 3);
+            sraw[rr][j] = __ldg((const uint32_t *)min((a & ~(uintptr_t)3) + 4 * (uintptr_t)j, last_word));
         }
-    } else {
-        const int cy = min(my * 8 + r, (G.h + 1) / 2 - 1);
-        const uint8_t *row0 = bgr + (size_t)min(2 * cy, G.h - 1) * stride, *row1 = bgr + (size_t)min(2 * cy + 1, G.h - 1) * stride;
+    }
+    __syncthreads();
+    // 2. colour conversion (jccolor.c) and h2v2 downsampling (jcsample.c); edges by index clamping
+    for (int qd = tid; qd < JD_MCU * 64; qd += JD_T) {
+        const int qy = qd / (JD_MCU * 8), qx = qd - qy * (JD_MCU * 8);
+        const int lc0 = min(mx0 * 16 + 2 * qx, G.w - 1) - mx0 * 16, lc1 = min(mx0 * 16 + 2 * qx + 1, G.w - 1) - mx0 * 16;
+        const int cyy = min(my * 8 + qy, (G.h + 1) / 2 - 1);
+        const int ly0 = min(2 * cyy, G.h - 1) - my * 16, ly1 = min(2 * cyy + 1, G.h - 1) - my * 16;
+        int cb = 0, cr = 0;
+        auto fetch = [&](int ly, int lc, int &R, int &Gc, int &B) {
+            const uint8_t *p = (const uint8_t *)sraw[ly] + smis[ly] + 3 * lc;
+            B = p[0]; Gc = p[1]; R = p[2];
+        };
+        auto luma = [](int R, int Gc, int B) {
+            return ((JFIX16(0.29900) * R + JFIX16(0.58700) * Gc + JFIX16(0.11400) * B + 32768) >> 16) - 128;
+        };
+        auto chroma = [&](int R, int Gc, int B) {
+            cb += (-JFIX16(0.16874) * R - JFIX16(0.33126) * Gc + JFIX16(0.50000) * B + (128 << 16) + 32767) >> 16;
+            cr += (JFIX16(0.50000) * R - JFIX16(0.41869) * Gc - JFIX16(0.08131) * B + (128 << 16) + 32767) >> 16;
+        };
+        const bool same = ly0 == 2 * qy && ly1 == 2 * qy + 1;   // false only in MCU rows padded past the image
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int cx = mx * 8 + i;
-            int s = 0;
+        for (int k = 0; k < 4; k++) {
+            int R, Gc, B;
+            fetch(2 * qy + (k >> 1), (k & 1) ? lc1 : lc0, R, Gc, B);
+            sY[2 * qy + (k >> 1)][2 * qx + (k & 1)] = (int8_t)luma(R, Gc, B);
+            if (same) chroma(R, Gc, B);
+        }
+        if (!same) {
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const uint8_t *p = ((k & 2) ? row1 : row0) + 3 * min(2 * cx + (k & 1), G.w - 1);
-                const int R = p[2], Gc = p[1], B = p[0];
-                s += b == 4 ? (-JFIX16(0.16874) * R - JFIX16(0.33126) * Gc + JFIX16(0.50000) * B + (128 << 16) + 32767) >> 16
-                            : (JFIX16(0.50000) * R - JFIX16(0.41869) * Gc - JFIX16(0.08131) * B + (128 << 16) + 32767) >> 16;
+                int R, Gc, B;
+                fetch((k >> 1) ? ly1 : ly0, (k & 1) ? lc1 : lc0, R, Gc, B);
+                chroma(R, Gc, B);
             }
-            x[i] = ((s + ((cx & 1) ? 2 : 1)) >> 2) - 128;
+        }
+        const int bias = (qx & 1) ? 2 : 1;                      // mx0 * 8 is even: the parity of the global column
+        sC[0][qy][qx] = (int8_t)(((cb + bias) >> 2) - 128);
+        sC[1][qy][qx] = (int8_t)(((cr + bias) >> 2) - 128);
+    }
+    __syncthreads();
+    // 3. forward DCT of block lb = (MCU m, component block b)
+    const int lb = tid >> 3, r = tid & 7;
+    const int m = lb / 6, b = lb - m * 6;
+    int x[8], o[8];
+    bool real = m < nm;
+    if (b < 4) {
+        real = real && my * 2 + (b >> 1) < G.hibY && (mx0 + m) * 2 + (b & 1) < G.wibY;   // else a dummy block
+        const int2 v = *(const int2 *)&sY[(b >> 1) * 8 + r][m * 16 + (b & 1) * 8];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            x[i] = (int)(int8_t)(v.x >> (8 * i));
+            x[4 + i] = (int)(int8_t)(v.y >> (8 * i));
+        }
+    } else {
+        const int2 v = *(const int2 *)&sC[b - 4][r][m * 8];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            x[i] = (int)(int8_t)(v.x >> (8 * i));
+            x[4 + i] = (int)(int8_t)(v.y >> (8 * i));
         }
     }
     fdct_1d(x, o, true);
 #pragma unroll
-    for (int i = 0; i < 8; i++) sm[lb][r][i] = o[i];
+    for (int i = 0; i < 8; i++) sT[lb][r][i] = o[i];
     __syncwarp();
 #pragma unroll
-    for (int i = 0; i < 8; i++) x[i] = sm[lb][i][r];      // column r
+    for (int i = 0; i < 8; i++) x[i] = sT[lb][i][r];      // column r
     fdct_1d(x, o, false);
-    if (!valid) return;
-    const uint8_t *q = c_quant[b < 4 ? 0 : 1];
+    const int qt = b < 4 ? 0 : 1;
 #pragma unroll
     for (int i = 0; i < 8; i++) {                          // coefficient (row i, column r)
-        const int n = 8 * i + r, d = (int)q[n] << 3, v = o[i];
-        const int qv = real ? (v < 0 ? -((-v + (d >> 1)) / d) : (v + (d >> 1)) / d) : 0;
-        coef[(size_t)c_izz[n] * G.cstride + g] = (int16_t)qv;
+        const int n = 8 * i + r, d = sD[qt][n], v = o[i];
+        // (|v| + d / 2) / d by reciprocal, corrected to the exact quotient
+        const unsigned a = (unsigned)abs(v) + (unsigned)(d >> 1);
+        unsigned qv = (unsigned)((float)a * sRcp[qt][n]);
+        int rem = (int)a - (int)qv * d;
+        if (rem < 0) { qv--; rem += d; }
+        if (rem >= d) qv++;
+        sO[sIzz[n]][lb] = real ? (int16_t)(v < 0 ? -(int)qv : (int)qv) : (int16_t)0;
+    }
+    __syncthreads();
+    // 4. zigzag-major planes [k][block]
+    const size_t g0 = ((size_t)my * G.mcux + mx0) * 6;
+    for (int t = tid; t < 64 * (JD_BLOCKS / 2); t += JD_T) {
+        const int k = t / (JD_BLOCKS / 2), j = t - k * (JD_BLOCKS / 2);
+        if (2 * j < nm * 6) *(uint32_t *)(coef + (size_t)k * G.cstride + g0 + 2 * j) = ((const uint32_t *)sO[k])[j];
     }
 }
 
@@ -206,16 +285,23 @@ __device__ __forceinline__ void walk_block(const int16_t *__restrict__ coef, con
         return;
     }
     int r = 0;
-    for (int k = 1; k < 64; k++) {
-        int v = coef[(size_t)k * G.cstride + g];
-        if (v == 0) { r++; continue; }
-        while (r > 15) { sink(c_hcode[tac][0xF0], c_hlen[tac][0xF0]); r -= 16; }
-        t2 = v;
-        if (v < 0) { v = -v; t2--; }
-        nb = bit_length(v);
-        sink(c_hcode[tac][(r << 4) + nb], c_hlen[tac][(r << 4) + nb]);
-        sink((unsigned)t2, nb);
-        r = 0;
+    for (int k0 = 0; k0 < 64; k0 += 8) {
+        int vv[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) vv[j] = coef[(size_t)(k0 + j) * G.cstride + g];   // eight loads in flight
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (k0 + j == 0) continue;
+            int v = vv[j];
+            if (v == 0) { r++; continue; }
+            while (r > 15) { sink(c_hcode[tac][0xF0], c_hlen[tac][0xF0]); r -= 16; }
+            t2 = v;
+            if (v < 0) { v = -v; t2--; }
+            nb = bit_length(v);
+            sink(c_hcode[tac][(r << 4) + nb], c_hlen[tac][(r << 4) + nb]);
+            sink((unsigned)t2, nb);
+            r = 0;
+        }
     }
     if (r > 0) sink(c_hcode[tac][0], c_hlen[tac][0]);
 }
@@ -278,11 +364,18 @@ __global__ void __launch_bounds__(256) jpeg_emit_kernel(const int16_t *__restric
 }
 
 // ---------------------------------------------------------------------------
-// exclusive prefix sum of n 64-bit values (in place), total to *total: 1024 values per CTA
+// exclusive prefix sum of n 64-bit values (in place), total to *total: 1024 values per CTA.  With
+// `tb` the count is not known on the host: n = the 32-byte chunks of a stream of *tb bits (the grid
+// covers the host's bound, CTAs past the real count leave at once).
+__device__ __forceinline__ size_t stream_chunks(const unsigned long long *tb) { return (size_t)((((*tb + 7) >> 3) + 31) >> 5); }
+
 __global__ void __launch_bounds__(1024) scan_block_kernel(unsigned long long *__restrict__ v, size_t n,
-                                                          unsigned long long *__restrict__ sums)
+                                                          unsigned long long *__restrict__ sums,
+                                                          const unsigned long long *__restrict__ tb)
 {
     __shared__ unsigned long long ws[32];
+    if (tb) n = stream_chunks(tb);
+    if ((size_t)blockIdx.x * 1024 >= n) return;
     const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned long long x = i < n ? v[i] : 0ull;
@@ -311,10 +404,12 @@ __global__ void __launch_bounds__(1024) scan_block_kernel(unsigned long long *__
 
 // one CTA: exclusive scan of the per-CTA sums (any count), total out
 __global__ void __launch_bounds__(1024) scan_sums_kernel(unsigned long long *__restrict__ sums, int m,
-                                                         unsigned long long *__restrict__ total)
+                                                         unsigned long long *__restrict__ total,
+                                                         const unsigned long long *__restrict__ tb)
 {
     __shared__ unsigned long long ws[32];
     __shared__ unsigned long long carry;
+    if (tb) m = (int)((stream_chunks(tb) + 1023) / 1024);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
@@ -349,19 +444,21 @@ __global__ void __launch_bounds__(1024) scan_sums_kernel(unsigned long long *__r
 }
 
 __global__ void __launch_bounds__(1024) scan_add_kernel(unsigned long long *__restrict__ v, size_t n,
-                                                        const unsigned long long *__restrict__ sums)
+                                                        const unsigned long long *__restrict__ sums,
+                                                        const unsigned long long *__restrict__ tb)
 {
+    if (tb) n = stream_chunks(tb);
     const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
     if (i < n) v[i] += sums[blockIdx.x];
 }
 
 static int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums,
-                              unsigned long long *total)
+                              unsigned long long *total, const unsigned long long *tb)
 {
     const int m = (int)((n + 1023) / 1024);
-    scan_block_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums);
-    scan_sums_kernel<<<1, 1024, 0, ctx->stream>>>(sums, m, total);
-    scan_add_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums);
+    scan_block_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums, tb);
+    scan_sums_kernel<<<1, 1024, 0, ctx->stream>>>(sums, m, total, tb);
+    scan_add_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums, tb);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     return OICS_OK;
@@ -377,12 +474,20 @@ __device__ __forceinline__ uint32_t stream_byte(const uint32_t *__restrict__ wor
     return b;
 }
 
-__global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *__restrict__ words,
-                                                               const unsigned long long *__restrict__ total_bits,
-                                                               unsigned long long *__restrict__ cnt, size_t nchunks)
+// The grids of the kernels below cover the host's bound on the stream (208 bytes per block); the real
+// size is read from *total_bits on the device, so that no host round trip sits between the kernels.
+__global__ void __launch_bounds__(256) jpeg_zero_kernel(uint4 *__restrict__ words, const unsigned long long *__restrict__ total_bits)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nchunks) return;
+    if (i < ((*total_bits + 7) >> 3) / 16 + 2) words[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+__global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *__restrict__ words,
+                                                               const unsigned long long *__restrict__ total_bits,
+                                                               unsigned long long *__restrict__ cnt)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= stream_chunks(total_bits)) return;
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
     unsigned c = 0;
@@ -390,13 +495,27 @@ __global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *_
     cnt[i] = c;
 }
 
+// header (cached on the device, SOF0 height / width patched in) + stuffed stream + EOI
 __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *__restrict__ words,
                                                                const unsigned long long *__restrict__ total_bits,
-                                                               const unsigned long long *__restrict__ off, size_t nchunks,
-                                                               uint8_t *__restrict__ out, size_t cap)
+                                                               const unsigned long long *__restrict__ off,
+                                                               const uint8_t *__restrict__ header, int hdr, int sof, int w,
+                                                               int h, uint8_t *__restrict__ file, size_t file_cap)
 {
+    if (blockIdx.x == 0) {
+        for (int t = threadIdx.x; t < hdr; t += blockDim.x) {
+            uint8_t v = header[t];
+            if (t == sof) v = (uint8_t)(h >> 8);
+            if (t == sof + 1) v = (uint8_t)(h & 255);
+            if (t == sof + 2) v = (uint8_t)(w >> 8);
+            if (t == sof + 3) v = (uint8_t)(w & 255);
+            if ((size_t)t < file_cap) file[t] = v;
+        }
+    }
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nchunks) return;
+    if (i >= stream_chunks(total_bits)) return;
+    uint8_t *out = file + hdr;
+    const size_t cap = file_cap > (size_t)hdr ? file_cap - hdr : 0;
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
     size_t o = 32 * i + (size_t)off[i];
@@ -439,7 +558,7 @@ static void host_huff(const uint8_t *bits, const uint8_t *vals, uint16_t *code, 
     }
 }
 
-static size_t host_header(int w, int h, const uint8_t *ql, const uint8_t *qc, uint8_t *o)
+static size_t host_header(const uint8_t *ql, const uint8_t *qc, uint8_t *o, int *sof)
 {
     size_t n = 0;
     auto put = [&](std::initializer_list<int> b) { for (int v : b) o[n++] = (uint8_t)v; };
@@ -448,7 +567,8 @@ static size_t host_header(int w, int h, const uint8_t *ql, const uint8_t *qc, ui
         put({0xFF, 0xDB, 0, 67, t});
         for (int k = 0; k < 64; k++) o[n++] = (t ? qc : ql)[h_zz[k]];
     }
-    put({0xFF, 0xC0, 0, 17, 8, h >> 8, h & 255, w >> 8, w & 255, 3, 1, 0x22, 0, 2, 0x11, 1, 3, 0x11, 1});
+    *sof = (int)n + 5;   // height (2 bytes), width (2 bytes): written by the kernel
+    put({0xFF, 0xC0, 0, 17, 8, 0, 0, 0, 0, 3, 1, 0x22, 0, 2, 0x11, 1, 3, 0x11, 1});
     const struct { int id; const uint8_t *bits, *vals; int nv; } dht[4] = {
         {0x00, h_dc_l_bits, h_dc_vals, 12}, {0x10, h_ac_l_bits, h_ac_l_vals, 162},
         {0x01, h_dc_c_bits, h_dc_vals, 12}, {0x11, h_ac_c_bits, h_ac_c_vals, 162}};
@@ -462,10 +582,32 @@ static size_t host_header(int w, int h, const uint8_t *ql, const uint8_t *qc, ui
     return n;
 }
 
-// BGR image on the device -> JPEG file bytes on the device (d_out, capacity d_cap); *size = file size
-// (OICS_ERR_CAPACITY with the needed size if it does not fit).
-int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
-                           size_t d_cap, size_t *size)
+// The tables that do not depend on the quality: once per device.
+static int32_t fixed_tables(int device)
+{
+    static std::mutex mu;
+    static bool done[64] = {false};
+    std::lock_guard<std::mutex> lk(mu);
+    if (device >= 0 && device < 64 && done[device]) return OICS_OK;
+    uint8_t izz[64], hlen[4][256];
+    uint16_t hcode[4][256];
+    for (int k = 0; k < 64; k++) izz[h_zz[k]] = (uint8_t)k;
+    host_huff(h_dc_l_bits, h_dc_vals, hcode[0], hlen[0]);
+    host_huff(h_ac_l_bits, h_ac_l_vals, hcode[1], hlen[1]);
+    host_huff(h_dc_c_bits, h_dc_vals, hcode[2], hlen[2]);
+    host_huff(h_ac_c_bits, h_ac_c_vals, hcode[3], hlen[3]);
+    OICS_CUDA_TRY(cudaMemcpyToSymbol(c_izz, izz, sizeof(izz)));
+    OICS_CUDA_TRY(cudaMemcpyToSymbol(c_hcode, hcode, sizeof(hcode)));
+    OICS_CUDA_TRY(cudaMemcpyToSymbol(c_hlen, hlen, sizeof(hlen)));
+    if (device >= 0 && device < 64) done[device] = true;
+    return OICS_OK;
+}
+
+// Enqueue the encoder on ctx->stream without a host round trip: the file lands in d_out (writes past
+// d_cap are dropped) and d_totals[0..1] (device) receive the entropy-coded bits and the stuffed 0xFF
+// count; the file size is jpeg_file_size(*hdr_len, totals) once the caller has read them back.
+int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len)
 {
     cudaStream_t st = ctx->stream;
     if (w <= 0 || h <= 0 || w > 65535 || h > 65535) {
@@ -478,59 +620,72 @@ int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, siz
     G.wibY = cdiv(w, 8); G.hibY = cdiv(h, 8);
     G.nblocks = 6 * G.mcux * G.mcuy;
     G.cstride = ((size_t)G.nblocks + 63) & ~(size_t)63;
-    // tables
-    uint8_t q[2][64], izz[64], hlen[4][256], header[1024];
-    uint16_t hcode[4][256];
-    host_quant(h_ql, quality, q[0]);
-    host_quant(h_qc, quality, q[1]);
-    for (int k = 0; k < 64; k++) izz[h_zz[k]] = (uint8_t)k;
-    host_huff(h_dc_l_bits, h_dc_vals, hcode[0], hlen[0]);
-    host_huff(h_ac_l_bits, h_ac_l_vals, hcode[1], hlen[1]);
-    host_huff(h_dc_c_bits, h_dc_vals, hcode[2], hlen[2]);
-    host_huff(h_ac_c_bits, h_ac_c_vals, hcode[3], hlen[3]);
-    const size_t hdr = host_header(w, h, q[0], q[1], header);
-    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_quant, q, sizeof(q), 0, cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_izz, izz, sizeof(izz), 0, cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_hcode, hcode, sizeof(hcode), 0, cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemcpyToSymbolAsync(c_hlen, hlen, sizeof(hlen), 0, cudaMemcpyHostToDevice, st));
-    if (hdr + 2 > d_cap) { *size = hdr + 2; set_error("jpeg: output capacity %zu is below the header", d_cap); return OICS_ERR_CAPACITY; }
-    OICS_CUDA_TRY(cudaMemcpyAsync(d_out, header, hdr, cudaMemcpyHostToDevice, st));
-    // scratch: cplx = coefficients, labels = bit counts / offsets + scan sums + totals, cplx2 = bit stream
+    OICS_TRY(fixed_tables(ctx->device));
+    quality = std::min(100, std::max(1, quality));
+    JpegQuant Q;
+    host_quant(h_ql, quality, Q.q[0]);
+    host_quant(h_qc, quality, Q.q[1]);
+    for (int t = 0; t < 2; t++)
+        for (int k = 0; k < 64; k++) Q.rcp[t][k] = 1.0f / (float)((int)Q.q[t][k] << 3);
+    if (ctx->jpeg_hdr_quality != quality) {                 // the header of this quality, cached on the device
+        ctx->jpeg_hdr_len = host_header(Q.q[0], Q.q[1], ctx->jpeg_hdr_host, &ctx->jpeg_hdr_sof);
+        OICS_TRY(ctx->jpeg_hdr.ensure(1024));
+        OICS_CUDA_TRY(cudaMemcpyAsync(ctx->jpeg_hdr.p, ctx->jpeg_hdr_host, ctx->jpeg_hdr_len, cudaMemcpyHostToDevice, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        ctx->jpeg_hdr_quality = quality;
+    }
+    const size_t hdr = ctx->jpeg_hdr_len;
+    *hdr_len = hdr;
+    // scratch: cplx = coefficients, labels = bit counts / offsets + scan sums, cplx2 = bit stream,
+    // mag = 0xFF counts per 32-byte chunk + scan sums
     const size_t nb = (size_t)G.nblocks;
+    const size_t bound = nb * 208 + 64;                      // bytes: 20 DC + 63 * 26 AC bits per block at most
+    const size_t nchunks = (bound + 31) / 32;
+    const size_t nsums = (nb + 1023) / 1024 + 8, nsums2 = (nchunks + 1023) / 1024 + 8;
     OICS_TRY(ctx->cplx.ensure(64 * G.cstride * sizeof(int16_t)));
-    const size_t nsums = (nb + 1023) / 1024 + 8;
-    OICS_TRY(ctx->labels.ensure((nb + nsums + 8) * sizeof(unsigned long long)));
+    OICS_TRY(ctx->labels.ensure((nb + nsums) * sizeof(unsigned long long)));
+    OICS_TRY(ctx->cplx2.ensure(bound + 64));
+    OICS_TRY(ctx->mag.ensure((nchunks + nsums2) * sizeof(unsigned long long)));
     int16_t *coef = ctx->cplx.as<int16_t>();
-    unsigned long long *bits = ctx->labels.as<unsigned long long>(), *sums = bits + nb, *totals = sums + nsums;
-    jpeg_dct_kernel<<<cdiv(G.nblocks, 32), 256, 0, st>>>(dbgr, stride, G, coef);
+    unsigned long long *bits = ctx->labels.as<unsigned long long>(), *sums = bits + nb;
+    unsigned long long *cnt = ctx->mag.as<unsigned long long>(), *sums2 = cnt + nchunks;
+    uint32_t *words = ctx->cplx2.as<uint32_t>();
+    const int strips = cdiv(G.mcux, JD_MCU);
+    jpeg_dct_kernel<<<G.mcuy * strips, JD_T, 0, st>>>(dbgr, stride, G, Q, strips, coef);
     jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
-    OICS_TRY(exclusive_scan(ctx, bits, nb, sums, totals));
-    unsigned long long total_bits = 0;
-    OICS_CUDA_TRY(cudaMemcpyAsync(&total_bits, totals, sizeof(total_bits), cudaMemcpyDeviceToHost, st));
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));   // also: the host tables above have been consumed
-    const size_t nbytes = (size_t)((total_bits + 7) >> 3), nwords = (nbytes + 3) / 4 + 2;
-    OICS_TRY(ctx->cplx2.ensure(nwords * sizeof(uint32_t)));
-    uint32_t *words = ctx->cplx2.as<uint32_t>();
-    OICS_CUDA_TRY(cudaMemsetAsync(words, 0, nwords * sizeof(uint32_t), st));
+    OICS_TRY(exclusive_scan(ctx, bits, nb, sums, d_totals, nullptr));
+    jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
     jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, words);
-    const size_t nchunks = (nbytes + 31) / 32;
-    const size_t nsums2 = (nchunks + 1023) / 1024 + 8;
-    OICS_TRY(ctx->mag.ensure((nchunks + nsums2 + 8) * sizeof(unsigned long long)));
-    unsigned long long *cnt = ctx->mag.as<unsigned long long>(), *sums2 = cnt + nchunks, *total_ff = sums2 + nsums2;
-    jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, totals, cnt, nchunks);
+    jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
     OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches += 2;
-    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums2, total_ff));
-    jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, totals, cnt, nchunks, d_out + hdr,
-                                                                                    d_cap - hdr);
+    ctx->launches += 3;
+    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums2, d_totals + 1, d_totals));
+    jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
+        words, d_totals, cnt, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
-    unsigned long long nff = 0;
-    OICS_CUDA_TRY(cudaMemcpyAsync(&nff, total_ff, sizeof(nff), cudaMemcpyDeviceToHost, st));
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));
-    *size = hdr + nbytes + (size_t)nff + 2;
+    return OICS_OK;
+}
+
+size_t jpeg_file_size(size_t hdr_len, const unsigned long long *totals)
+{
+    return hdr_len + (size_t)((totals[0] + 7) >> 3) + (size_t)totals[1] + 2;
+}
+
+// BGR image on the device -> JPEG file bytes on the device (d_out, capacity d_cap); *size = file size
+// (OICS_ERR_CAPACITY with the needed size if it does not fit).
+int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                           size_t d_cap, size_t *size)
+{
+    OICS_TRY(ctx->jpeg_totals.ensure(2 * sizeof(unsigned long long)));
+    size_t hdr = 0;
+    OICS_TRY(jpeg_encode_enqueue(ctx, dbgr, w, h, stride, quality, d_out, d_cap, ctx->jpeg_totals.as<unsigned long long>(), &hdr));
+    unsigned long long totals[2] = {0, 0};
+    OICS_CUDA_TRY(cudaMemcpyAsync(totals, ctx->jpeg_totals.p, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    *size = jpeg_file_size(hdr, totals);
     if (*size > d_cap) {
         set_error("jpeg: the file needs %zu bytes, capacity %zu", *size, d_cap);
         return OICS_ERR_CAPACITY;
