@@ -31,7 +31,7 @@ WHITE = (255, 255, 255, 0)
 
 def build(force: bool = False) -> str:
     """Compile the C restatement into oracle/_ref/ (recipe: oracle/Makefile)."""
-    srcs = [os.path.join(_HERE, f) for f in ("oics_oracle.c", "oics_oracle_lines.c", "oics_oracle_jpeg.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("oics_oracle.c", "oics_oracle_lines.c", "oics_oracle_jpeg.c", "oics_oracle_jpegdec.c", "Makefile")]
     if (not force and os.path.exists(_SO)
             and all(os.path.getmtime(_SO) >= os.path.getmtime(s) for s in srcs)):
         return _SO
@@ -432,3 +432,19 @@ def jpeg_encode(bgr, quality=100) -> bytes:
     n = lib().orc_jpeg_encode(_p(bgr), w, h, w * 3, int(quality), _p(out), C.c_long(cap))
     assert n <= cap
     return out[:n].tobytes()
+
+
+# --------------------------------------------------------------------------- N2: imread(JPEG)
+def jpeg_decode(data) -> np.ndarray:
+    """imgcodecs::imread(path, IMREAD_COLOR) (omr.rs:349, transfer.rs:43) of a baseline JPEG file's
+    bytes -> BGR image.  Raises ValueError for corrupt (-1) or unsupported (-2) files."""
+    buf = np.frombuffer(bytes(data), np.uint8)
+    w, h, nc = C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = lib().orc_jpeg_info(_p(buf), C.c_long(buf.size), C.byref(w), C.byref(h), C.byref(nc))
+    if rc:
+        raise ValueError(f"jpeg: header rejected ({rc})")
+    out = np.empty((h.value, w.value, 3), np.uint8)
+    rc = lib().orc_jpeg_decode(_p(buf), C.c_long(buf.size), _p(out), C.c_long(w.value * 3))
+    if rc:
+        raise ValueError(f"jpeg: decode failed ({rc})")
+    return out

@@ -224,3 +224,40 @@ def test_jpeg_encode_bytes_equal_cv2(orc, shape):
         for q in (100, 95, 75, 30):
             ref = bytes(cv2.imencode(".jpg", im, [cv2.IMWRITE_JPEG_QUALITY, q])[1])
             assert orc.jpeg_encode(im, q) == ref, (shape, q)
+
+
+# ----------------------------------------------------------------------------- N2: imread(JPEG)
+_JPEG_VARIANTS = {
+    "420": [],
+    "444": [cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_444],
+    "422": [cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_422],
+    "optimised-tables": [cv2.IMWRITE_JPEG_OPTIMIZE, 1],
+    "restart-3": [cv2.IMWRITE_JPEG_RST_INTERVAL, 3],
+}
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (64, 48), (16, 16), (1, 1), (5, 4), (9, 2), (33, 17), (230, 248)])
+def test_jpeg_decode_equals_cv2(orc, shape):
+    """omr.rs:349: the card is read with imread(path, IMREAD_COLOR).  The restatement of libjpeg's
+    baseline decompressor must give cv2's pixels bit for bit: 4:2:0 / 4:2:2 / 4:4:4 / grey files,
+    optimised Huffman tables, restart intervals, several qualities."""
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    img = (rng.random(shape + (3,)) * 255).astype(np.uint8)
+    img[shape[0] // 4:shape[0] // 2, shape[1] // 5:shape[1] // 2] = (10, 200, 90)
+    smooth = cv2.GaussianBlur(img, (7, 7), 2.0)
+    for im in (img, smooth, np.full(shape + (3,), 255, np.uint8)):
+        for q in (100, 90, 30):
+            for name, extra in _JPEG_VARIANTS.items():
+                enc = cv2.imencode(".jpg", im, [cv2.IMWRITE_JPEG_QUALITY, q] + extra)[1]
+                assert np.array_equal(orc.jpeg_decode(enc.tobytes()), cv2.imdecode(enc, cv2.IMREAD_COLOR)), (shape, q, name)
+        enc = cv2.imencode(".jpg", cv2.cvtColor(im, cv2.COLOR_BGR2GRAY), [cv2.IMWRITE_JPEG_QUALITY, 90])[1]
+        assert np.array_equal(orc.jpeg_decode(enc.tobytes()), cv2.imdecode(enc, cv2.IMREAD_COLOR)), (shape, "grey")
+
+
+def test_jpeg_decode_rejects_what_it_does_not_cover(orc):
+    img = np.zeros((16, 16, 3), np.uint8)
+    prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()
+    with pytest.raises(ValueError):
+        orc.jpeg_decode(prog)
+    with pytest.raises(ValueError):
+        orc.jpeg_decode(b"not a jpeg at all")
