@@ -246,6 +246,16 @@ OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t
                                       double hough_max_line_gap, uint8_t *dst, size_t dst_cap,
                                       int32_t *dst_w, int32_t *dst_h, double *angle, int32_t *need_check);
 
+/* N2, input side: imgcodecs::imread(path, IMREAD_COLOR) (omr.rs:349, transfer.rs:43,62) for a baseline
+ * JPEG file already in host memory.  oics_jpeg_info parses the header only (host, no context): image
+ * size and component count.  oics_jpeg_decode decodes on the GPU -- the pixels are libjpeg(-turbo)'s /
+ * cv::imread's bit for bit -- into `bgr` (host or device, rows `stride` bytes apart, 0 = packed).
+ * OICS_ERR_UNSUPPORTED for files outside the covered subset (progressive, restart intervals, CMYK,
+ * subsampling other than 4:4:4 / 4:2:2 / 4:2:0): the caller keeps imread for those. */
+OICS_API int32_t oics_jpeg_info(const uint8_t *file, size_t file_size, int32_t *w, int32_t *h, int32_t *channels);
+OICS_API int32_t oics_jpeg_decode(oics_ctx *ctx, const uint8_t *file, size_t file_size, uint8_t *bgr, size_t stride,
+                                  size_t bgr_cap, int32_t *w, int32_t *h);
+
 /* Batch form replacing the thread-pool fan-out (task.rs:19-68, thread_pool.rs:56-73):
  * n equally sized BGR cards `card_stride` bytes apart (host or device); per card the
  * selected angle, need_check and status (OICS_OK or an error for that card only).

@@ -71,6 +71,8 @@ SIGNATURES = {
     "oics_warp_affine": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _dp, _i32, C.POINTER(C.c_uint8), _u8p, _i32, _i32, _i32]),
     "oics_rotate": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _f64, _f64, _i32, C.POINTER(C.c_uint8), _i32, _u8p, _sz, _ip, _ip]),
     "oics_jpeg_encode": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _u8p, _sz, C.POINTER(_sz)]),
+    "oics_jpeg_info": (_i32, [_u8p, _sz, _ip, _ip, _ip]),
+    "oics_jpeg_decode": (_i32, [_ctx, _u8p, _sz, _u8p, _sz, _sz, _ip, _ip]),
     "oics_reconcile": (_i32, [C.POINTER(OmrResultC), _f64, _dp, _ip]),
     "oics_correct_default": (_i32, [_ctx, _u8p, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64, _u8p, _sz, _ip, _ip, _dp, _ip]),
     "oics_correct_batch": (_i32, [_ctx, _u8p, _i32, _sz, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64,

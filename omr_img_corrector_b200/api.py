@@ -386,6 +386,25 @@ class Context:
         check(self._lib.oics_jpeg_encode(self._h, p, w, h, stride, int(quality), out.ctypes.data, out.size, C.byref(n)))
         return out[:n.value].tobytes()
 
+    def jpeg_decode(self, data, out=None):
+        """imgcodecs::imread(path, IMREAD_COLOR) (omr.rs:349, transfer.rs:43) of a baseline JPEG file's
+        bytes -> BGR image, decoded on the GPU.  `out`: optional flat uint8 buffer (e.g. pinned memory,
+        or a torch CUDA tensor: the pixels then stay on the device)."""
+        buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+        w, h, nc = C.c_int32(), C.c_int32(), C.c_int32()
+        check(self._lib.oics_jpeg_info(buf.ctypes.data, buf.size, C.byref(w), C.byref(h), C.byref(nc)))
+        need = w.value * h.value * 3
+        if out is None:
+            out = np.empty(need, np.uint8)
+        if hasattr(out, "data_ptr"):
+            ptr, cap = out.data_ptr(), out.numel()
+        else:
+            ptr, cap = out.ctypes.data, out.size
+        check(self._lib.oics_jpeg_decode(self._h, buf.ctypes.data, buf.size, ptr, 0, cap, C.byref(w), C.byref(h)))
+        if hasattr(out, "data_ptr"):
+            return out[:need].view(h.value, w.value, 3)
+        return out[:need].reshape(h.value, w.value, 3)
+
     # -- pipeline
     def correct_default(self, bgr, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, want_image=True,
                         out=None):

@@ -469,6 +469,50 @@ OICS_API int32_t oics_jpeg_encode(oics_ctx *ctx, const uint8_t *bgr, int32_t w, 
     return OICS_OK;
 }
 
+OICS_API int32_t oics_jpeg_info(const uint8_t *file, size_t file_size, int32_t *w, int32_t *h, int32_t *channels)
+{
+    if (!file || !w || !h) {
+        set_error("invalid argument: file, w, h");
+        return OICS_ERR_INVALID_ARG;
+    }
+    int iw = 0, ih = 0, nc = 0;
+    OICS_TRY(jpeg_info_host(file, file_size, &iw, &ih, &nc));
+    *w = iw;
+    *h = ih;
+    if (channels) *channels = nc;
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_jpeg_decode(oics_ctx *ctx, const uint8_t *file, size_t file_size, uint8_t *bgr, size_t stride,
+                                  size_t bgr_cap, int32_t *w, int32_t *h)
+{
+    CtxGuard g(ctx);
+    if (g.status) return g.status;
+    OICS_ARG(file && bgr && w && h);
+    OICS_ARG(!is_device_ptr(file));
+    int iw = 0, ih = 0, nc = 0;
+    OICS_TRY(jpeg_info_host(file, file_size, &iw, &ih, &nc));
+    *w = iw;
+    *h = ih;
+    if (stride == 0) stride = (size_t)iw * 3;
+    OICS_ARG(stride >= (size_t)iw * 3);
+    if (stride * (size_t)(ih - 1) + (size_t)iw * 3 > bgr_cap) {
+        set_error("jpeg: the image needs %zu bytes, capacity %zu", stride * (size_t)(ih - 1) + (size_t)iw * 3, bgr_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    if (is_device_ptr(bgr)) {
+        OICS_TRY(jpeg_decode_device(ctx, file, file_size, bgr, stride, &iw, &ih));
+        OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        return OICS_OK;
+    }
+    OICS_TRY(ctx->out_img.ensure((size_t)iw * 3 * ih));
+    OICS_TRY(jpeg_decode_device(ctx, file, file_size, ctx->out_img.as<uint8_t>(), (size_t)iw * 3, &iw, &ih));
+    OICS_CUDA_TRY(cudaMemcpy2DAsync(bgr, stride, ctx->out_img.p, (size_t)iw * 3, (size_t)iw * 3, (size_t)ih, cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
 // correct_default for a BGR card already on the device
 static int32_t correct_one(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint16_t max_angle,
                            double step, int max_w, int max_h, double min_len, double max_gap, uint8_t *dst,

@@ -452,7 +452,7 @@ __global__ void __launch_bounds__(1024) scan_add_kernel(unsigned long long *__re
     if (i < n) v[i] += sums[blockIdx.x];
 }
 
-static int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums,
+int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums,
                               unsigned long long *total, const unsigned long long *tb)
 {
     const int m = (int)((n + 1023) / 1024);

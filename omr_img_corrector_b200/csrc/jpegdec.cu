@@ -1,0 +1,811 @@
+// N2 (input side): imgcodecs::imread(path, IMREAD_COLOR) (omr.rs:349, transfer.rs:43,62) of a
+// baseline JPEG = libjpeg(-turbo)'s decompressor with its defaults, bit for bit, on the GPU -- so a
+// card reaches the device as the few-MB file it is stored as instead of 26 MB of pixels, and the
+// host does no codec work at all.
+//
+//   host              marker parsing (DQT / DHT / SOF0 / SOS), Huffman lookup tables -> one small upload
+//   jdec_unstuff_*    0xFF 0x00 -> 0xFF: count per 32-byte chunk, scan, compact into MSB-first words
+//   jdec_sync_kernel  Huffman decoding is sequential, so the stream is cut into 512-bit subsequences
+//                     and every thread decodes one from a guessed state (bit position, coefficient
+//                     index, block of the MCU); Huffman streams self-synchronise, so feeding every
+//                     thread its predecessor's exit state and repeating until nothing changes
+//                     (a few rounds; unchanged threads leave at once) gives each subsequence its true
+//                     entry state (Weissenberger & Schmidt, "Massively parallel Huffman decoding on
+//                     GPUs", restated for JPEG's (position, k, block) state).
+//   scan              blocks completed per subsequence -> first block index of every subsequence
+//   jdec_write_kernel the same decode once more, now storing coefficients [block][64] (natural order)
+//   jdec_mcu_dc_*     DC prediction: per-MCU sums of the DC differences (three 21-bit fields in one
+//                     64-bit word), scan
+//   jdec_idct_kernel  8 threads per block: dequantise, jidctint.c islow IDCT (column then row through
+//                     a conflict-free transpose), range limit -> component planes
+//   jdec_color_kernel jdsample.c fancy h2v1 / h2v2 upsampling (jdmainct.c edge rows, jinit_upsampler's
+//                     width rule), jdcolor.c YCC -> RGB, BGR out
+// Covered: 8-bit baseline / extended sequential, one interleaved scan, grey or Y Cb Cr with luma
+// sampling 1x1, 2x1 or 2x2, any Huffman tables, no restart intervals.  Anything else:
+// OICS_ERR_UNSUPPORTED (the caller keeps its imread for those).
+#include <algorithm>
+#include <cstring>
+
+#include "common.h"
+
+namespace oics {
+
+static const uint8_t d_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48,
+                                 41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+// What the kernels need from the header; uploaded once per file.
+struct JdecTables {
+    uint16_t lut[6][256];     // [2 * comp + (0 DC, 1 AC)]: (length << 8) | symbol for codes of <= 8 bits, else 0
+    int32_t maxcode[6][18];   // canonical decode of the longer codes (jdhuff.c)
+    int32_t valptr[6][18];
+    uint8_t vals[6][256];
+    uint16_t quant[3][64];    // natural order
+    uint8_t zz[64];           // zigzag position -> natural index
+    uint8_t comp_of[8];       // block of the MCU -> component
+    int32_t nbm;              // blocks per MCU
+};
+
+struct JdecHeader {
+    int w = 0, h = 0, ncomp = 0, hs = 1, vs = 1;   // luma sampling; chroma is 1x1
+    size_t scan_off = 0, scan_len = 0;             // entropy-coded bytes (stuffed), EOI excluded
+};
+
+static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTables *T)
+{
+    if (n < 4 || f[0] != 0xFF || f[1] != 0xD8) { set_error("jpeg: not a JPEG file"); return OICS_ERR_INVALID_ARG; }
+    uint8_t bits[8][17], vals[8][256];
+    uint16_t q[4][64];
+    bool have_h[8] = {false}, have_q[4] = {false};
+    int tq[3] = {0, 0, 0}, hsf[3] = {1, 1, 1}, vsf[3] = {1, 1, 1};
+    bool have_sof = false;
+    size_t p = 2;
+    auto bad = [&](const char *why) { set_error("jpeg: %s", why); return OICS_ERR_INVALID_ARG; };
+    auto unsupported = [&](const char *why) { set_error("jpeg: %s is not covered by the CUDA decoder", why); return OICS_ERR_UNSUPPORTED; };
+    while (p + 4 <= n) {
+        if (f[p] != 0xFF) return bad("marker expected");
+        while (p < n && f[p] == 0xFF) p++;
+        if (p >= n) return bad("truncated");
+        const int m = f[p++];
+        if (m == 0xD8 || m == 0x01 || (m >= 0xD0 && m <= 0xD7)) continue;
+        if (m == 0xD9 || p + 2 > n) return bad("no scan");
+        const size_t L = ((size_t)f[p] << 8) | f[p + 1];
+        if (L < 2 || p + L > n) return bad("segment length");
+        const uint8_t *s = f + p + 2;
+        const size_t sl = L - 2;
+        if (m == 0xDB) {
+            for (size_t i = 0; i < sl;) {
+                const int pq = s[i] >> 4, t = s[i] & 15;
+                i++;
+                if (t > 3 || i + (pq ? 128 : 64) > sl) return bad("DQT");
+                for (int k = 0; k < 64; k++, i += pq ? 2 : 1) q[t][d_zz[k]] = pq ? (uint16_t)((s[i] << 8) | s[i + 1]) : s[i];
+                have_q[t] = true;
+            }
+        } else if (m == 0xC4) {
+            for (size_t i = 0; i < sl;) {
+                const int tc = s[i] >> 4, th = s[i] & 15;
+                i++;
+                if (tc > 1 || th > 3 || i + 16 > sl) return bad("DHT");
+                int cnt = 0;
+                bits[tc * 4 + th][0] = 0;
+                for (int k = 1; k <= 16; k++) cnt += (bits[tc * 4 + th][k] = s[i + k - 1]);
+                i += 16;
+                if (cnt > 256 || i + cnt > sl) return bad("DHT");
+                memcpy(vals[tc * 4 + th], s + i, cnt);
+                i += cnt;
+                have_h[tc * 4 + th] = true;
+            }
+        } else if (m == 0xC0 || m == 0xC1) {
+            if (sl < 6 || s[0] != 8) return unsupported("sample precision other than 8 bits");
+            H->h = (s[1] << 8) | s[2];
+            H->w = (s[3] << 8) | s[4];
+            H->ncomp = s[5];
+            if (!H->w || !H->h) return unsupported("a DNL-defined height");
+            if ((H->ncomp != 1 && H->ncomp != 3) || sl < (size_t)(6 + 3 * H->ncomp)) return unsupported("this component count");
+            for (int c = 0; c < H->ncomp; c++) {
+                if (s[6 + 3 * c] != c + 1) return unsupported("component ids other than 1 2 3");
+                hsf[c] = s[7 + 3 * c] >> 4;
+                vsf[c] = s[7 + 3 * c] & 15;
+                tq[c] = s[8 + 3 * c];
+                if (tq[c] > 3) return bad("SOF");
+            }
+            if (H->ncomp == 1) {
+                hsf[0] = vsf[0] = 1;
+            } else {
+                const int k = hsf[0] * 10 + vsf[0];
+                if (hsf[1] != 1 || vsf[1] != 1 || hsf[2] != 1 || vsf[2] != 1 || (k != 11 && k != 21 && k != 22))
+                    return unsupported("this chroma subsampling");
+            }
+            H->hs = hsf[0];
+            H->vs = vsf[0];
+            have_sof = true;
+        } else if (m >= 0xC2 && m <= 0xCF && m != 0xC8 && m != 0xCC) {
+            return unsupported("progressive / lossless / arithmetic coding");
+        } else if (m == 0xDD) {
+            if (sl < 2) return bad("DRI");
+            if ((s[0] << 8) | s[1]) return unsupported("restart intervals");
+        } else if (m == 0xEE) {
+            if (sl >= 12 && !memcmp(s, "Adobe", 5) && H->ncomp == 3 && s[11] != 1) return unsupported("an Adobe RGB / CMYK file");
+        } else if (m == 0xDA) {
+            if (!have_sof || sl < 1 || s[0] != H->ncomp || sl < (size_t)(1 + 2 * H->ncomp + 3)) return unsupported("a non-interleaved scan");
+            memset(T, 0, sizeof(*T));
+            int nb = 0;
+            for (int c = 0; c < H->ncomp; c++) {
+                if (s[1 + 2 * c] != c + 1) return unsupported("a reordered scan");
+                const int td = s[2 + 2 * c] >> 4, ta = s[2 + 2 * c] & 15;
+                if (td > 3 || ta > 3 || !have_h[td] || !have_h[4 + ta] || !have_q[tq[c]]) return bad("missing table");
+                for (int k = 0; k < 64; k++) T->quant[c][k] = q[tq[c]][k];
+                for (int a = 0; a < 2; a++) {
+                    const uint8_t *b = bits[a ? 4 + ta : td], *v = vals[a ? 4 + ta : td];
+                    const int t = 2 * c + a;
+                    int code = 0, k = 0;
+                    for (int l = 1; l <= 16; l++) {
+                        T->valptr[t][l] = k - code;
+                        for (int i = 0; i < b[l]; i++, code++, k++) {
+                            if (l <= 8)
+                                for (int fill = 0; fill < (1 << (8 - l)); fill++)
+                                    T->lut[t][((code << (8 - l)) | fill) & 255] = (uint16_t)((l << 8) | v[k]);
+                        }
+                        T->maxcode[t][l] = b[l] ? code - 1 : -1;
+                        code <<= 1;
+                    }
+                    memcpy(T->vals[t], v, 256);
+                }
+                for (int i = 0; i < hsf[c] * vsf[c]; i++) T->comp_of[nb++] = (uint8_t)c;
+            }
+            T->nbm = nb;
+            memcpy(T->zz, d_zz, 64);
+            H->scan_off = p + L;
+            size_t end = n;                                  // EOI (and anything behind it) is not entropy data
+            if (end >= 2 && f[end - 2] == 0xFF && f[end - 1] == 0xD9) end -= 2;
+            if (end <= H->scan_off) return bad("empty scan");
+            H->scan_len = end - H->scan_off;
+            return OICS_OK;
+        }
+        p += L;
+    }
+    return bad("no scan");
+}
+
+// ---------------------------------------------------------------------------
+// unstuffing: byte j of the scan is dropped iff it is the 0x00 behind a 0xFF.  Any other byte behind
+// a 0xFF is a marker inside the scan (restart, premature EOI): *flag |= 1.
+__global__ void __launch_bounds__(256) jdec_unstuff_count_kernel(const uint8_t *__restrict__ s, size_t n,
+                                                                 unsigned long long *__restrict__ cnt, int *__restrict__ flag)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i * 32 >= n) return;
+    unsigned c = 0;
+    bool marker = false;
+    uint8_t prev = i ? s[i * 32 - 1] : 0;
+    const size_t j1 = min(n, i * 32 + 32);
+    for (size_t j = i * 32; j < j1; j++) {
+        const uint8_t b = s[j];
+        if (prev == 0xFF) {
+            if (b == 0) c++;
+            else marker = true;
+        }
+        prev = b;
+    }
+    if (j1 == n && prev == 0xFF) marker = true;
+    cnt[i] = c;
+    if (marker) atomicOr(flag, 1);
+}
+
+// kept bytes -> MSB-first 32-bit words (byte i of the stream lands at byte address i ^ 3)
+__global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *__restrict__ s, size_t n,
+                                                                 const unsigned long long *__restrict__ off,
+                                                                 uint8_t *__restrict__ out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i * 32 >= n) return;
+    size_t o = i * 32 - (size_t)off[i];
+    uint8_t prev = i ? s[i * 32 - 1] : 0;
+    const size_t j1 = min(n, i * 32 + 32);
+    for (size_t j = i * 32; j < j1; j++) {
+        const uint8_t b = s[j];
+        if (!(prev == 0xFF && b == 0)) out[(o++) ^ 3] = b;
+        prev = b;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// The sequential decoder of jdhuff.c as a state machine: state = (bit position p, coefficient index
+// k of the block being filled, block bi of the MCU).  One step = one Huffman symbol plus its value
+// bits.  SINK receives (block ordinal since the start, zigzag position, value) of every coefficient
+// (the DC value is the DIFFERENCE; prediction is a later scan).
+#define JD_SUB 512   // bits per subsequence
+
+struct JdecShared {
+    uint16_t lut[6][256];
+    int32_t maxcode[6][18];
+    int32_t valptr[6][18];
+    uint8_t vals[6][256];
+    uint8_t comp_of[8];
+    int32_t nbm;
+};
+
+__device__ __forceinline__ void jdec_load_tables(JdecShared &S, const JdecTables *__restrict__ T)
+{
+    for (int i = threadIdx.x; i < 6 * 256; i += blockDim.x) {
+        (&S.lut[0][0])[i] = (&T->lut[0][0])[i];
+        (&S.vals[0][0])[i] = (&T->vals[0][0])[i];
+    }
+    for (int i = threadIdx.x; i < 6 * 18; i += blockDim.x) {
+        (&S.maxcode[0][0])[i] = (&T->maxcode[0][0])[i];
+        (&S.valptr[0][0])[i] = (&T->valptr[0][0])[i];
+    }
+    if (threadIdx.x < 8) S.comp_of[threadIdx.x] = T->comp_of[threadIdx.x];
+    if (threadIdx.x == 0) S.nbm = T->nbm;
+    __syncthreads();
+}
+
+__device__ __forceinline__ unsigned long long jdec_pack(unsigned long long p, int k, int bi)
+{
+    return (p << 12) | ((unsigned long long)k << 4) | (unsigned long long)bi;
+}
+
+struct NoSink {
+    __device__ __forceinline__ void operator()(unsigned, int, int) {}
+};
+
+// Decode from state (p, k, bi) until p >= end.  Returns the number of blocks completed.
+template <typename SINK>
+__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t *__restrict__ words, unsigned long long &p,
+                                             int &k, int &bi, unsigned long long end, SINK &sink)
+{
+    unsigned done = 0;
+    unsigned long long wi = ~0ull - 1;   // never the predecessor of a real word index
+    uint32_t a = 0, b = 0;
+    while (p < end) {
+        const unsigned long long w = p >> 5;
+        if (w != wi) {
+            if (w == wi + 1) { a = b; b = __ldg(words + w + 1); }
+            else { a = __ldg(words + w); b = __ldg(words + w + 1); }
+            wi = w;
+        }
+        const uint32_t v = __funnelshift_l(b, a, (int)(p & 31));   // the next 32 bits of the stream
+        const int t = 2 * S.comp_of[bi] + (k ? 1 : 0);
+        int len, sym;
+        const unsigned e = S.lut[t][v >> 24];
+        if (e) {
+            len = e >> 8;
+            sym = e & 255;
+        } else {
+            len = 16;
+            sym = 0;
+            const int code16 = (int)(v >> 16);
+#pragma unroll 1
+            for (int l = 9; l <= 16; l++) {
+                const int c = code16 >> (16 - l);
+                if (c <= S.maxcode[t][l]) {
+                    len = l;
+                    sym = S.vals[t][(c + S.valptr[t][l]) & 255];
+                    break;
+                }
+            }
+        }
+        const int s = sym & 15;
+        int val = s ? (int)((v << len) >> (32 - s)) : 0;
+        if (s && val < (1 << (s - 1))) val += 1 - (1 << s);
+        p += len + s;
+        if (k == 0) {
+            sink(done, 0, val);
+            k = 1;
+        } else {
+            const int r = sym >> 4;
+            if (s) {
+                k += r;
+                if (k < 64) sink(done, k, val);
+                k++;
+            } else if (r == 15) {
+                k += 16;
+            } else {
+                k = 64;
+            }
+        }
+        if (k >= 64) {
+            k = 0;
+            bi = bi + 1 == S.nbm ? 0 : bi + 1;
+            done++;
+        }
+    }
+    return done;
+}
+
+// One round of the synchronisation: thread j decodes subsequence j from its predecessor's exit state
+// unless that is the state it used last time.  round 0: from the guess (j * JD_SUB, 0, 0).
+__global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
+                                                        const unsigned long long *__restrict__ removed, size_t scan_len,
+                                                        unsigned long long *__restrict__ used, unsigned long long *__restrict__ out,
+                                                        unsigned long long *__restrict__ nblk, int round, int *__restrict__ changed)
+{
+    __shared__ JdecShared S;
+    jdec_load_tables(S, T);
+    const unsigned long long total = 8ull * (scan_len - *removed);
+    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j * JD_SUB >= total) return;
+    unsigned long long x = jdec_pack(j * JD_SUB, 0, 0);
+    if (round > 0) {
+        if (j > 0) x = out[j - 1];
+        if (x == used[j]) return;
+    }
+    unsigned long long p = x >> 12;
+    int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
+    NoSink sink;
+    const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+    used[j] = x;
+    out[j] = jdec_pack(p, k, bi);
+    nblk[j] = n;
+    if (round > 0) atomicOr(changed + round, 1);
+}
+
+// ---- synchronisation with memoised candidates -------------------------------------------------
+// Streams with long periodic stretches (the white of a scanned card: every MCU is the same 32 bits)
+// do not self-synchronise in (k, block): a decoder that entered with the wrong block phase parses
+// them consistently forever, and the plain scheme above then advances one subsequence per round.
+// Instead every subsequence keeps a small table  entry state -> (exit state, blocks completed)  of
+// the candidates it has decoded so far; each round it decodes one exit state of its predecessor's
+// table that it has not seen yet.  Few distinct phases exist, so after a few rounds the tables are
+// closed (every exit of table j-1 is a key of table j), and the true chain -- table 0 holds the real
+// start -- is a walk of lookups, done hierarchically by warps whose lanes each hold one table row
+// (no load depends on the walked state).
+#define JD_M 16      // candidates per subsequence
+#define JD_GROUP 256 // subsequences per lookup group
+
+__global__ void __launch_bounds__(128) jdec_memo_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
+                                                        const unsigned long long *__restrict__ removed, size_t scan_len,
+                                                        unsigned long long *keys, unsigned long long *exits,
+                                                        unsigned *nbs, unsigned *cntm, int round, int *__restrict__ flags)
+{
+    __shared__ JdecShared S;
+    const unsigned long long total = 8ull * (scan_len - *removed);
+    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    bool need = false;
+    unsigned long long x = 0;
+    unsigned cm = 0;
+    if (j * JD_SUB < total) {
+        if (round == 0) {
+            x = jdec_pack(j * JD_SUB, 0, 0);      // for j = 0 this is the true start
+            need = true;
+        } else if (j > 0) {
+            const unsigned cp = min(__ldcg(cntm + j - 1), (unsigned)JD_M);
+            cm = min(__ldcg(cntm + j), (unsigned)JD_M);
+            for (unsigned a = 0; a < cp && !need; a++) {
+                const unsigned long long e = __ldcg(exits + (j - 1) * JD_M + a);
+                bool found = false;
+                for (unsigned b = 0; b < cm; b++) found |= __ldcg(keys + j * JD_M + b) == e;
+                if (!found) {
+                    x = e;
+                    need = true;
+                }
+            }
+        }
+    }
+    if (!__syncthreads_or(need)) return;
+    jdec_load_tables(S, T);
+    if (!need) return;
+    if (cm >= JD_M) {
+        atomicOr(flags, 2);                         // table full: the caller falls back to the plain rounds
+        return;
+    }
+    unsigned long long p = x >> 12;
+    int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
+    NoSink sink;
+    const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+    keys[j * JD_M + cm] = x;
+    exits[j * JD_M + cm] = jdec_pack(p, k, bi);
+    nbs[j * JD_M + cm] = n;
+    __threadfence();
+    cntm[j] = cm + 1;
+    atomicOr(flags + 1 + round, 1);
+}
+
+// one warp = (group, candidate a of the group's first subsequence): the exit state of the group
+__global__ void __launch_bounds__(128) jdec_group_kernel(const unsigned long long *__restrict__ keys,
+                                                         const unsigned long long *__restrict__ exits,
+                                                         const unsigned *__restrict__ cntm, size_t nsub, size_t ngroups,
+                                                         unsigned long long *__restrict__ gexit, int *__restrict__ flags)
+{
+    const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (wid >= ngroups * JD_M) return;
+    const size_t g = wid / JD_M, j0 = g * JD_GROUP, j1 = min(nsub, j0 + JD_GROUP);
+    const int a = (int)(wid - g * JD_M);
+    if (a >= (int)cntm[j0]) return;
+    unsigned long long state = keys[j0 * JD_M + a];
+    bool lost = false;
+    for (size_t j = j0; j < j1; j++) {
+        const bool live = lane < (int)min(cntm[j], (unsigned)JD_M);
+        const unsigned long long kk = live ? keys[j * JD_M + lane] : 0ull, ee = live ? exits[j * JD_M + lane] : 0ull;
+        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
+        if (!m) { lost = true; break; }
+        state = __shfl_sync(0xffffffffu, ee, __ffs(m) - 1);
+    }
+    if (lane == 0) {
+        gexit[wid] = lost ? ~0ull : state;
+    }
+}
+
+// one warp: the true entry state of every group
+__global__ void __launch_bounds__(32) jdec_top_kernel(const unsigned long long *__restrict__ keys,
+                                                      const unsigned long long *__restrict__ gexit,
+                                                      const unsigned *__restrict__ cntm, size_t ngroups,
+                                                      unsigned long long *__restrict__ gin, int *__restrict__ flags)
+{
+    const int lane = threadIdx.x;
+    unsigned long long state = jdec_pack(0, 0, 0);
+    for (size_t g = 0; g < ngroups; g++) {
+        if (lane == 0) gin[g] = state;
+        const size_t j0 = g * JD_GROUP;
+        const bool live = lane < (int)min(cntm[j0], (unsigned)JD_M);
+        const unsigned long long kk = live ? keys[j0 * JD_M + lane] : 0ull, ee = live ? gexit[g * JD_M + lane] : ~0ull;
+        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
+        const unsigned long long nx = m ? __shfl_sync(0xffffffffu, ee, __ffs(m) - 1) : ~0ull;
+        if (nx == ~0ull) {                          // not closed: fall back
+            if (lane == 0) atomicOr(flags, 4);
+            return;
+        }
+        state = nx;
+    }
+}
+
+// one warp per group: entry state and block count of each of its subsequences
+__global__ void __launch_bounds__(128) jdec_fill_kernel(const unsigned long long *__restrict__ keys,
+                                                        const unsigned long long *__restrict__ exits,
+                                                        const unsigned *__restrict__ nbs, const unsigned *__restrict__ cntm,
+                                                        size_t nsub, size_t ngroups, const unsigned long long *__restrict__ gin,
+                                                        unsigned long long *__restrict__ used, unsigned long long *__restrict__ nblk,
+                                                        int *__restrict__ flags)
+{
+    const size_t g = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= ngroups) return;
+    const size_t j0 = g * JD_GROUP, j1 = min(nsub, j0 + JD_GROUP);
+    unsigned long long state = gin[g];
+    for (size_t j = j0; j < j1; j++) {
+        const bool live = lane < (int)min(cntm[j], (unsigned)JD_M);
+        const unsigned long long kk = live ? keys[j * JD_M + lane] : 0ull, ee = live ? exits[j * JD_M + lane] : 0ull;
+        const unsigned nn = live ? nbs[j * JD_M + lane] : 0u;
+        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
+        if (!m) {
+            if (lane == 0) atomicOr(flags, 4);
+            return;
+        }
+        const int src = __ffs(m) - 1;
+        if (lane == 0) used[j] = state;
+        const unsigned nb = __shfl_sync(0xffffffffu, nn, src);
+        if (lane == 0) nblk[j] = nb;
+        state = __shfl_sync(0xffffffffu, ee, src);
+    }
+}
+
+struct CoefSink {
+    int16_t *coef;             // [block][64], natural order
+    unsigned long long base;   // ordinal of the first block this thread touches
+    unsigned long long nblocks;
+    const uint8_t *zz;
+    __device__ __forceinline__ void operator()(unsigned done, int k, int v)
+    {
+        const unsigned long long g = base + done;
+        if (g < nblocks) coef[g * 64 + zz[k]] = (int16_t)v;
+    }
+};
+
+__global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
+                                                         const unsigned long long *__restrict__ removed, size_t scan_len,
+                                                         const unsigned long long *__restrict__ used,
+                                                         const unsigned long long *__restrict__ first_block,
+                                                         unsigned long long nblocks, int16_t *__restrict__ coef)
+{
+    __shared__ JdecShared S;
+    __shared__ uint8_t zz[64];
+    if (threadIdx.x < 64) zz[threadIdx.x] = T->zz[threadIdx.x];
+    jdec_load_tables(S, T);
+    const unsigned long long total = 8ull * (scan_len - *removed);
+    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j * JD_SUB >= total) return;
+    const unsigned long long x = used[j];
+    unsigned long long p = x >> 12;
+    int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
+    // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
+    // coefficients were stored by the predecessor under the same ordinal
+    CoefSink sink{coef, first_block[j], nblocks, zz};
+    jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+}
+
+// ---------------------------------------------------------------------------
+// DC prediction.  The running sums are the DC values themselves (|DC| < 2^15 even for hostile
+// streams that stay decodable), so the three components share one 64-bit scan as 21-bit fields.
+struct JdecGeom {
+    int w, h, ncomp, hs, vs, mcux, mcuy, nbm;
+    int pw[3], ph[3];          // component planes (whole MCUs)
+    size_t poff[3];            // byte offsets of the planes
+};
+
+__device__ __forceinline__ long long sext21(long long v) { return (v << 43) >> 43; }
+
+__global__ void __launch_bounds__(256) jdec_mcu_dc_kernel(const int16_t *__restrict__ coef, JdecGeom G,
+                                                          unsigned long long *__restrict__ sums)
+{
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= G.mcux * G.mcuy) return;
+    const int ny = G.hs * G.vs;
+    long long y = 0, cb = 0, cr = 0;
+    for (int b = 0; b < ny; b++) y += coef[((size_t)m * G.nbm + b) * 64];
+    if (G.ncomp == 3) {
+        cb = coef[((size_t)m * G.nbm + ny) * 64];
+        cr = coef[((size_t)m * G.nbm + ny + 1) * 64];
+    }
+    sums[m] = (unsigned long long)(y + cb * (1ll << 21) + cr * (1ll << 42));
+}
+
+// jidctint.c jpeg_idct_islow, one dimension
+#define JDFIX(x) ((int)((x) * 8192.0 + 0.5))
+__device__ __forceinline__ void idct_1d(const int (&in)[8], int (&o)[8], int shift)
+{
+    int z2 = in[2], z3 = in[6];
+    int z1 = (z2 + z3) * JDFIX(0.541196100);
+    const int tmp2 = z1 + z3 * (-JDFIX(1.847759065)), tmp3 = z1 + z2 * JDFIX(0.765366865);
+    const int tmp0 = (in[0] + in[4]) * 8192, tmp1 = (in[0] - in[4]) * 8192;
+    const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+    int t0 = in[7], t1 = in[5], t2 = in[3], t3 = in[1];
+    z1 = t0 + t3;
+    z2 = t1 + t2;
+    z3 = t0 + t2;
+    int z4 = t1 + t3;
+    const int z5 = (z3 + z4) * JDFIX(1.175875602);
+    t0 *= JDFIX(0.298631336);
+    t1 *= JDFIX(2.053119869);
+    t2 *= JDFIX(3.072711026);
+    t3 *= JDFIX(1.501321110);
+    z1 *= -JDFIX(0.899976223);
+    z2 *= -JDFIX(2.562915447);
+    z3 = z3 * (-JDFIX(1.961570560)) + z5;
+    z4 = z4 * (-JDFIX(0.390180644)) + z5;
+    t0 += z1 + z3;
+    t1 += z2 + z4;
+    t2 += z2 + z3;
+    t3 += z1 + z4;
+    const int rnd = 1 << (shift - 1);
+    o[0] = (tmp10 + t3 + rnd) >> shift;
+    o[7] = (tmp10 - t3 + rnd) >> shift;
+    o[1] = (tmp11 + t2 + rnd) >> shift;
+    o[6] = (tmp11 - t2 + rnd) >> shift;
+    o[2] = (tmp12 + t1 + rnd) >> shift;
+    o[5] = (tmp12 - t1 + rnd) >> shift;
+    o[3] = (tmp13 + t0 + rnd) >> shift;
+    o[4] = (tmp13 - t0 + rnd) >> shift;
+}
+
+// 256 threads = 32 blocks; thread = row r of its block (load, dequantise), then column r, then row r
+__global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__restrict__ T, const int16_t *__restrict__ coef,
+                                                        const unsigned long long *__restrict__ dc_prefix, JdecGeom G,
+                                                        uint8_t *__restrict__ planes)
+{
+    __shared__ int sm[32][8][9];
+    __shared__ uint16_t sq[3][64];
+    for (int i = threadIdx.x; i < 192; i += 256) (&sq[0][0])[i] = (&T->quant[0][0])[i];
+    __syncthreads();
+    const int lb = threadIdx.x >> 3, r = threadIdx.x & 7;
+    const size_t g = (size_t)blockIdx.x * 32 + lb, nblocks = (size_t)G.mcux * G.mcuy * G.nbm;
+    const bool valid = g < nblocks;
+    const size_t gg = valid ? g : 0;
+    const int mcu = (int)(gg / G.nbm), bi = (int)(gg - (size_t)mcu * G.nbm);
+    const int ny = G.hs * G.vs, comp = bi < ny ? 0 : bi - ny + 1;
+    const int4 raw = *reinterpret_cast<const int4 *>(coef + gg * 64 + 8 * r);
+    int x[8], o[8];
+    x[0] = (int)(int16_t)(raw.x & 0xffff); x[1] = raw.x >> 16;
+    x[2] = (int)(int16_t)(raw.y & 0xffff); x[3] = raw.y >> 16;
+    x[4] = (int)(int16_t)(raw.z & 0xffff); x[5] = raw.z >> 16;
+    x[6] = (int)(int16_t)(raw.w & 0xffff); x[7] = raw.w >> 16;
+    if (r == 0) {   // DC = the predictor carried into this MCU + the differences up to this block
+        const long long P = (long long)dc_prefix[mcu];
+        const long long fy = sext21(P), P1 = (P - fy) >> 21, fcb = sext21(P1), fcr = (P1 - fcb) >> 21;
+        int dc = (int)(comp == 0 ? fy : comp == 1 ? fcb : fcr);
+        const int b0 = comp == 0 ? 0 : bi;
+        for (int b = b0; b <= bi; b++) dc += coef[((size_t)mcu * G.nbm + b) * 64];
+        x[0] = (int)(int16_t)dc;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) sm[lb][r][i] = x[i] * (int)sq[comp][8 * r + i];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = sm[lb][i][r];
+    idct_1d(x, o, 13 - 2);
+#pragma unroll
+    for (int i = 0; i < 8; i++) sm[lb][i][r] = o[i];        // only this thread touches column r
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = sm[lb][r][i];
+    idct_1d(x, o, 13 + 2 + 3);
+    if (!valid) return;
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        lo |= (uint32_t)min(255, max(0, o[i] + 128)) << (8 * i);
+        hi |= (uint32_t)min(255, max(0, o[4 + i] + 128)) << (8 * i);
+    }
+    const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
+    int by = my, bx = mx;
+    if (comp == 0) {
+        by = my * G.vs + bi / G.hs;
+        bx = mx * G.hs + bi % G.hs;
+    }
+    *reinterpret_cast<uint2 *>(planes + G.poff[comp] + ((size_t)by * 8 + r) * G.pw[comp] + (size_t)bx * 8) = make_uint2(lo, hi);
+}
+
+// jdsample.c + jdcolor.c: one thread = output pixels (y, 2c) and (y, 2c + 1)
+__global__ void __launch_bounds__(256) jdec_color_kernel(const uint8_t *__restrict__ planes, JdecGeom G,
+                                                         uint8_t *__restrict__ bgr, size_t stride)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (2 * c >= G.w) return;
+    const uint8_t *Y = planes + G.poff[0] + (size_t)y * G.pw[0] + 2 * c;
+    uint8_t *o = bgr + (size_t)y * stride + 6 * (size_t)c;
+    const bool two = 2 * c + 1 < G.w;
+    if (G.ncomp == 1) {
+        o[0] = o[1] = o[2] = Y[0];
+        if (two) o[3] = o[4] = o[5] = Y[1];
+        return;
+    }
+    int cbv[2], crv[2];
+    const int cw = (G.w + G.hs - 1) / G.hs, chh = (G.h + G.vs - 1) / G.vs;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint8_t *P = planes + G.poff[1 + k];
+        const int pw = G.pw[1 + k];
+        int v0, v1;
+        if (G.hs == 1) {
+            v0 = P[(size_t)y * pw + 2 * c];
+            v1 = two ? P[(size_t)y * pw + 2 * c + 1] : 0;
+        } else if (cw <= 2) {                       // jinit_upsampler: fancy only if downsampled_width > 2
+            v0 = v1 = P[(size_t)(y / G.vs) * pw + c];
+        } else if (G.vs == 1) {                     // h2v1_fancy_upsample
+            const uint8_t *in = P + (size_t)y * pw;
+            const int cur = in[c];
+            v0 = c == 0 ? cur : (cur * 3 + in[c - 1] + 1) >> 2;
+            v1 = c == cw - 1 ? cur : (cur * 3 + in[c + 1] + 2) >> 2;
+        } else {                                    // h2v2_fancy_upsample
+            const int r0 = y >> 1, r1 = min(chh - 1, max(0, (y & 1) ? r0 + 1 : r0 - 1));
+            const uint8_t *a = P + (size_t)r0 * pw, *b = P + (size_t)r1 * pw;
+            const int cur = a[c] * 3 + b[c];
+            v0 = c == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + a[c - 1] * 3 + b[c - 1] + 8) >> 4;
+            v1 = c == cw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + a[c + 1] * 3 + b[c + 1] + 7) >> 4;
+        }
+        (k ? crv : cbv)[0] = v0 - 128;
+        (k ? crv : cbv)[1] = v1 - 128;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        if (i && !two) break;
+        const int yy = Y[i], cb = cbv[i], cr = crv[i];
+        const int R = yy + ((91881 * cr + 32768) >> 16);
+        const int Gv = yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16);
+        const int B = yy + ((116130 * cb + 32768) >> 16);
+        o[3 * i] = (uint8_t)min(255, max(0, B));
+        o[3 * i + 1] = (uint8_t)min(255, max(0, Gv));
+        o[3 * i + 2] = (uint8_t)min(255, max(0, R));
+    }
+}
+
+// ---------------------------------------------------------------------------
+int32_t jpeg_info_host(const uint8_t *file, size_t n, int *w, int *h, int *ncomp)
+{
+    JdecHeader H;
+    JdecTables T;
+    OICS_TRY(parse_header(file, n, &H, &T));
+    *w = H.w;
+    *h = H.h;
+    *ncomp = H.ncomp;
+    return OICS_OK;
+}
+
+// file bytes on the HOST -> BGR image on the DEVICE (rows `stride` bytes apart).  The entropy-coded
+// segment and one table block are what crosses PCIe.  Synchronises ctx->stream once (convergence
+// and marker flags).
+int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out)
+{
+    cudaStream_t st = ctx->stream;
+    JdecHeader H;
+    OICS_TRY(ctx->pin_small.ensure(sizeof(JdecTables) + 256));
+    // the pinned staging block is reused by the next call: wait for the previous upload
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    JdecTables *T = ctx->pin_small.as<JdecTables>();
+    OICS_TRY(parse_header(file, n, &H, T));
+    *w_out = H.w;
+    *h_out = H.h;
+    if (stride < (size_t)H.w * 3) { set_error("jpeg: stride %zu is below 3 * width", stride); return OICS_ERR_INVALID_ARG; }
+    JdecGeom G;
+    G.w = H.w; G.h = H.h; G.ncomp = H.ncomp; G.hs = H.hs; G.vs = H.vs;
+    G.mcux = cdiv(H.w, 8 * H.hs); G.mcuy = cdiv(H.h, 8 * H.vs);
+    G.nbm = T->nbm;
+    size_t off = 0;
+    for (int c = 0; c < 3; c++) {
+        G.pw[c] = c < H.ncomp ? G.mcux * 8 * (c ? 1 : H.hs) : 0;
+        G.ph[c] = c < H.ncomp ? G.mcuy * 8 * (c ? 1 : H.vs) : 0;
+        G.poff[c] = off;
+        off += ((size_t)G.pw[c] * G.ph[c] + 255) & ~(size_t)255;
+    }
+    const size_t nmcu = (size_t)G.mcux * G.mcuy, nblocks = nmcu * G.nbm;
+    const size_t slen = H.scan_len, nchunks = (slen + 31) / 32, nsub = (slen * 8 + JD_SUB - 1) / JD_SUB;
+    const size_t nsum_c = (nchunks + 1023) / 1024 + 8, nsum_s = (nsub + 1023) / 1024 + 8, nsum_m = (nmcu + 1023) / 1024 + 8;
+    // scratch
+    OICS_TRY(ctx->jd_file.ensure(slen + 64));
+    OICS_TRY(ctx->jd_words.ensure(slen + 256));
+    OICS_TRY(ctx->jd_tables.ensure(sizeof(JdecTables)));
+    const size_t ngroups = (nsub + JD_GROUP - 1) / JD_GROUP;
+    const size_t n_state = nchunks + nsum_c + 3 * nsub + nsum_s + nmcu + nsum_m + 2 * nsub * JD_M + ngroups * (JD_M + 1) + 64;
+    OICS_TRY(ctx->jd_state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
+    OICS_TRY(ctx->jd_coef.ensure(nblocks * 64 * sizeof(int16_t) + 256));
+    OICS_TRY(ctx->jd_planes.ensure(off + 256));
+    unsigned long long *cnt = ctx->jd_state.as<unsigned long long>(), *sums_c = cnt + nchunks, *used = sums_c + nsum_c;
+    unsigned long long *out = used + nsub, *nblk = out + nsub, *sums_s = nblk + nsub, *mcu = sums_s + nsum_s;
+    unsigned long long *sums_m = mcu + nmcu, *keys = sums_m + nsum_m, *exits = keys + nsub * JD_M, *gexit = exits + nsub * JD_M;
+    unsigned long long *gin = gexit + ngroups * JD_M, *removed = gin + ngroups, *tot_blocks = removed + 1, *tot_dc = removed + 2;
+    int *flags = reinterpret_cast<int *>(removed + 4);   // [0]: 1 marker inside the scan, 2 memo table full, 4 not closed; [1 + r]: round r added entries
+    unsigned *nbs = reinterpret_cast<unsigned *>(removed + 64), *cntm = nbs + nsub * JD_M;
+    const int ROUNDS = 10;
+    uint8_t *d_scan = ctx->jd_file.as<uint8_t>();
+    uint32_t *words = ctx->jd_words.as<uint32_t>();
+    JdecTables *dT = ctx->jd_tables.as<JdecTables>();
+    int16_t *coef = ctx->jd_coef.as<int16_t>();
+    OICS_CUDA_TRY(cudaMemcpyAsync(dT, T, sizeof(JdecTables), cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(d_scan, file + H.scan_off, slen, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 256, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(nblk, 0, nsub * sizeof(unsigned long long), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(removed, 0, 64 * sizeof(unsigned long long), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(cntm, 0, nsub * sizeof(unsigned), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(coef, 0, nblocks * 64 * sizeof(int16_t), st));
+    const unsigned gc = (unsigned)((nchunks + 255) / 256), gs = (unsigned)((nsub + 127) / 128);
+    jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, flags);
+    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums_c, removed, nullptr));
+    jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, reinterpret_cast<uint8_t *>(words));
+    ctx->launches += 2;
+    int hflags[32];
+    bool plain = false;
+    for (int pass = 0;; pass++) {
+        // candidate tables until closed, then the chain of lookups
+        for (int r = pass ? 1 : 0; r <= ROUNDS; r++)
+            jdec_memo_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, keys, exits, nbs, cntm, r, flags);
+        jdec_group_kernel<<<(unsigned)((ngroups * JD_M * 32 + 127) / 128), 128, 0, st>>>(keys, exits, cntm, nsub, ngroups, gexit, flags);
+        jdec_top_kernel<<<1, 32, 0, st>>>(keys, gexit, cntm, ngroups, gin, flags);
+        jdec_fill_kernel<<<(unsigned)((ngroups * 32 + 127) / 128), 128, 0, st>>>(keys, exits, nbs, cntm, nsub, ngroups, gin, used, nblk, flags);
+        OICS_CUDA_TRY(cudaGetLastError());
+        ctx->launches += ROUNDS + 4;
+        OICS_CUDA_TRY(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        if (hflags[0] & 1) {
+            set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
+            return OICS_ERR_UNSUPPORTED;
+        }
+        if (hflags[0] & 2 || pass >= 16) { plain = true; break; }
+        if (!(hflags[0] & 4) && !hflags[1 + ROUNDS]) break;   // closed and resolved
+        OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
+    }
+    if (plain) {
+        // fallback: predecessor's exit state fed forward, one subsequence further per round
+        OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
+        OICS_CUDA_TRY(cudaMemsetAsync(nblk, 0, nsub * sizeof(unsigned long long), st));
+        jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, 0, flags);
+        for (;;) {
+            for (int r = 1; r <= ROUNDS; r++) jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, r, flags);
+            ctx->launches += ROUNDS;
+            OICS_CUDA_TRY(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, st));
+            OICS_CUDA_TRY(cudaStreamSynchronize(st));
+            if (!hflags[ROUNDS]) break;
+            OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
+        }
+    }
+    OICS_TRY(exclusive_scan(ctx, nblk, nsub, sums_s, tot_blocks, nullptr));
+    jdec_write_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, nblk, (unsigned long long)nblocks, coef);
+    jdec_mcu_dc_kernel<<<(unsigned)((nmcu + 255) / 256), 256, 0, st>>>(coef, G, mcu);
+    OICS_TRY(exclusive_scan(ctx, mcu, nmcu, sums_m, tot_dc, nullptr));
+    jdec_idct_kernel<<<(unsigned)((nblocks + 31) / 32), 256, 0, st>>>(dT, coef, mcu, G, ctx->jd_planes.as<uint8_t>());
+    jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(H.w, 2), 256), (unsigned)H.h), 256, 0, st>>>(ctx->jd_planes.as<uint8_t>(), G, d_bgr, stride);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 4;
+    return OICS_OK;
+}
+
+}  // namespace oics

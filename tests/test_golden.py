@@ -192,3 +192,41 @@ def test_cuda_matches_golden(path):
     from omr_img_corrector_b200 import api
     with api.Context(0) as ctx:
         _check(CudaImpl(ctx, api), api, path)
+
+
+# ----------------------------------------------------------------------------- N2: JPEG files
+JPEGS = sorted(glob.glob(os.path.join(HERE, "golden", "jpeg", "*.jpg")))
+
+
+def _jpeg_expected():
+    return np.load(os.path.join(HERE, "golden", "jpeg", "expected_pixels.npz"))
+
+
+def test_jpeg_goldens_exist():
+    assert len(JPEGS) >= 12
+
+
+@pytest.mark.parametrize("path", JPEGS, ids=[os.path.basename(f) for f in JPEGS])
+def test_oracle_decodes_golden_jpeg(orc, path):
+    """cv2.imdecode's pixels of cv2-written files (tools/make_jpeg_goldens.py), bit for bit."""
+    want = _jpeg_expected()[os.path.basename(path)[:-4]]
+    assert np.array_equal(orc.jpeg_decode(open(path, "rb").read()), want)
+
+
+@pytest.mark.parametrize("path", [p for p in JPEGS if "420_q100" in p or "420_q75" in p],
+                         ids=lambda p: os.path.basename(p))
+def test_oracle_reencodes_golden_jpeg(orc, path):
+    """imwrite side: encoding the decoded pixels at the file's quality reproduces cv2's own encoding of them."""
+    import cv2
+    px = _jpeg_expected()[os.path.basename(path)[:-4]]
+    q = 100 if "q100" in path else 75
+    assert orc.jpeg_encode(px, q) == bytes(cv2.imencode(".jpg", px, [cv2.IMWRITE_JPEG_QUALITY, q])[1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", JPEGS, ids=[os.path.basename(f) for f in JPEGS])
+def test_cuda_decodes_golden_jpeg(path):
+    from omr_img_corrector_b200 import api
+    want = _jpeg_expected()[os.path.basename(path)[:-4]]
+    with api.Context(0) as ctx:
+        assert np.array_equal(ctx.jpeg_decode(open(path, "rb").read()), want)

@@ -569,3 +569,42 @@ def test_correct_batch_jpeg_files(ctx, orc, dataset_like):
         assert (ang[i], bool(need[i])) == (ra, bool(rneed))
         assert tuple(sizes[i]) == (rout.shape[1], rout.shape[0])
         assert outs[i][:fsz[i]].tobytes() == orc.jpeg_encode(rout, 100), i
+
+
+# ----------------------------------------------------------------------------- N2: imread(JPEG)
+@pytest.mark.parametrize("shape", [(37, 53), (64, 48), (16, 16), (95, 130), (1, 1), (9, 7), (5, 4), (33, 17), (230, 248), (700, 500)])
+def test_jpeg_decode_pixels(ctx, orc, shape):
+    """omr.rs:349 imread(IMREAD_COLOR): the CUDA decoder (parallel Huffman decode, IDCT, fancy
+    upsampling, colour conversion) gives the oracle's = libjpeg's pixels bit for bit."""
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    img = (rng.random(shape + (3,)) * 255).astype(np.uint8)
+    img[shape[0] // 4:shape[0] // 2, shape[1] // 5:shape[1] // 2] = (10, 200, 90)
+    white = np.full(shape + (3,), 255, np.uint8)
+    white[shape[0] // 3:shape[0] // 3 + 2] = 0
+    for im in (img, white):
+        for q in (100, 90, 30):
+            data = orc.jpeg_encode(im, q)
+            assert np.array_equal(ctx.jpeg_decode(data), orc.jpeg_decode(data)), (shape, q)
+
+
+def test_jpeg_decode_a4_card_round_trip(ctx, orc):
+    """A full A4 card: written by the CUDA encoder, read back by the CUDA decoder, equal to the oracle's
+    decode of the same bytes; decoding is repeatable (the synchronisation rounds are deterministic)."""
+    g, a = synth.base_card(1)
+    bgr = ctx.rotate_mat(synth.to_bgr(g), -a, 1.0, api.INTER_LINEAR, api.WHITE, api.CLIP_DEFAULT)
+    data = ctx.jpeg_encode(bgr, 100)
+    got = ctx.jpeg_decode(data)
+    assert np.array_equal(got, orc.jpeg_decode(data))
+    assert np.array_equal(ctx.jpeg_decode(data), got)
+
+
+def test_jpeg_decode_rejects_what_it_does_not_cover(ctx):
+    with pytest.raises(api.OicsError):
+        ctx.jpeg_decode(b"\xff\xd8 definitely not a jpeg")
+    import cv2
+    prog = cv2.imencode(".jpg", np.zeros((16, 16, 3), np.uint8), [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()
+    with pytest.raises(api.OicsError):
+        ctx.jpeg_decode(prog)
+    rst = cv2.imencode(".jpg", np.zeros((64, 64, 3), np.uint8), [cv2.IMWRITE_JPEG_RST_INTERVAL, 2])[1].tobytes()
+    with pytest.raises(api.OicsError):
+        ctx.jpeg_decode(rst)
