@@ -256,6 +256,7 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
 {
     unsigned done = 0;
     unsigned long long wi = ~0ull - 1;   // never the predecessor of a real word index
+    int tdc = 2 * S.comp_of[bi];         // table pair of the current block (off the per-symbol path)
     uint32_t a = 0, b = 0;
     while (p < end) {
         const unsigned long long w = p >> 5;
@@ -265,7 +266,7 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
             wi = w;
         }
         const uint32_t v = __funnelshift_l(b, a, (int)(p & 31));   // the next 32 bits of the stream
-        const int t = 2 * S.comp_of[bi] + (k ? 1 : 0);
+        const int t = tdc + (k ? 1 : 0);
         int len, sym;
         const unsigned e = S.lut[t][v >> 24];
         if (e) {
@@ -307,6 +308,7 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
         if (k >= 64) {
             k = 0;
             bi = bi + 1 == S.nbm ? 0 : bi + 1;
+            tdc = 2 * S.comp_of[bi];
             done++;
         }
     }
@@ -315,168 +317,80 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
 
 // One round of the synchronisation: thread j decodes subsequence j from its predecessor's exit state
 // unless that is the state it used last time.  round 0: from the guess (j * JD_SUB, 0, 0).
+// Uniform stretches (the white of a scanned card: every MCU is the same few bits) do not
+// self-synchronise in (k, block): decoders that entered with a wrong phase parse them consistently,
+// and their states at the subsequence boundaries cycle through a few values round after round until
+// the true state arrives from the left, one subsequence per round.  Each thread therefore remembers
+// the last JD_M (entry -> exit, blocks) pairs it decoded: a round whose input it has seen before costs
+// a lookup, so only the front of the true chain decodes.
+#define JD_M 4
+
 __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
                                                         const unsigned long long *__restrict__ removed, size_t scan_len,
-                                                        unsigned long long *__restrict__ used, unsigned long long *__restrict__ out,
-                                                        unsigned long long *__restrict__ nblk, int round, int *__restrict__ changed)
-{
-    __shared__ JdecShared S;
-    jdec_load_tables(S, T);
-    const unsigned long long total = 8ull * (scan_len - *removed);
-    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j * JD_SUB >= total) return;
-    unsigned long long x = jdec_pack(j * JD_SUB, 0, 0);
-    if (round > 0) {
-        if (j > 0) x = out[j - 1];
-        if (x == used[j]) return;
-    }
-    unsigned long long p = x >> 12;
-    int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
-    NoSink sink;
-    const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
-    used[j] = x;
-    out[j] = jdec_pack(p, k, bi);
-    nblk[j] = n;
-    if (round > 0) atomicOr(changed + round, 1);
-}
-
-// ---- synchronisation with memoised candidates -------------------------------------------------
-// Streams with long periodic stretches (the white of a scanned card: every MCU is the same 32 bits)
-// do not self-synchronise in (k, block): a decoder that entered with the wrong block phase parses
-// them consistently forever, and the plain scheme above then advances one subsequence per round.
-// Instead every subsequence keeps a small table  entry state -> (exit state, blocks completed)  of
-// the candidates it has decoded so far; each round it decodes one exit state of its predecessor's
-// table that it has not seen yet.  Few distinct phases exist, so after a few rounds the tables are
-// closed (every exit of table j-1 is a key of table j), and the true chain -- table 0 holds the real
-// start -- is a walk of lookups, done hierarchically by warps whose lanes each hold one table row
-// (no load depends on the walked state).
-#define JD_M 16      // candidates per subsequence
-#define JD_GROUP 256 // subsequences per lookup group
-
-__global__ void __launch_bounds__(128) jdec_memo_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
-                                                        const unsigned long long *__restrict__ removed, size_t scan_len,
-                                                        unsigned long long *keys, unsigned long long *exits,
-                                                        unsigned *nbs, unsigned *cntm, int round, int *__restrict__ flags)
+                                                        unsigned long long *used, unsigned long long *out,
+                                                        unsigned long long *__restrict__ nblk, unsigned long long *mkey,
+                                                        unsigned long long *mout, unsigned *mnb, unsigned *mcnt, int round,
+                                                        int *__restrict__ changed)
 {
     __shared__ JdecShared S;
     const unsigned long long total = 8ull * (scan_len - *removed);
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    bool need = false;
-    unsigned long long x = 0;
-    unsigned cm = 0;
-    if (j * JD_SUB < total) {
-        if (round == 0) {
-            x = jdec_pack(j * JD_SUB, 0, 0);      // for j = 0 this is the true start
-            need = true;
-        } else if (j > 0) {
-            const unsigned cp = min(__ldcg(cntm + j - 1), (unsigned)JD_M);
-            cm = min(__ldcg(cntm + j), (unsigned)JD_M);
-            for (unsigned a = 0; a < cp && !need; a++) {
-                const unsigned long long e = __ldcg(exits + (j - 1) * JD_M + a);
-                bool found = false;
-                for (unsigned b = 0; b < cm; b++) found |= __ldcg(keys + j * JD_M + b) == e;
-                if (!found) {
-                    x = e;
+    const bool live = j * JD_SUB < total;
+    bool tables = false;
+    unsigned long long mine = live && round > 0 ? used[j] : ~0ull;   // the entry state of my last decode / lookup
+    unsigned cnt = live && round > 0 ? mcnt[j] : 0;
+    // Inside the CTA the chain advances without leaving the kernel: one iteration = every thread looks
+    // at its predecessor's exit again.  Across CTAs it advances with the next launch.
+    for (int it = 0; it < (round ? 128 : 1); it++) {
+        bool need = false, hit = false;
+        unsigned long long x = jdec_pack(j * JD_SUB, 0, 0);
+        if (live) {
+            if (round == 0) {
+                need = true;
+            } else {
+                if (j > 0) x = __ldcg(out + j - 1);
+                if (x != mine) {
                     need = true;
+                    for (unsigned b = 0; b < min(cnt, (unsigned)JD_M); b++) {
+                        if (mkey[j * JD_M + b] == x) {          // seen before
+                            mine = x;
+                            __stcg(out + j, mout[j * JD_M + b]);
+                            nblk[j] = mnb[j * JD_M + b];
+                            need = false;
+                            hit = true;
+                            break;
+                        }
+                    }
                 }
             }
         }
-    }
-    if (!__syncthreads_or(need)) return;
-    jdec_load_tables(S, T);
-    if (!need) return;
-    if (cm >= JD_M) {
-        atomicOr(flags, 2);                         // table full: the caller falls back to the plain rounds
-        return;
-    }
-    unsigned long long p = x >> 12;
-    int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
-    NoSink sink;
-    const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
-    keys[j * JD_M + cm] = x;
-    exits[j * JD_M + cm] = jdec_pack(p, k, bi);
-    nbs[j * JD_M + cm] = n;
-    __threadfence();
-    cntm[j] = cm + 1;
-    atomicOr(flags + 1 + round, 1);
-}
-
-// one warp = (group, candidate a of the group's first subsequence): the exit state of the group
-__global__ void __launch_bounds__(128) jdec_group_kernel(const unsigned long long *__restrict__ keys,
-                                                         const unsigned long long *__restrict__ exits,
-                                                         const unsigned *__restrict__ cntm, size_t nsub, size_t ngroups,
-                                                         unsigned long long *__restrict__ gexit, int *__restrict__ flags)
-{
-    const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (wid >= ngroups * JD_M) return;
-    const size_t g = wid / JD_M, j0 = g * JD_GROUP, j1 = min(nsub, j0 + JD_GROUP);
-    const int a = (int)(wid - g * JD_M);
-    if (a >= (int)cntm[j0]) return;
-    unsigned long long state = keys[j0 * JD_M + a];
-    bool lost = false;
-    for (size_t j = j0; j < j1; j++) {
-        const bool live = lane < (int)min(cntm[j], (unsigned)JD_M);
-        const unsigned long long kk = live ? keys[j * JD_M + lane] : 0ull, ee = live ? exits[j * JD_M + lane] : 0ull;
-        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
-        if (!m) { lost = true; break; }
-        state = __shfl_sync(0xffffffffu, ee, __ffs(m) - 1);
-    }
-    if (lane == 0) {
-        gexit[wid] = lost ? ~0ull : state;
-    }
-}
-
-// one warp: the true entry state of every group
-__global__ void __launch_bounds__(32) jdec_top_kernel(const unsigned long long *__restrict__ keys,
-                                                      const unsigned long long *__restrict__ gexit,
-                                                      const unsigned *__restrict__ cntm, size_t ngroups,
-                                                      unsigned long long *__restrict__ gin, int *__restrict__ flags)
-{
-    const int lane = threadIdx.x;
-    unsigned long long state = jdec_pack(0, 0, 0);
-    for (size_t g = 0; g < ngroups; g++) {
-        if (lane == 0) gin[g] = state;
-        const size_t j0 = g * JD_GROUP;
-        const bool live = lane < (int)min(cntm[j0], (unsigned)JD_M);
-        const unsigned long long kk = live ? keys[j0 * JD_M + lane] : 0ull, ee = live ? gexit[g * JD_M + lane] : ~0ull;
-        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
-        const unsigned long long nx = m ? __shfl_sync(0xffffffffu, ee, __ffs(m) - 1) : ~0ull;
-        if (nx == ~0ull) {                          // not closed: fall back
-            if (lane == 0) atomicOr(flags, 4);
-            return;
+        const int any_need = __syncthreads_or(need), any_hit = __syncthreads_or(hit);
+        if (!any_need && !any_hit) break;
+        if (round > 0 && threadIdx.x == 0) changed[round] = 1;
+        if (any_need && !tables) {
+            jdec_load_tables(S, T);
+            tables = true;
         }
-        state = nx;
-    }
-}
-
-// one warp per group: entry state and block count of each of its subsequences
-__global__ void __launch_bounds__(128) jdec_fill_kernel(const unsigned long long *__restrict__ keys,
-                                                        const unsigned long long *__restrict__ exits,
-                                                        const unsigned *__restrict__ nbs, const unsigned *__restrict__ cntm,
-                                                        size_t nsub, size_t ngroups, const unsigned long long *__restrict__ gin,
-                                                        unsigned long long *__restrict__ used, unsigned long long *__restrict__ nblk,
-                                                        int *__restrict__ flags)
-{
-    const size_t g = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (g >= ngroups) return;
-    const size_t j0 = g * JD_GROUP, j1 = min(nsub, j0 + JD_GROUP);
-    unsigned long long state = gin[g];
-    for (size_t j = j0; j < j1; j++) {
-        const bool live = lane < (int)min(cntm[j], (unsigned)JD_M);
-        const unsigned long long kk = live ? keys[j * JD_M + lane] : 0ull, ee = live ? exits[j * JD_M + lane] : 0ull;
-        const unsigned nn = live ? nbs[j * JD_M + lane] : 0u;
-        const unsigned m = __ballot_sync(0xffffffffu, live && kk == state);
-        if (!m) {
-            if (lane == 0) atomicOr(flags, 4);
-            return;
+        if (need) {
+            unsigned long long p = x >> 12;
+            int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
+            NoSink sink;
+            const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+            const unsigned long long e = jdec_pack(p, k, bi);
+            mine = x;
+            __stcg(out + j, e);
+            nblk[j] = n;
+            const unsigned slot = cnt % JD_M;               // the oldest entry is replaced
+            mkey[j * JD_M + slot] = x;
+            mout[j * JD_M + slot] = e;
+            mnb[j * JD_M + slot] = n;
+            cnt++;
         }
-        const int src = __ffs(m) - 1;
-        if (lane == 0) used[j] = state;
-        const unsigned nb = __shfl_sync(0xffffffffu, nn, src);
-        if (lane == 0) nblk[j] = nb;
-        state = __shfl_sync(0xffffffffu, ee, src);
+        __syncthreads();                                    // exits written above are read by the neighbours next
+    }
+    if (live) {
+        used[j] = mine;
+        mcnt[j] = cnt;
     }
 }
 
@@ -734,18 +648,16 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
     OICS_TRY(ctx->jd_file.ensure(slen + 64));
     OICS_TRY(ctx->jd_words.ensure(slen + 256));
     OICS_TRY(ctx->jd_tables.ensure(sizeof(JdecTables)));
-    const size_t ngroups = (nsub + JD_GROUP - 1) / JD_GROUP;
-    const size_t n_state = nchunks + nsum_c + 3 * nsub + nsum_s + nmcu + nsum_m + 2 * nsub * JD_M + ngroups * (JD_M + 1) + 64;
+    const size_t n_state = nchunks + nsum_c + 3 * nsub + nsum_s + nmcu + nsum_m + 2 * nsub * JD_M + 64;
     OICS_TRY(ctx->jd_state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
     OICS_TRY(ctx->jd_coef.ensure(nblocks * 64 * sizeof(int16_t) + 256));
     OICS_TRY(ctx->jd_planes.ensure(off + 256));
     unsigned long long *cnt = ctx->jd_state.as<unsigned long long>(), *sums_c = cnt + nchunks, *used = sums_c + nsum_c;
     unsigned long long *out = used + nsub, *nblk = out + nsub, *sums_s = nblk + nsub, *mcu = sums_s + nsum_s;
-    unsigned long long *sums_m = mcu + nmcu, *keys = sums_m + nsum_m, *exits = keys + nsub * JD_M, *gexit = exits + nsub * JD_M;
-    unsigned long long *gin = gexit + ngroups * JD_M, *removed = gin + ngroups, *tot_blocks = removed + 1, *tot_dc = removed + 2;
-    int *flags = reinterpret_cast<int *>(removed + 4);   // [0]: 1 marker inside the scan, 2 memo table full, 4 not closed; [1 + r]: round r added entries
-    unsigned *nbs = reinterpret_cast<unsigned *>(removed + 64), *cntm = nbs + nsub * JD_M;
-    const int ROUNDS = 10;
+    unsigned long long *sums_m = mcu + nmcu, *mkey = sums_m + nsum_m, *mout = mkey + nsub * JD_M, *removed = mout + nsub * JD_M;
+    unsigned long long *tot_blocks = removed + 1, *tot_dc = removed + 2;
+    unsigned *mnb = reinterpret_cast<unsigned *>(removed + 64), *mcnt = mnb + nsub * JD_M;
+    int *flags = reinterpret_cast<int *>(removed + 4);   // [0]: a marker inside the scan; [r]: round r changed something
     uint8_t *d_scan = ctx->jd_file.as<uint8_t>();
     uint32_t *words = ctx->jd_words.as<uint32_t>();
     JdecTables *dT = ctx->jd_tables.as<JdecTables>();
@@ -755,7 +667,7 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
     OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 256, st));
     OICS_CUDA_TRY(cudaMemsetAsync(nblk, 0, nsub * sizeof(unsigned long long), st));
     OICS_CUDA_TRY(cudaMemsetAsync(removed, 0, 64 * sizeof(unsigned long long), st));
-    OICS_CUDA_TRY(cudaMemsetAsync(cntm, 0, nsub * sizeof(unsigned), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(mcnt, 0, nsub * sizeof(unsigned), st));
     OICS_CUDA_TRY(cudaMemsetAsync(coef, 0, nblocks * 64 * sizeof(int16_t), st));
     const unsigned gc = (unsigned)((nchunks + 255) / 256), gs = (unsigned)((nsub + 127) / 128);
     jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, flags);
@@ -763,38 +675,23 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
     jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, reinterpret_cast<uint8_t *>(words));
     ctx->launches += 2;
     int hflags[32];
-    bool plain = false;
-    for (int pass = 0;; pass++) {
-        // candidate tables until closed, then the chain of lookups
-        for (int r = pass ? 1 : 0; r <= ROUNDS; r++)
-            jdec_memo_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, keys, exits, nbs, cntm, r, flags);
-        jdec_group_kernel<<<(unsigned)((ngroups * JD_M * 32 + 127) / 128), 128, 0, st>>>(keys, exits, cntm, nsub, ngroups, gexit, flags);
-        jdec_top_kernel<<<1, 32, 0, st>>>(keys, gexit, cntm, ngroups, gin, flags);
-        jdec_fill_kernel<<<(unsigned)((ngroups * 32 + 127) / 128), 128, 0, st>>>(keys, exits, nbs, cntm, nsub, ngroups, gin, used, nblk, flags);
-        OICS_CUDA_TRY(cudaGetLastError());
-        ctx->launches += ROUNDS + 4;
-        OICS_CUDA_TRY(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, st));
-        OICS_CUDA_TRY(cudaStreamSynchronize(st));
-        if (hflags[0] & 1) {
-            set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
-            return OICS_ERR_UNSUPPORTED;
-        }
-        if (hflags[0] & 2 || pass >= 16) { plain = true; break; }
-        if (!(hflags[0] & 4) && !hflags[1 + ROUNDS]) break;   // closed and resolved
-        OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
-    }
-    if (plain) {
-        // fallback: predecessor's exit state fed forward, one subsequence further per round
-        OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
-        OICS_CUDA_TRY(cudaMemsetAsync(nblk, 0, nsub * sizeof(unsigned long long), st));
-        jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, 0, flags);
-        for (;;) {
-            for (int r = 1; r <= ROUNDS; r++) jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, r, flags);
-            ctx->launches += ROUNDS;
+    {
+        // every thread is fed its predecessor's exit state until a round changes nothing; the host looks
+        // at the flags after 8 rounds (enough for photographic content), then every 31 (long uniform
+        // stretches -- the white of a scanned card -- advance one subsequence per round)
+        jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, mkey, mout, mnb, mcnt, 0, flags);
+        for (int rounds = 8;; rounds = 31) {
+            for (int r = 1; r <= rounds; r++) jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, mkey, mout, mnb, mcnt, r, flags);
+            OICS_CUDA_TRY(cudaGetLastError());
+            ctx->launches += rounds;
             OICS_CUDA_TRY(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, st));
             OICS_CUDA_TRY(cudaStreamSynchronize(st));
-            if (!hflags[ROUNDS]) break;
-            OICS_CUDA_TRY(cudaMemsetAsync(flags, 0, 32 * sizeof(int), st));
+            if (hflags[0] & 1) {
+                set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
+                return OICS_ERR_UNSUPPORTED;
+            }
+            if (!hflags[rounds]) break;
+            OICS_CUDA_TRY(cudaMemsetAsync(flags + 1, 0, 31 * sizeof(int), st));
         }
     }
     OICS_TRY(exclusive_scan(ctx, nblk, nsub, sums_s, tot_blocks, nullptr));
