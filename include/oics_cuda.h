@@ -277,6 +277,18 @@ OICS_API int32_t oics_correct_batch_jpeg(oics_ctx *ctx, const uint8_t *bgrs, int
                                          const size_t *dst_caps, size_t *dst_sizes, int32_t *dst_ws, int32_t *dst_hs,
                                          double *angles, int32_t *need_checks, int32_t *statuses);
 
+/* The whole of omr::correct_default for a batch (omr.rs:339-452 including imread at :349 and imwrite at
+ * :447-448): files[c] / file_sizes[c] are baseline JPEG files in host memory (pinned for asynchronous
+ * copies), decoded on the device -- a few MB per card cross PCIe in each direction and the host does no
+ * codec work.  All cards must have the size of files[0]; a file that cannot be decoded (or differs in
+ * size) gets its error in statuses[c] and the batch goes on.  jpeg_quality 0: dsts receive BGR pixels,
+ * 1..100: the JPEG file imwrite would produce, its size in dst_sizes[c]. */
+OICS_API int32_t oics_correct_batch_files(oics_ctx *ctx, const uint8_t *const *files, const size_t *file_sizes, int32_t n_cards,
+                                          uint16_t max_angle, double step, int32_t max_w, int32_t max_h,
+                                          double hough_min_line_length, double hough_max_line_gap, int32_t jpeg_quality,
+                                          uint8_t *const *dsts, const size_t *dst_caps, size_t *dst_sizes, int32_t *dst_ws,
+                                          int32_t *dst_hs, double *angles, int32_t *need_checks, int32_t *statuses);
+
 #ifdef __cplusplus
 }
 #endif

@@ -77,6 +77,8 @@ SIGNATURES = {
     "oics_correct_default": (_i32, [_ctx, _u8p, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64, _u8p, _sz, _ip, _ip, _dp, _ip]),
     "oics_correct_batch": (_i32, [_ctx, _u8p, _i32, _sz, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64,
                                   C.POINTER(C.c_void_p), C.POINTER(_sz), _ip, _ip, _dp, _ip, _ip]),
+    "oics_correct_batch_files": (_i32, [_ctx, C.POINTER(C.c_void_p), C.POINTER(_sz), _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64, _i32,
+                                        C.POINTER(C.c_void_p), C.POINTER(_sz), C.POINTER(_sz), _ip, _ip, _dp, _ip, _ip]),
     "oics_correct_batch_jpeg": (_i32, [_ctx, _u8p, _i32, _sz, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, _f64, _f64, _i32,
                                        C.POINTER(C.c_void_p), C.POINTER(_sz), C.POINTER(_sz), _ip, _ip, _dp, _ip, _ip]),
 }

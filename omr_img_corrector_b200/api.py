@@ -464,6 +464,32 @@ class Context:
                                                 _dptr(angles), needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
         return angles, needs.astype(bool), stats, sizes.T.copy(), np.array(list(fsz), np.int64)
 
+    def correct_batch_files(self, files, max_angle, step, max_w, max_h, hough_min_len, hough_max_gap, outs=None,
+                            jpeg_quality=100):
+        """omr::correct_default from file bytes to file bytes: `files` is a list of uint8 numpy arrays (JPEG
+        files, ideally views of pinned memory), all cards of the first file's size.  jpeg_quality 0 -> the
+        buffers in `outs` receive BGR pixels, 1..100 -> the JPEG file imwrite would write.
+        -> (angles, need_checks, statuses, dst sizes [n, 2], file sizes)"""
+        n = len(files)
+        files = [f if isinstance(f, np.ndarray) else np.frombuffer(f, np.uint8) for f in files]
+        fptr = (C.c_void_p * n)(*[f.ctypes.data for f in files])
+        flen = (C.c_size_t * n)(*[f.size for f in files])
+        angles = np.zeros(n, np.float64)
+        needs = np.zeros(n, np.int32)
+        stats = np.zeros(n, np.int32)
+        sizes = np.zeros((2, n), np.int32)
+        dsts = caps = None
+        if outs is not None:
+            dsts = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+            caps = (C.c_size_t * n)(*[o.size for o in outs])
+        ip = C.POINTER(C.c_int32)
+        fsz = (C.c_size_t * n)()
+        check(self._lib.oics_correct_batch_files(self._h, fptr, flen, n, int(max_angle), float(step), max_w, max_h,
+                                                 float(hough_min_len), float(hough_max_gap), int(jpeg_quality), dsts, caps, fsz,
+                                                 sizes[0].ctypes.data_as(ip), sizes[1].ctypes.data_as(ip), _dptr(angles),
+                                                 needs.ctypes.data_as(ip), stats.ctypes.data_as(ip)))
+        return angles, needs.astype(bool), stats, sizes.T.copy(), np.array(list(fsz), np.int64)
+
 
 _default = {}
 _default_lock = threading.Lock()

@@ -590,19 +590,23 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                                   int32_t max_h, double hough_min_line_length, double hough_max_line_gap,
                                   int32_t jpeg_quality, uint8_t *const *dsts, const size_t *dst_caps, size_t *dst_sizes,
                                   int32_t *dst_ws, int32_t *dst_hs, double *angles, int32_t *need_checks,
-                                  int32_t *statuses)
+                                  int32_t *statuses, const uint8_t *const *files = nullptr, const size_t *file_sizes = nullptr)
 {
+    // files != nullptr: the cards arrive as JPEG files in host memory (imread, omr.rs:349) and are decoded
+    // on the device, each on its own stream, into the slot the upload would have filled
     CtxGuard g(ctx);
     if (g.status) return g.status;
-    OICS_TRY(check_image(bgrs, w, h, stride, 3));
+    if (!files) OICS_TRY(check_image(bgrs, w, h, stride, 3));
+    OICS_ARG(!files || (file_sizes && w > 0 && h > 0));
     OICS_ARG(n_cards >= 0 && angles && need_checks && statuses);
     OICS_ARG(jpeg_quality >= 0 && jpeg_quality <= 100 && (!jpeg_quality || !dsts || dst_sizes));
     OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
     OICS_ARG(!dsts || dst_caps);
     if (n_cards == 0) return OICS_OK;
-    const bool dev_in = is_device_ptr(bgrs);
+    const bool dev_in = !files && is_device_ptr(bgrs);
     const size_t row = (size_t)w * 3, card_bytes = row * h;
     const int B = std::min<int>(n_cards, 8);    // cards per sub-batch
+    std::vector<int32_t> file_status((size_t)n_cards, OICS_OK);
     const int n_sub = cdiv(n_cards, B);
     cudaStream_t st = ctx->stream, up = nullptr, down = nullptr;
     cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
@@ -676,7 +680,15 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (e == cudaSuccess) e = cudaEventRecord(in_ready[s], up);
         return e;
     };
-    if (!dev_in) {
+    auto decode = [&](int k) -> int32_t {   // files of sub-batch k -> in_slot[k & 1]
+        const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
+        return jpeg_decode_batch_device(ctx, files + c0, file_sizes + c0, nb, w, h, in_slot[s]->as<uint8_t>(), card_bytes,
+                                        k >= 2 ? in_free[s] : nullptr, up, in_ready[s], file_status.data() + c0);
+    };
+    if (files) {
+        OICS_BATCH_TRY(decode(0));
+        if (n_sub > 1) OICS_BATCH_TRY(decode(1));
+    } else if (!dev_in) {
         OICS_BATCH_CUDA(upload(0));
         if (n_sub > 1) OICS_BATCH_CUDA(upload(1));
     }
@@ -701,7 +713,15 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             const int c = c0 + i;
             const uint8_t *card = dsrc + (size_t)i * dcard;
             oics_omr_result p = {0, 0, 0, cand.data(), (int32_t)cand.size()};
-            int32_t stc = oics_rule_a(hh.data() + (size_t)i * 2 * N, v.data() + (size_t)i * 2 * N, N, step, &p);
+            int32_t stc = file_status[c];       // a file that did not decode: its status, nothing else
+            if (stc != OICS_OK) {
+                statuses[c] = stc;
+                angles[c] = 0.0;
+                need_checks[c] = 0;
+                if (dst_sizes) dst_sizes[c] = 0;
+                continue;
+            }
+            stc = oics_rule_a(hh.data() + (size_t)i * 2 * N, v.data() + (size_t)i * 2 * N, N, step, &p);
             double a = 0.0;
             int32_t need = 0;
             if (stc == OICS_OK) {
@@ -770,7 +790,10 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (rc != OICS_OK) break;
         if (!dev_in) {
             OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
-            if (k + 2 < n_sub) OICS_BATCH_CUDA(upload(k + 2));
+            if (k + 2 < n_sub) {
+                if (files) OICS_BATCH_TRY(decode(k + 2));
+                else OICS_BATCH_CUDA(upload(k + 2));
+            }
         }
         if (jpeg_quality && dsts) {   // file sizes of the sub-batch: one read-back
             std::vector<unsigned long long> totals((size_t)2 * nb, 0ull);
@@ -815,6 +838,22 @@ OICS_API int32_t oics_correct_batch(oics_ctx *ctx, const uint8_t *bgrs, int32_t 
     return correct_batch_impl(ctx, bgrs, n_cards, card_stride, w, h, stride, max_angle, step, max_w, max_h,
                               hough_min_line_length, hough_max_line_gap, 0, dsts, dst_caps, nullptr, dst_ws, dst_hs, angles,
                               need_checks, statuses);
+}
+
+OICS_API int32_t oics_correct_batch_files(oics_ctx *ctx, const uint8_t *const *files, const size_t *file_sizes, int32_t n_cards,
+                                          uint16_t max_angle, double step, int32_t max_w, int32_t max_h,
+                                          double hough_min_line_length, double hough_max_line_gap, int32_t jpeg_quality,
+                                          uint8_t *const *dsts, const size_t *dst_caps, size_t *dst_sizes, int32_t *dst_ws,
+                                          int32_t *dst_hs, double *angles, int32_t *need_checks, int32_t *statuses)
+{
+    OICS_ARG(files && file_sizes && n_cards >= 0);
+    if (n_cards == 0) return OICS_OK;
+    int w = 0, h = 0, nc = 0;
+    OICS_ARG(files[0]);
+    OICS_TRY(jpeg_info_host(files[0], file_sizes[0], &w, &h, &nc));   // the batch's card size; other sizes fail per card
+    return correct_batch_impl(ctx, nullptr, n_cards, (size_t)w * 3 * h, w, h, w * 3, max_angle, step, max_w, max_h,
+                              hough_min_line_length, hough_max_line_gap, jpeg_quality, dsts, dst_caps, dst_sizes, dst_ws,
+                              dst_hs, angles, need_checks, statuses, files, file_sizes);
 }
 
 OICS_API int32_t oics_correct_batch_jpeg(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_cards, size_t card_stride,

@@ -85,6 +85,8 @@ struct SweepCache {
 
 }  // namespace oics
 
+#define OICS_JD_SLOTS 9
+
 struct oics_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;      // stream all work is issued on
@@ -102,7 +104,8 @@ struct oics_ctx {
         sums, edges, mag, dxy, labels, accum, lines, misc, cplx, cplx2, twid, fmag;
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;
-    oics::DevBuf wplanes, wmeta, wlists, jpeg_raw, jpeg_hdr, jpeg_totals, jd_file, jd_words, jd_tables, jd_state, jd_coef, jd_planes;
+    oics::DevBuf wplanes, wmeta, wlists, jpeg_raw, jpeg_hdr, jpeg_totals;
+    void *jd_slots[OICS_JD_SLOTS] = {};   // jpegdec.cu: decodes in flight (slot 0 = ctx->stream, the others own a stream)
     // jpeg.cu: the file header of the last quality used (host copy and its device cache)
     int jpeg_hdr_quality = 0, jpeg_hdr_sof = 0;
     size_t jpeg_hdr_len = 0;
@@ -168,11 +171,15 @@ int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, siz
 int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
                             size_t d_cap, unsigned long long *d_totals, size_t *hdr_len);
 size_t jpeg_file_size(size_t hdr_len, const unsigned long long *totals);
-int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums, unsigned long long *total,
-                       const unsigned long long *tb);
+int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, size_t n, unsigned long long *sums,
+                       unsigned long long *total, const unsigned long long *tb);
 // N2: imread(JPEG) (jpegdec.cu)
 int32_t jpeg_info_host(const uint8_t *file, size_t n, int *w, int *h, int *ncomp);
 int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out);
+int32_t jpeg_decode_batch_device(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+                                 uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev, cudaStream_t join, cudaEvent_t ready,
+                                 int32_t *statuses);
+void jpeg_decode_release(oics_ctx *ctx);
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 

@@ -452,13 +452,13 @@ __global__ void __launch_bounds__(1024) scan_add_kernel(unsigned long long *__re
     if (i < n) v[i] += sums[blockIdx.x];
 }
 
-int32_t exclusive_scan(oics_ctx *ctx, unsigned long long *v, size_t n, unsigned long long *sums,
-                              unsigned long long *total, const unsigned long long *tb)
+int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, size_t n, unsigned long long *sums,
+                       unsigned long long *total, const unsigned long long *tb)
 {
     const int m = (int)((n + 1023) / 1024);
-    scan_block_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums, tb);
-    scan_sums_kernel<<<1, 1024, 0, ctx->stream>>>(sums, m, total, tb);
-    scan_add_kernel<<<m, 1024, 0, ctx->stream>>>(v, n, sums, tb);
+    scan_block_kernel<<<m, 1024, 0, st>>>(v, n, sums, tb);
+    scan_sums_kernel<<<1, 1024, 0, st>>>(sums, m, total, tb);
+    scan_add_kernel<<<m, 1024, 0, st>>>(v, n, sums, tb);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     return OICS_OK;
@@ -655,13 +655,13 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
-    OICS_TRY(exclusive_scan(ctx, bits, nb, sums, d_totals, nullptr));
+    OICS_TRY(exclusive_scan(ctx, st, bits, nb, sums, d_totals, nullptr));
     jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
     jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, words);
     jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
-    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums2, d_totals + 1, d_totals));
+    OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums2, d_totals + 1, d_totals));
     jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
         words, d_totals, cnt, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
     OICS_CUDA_TRY(cudaGetLastError());

@@ -25,6 +25,7 @@
 // OICS_ERR_UNSUPPORTED (the caller keeps its imread for those).
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 #include "common.h"
 
@@ -615,22 +616,54 @@ int32_t jpeg_info_host(const uint8_t *file, size_t n, int *w, int *h, int *ncomp
     return OICS_OK;
 }
 
-// file bytes on the HOST -> BGR image on the DEVICE (rows `stride` bytes apart).  The entropy-coded
-// segment and one table block are what crosses PCIe.  Synchronises ctx->stream once (convergence
-// and marker flags).
-int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out)
-{
-    cudaStream_t st = ctx->stream;
+// One decode in flight: its stream, scratch and the pointers of the current file.  The batch driver
+// keeps several (one per card of a sub-batch, each on its own stream): the synchronisation rounds of
+// a card are latency-bound chains that leave the GPU almost empty, so cards overlap.
+struct JdecSlot {
+    cudaStream_t st = nullptr;
+    bool own_stream = false;
+    DevBuf file, words, tables, state, coef, planes;
+    PinnedBuf pin;            // JdecTables staging + the flags read-back
     JdecHeader H;
-    OICS_TRY(ctx->pin_small.ensure(sizeof(JdecTables) + 256));
-    // the pinned staging block is reused by the next call: wait for the previous upload
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));
-    JdecTables *T = ctx->pin_small.as<JdecTables>();
-    OICS_TRY(parse_header(file, n, &H, T));
-    *w_out = H.w;
-    *h_out = H.h;
-    if (stride < (size_t)H.w * 3) { set_error("jpeg: stride %zu is below 3 * width", stride); return OICS_ERR_INVALID_ARG; }
     JdecGeom G;
+    size_t nsub = 0, nblocks = 0, nmcu = 0, nsum_s = 0, nsum_m = 0;
+    unsigned long long *used = nullptr, *out = nullptr, *nblk = nullptr, *sums_s = nullptr, *mcu = nullptr, *sums_m = nullptr;
+    unsigned long long *mkey = nullptr, *mout = nullptr, *removed = nullptr;
+    unsigned *mnb = nullptr, *mcnt = nullptr;
+    int *flags = nullptr;
+    int rounds = 0;           // rounds of the batch whose flags are being read back
+    cudaEvent_t ev = nullptr;
+    cudaEvent_t done_ev()
+    {
+        if (!ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        return ev;
+    }
+    int *hflags() { return reinterpret_cast<int *>(pin.as<uint8_t>() + sizeof(JdecTables) + 64); }
+};
+
+static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
+{
+    const unsigned gs = (unsigned)((S.nsub + 127) / 128);
+    for (int r = 1; r <= rounds; r++)
+        jdec_sync_kernel<<<gs, 128, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used,
+                                                S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags);
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += rounds;
+    S.rounds = rounds;
+    OICS_CUDA_TRY(cudaMemcpyAsync(S.hflags(), S.flags, 32 * sizeof(int), cudaMemcpyDeviceToHost, S.st));
+    return OICS_OK;
+}
+
+// parse, upload, unstuff, first rounds of the synchronisation -- everything enqueued, nothing awaited
+static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_t n)
+{
+    cudaStream_t st = S.st;
+    OICS_TRY(S.pin.ensure(sizeof(JdecTables) + 64 + 32 * sizeof(int)));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));   // the staging block may still be in flight from the previous file
+    JdecTables *T = S.pin.as<JdecTables>();
+    OICS_TRY(parse_header(file, n, &S.H, T));
+    const JdecHeader &H = S.H;
+    JdecGeom &G = S.G;
     G.w = H.w; G.h = H.h; G.ncomp = H.ncomp; G.hs = H.hs; G.vs = H.vs;
     G.mcux = cdiv(H.w, 8 * H.hs); G.mcuy = cdiv(H.h, 8 * H.vs);
     G.nbm = T->nbm;
@@ -641,67 +674,177 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
         G.poff[c] = off;
         off += ((size_t)G.pw[c] * G.ph[c] + 255) & ~(size_t)255;
     }
-    const size_t nmcu = (size_t)G.mcux * G.mcuy, nblocks = nmcu * G.nbm;
+    S.nmcu = (size_t)G.mcux * G.mcuy;
+    S.nblocks = S.nmcu * G.nbm;
     const size_t slen = H.scan_len, nchunks = (slen + 31) / 32, nsub = (slen * 8 + JD_SUB - 1) / JD_SUB;
-    const size_t nsum_c = (nchunks + 1023) / 1024 + 8, nsum_s = (nsub + 1023) / 1024 + 8, nsum_m = (nmcu + 1023) / 1024 + 8;
-    // scratch
-    OICS_TRY(ctx->jd_file.ensure(slen + 64));
-    OICS_TRY(ctx->jd_words.ensure(slen + 256));
-    OICS_TRY(ctx->jd_tables.ensure(sizeof(JdecTables)));
-    const size_t n_state = nchunks + nsum_c + 3 * nsub + nsum_s + nmcu + nsum_m + 2 * nsub * JD_M + 64;
-    OICS_TRY(ctx->jd_state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
-    OICS_TRY(ctx->jd_coef.ensure(nblocks * 64 * sizeof(int16_t) + 256));
-    OICS_TRY(ctx->jd_planes.ensure(off + 256));
-    unsigned long long *cnt = ctx->jd_state.as<unsigned long long>(), *sums_c = cnt + nchunks, *used = sums_c + nsum_c;
-    unsigned long long *out = used + nsub, *nblk = out + nsub, *sums_s = nblk + nsub, *mcu = sums_s + nsum_s;
-    unsigned long long *sums_m = mcu + nmcu, *mkey = sums_m + nsum_m, *mout = mkey + nsub * JD_M, *removed = mout + nsub * JD_M;
-    unsigned long long *tot_blocks = removed + 1, *tot_dc = removed + 2;
-    unsigned *mnb = reinterpret_cast<unsigned *>(removed + 64), *mcnt = mnb + nsub * JD_M;
-    int *flags = reinterpret_cast<int *>(removed + 4);   // [0]: a marker inside the scan; [r]: round r changed something
-    uint8_t *d_scan = ctx->jd_file.as<uint8_t>();
-    uint32_t *words = ctx->jd_words.as<uint32_t>();
-    JdecTables *dT = ctx->jd_tables.as<JdecTables>();
-    int16_t *coef = ctx->jd_coef.as<int16_t>();
-    OICS_CUDA_TRY(cudaMemcpyAsync(dT, T, sizeof(JdecTables), cudaMemcpyHostToDevice, st));
+    const size_t nsum_c = (nchunks + 1023) / 1024 + 8;
+    S.nsub = nsub;
+    S.nsum_s = (nsub + 1023) / 1024 + 8;
+    S.nsum_m = (S.nmcu + 1023) / 1024 + 8;
+    OICS_TRY(S.file.ensure(slen + 64));
+    OICS_TRY(S.words.ensure(slen + 256));
+    OICS_TRY(S.tables.ensure(sizeof(JdecTables)));
+    const size_t n_state = nchunks + nsum_c + 3 * nsub + S.nsum_s + S.nmcu + S.nsum_m + 2 * nsub * JD_M + 64;
+    OICS_TRY(S.state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
+    OICS_TRY(S.coef.ensure(S.nblocks * 64 * sizeof(int16_t) + 256));
+    OICS_TRY(S.planes.ensure(off + 256));
+    unsigned long long *cnt = S.state.as<unsigned long long>(), *sums_c = cnt + nchunks;
+    S.used = sums_c + nsum_c;
+    S.out = S.used + nsub;
+    S.nblk = S.out + nsub;
+    S.sums_s = S.nblk + nsub;
+    S.mcu = S.sums_s + S.nsum_s;
+    S.sums_m = S.mcu + S.nmcu;
+    S.mkey = S.sums_m + S.nsum_m;
+    S.mout = S.mkey + nsub * JD_M;
+    S.removed = S.mout + nsub * JD_M;                       // [0] removed bytes, [1] blocks, [2] DC total, [4..] flags
+    S.flags = reinterpret_cast<int *>(S.removed + 4);       // [0]: a marker inside the scan; [r]: round r changed something
+    S.mnb = reinterpret_cast<unsigned *>(S.removed + 64);
+    S.mcnt = S.mnb + nsub * JD_M;
+    uint8_t *d_scan = S.file.as<uint8_t>();
+    uint32_t *words = S.words.as<uint32_t>();
+    OICS_CUDA_TRY(cudaMemcpyAsync(S.tables.p, T, sizeof(JdecTables), cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(d_scan, file + H.scan_off, slen, cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 256, st));
-    OICS_CUDA_TRY(cudaMemsetAsync(nblk, 0, nsub * sizeof(unsigned long long), st));
-    OICS_CUDA_TRY(cudaMemsetAsync(removed, 0, 64 * sizeof(unsigned long long), st));
-    OICS_CUDA_TRY(cudaMemsetAsync(mcnt, 0, nsub * sizeof(unsigned), st));
-    OICS_CUDA_TRY(cudaMemsetAsync(coef, 0, nblocks * 64 * sizeof(int16_t), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(S.nblk, 0, nsub * sizeof(unsigned long long), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(S.removed, 0, 64 * sizeof(unsigned long long), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(S.coef.p, 0, S.nblocks * 64 * sizeof(int16_t), st));
     const unsigned gc = (unsigned)((nchunks + 255) / 256), gs = (unsigned)((nsub + 127) / 128);
-    jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, flags);
-    OICS_TRY(exclusive_scan(ctx, cnt, nchunks, sums_c, removed, nullptr));
+    jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, S.flags);
+    OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums_c, S.removed, nullptr));
     jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, reinterpret_cast<uint8_t *>(words));
-    ctx->launches += 2;
-    int hflags[32];
-    {
-        // every thread is fed its predecessor's exit state until a round changes nothing; the host looks
-        // at the flags after 8 rounds (enough for photographic content), then every 31 (long uniform
-        // stretches -- the white of a scanned card -- advance one subsequence per round)
-        jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, mkey, mout, mnb, mcnt, 0, flags);
-        for (int rounds = 8;; rounds = 31) {
-            for (int r = 1; r <= rounds; r++) jdec_sync_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, out, nblk, mkey, mout, mnb, mcnt, r, flags);
-            OICS_CUDA_TRY(cudaGetLastError());
-            ctx->launches += rounds;
-            OICS_CUDA_TRY(cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, st));
-            OICS_CUDA_TRY(cudaStreamSynchronize(st));
-            if (hflags[0] & 1) {
-                set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
-                return OICS_ERR_UNSUPPORTED;
-            }
-            if (!hflags[rounds]) break;
-            OICS_CUDA_TRY(cudaMemsetAsync(flags + 1, 0, 31 * sizeof(int), st));
-        }
+    // every thread is fed its predecessor's exit state until a round changes nothing; the host looks at
+    // the flags after 4 rounds (each launch advances the chain through whole CTAs), then every 8
+    jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+                                          S.mnb, S.mcnt, 0, S.flags);
+    ctx->launches += 3;
+    return jdec_rounds(ctx, S, 4);
+}
+
+// wait for the rounds in flight; *done = converged, else more rounds are enqueued
+static int32_t jdec_poll(oics_ctx *ctx, JdecSlot &S, bool *done)
+{
+    OICS_CUDA_TRY(cudaStreamSynchronize(S.st));
+    const int *hf = S.hflags();
+    if (hf[0] & 1) {
+        set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
+        return OICS_ERR_UNSUPPORTED;
     }
-    OICS_TRY(exclusive_scan(ctx, nblk, nsub, sums_s, tot_blocks, nullptr));
-    jdec_write_kernel<<<gs, 128, 0, st>>>(dT, words, removed, slen, used, nblk, (unsigned long long)nblocks, coef);
-    jdec_mcu_dc_kernel<<<(unsigned)((nmcu + 255) / 256), 256, 0, st>>>(coef, G, mcu);
-    OICS_TRY(exclusive_scan(ctx, mcu, nmcu, sums_m, tot_dc, nullptr));
-    jdec_idct_kernel<<<(unsigned)((nblocks + 31) / 32), 256, 0, st>>>(dT, coef, mcu, G, ctx->jd_planes.as<uint8_t>());
-    jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(H.w, 2), 256), (unsigned)H.h), 256, 0, st>>>(ctx->jd_planes.as<uint8_t>(), G, d_bgr, stride);
+    *done = !hf[S.rounds];
+    if (*done) return OICS_OK;
+    OICS_CUDA_TRY(cudaMemsetAsync(S.flags + 1, 0, 31 * sizeof(int), S.st));
+    return jdec_rounds(ctx, S, 8);
+}
+
+// coefficients, DC prediction, IDCT, upsampling + colour -> d_bgr (enqueued on the slot's stream)
+static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t stride)
+{
+    cudaStream_t st = S.st;
+    const unsigned gs = (unsigned)((S.nsub + 127) / 128);
+    int16_t *coef = S.coef.as<int16_t>();
+    OICS_TRY(exclusive_scan(ctx, st, S.nblk, S.nsub, S.sums_s, S.removed + 1, nullptr));
+    jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
+                                           (unsigned long long)S.nblocks, coef);
+    jdec_mcu_dc_kernel<<<(unsigned)((S.nmcu + 255) / 256), 256, 0, st>>>(coef, S.G, S.mcu);
+    OICS_TRY(exclusive_scan(ctx, st, S.mcu, S.nmcu, S.sums_m, S.removed + 2, nullptr));
+    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.G, S.planes.as<uint8_t>());
+    jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;
+    return OICS_OK;
+}
+
+static JdecSlot *jdec_slot(oics_ctx *ctx, int i)
+{
+    if (!ctx->jd_slots[i]) {
+        JdecSlot *S = new JdecSlot();
+        if (i == 0) {
+            S->st = ctx->stream;
+        } else {
+            if (cudaStreamCreateWithFlags(&S->st, cudaStreamNonBlocking) != cudaSuccess) { delete S; return nullptr; }
+            S->own_stream = true;
+        }
+        ctx->jd_slots[i] = S;
+    }
+    JdecSlot *S = static_cast<JdecSlot *>(ctx->jd_slots[i]);
+    if (i == 0) S->st = ctx->stream;
+    return S;
+}
+
+void jpeg_decode_release(oics_ctx *ctx)
+{
+    for (void *&p : ctx->jd_slots) {
+        JdecSlot *S = static_cast<JdecSlot *>(p);
+        if (!S) continue;
+        if (S->own_stream) { cudaStreamSynchronize(S->st); cudaStreamDestroy(S->st); }
+        if (S->ev) cudaEventDestroy(S->ev);
+        for (DevBuf *b : {&S->file, &S->words, &S->tables, &S->state, &S->coef, &S->planes}) b->release();
+        S->pin.release();
+        delete S;
+        p = nullptr;
+    }
+}
+
+// file bytes on the HOST -> BGR image on the DEVICE (rows `stride` bytes apart), on ctx->stream.  The
+// entropy-coded segment and one table block are what crosses PCIe.
+int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out)
+{
+    JdecSlot *S = jdec_slot(ctx, 0);
+    if (!S) { set_error("jpeg: no decode slot"); return OICS_ERR_CUDA; }
+    OICS_TRY(jdec_begin(ctx, *S, file, n));
+    *w_out = S->H.w;
+    *h_out = S->H.h;
+    if (stride < (size_t)S->H.w * 3) { set_error("jpeg: stride %zu is below 3 * width", stride); return OICS_ERR_INVALID_ARG; }
+    for (bool done = false; !done;) OICS_TRY(jdec_poll(ctx, *S, &done));
+    return jdec_finish(ctx, *S, d_bgr, stride);
+}
+
+// `n_files` files (host) -> BGR cards on the device at d_bgr + i * card_bytes, all of size w x h; every
+// card decodes on its own stream, `ready` is recorded on `join` when all of them are done.  Before
+// touching d_bgr the slot streams wait for `free_ev` (may be null).  statuses[i] per file.
+int32_t jpeg_decode_batch_device(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+                                 uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev, cudaStream_t join, cudaEvent_t ready,
+                                 int32_t *statuses)
+{
+    if (n_files > OICS_JD_SLOTS - 1) { set_error("jpeg: at most %d files per call", OICS_JD_SLOTS - 1); return OICS_ERR_INVALID_ARG; }
+    std::vector<JdecSlot *> slots((size_t)n_files, nullptr);
+    for (int i = 0; i < n_files; i++) {
+        statuses[i] = OICS_OK;
+        JdecSlot *S = jdec_slot(ctx, 1 + i);
+        if (!S) { set_error("jpeg: no decode slot"); return OICS_ERR_CUDA; }
+        slots[i] = S;
+        int32_t rc = jdec_begin(ctx, *S, files[i], sizes[i]);
+        if (rc == OICS_OK && (S->H.w != w || S->H.h != h)) {
+            set_error("jpeg: file %d is %dx%d, the batch is %dx%d", i, S->H.w, S->H.h, w, h);
+            rc = OICS_ERR_INVALID_ARG;
+        }
+        if (rc == OICS_ERR_CUDA) return rc;
+        statuses[i] = rc;
+    }
+    for (bool all = false; !all;) {
+        all = true;
+        for (int i = 0; i < n_files; i++) {
+            if (statuses[i] != OICS_OK || slots[i]->rounds == 0) continue;
+            bool done = false;
+            const int32_t rc = jdec_poll(ctx, *slots[i], &done);
+            if (rc == OICS_ERR_CUDA) return rc;
+            if (rc != OICS_OK) statuses[i] = rc;
+            else if (done) slots[i]->rounds = 0;
+            else all = false;
+        }
+    }
+    for (int i = 0; i < n_files; i++) {
+        JdecSlot &S = *slots[i];
+        if (statuses[i] == OICS_OK) {
+            if (free_ev) OICS_CUDA_TRY(cudaStreamWaitEvent(S.st, free_ev, 0));
+            const int32_t rc = jdec_finish(ctx, S, d_bgr + (size_t)i * card_bytes, (size_t)w * 3);
+            if (rc == OICS_ERR_CUDA) return rc;
+            statuses[i] = rc;
+        }
+        OICS_CUDA_TRY(cudaEventRecord(S.done_ev(), S.st));
+        OICS_CUDA_TRY(cudaStreamWaitEvent(join, S.done_ev(), 0));
+    }
+    if (ready) OICS_CUDA_TRY(cudaEventRecord(ready, join));
     return OICS_OK;
 }
 

@@ -608,3 +608,35 @@ def test_jpeg_decode_rejects_what_it_does_not_cover(ctx):
     rst = cv2.imencode(".jpg", np.zeros((64, 64, 3), np.uint8), [cv2.IMWRITE_JPEG_RST_INTERVAL, 2])[1].tobytes()
     with pytest.raises(api.OicsError):
         ctx.jpeg_decode(rst)
+
+
+def test_correct_batch_files_jpeg_in_jpeg_out(ctx, orc, dataset_like):
+    """oics_correct_batch_files: omr::correct_default from imread (omr.rs:349) to imwrite (omr.rs:447-448)
+    with both codecs on the device.  Every returned file equals the oracle's encoding of the oracle's
+    deskew of the oracle's decode of the input file; a corrupt and a wrongly sized file fail alone."""
+    bgr, _ = dataset_like
+    base = np.ascontiguousarray(bgr[100:400, 200:460])
+    blank = np.full((300, 260, 3), 255, np.uint8)
+    blank[40:43, 30:230] = 0
+    blank[45:240, 60:63] = 0
+    cards = [orc.rotate_mat(base, -4.0 + 0.75 * i, 1.0, 1, orc.WHITE, 0) if i % 5 != 3 else blank for i in range(19)]
+    files = [np.frombuffer(orc.jpeg_encode(c, 100 if i % 2 else 90), np.uint8).copy() for i, c in enumerate(cards)]
+    files[6] = np.frombuffer(orc.jpeg_encode(np.zeros((64, 64, 3), np.uint8), 90), np.uint8).copy()   # other size
+    files[13] = files[13][:40].copy()                                                                   # truncated
+    params = (5, 0.5, 0, 0, 50.0, 5.0)
+    outs = [np.zeros(520 * 520 * 3, np.uint8) for _ in cards]
+    ang, need, stat, sizes, fsz = ctx.correct_batch_files(files, *params, outs=outs, jpeg_quality=100)
+    for i in range(len(cards)):
+        if i in (6, 13):
+            assert stat[i] != 0 and fsz[i] == 0
+            continue
+        assert stat[i] == 0
+        ra, rneed, rout = orc.correct_default(orc.jpeg_decode(files[i].tobytes()), *params)
+        assert (ang[i], bool(need[i])) == (ra, bool(rneed))
+        assert tuple(sizes[i]) == (rout.shape[1], rout.shape[0])
+        assert outs[i][:fsz[i]].tobytes() == orc.jpeg_encode(rout, 100), i
+    # pixels out instead of files
+    ang2, need2, stat2, sizes2, _ = ctx.correct_batch_files(files[:5], *params, outs=outs[:5], jpeg_quality=0)
+    for i in range(5):
+        ra, rneed, rout = orc.correct_default(orc.jpeg_decode(files[i].tobytes()), *params)
+        assert ang2[i] == ra and np.array_equal(outs[i][:rout.size].reshape(rout.shape), rout)
