@@ -319,6 +319,40 @@ def run_gpu(args, rank, local_rank, world):
                            "h2d_bytes_per_step": int(E * W * H * 3), "d2h_bytes_per_step": int(fsz.sum()) + E * 16,
                            "mismatches": jbad}
 
+        # the whole of omr::correct_default as the reference runs it, file to file: imread of a JPEG
+        # (omr.rs:349) ... imwrite of a JPEG (omr.rs:447-448), both codecs on the device
+        distinct = [ctx.jpeg_encode(c, 100) for c in bgr_cards]
+        fmax = max(len(d) for d in distinct)
+        host_files = torch.empty((E, fmax), dtype=torch.uint8).pin_memory()
+        files = []
+        for i in range(E):
+            d = distinct[i % len(distinct)]
+            host_files[i, :len(d)] = torch.frombuffer(bytearray(d), dtype=torch.uint8)
+            files.append(host_files[i].numpy()[:len(d)])
+
+        def e2e_files_step():
+            return ctx.correct_batch_files(files, MAX_ANGLE, STEP, 0, 0, 125.0, 15.0, outs=outs, jpeg_quality=100)
+
+        for _ in range(2):
+            ang3, need3, stat3, sizes3, fsz3 = e2e_files_step()
+        fbad = int(sum(1 for i in range(E) if stat3[i] != 0 or abs(ang3[i] - skews[i % len(bgr_cards)]) > 0.1 + 1e-9))
+        barrier()
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        k0.record(stream)
+        for _ in range(ksteps):
+            e2e_files_step()
+        k1.record(stream)
+        k1.synchronize()
+        barrier()
+        t_k = torch.tensor([k0.elapsed_time(k1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_k, op=dist.ReduceOp.MAX)
+        e2e["jpeg_io"] = {"value": world * E * ksteps / (float(t_k.item()) / 1000.0), "unit": UNIT,
+                          "what": "oics_correct_batch_files: JPEG (quality 100) files in pinned host memory in, JPEG files out; "
+                                  "decode, deskew and encode on the device",
+                          "h2d_bytes_per_step": int(sum(f.size for f in files)), "d2h_bytes_per_step": int(fsz3.sum()) + E * 16,
+                          "mismatches": fbad}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
