@@ -5,7 +5,7 @@
 //
 //   host              marker parsing (DQT / DHT / SOF0 / SOS), Huffman lookup tables -> one small upload
 //   jdec_unstuff_*    0xFF 0x00 -> 0xFF: count per 32-byte chunk, scan, compact into MSB-first words
-//   jdec_sync_kernel  Huffman decoding is sequential, so the stream is cut into 512-bit subsequences
+//   jdec_sync_kernel  Huffman decoding is sequential, so the stream is cut into 1024-bit subsequences
 //                     and every thread decodes one from a guessed state (bit position, coefficient
 //                     index, block of the MCU); Huffman streams self-synchronise, so feeding every
 //                     thread its predecessor's exit state and repeating until nothing changes
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *
 // k of the block being filled, block bi of the MCU).  One step = one Huffman symbol plus its value
 // bits.  SINK receives (block ordinal since the start, zigzag position, value) of every coefficient
 // (the DC value is the DIFFERENCE; prediction is a later scan).
-#define JD_SUB 512   // bits per subsequence
+#define JD_SUB 1024   // bits per subsequence
 
 struct JdecShared {
     uint16_t lut[6][256];
@@ -251,10 +251,30 @@ struct NoSink {
 };
 
 // Decode from state (p, k, bi) until p >= end.  Returns the number of blocks completed.
+// The CTA's part of the stream (128 subsequences = 2048 words, + 2: a value field may reach into the
+// next word) staged in shared memory: in a warp some lane needs a new word at almost every symbol,
+// and a global load there stalls all 32.  One pad word per 16 keeps the lanes (16 words apart) in
+// different banks.
+#define JD_WIN (128 * (JD_SUB / 32) + 2)
+#define JD_WPS (JD_SUB / 32)   // words per subsequence
+#define JD_WIN_WORDS (JD_WIN + JD_WIN / JD_WPS + 1)
+
+__device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *__restrict__ words)
+{
+    const size_t base = (size_t)blockIdx.x * 128 * (JD_SUB / 32);
+    for (int i = threadIdx.x; i < JD_WIN; i += blockDim.x) sw[i + i / JD_WPS] = __ldg(words + base + i);
+    __syncthreads();
+}
+
 template <typename SINK>
-__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t *__restrict__ words, unsigned long long &p,
+__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t *sw, unsigned long long &p,
                                              int &k, int &bi, unsigned long long end, SINK &sink)
 {
+    const unsigned long long wbase = (unsigned long long)blockIdx.x * 128 * (JD_SUB / 32);
+    auto word = [&](unsigned long long w) {
+        const int i = min((int)(w - wbase), JD_WIN - 1);
+        return sw[i + i / JD_WPS];
+    };
     unsigned done = 0;
     unsigned long long wi = ~0ull - 1;   // never the predecessor of a real word index
     int tdc = 2 * S.comp_of[bi];         // table pair of the current block (off the per-symbol path)
@@ -262,8 +282,8 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
     while (p < end) {
         const unsigned long long w = p >> 5;
         if (w != wi) {
-            if (w == wi + 1) { a = b; b = __ldg(words + w + 1); }
-            else { a = __ldg(words + w); b = __ldg(words + w + 1); }
+            if (w == wi + 1) { a = b; b = word(w + 1); }
+            else { a = word(w); b = word(w + 1); }
             wi = w;
         }
         const uint32_t v = __funnelshift_l(b, a, (int)(p & 31));   // the next 32 bits of the stream
@@ -334,6 +354,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
                                                         int *__restrict__ changed)
 {
     __shared__ JdecShared S;
+    __shared__ uint32_t sw[JD_WIN_WORDS];
     const unsigned long long total = 8ull * (scan_len - *removed);
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = j * JD_SUB < total;
@@ -370,13 +391,14 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
         if (round > 0 && threadIdx.x == 0) changed[round] = 1;
         if (any_need && !tables) {
             jdec_load_tables(S, T);
+            jdec_stage_words(sw, words);
             tables = true;
         }
         if (need) {
             unsigned long long p = x >> 12;
             int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
             NoSink sink;
-            const unsigned n = jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+            const unsigned n = jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
             const unsigned long long e = jdec_pack(p, k, bi);
             mine = x;
             __stcg(out + j, e);
@@ -415,8 +437,10 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
 {
     __shared__ JdecShared S;
     __shared__ uint8_t zz[64];
+    __shared__ uint32_t sw[JD_WIN_WORDS];
     if (threadIdx.x < 64) zz[threadIdx.x] = T->zz[threadIdx.x];
     jdec_load_tables(S, T);
+    jdec_stage_words(sw, words);
     const unsigned long long total = 8ull * (scan_len - *removed);
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j * JD_SUB >= total) return;
@@ -426,7 +450,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
     // coefficients were stored by the predecessor under the same ordinal
     CoefSink sink{coef, first_block[j], nblocks, zz};
-    jdec_run(S, words, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+    jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
 }
 
 // ---------------------------------------------------------------------------
@@ -682,7 +706,7 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     S.nsum_s = (nsub + 1023) / 1024 + 8;
     S.nsum_m = (S.nmcu + 1023) / 1024 + 8;
     OICS_TRY(S.file.ensure(slen + 64));
-    OICS_TRY(S.words.ensure(slen + 256));
+    OICS_TRY(S.words.ensure(slen + 8704));   // the last CTA stages a whole window: zero padding behind the stream
     OICS_TRY(S.tables.ensure(sizeof(JdecTables)));
     const size_t n_state = nchunks + nsum_c + 3 * nsub + S.nsum_s + S.nmcu + S.nsum_m + 2 * nsub * JD_M + 64;
     OICS_TRY(S.state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
@@ -705,7 +729,7 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     uint32_t *words = S.words.as<uint32_t>();
     OICS_CUDA_TRY(cudaMemcpyAsync(S.tables.p, T, sizeof(JdecTables), cudaMemcpyHostToDevice, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(d_scan, file + H.scan_off, slen, cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 256, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 8704, st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.nblk, 0, nsub * sizeof(unsigned long long), st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.removed, 0, 64 * sizeof(unsigned long long), st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.coef.p, 0, S.nblocks * 64 * sizeof(int16_t), st));
