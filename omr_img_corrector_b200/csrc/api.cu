@@ -680,14 +680,25 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (e == cudaSuccess) e = cudaEventRecord(in_ready[s], up);
         return e;
     };
-    auto decode = [&](int k) -> int32_t {   // files of sub-batch k -> in_slot[k & 1]
+    // files of sub-batch k -> in_slot[k & 1], in two steps (jpegdec.cu): `begin` only enqueues (upload, unstuffing,
+    // first synchronisation rounds, each card on its own stream) and touches nothing but decoder scratch, so it is
+    // issued a whole sweep ahead; `finish` writes the cards once the slot is free
+    auto decode_begin = [&](int k) -> int32_t {
+        const int c0 = k * B, nb = std::min(B, n_cards - c0);
+        return jpeg_decode_batch_begin(ctx, files + c0, file_sizes + c0, nb, w, h, file_status.data() + c0);
+    };
+    auto decode_finish = [&](int k) -> int32_t {
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
-        return jpeg_decode_batch_device(ctx, files + c0, file_sizes + c0, nb, w, h, in_slot[s]->as<uint8_t>(), card_bytes,
-                                        k >= 2 ? in_free[s] : nullptr, up, in_ready[s], file_status.data() + c0);
+        return jpeg_decode_batch_finish(ctx, nb, w, in_slot[s]->as<uint8_t>(), card_bytes, k >= 2 ? in_free[s] : nullptr, up,
+                                        in_ready[s], file_status.data() + c0);
     };
     if (files) {
-        OICS_BATCH_TRY(decode(0));
-        if (n_sub > 1) OICS_BATCH_TRY(decode(1));
+        OICS_BATCH_TRY(decode_begin(0));
+        OICS_BATCH_TRY(decode_finish(0));
+        if (n_sub > 1) {
+            OICS_BATCH_TRY(decode_begin(1));
+            OICS_BATCH_TRY(decode_finish(1));
+        }
     } else if (!dev_in) {
         OICS_BATCH_CUDA(upload(0));
         if (n_sub > 1) OICS_BATCH_CUDA(upload(1));
@@ -699,6 +710,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
         const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
         const size_t dcard = dev_in ? card_stride : card_bytes, dstride = dev_in ? (size_t)stride : row;
+        if (files && k + 2 < n_sub) OICS_BATCH_TRY(decode_begin(k + 2));   // its chains run beside this sub-batch's sweep
         if (!dev_in) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, in_ready[s], 0));
         // P0 for every card of the sub-batch (one launch), then one fused sweep over all of them
         OICS_BATCH_TRY(preprocess_batch_device(ctx, dsrc, nb, dcard, w, h, dstride, OICS_PRE_OMR, ow, oh, ctx->bin.as<uint8_t>()));
@@ -791,7 +803,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (!dev_in) {
             OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
             if (k + 2 < n_sub) {
-                if (files) OICS_BATCH_TRY(decode(k + 2));
+                if (files) OICS_BATCH_TRY(decode_finish(k + 2));
                 else OICS_BATCH_CUDA(upload(k + 2));
             }
         }

@@ -176,9 +176,10 @@ int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, si
 // N2: imread(JPEG) (jpegdec.cu)
 int32_t jpeg_info_host(const uint8_t *file, size_t n, int *w, int *h, int *ncomp);
 int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out);
-int32_t jpeg_decode_batch_device(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
-                                 uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev, cudaStream_t join, cudaEvent_t ready,
-                                 int32_t *statuses);
+int32_t jpeg_decode_batch_begin(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+                                int32_t *statuses);
+int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
+                                 cudaStream_t join, cudaEvent_t ready, int32_t *statuses);
 void jpeg_decode_release(oics_ctx *ctx);
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }

@@ -823,21 +823,23 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
     return jdec_finish(ctx, *S, d_bgr, stride);
 }
 
-// `n_files` files (host) -> BGR cards on the device at d_bgr + i * card_bytes, all of size w x h; every
-// card decodes on its own stream, `ready` is recorded on `join` when all of them are done.  Before
-// touching d_bgr the slot streams wait for `free_ev` (may be null).  statuses[i] per file.
-int32_t jpeg_decode_batch_device(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
-                                 uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev, cudaStream_t join, cudaEvent_t ready,
-                                 int32_t *statuses)
+// A sub-batch of files (host) -> BGR cards on the device, every card on its own stream, in two calls so
+// that the caller can put other work between them:
+//   begin   parse, upload, unstuff and the first synchronisation rounds of every file -- enqueued only;
+//           statuses[i] per file (a file of another size than w x h is refused)
+//   finish  wait for the chains (normally long converged by now), then coefficients .. colour into
+//           d_bgr + i * card_bytes; the slot streams wait for `free_ev` (may be null) before writing
+//           there, and `ready` is recorded on `join` once all cards are done
+int32_t jpeg_decode_batch_begin(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+                                int32_t *statuses)
 {
     if (n_files > OICS_JD_SLOTS - 1) { set_error("jpeg: at most %d files per call", OICS_JD_SLOTS - 1); return OICS_ERR_INVALID_ARG; }
-    std::vector<JdecSlot *> slots((size_t)n_files, nullptr);
     for (int i = 0; i < n_files; i++) {
         statuses[i] = OICS_OK;
         JdecSlot *S = jdec_slot(ctx, 1 + i);
         if (!S) { set_error("jpeg: no decode slot"); return OICS_ERR_CUDA; }
-        slots[i] = S;
-        int32_t rc = jdec_begin(ctx, *S, files[i], sizes[i]);
+        S->rounds = 0;
+        int32_t rc = files[i] ? jdec_begin(ctx, *S, files[i], sizes[i]) : OICS_ERR_INVALID_ARG;
         if (rc == OICS_OK && (S->H.w != w || S->H.h != h)) {
             set_error("jpeg: file %d is %dx%d, the batch is %dx%d", i, S->H.w, S->H.h, w, h);
             rc = OICS_ERR_INVALID_ARG;
@@ -845,6 +847,14 @@ int32_t jpeg_decode_batch_device(oics_ctx *ctx, const uint8_t *const *files, con
         if (rc == OICS_ERR_CUDA) return rc;
         statuses[i] = rc;
     }
+    return OICS_OK;
+}
+
+int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
+                                 cudaStream_t join, cudaEvent_t ready, int32_t *statuses)
+{
+    std::vector<JdecSlot *> slots((size_t)n_files, nullptr);
+    for (int i = 0; i < n_files; i++) slots[i] = jdec_slot(ctx, 1 + i);
     for (bool all = false; !all;) {
         all = true;
         for (int i = 0; i < n_files; i++) {
