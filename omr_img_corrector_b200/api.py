@@ -386,6 +386,13 @@ class Context:
         check(self._lib.oics_jpeg_encode(self._h, p, w, h, stride, int(quality), out.ctypes.data, out.size, C.byref(n)))
         return out[:n.value].tobytes()
 
+    def jpeg_info(self, data):
+        """Header of a JPEG file's bytes -> (width, height, components); host only."""
+        buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+        w, h, nc = C.c_int32(), C.c_int32(), C.c_int32()
+        check(self._lib.oics_jpeg_info(buf.ctypes.data, buf.size, C.byref(w), C.byref(h), C.byref(nc)))
+        return w.value, h.value, nc.value
+
     def jpeg_decode(self, data, out=None):
         """imgcodecs::imread(path, IMREAD_COLOR) (omr.rs:349, transfer.rs:43) of a baseline JPEG file's
         bytes -> BGR image, decoded on the GPU.  `out`: optional flat uint8 buffer (e.g. pinned memory,

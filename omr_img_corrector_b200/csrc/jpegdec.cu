@@ -52,6 +52,33 @@ struct JdecHeader {
     size_t scan_off = 0, scan_len = 0;             // entropy-coded bytes (stuffed), EOI excluded
 };
 
+
+// cv::imread applies the Exif Orientation tag (IMREAD_COLOR without IMREAD_IGNORE_ORIENTATION): returns the
+// tag's value (1 = upright / absent) from an APP1 "Exif" segment
+static int exif_orientation(const uint8_t *s, long n)
+{
+    if (n < 14 || memcmp(s, "Exif\0\0", 6)) return 1;
+    const uint8_t *t = s + 6;
+    const long tn = n - 6;
+    const int le = t[0] == 'I' && t[1] == 'I';
+    if (!le && !(t[0] == 'M' && t[1] == 'M')) return 1;
+#define RD16(o) (le ? (t[o] | (t[(o) + 1] << 8)) : ((t[o] << 8) | t[(o) + 1]))
+#define RD32(o) (le ? ((long)t[o] | ((long)t[(o) + 1] << 8) | ((long)t[(o) + 2] << 16) | ((long)t[(o) + 3] << 24)) \
+                    : (((long)t[o] << 24) | ((long)t[(o) + 1] << 16) | ((long)t[(o) + 2] << 8) | (long)t[(o) + 3]))
+    if (tn < 8) return 1;
+    const long ifd = RD32(4);
+    if (ifd < 8 || ifd + 2 > tn) return 1;
+    const int cnt = RD16(ifd);
+    for (int i = 0; i < cnt; i++) {
+        const long e = ifd + 2 + 12L * i;
+        if (e + 12 > tn) break;
+        if (RD16(e) == 0x0112) return RD16(e + 8);
+    }
+#undef RD16
+#undef RD32
+    return 1;
+}
+
 static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTables *T)
 {
     if (n < 4 || f[0] != 0xFF || f[1] != 0xD8) { set_error("jpeg: not a JPEG file"); return OICS_ERR_INVALID_ARG; }
@@ -125,6 +152,9 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
         } else if (m == 0xDD) {
             if (sl < 2) return bad("DRI");
             if ((s[0] << 8) | s[1]) return unsupported("restart intervals");
+        } else if (m == 0xE1) {
+            const int o = exif_orientation(s, (long)sl);
+            if (o >= 2 && o <= 8) return unsupported("an Exif orientation other than upright (imread would rotate the image)");
         } else if (m == 0xEE) {
             if (sl >= 12 && !memcmp(s, "Adobe", 5) && H->ncomp == 3 && s[11] != 1) return unsupported("an Adobe RGB / CMYK file");
         } else if (m == 0xDA) {

@@ -34,6 +34,33 @@ static const uint8_t ZZ[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11,
                                41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
                                30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
+
+/* cv::imread applies the Exif Orientation tag (IMREAD_COLOR without IMREAD_IGNORE_ORIENTATION): returns the
+   tag's value (1 = upright / absent) from an APP1 "Exif" segment */
+static int exif_orientation(const uint8_t *s, long n)
+{
+    if (n < 14 || memcmp(s, "Exif\0\0", 6)) return 1;
+    const uint8_t *t = s + 6;
+    const long tn = n - 6;
+    const int le = t[0] == 'I' && t[1] == 'I';
+    if (!le && !(t[0] == 'M' && t[1] == 'M')) return 1;
+#define RD16(o) (le ? (t[o] | (t[(o) + 1] << 8)) : ((t[o] << 8) | t[(o) + 1]))
+#define RD32(o) (le ? ((long)t[o] | ((long)t[(o) + 1] << 8) | ((long)t[(o) + 2] << 16) | ((long)t[(o) + 3] << 24)) \
+                    : (((long)t[o] << 24) | ((long)t[(o) + 1] << 16) | ((long)t[(o) + 2] << 8) | (long)t[(o) + 3]))
+    if (tn < 8) return 1;
+    const long ifd = RD32(4);
+    if (ifd < 8 || ifd + 2 > tn) return 1;
+    const int cnt = RD16(ifd);
+    for (int i = 0; i < cnt; i++) {
+        const long e = ifd + 2 + 12L * i;
+        if (e + 12 > tn) break;
+        if (RD16(e) == 0x0112) return RD16(e + 8);
+    }
+#undef RD16
+#undef RD32
+    return 1;
+}
+
 static int parse(const uint8_t *f, long n, Hdr *H)
 {
     memset(H, 0, sizeof(*H));
@@ -106,6 +133,9 @@ static int parse(const uint8_t *f, long n, Hdr *H)
         } else if (m == 0xDD) {
             if (sl < 2) return ERR_FORMAT;
             H->restart = (s[0] << 8) | s[1];
+        } else if (m == 0xE1) {
+            const int o = exif_orientation(s, sl);
+            if (o >= 2 && o <= 8) return ERR_UNSUPPORTED;            /* imread would rotate / mirror the image */
         } else if (m == 0xEE) {
             if (sl >= 12 && !memcmp(s, "Adobe", 5) && H->ncomp == 3 && s[11] != 1) return ERR_UNSUPPORTED;
         } else if (m == 0xDA) {

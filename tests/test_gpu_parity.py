@@ -640,3 +640,42 @@ def test_correct_batch_files_jpeg_in_jpeg_out(ctx, orc, dataset_like):
     for i in range(5):
         ra, rneed, rout = orc.correct_default(orc.jpeg_decode(files[i].tobytes()), *params)
         assert ang2[i] == ra and np.array_equal(outs[i][:rout.size].reshape(rout.shape), rout)
+
+
+def test_file_task_runner_paths_in_paths_out(ctx, orc, dataset_like, tmp_path):
+    """task.rs:19-68 with the reference's own arguments: input paths, output paths.  The written files
+    equal the oracle's imwrite of the oracle's deskew of the oracle's imread; a file the device decoder
+    does not cover takes the caller's decoder; a missing file is an error event."""
+    import cv2
+    from omr_img_corrector_b200 import task
+    bgr, _ = dataset_like
+    base = np.ascontiguousarray(bgr[100:400, 200:460])
+    cards = [orc.rotate_mat(base, -3.0 + 1.5 * i, 1.0, 1, orc.WHITE, 0) for i in range(4)]
+    tasks = []
+    for i, c in enumerate(cards):
+        data = orc.jpeg_encode(c, 95) if i != 2 else cv2.imencode(".jpg", c, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()
+        (tmp_path / f"in{i}.jpg").write_bytes(data)
+        tasks.append(task.FileTask(i, str(tmp_path / f"in{i}.jpg"), str(tmp_path / f"out{i}.jpg")))
+    tasks.append(task.FileTask(9, str(tmp_path / "missing.jpg"), str(tmp_path / "out9.jpg")))
+    params = (5, 0.5, 0, 0, 50.0, 5.0)
+    events = []
+    task.run_file_tasks(ctx, tasks, *params, emit=lambda e, p: events.append((e, p)),
+                        fallback_decode=lambda b: cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR))
+    done = {p["task_id"]: p["result"] for e, p in events if e == "task_completed"}
+    assert sorted(p["task_id"] for e, p in events if e == "start_running_task") == [0, 1, 2, 3, 9]
+    assert done[9] == "error"
+    for i in range(4):
+        src = (tmp_path / f"in{i}.jpg").read_bytes()
+        pixels = orc.jpeg_decode(src) if i != 2 else cv2.imdecode(np.frombuffer(src, np.uint8), cv2.IMREAD_COLOR)
+        ra, rneed, rout = orc.correct_default(pixels, *params)
+        assert done[i] == ("debatable" if rneed else "finished")
+        assert (tmp_path / f"out{i}.jpg").read_bytes() == orc.jpeg_encode(rout, 100), i
+
+
+def test_jpeg_decode_refuses_exif_turned_files(ctx, orc):
+    """imread rotates by the Exif Orientation tag; the device decoder refuses such files (the caller keeps imread)."""
+    from tests.test_oracle_vs_cv2 import _with_exif_orientation
+    data = orc.jpeg_encode(np.full((24, 40, 3), 200, np.uint8), 90)
+    assert np.array_equal(ctx.jpeg_decode(_with_exif_orientation(data, 1)), orc.jpeg_decode(data))
+    with pytest.raises(api.OicsError):
+        ctx.jpeg_decode(_with_exif_orientation(data, 6))

@@ -261,3 +261,25 @@ def test_jpeg_decode_rejects_what_it_does_not_cover(orc):
         orc.jpeg_decode(prog)
     with pytest.raises(ValueError):
         orc.jpeg_decode(b"not a jpeg at all")
+
+
+def _with_exif_orientation(jpeg: bytes, orientation: int) -> bytes:
+    """Insert an APP1 Exif segment holding only the Orientation tag behind SOI."""
+    tiff = b"II*\x00\x08\x00\x00\x00" + b"\x01\x00" + b"\x12\x01\x03\x00\x01\x00\x00\x00" + bytes([orientation, 0, 0, 0]) + b"\x00\x00\x00\x00"
+    body = b"Exif\x00\x00" + tiff
+    return jpeg[:2] + b"\xff\xe1" + (len(body) + 2).to_bytes(2, "big") + body + jpeg[2:]
+
+
+def test_jpeg_decode_exif_orientation(orc):
+    """cv::imread turns the image by the Exif Orientation tag; the restatement (and the CUDA decoder,
+    which shares the rule) accepts upright files only and refuses the others instead of returning
+    pixels imread would not."""
+    img = np.zeros((24, 40, 3), np.uint8)
+    img[:8, :10] = (0, 0, 255)
+    enc = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 95])[1].tobytes()
+    upright = _with_exif_orientation(enc, 1)
+    assert np.array_equal(orc.jpeg_decode(upright), cv2.imdecode(np.frombuffer(upright, np.uint8), cv2.IMREAD_COLOR))
+    turned = _with_exif_orientation(enc, 6)
+    assert cv2.imdecode(np.frombuffer(turned, np.uint8), cv2.IMREAD_COLOR).shape[:2] == (40, 24)   # cv2 does rotate
+    with pytest.raises(ValueError):
+        orc.jpeg_decode(turned)
