@@ -679,3 +679,17 @@ def test_jpeg_decode_refuses_exif_turned_files(ctx, orc):
     assert np.array_equal(ctx.jpeg_decode(_with_exif_orientation(data, 1)), orc.jpeg_decode(data))
     with pytest.raises(api.OicsError):
         ctx.jpeg_decode(_with_exif_orientation(data, 6))
+
+
+def test_jpeg_codecs_large_image(ctx, orc):
+    """Both codecs at a scan-sized image (config 5 class, 54 MP): offsets beyond 2^31 bits of stream and
+    2^27 coefficients; busy content (noise) next to long uniform stretches (the decoder's hard case)."""
+    h, w = 9000, 6001
+    rng = np.random.default_rng(54)
+    img = np.full((h, w, 3), 255, np.uint8)
+    img[1000:1600, 500:5500] = rng.integers(0, 256, (600, 5000, 3), dtype=np.uint8)
+    img[4000:4040] = 0
+    img[6000:8000, 3000:3010] = (30, 60, 200)
+    data = ctx.jpeg_encode(img, 90)
+    assert data == orc.jpeg_encode(img, 90)
+    assert np.array_equal(ctx.jpeg_decode(data), orc.jpeg_decode(data))
