@@ -250,8 +250,9 @@ OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t
  * JPEG file already in host memory.  oics_jpeg_info parses the header only (host, no context): image
  * size and component count.  oics_jpeg_decode decodes on the GPU -- the pixels are libjpeg(-turbo)'s /
  * cv::imread's bit for bit -- into `bgr` (host or device, rows `stride` bytes apart, 0 = packed).
- * OICS_ERR_UNSUPPORTED for files outside the covered subset (progressive, restart intervals, CMYK,
- * subsampling other than 4:4:4 / 4:2:2 / 4:2:0): the caller keeps imread for those. */
+ * OICS_ERR_UNSUPPORTED for files outside the covered subset (progressive, non-interleaved scans, CMYK,
+ * subsampling other than 4:4:4 / 4:2:2 / 4:2:0, an Exif orientation other than upright): the caller keeps
+ * imread for those. */
 OICS_API int32_t oics_jpeg_info(const uint8_t *file, size_t file_size, int32_t *w, int32_t *h, int32_t *channels);
 OICS_API int32_t oics_jpeg_decode(oics_ctx *ctx, const uint8_t *file, size_t file_size, uint8_t *bgr, size_t stride,
                                   size_t bgr_cap, int32_t *w, int32_t *h);

@@ -21,7 +21,7 @@
 //   jdec_color_kernel jdsample.c fancy h2v1 / h2v2 upsampling (jdmainct.c edge rows, jinit_upsampler's
 //                     width rule), jdcolor.c YCC -> RGB, BGR out
 // Covered: 8-bit baseline / extended sequential, one interleaved scan, grey or Y Cb Cr with luma
-// sampling 1x1, 2x1 or 2x2, any Huffman tables, no restart intervals.  Anything else:
+// sampling 1x1, 2x1 or 2x2, any Huffman tables, restart intervals.  Anything else:
 // OICS_ERR_UNSUPPORTED (the caller keeps its imread for those).
 #include <algorithm>
 #include <cstring>
@@ -50,6 +50,7 @@ struct JdecTables {
 struct JdecHeader {
     int w = 0, h = 0, ncomp = 0, hs = 1, vs = 1;   // luma sampling; chroma is 1x1
     size_t scan_off = 0, scan_len = 0;             // entropy-coded bytes (stuffed), EOI excluded
+    int restart = 0;                               // DRI: MCUs per restart interval (0 = none)
 };
 
 
@@ -151,7 +152,7 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
             return unsupported("progressive / lossless / arithmetic coding");
         } else if (m == 0xDD) {
             if (sl < 2) return bad("DRI");
-            if ((s[0] << 8) | s[1]) return unsupported("restart intervals");
+            H->restart = (s[0] << 8) | s[1];
         } else if (m == 0xE1) {
             const int o = exif_orientation(s, (long)sl);
             if (o >= 2 && o <= 8) return unsupported("an Exif orientation other than upright (imread would rotate the image)");
@@ -199,14 +200,18 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
 }
 
 // ---------------------------------------------------------------------------
-// unstuffing: byte j of the scan is dropped iff it is the 0x00 behind a 0xFF.  Any other byte behind
-// a 0xFF is a marker inside the scan (restart, premature EOI): *flag |= 1.
-__global__ void __launch_bounds__(256) jdec_unstuff_count_kernel(const uint8_t *__restrict__ s, size_t n,
+// unstuffing: byte j of the scan is dropped iff it is the 0x00 behind a 0xFF or, in a file with restart
+// intervals, one of the two bytes of an RSTn marker.  Any other byte behind a 0xFF is a marker that does
+// not belong into the scan (premature EOI, or RSTn without DRI): *flag |= 1.  cnt[i] = dropped bytes of
+// chunk i in the low word, RSTn markers (counted at their second byte) in the high word.
+__device__ __forceinline__ bool is_rst(uint8_t b) { return b >= 0xD0 && b <= 0xD7; }
+
+__global__ void __launch_bounds__(256) jdec_unstuff_count_kernel(const uint8_t *__restrict__ s, size_t n, int restart,
                                                                  unsigned long long *__restrict__ cnt, int *__restrict__ flag)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i * 32 >= n) return;
-    unsigned c = 0;
+    unsigned c = 0, marks = 0;
     bool marker = false;
     uint8_t prev = i ? s[i * 32 - 1] : 0;
     const size_t j1 = min(n, i * 32 + 32);
@@ -214,28 +219,45 @@ __global__ void __launch_bounds__(256) jdec_unstuff_count_kernel(const uint8_t *
         const uint8_t b = s[j];
         if (prev == 0xFF) {
             if (b == 0) c++;
+            else if (restart && is_rst(b)) { c++; marks++; }
             else marker = true;
+        } else if (restart && b == 0xFF && j + 1 < n && is_rst(s[j + 1])) {
+            c++;
         }
         prev = b;
     }
     if (j1 == n && prev == 0xFF) marker = true;
-    cnt[i] = c;
+    cnt[i] = (unsigned long long)c | ((unsigned long long)marks << 32);
     if (marker) atomicOr(flag, 1);
 }
 
-// kept bytes -> MSB-first 32-bit words (byte i of the stream lands at byte address i ^ 3)
-__global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *__restrict__ s, size_t n,
+// kept bytes -> MSB-first 32-bit words (byte i of the stream lands at byte address i ^ 3); the bit position
+// behind the r-th RSTn marker (= where restart interval r + 1 begins) -> rst[r]
+__global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *__restrict__ s, size_t n, int restart,
                                                                  const unsigned long long *__restrict__ off,
-                                                                 uint8_t *__restrict__ out)
+                                                                 uint8_t *__restrict__ out, unsigned long long *__restrict__ rst,
+                                                                 unsigned nrst)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i * 32 >= n) return;
-    size_t o = i * 32 - (size_t)off[i];
+    size_t o = i * 32 - (size_t)(off[i] & 0xffffffffull);
+    unsigned mark = (unsigned)(off[i] >> 32);
     uint8_t prev = i ? s[i * 32 - 1] : 0;
     const size_t j1 = min(n, i * 32 + 32);
     for (size_t j = i * 32; j < j1; j++) {
         const uint8_t b = s[j];
-        if (!(prev == 0xFF && b == 0)) out[(o++) ^ 3] = b;
+        bool drop = false;
+        if (prev == 0xFF) {
+            if (b == 0) drop = true;
+            else if (restart && is_rst(b)) {
+                drop = true;
+                if (mark < nrst) rst[mark] = 8ull * o;
+                mark++;
+            }
+        } else if (restart && b == 0xFF && j + 1 < n && is_rst(s[j + 1])) {
+            drop = true;
+        }
+        if (!drop) out[(o++) ^ 3] = b;
         prev = b;
     }
 }
@@ -296,10 +318,27 @@ __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *_
     __syncthreads();
 }
 
+// Restart intervals: rst[r] = first bit of interval r + 1.  In front of it the stream holds up to 7 padding
+// one-bits, which no Huffman code consists of, so the symbol that would reach across the boundary is the
+// padding: the decoder drops it and continues at the boundary with the state of a fresh interval
+// (k = 0, block 0; the DC predictors are reset by the DC scan).  The interval of a state follows from its
+// bit position alone.
 template <typename SINK>
 __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t *sw, unsigned long long &p,
-                                             int &k, int &bi, unsigned long long end, SINK &sink)
+                                             int &k, int &bi, unsigned long long end, SINK &sink,
+                                             const unsigned long long *__restrict__ rst, unsigned nrst)
 {
+    unsigned ri = 0;                                 // boundaries at or before p
+    if (nrst) {
+        unsigned lo = 0, hi = nrst;
+        while (lo < hi) {
+            const unsigned mid = (lo + hi) >> 1;
+            if (__ldg(rst + mid) <= p) lo = mid + 1;
+            else hi = mid;
+        }
+        ri = lo;
+    }
+    unsigned long long bound = ri < nrst ? __ldg(rst + ri) : ~0ull;
     const unsigned long long wbase = (unsigned long long)blockIdx.x * 128 * (JD_SUB / 32);
     auto word = [&](unsigned long long w) {
         const int i = min((int)(w - wbase), JD_WIN - 1);
@@ -338,6 +377,15 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
             }
         }
         const int s = sym & 15;
+        if (p + len + s > bound) {                   // padding in front of a restart marker
+            p = bound;
+            k = 0;
+            bi = 0;
+            tdc = 2 * S.comp_of[0];
+            ri++;
+            bound = ri < nrst ? __ldg(rst + ri) : ~0ull;
+            continue;
+        }
         int val = s ? (int)((v << len) >> (32 - s)) : 0;
         if (s && val < (1 << (s - 1))) val += 1 - (1 << s);
         p += len + s;
@@ -381,11 +429,12 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
                                                         unsigned long long *used, unsigned long long *out,
                                                         unsigned long long *__restrict__ nblk, unsigned long long *mkey,
                                                         unsigned long long *mout, unsigned *mnb, unsigned *mcnt, int round,
-                                                        int *__restrict__ changed)
+                                                        int *__restrict__ changed, const unsigned long long *__restrict__ rst,
+                                                        unsigned nrst)
 {
     __shared__ JdecShared S;
     __shared__ uint32_t sw[JD_WIN_WORDS];
-    const unsigned long long total = 8ull * (scan_len - *removed);
+    const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = j * JD_SUB < total;
     bool tables = false;
@@ -428,7 +477,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
             unsigned long long p = x >> 12;
             int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
             NoSink sink;
-            const unsigned n = jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+            const unsigned n = jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
             const unsigned long long e = jdec_pack(p, k, bi);
             mine = x;
             __stcg(out + j, e);
@@ -463,7 +512,8 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
                                                          const unsigned long long *__restrict__ removed, size_t scan_len,
                                                          const unsigned long long *__restrict__ used,
                                                          const unsigned long long *__restrict__ first_block,
-                                                         unsigned long long nblocks, int16_t *__restrict__ coef)
+                                                         unsigned long long nblocks, int16_t *__restrict__ coef,
+                                                         const unsigned long long *__restrict__ rst, unsigned nrst)
 {
     __shared__ JdecShared S;
     __shared__ uint8_t zz[64];
@@ -471,7 +521,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     if (threadIdx.x < 64) zz[threadIdx.x] = T->zz[threadIdx.x];
     jdec_load_tables(S, T);
     jdec_stage_words(sw, words);
-    const unsigned long long total = 8ull * (scan_len - *removed);
+    const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j * JD_SUB >= total) return;
     const unsigned long long x = used[j];
@@ -480,7 +530,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
     // coefficients were stored by the predecessor under the same ordinal
     CoefSink sink{coef, first_block[j], nblocks, zz};
-    jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink);
+    jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
 }
 
 // ---------------------------------------------------------------------------
@@ -550,7 +600,7 @@ __device__ __forceinline__ void idct_1d(const int (&in)[8], int (&o)[8], int shi
 // 256 threads = 32 blocks; thread = row r of its block (load, dequantise), then column r, then row r
 __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__restrict__ T, const int16_t *__restrict__ coef,
                                                         const unsigned long long *__restrict__ dc_prefix, JdecGeom G,
-                                                        uint8_t *__restrict__ planes)
+                                                        int restart, uint8_t *__restrict__ planes)
 {
     __shared__ int sm[32][8][9];
     __shared__ uint16_t sq[3][64];
@@ -569,7 +619,8 @@ __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__rest
     x[4] = (int)(int16_t)(raw.z & 0xffff); x[5] = raw.z >> 16;
     x[6] = (int)(int16_t)(raw.w & 0xffff); x[7] = raw.w >> 16;
     if (r == 0) {   // DC = the predictor carried into this MCU + the differences up to this block
-        const long long P = (long long)dc_prefix[mcu];
+        // the predictors restart at 0 with every restart interval: sums relative to the interval's first MCU
+        const long long P = (long long)(dc_prefix[mcu] - (restart ? dc_prefix[mcu - mcu % restart] : 0ull));
         const long long fy = sext21(P), P1 = (P - fy) >> 21, fcb = sext21(P1), fcr = (P1 - fcb) >> 21;
         int dc = (int)(comp == 0 ? fy : comp == 1 ? fcb : fcr);
         const int b0 = comp == 0 ? 0 : bi;
@@ -682,7 +733,8 @@ struct JdecSlot {
     JdecGeom G;
     size_t nsub = 0, nblocks = 0, nmcu = 0, nsum_s = 0, nsum_m = 0;
     unsigned long long *used = nullptr, *out = nullptr, *nblk = nullptr, *sums_s = nullptr, *mcu = nullptr, *sums_m = nullptr;
-    unsigned long long *mkey = nullptr, *mout = nullptr, *removed = nullptr;
+    unsigned long long *mkey = nullptr, *mout = nullptr, *removed = nullptr, *rst = nullptr;
+    unsigned nrst = 0;
     unsigned *mnb = nullptr, *mcnt = nullptr;
     int *flags = nullptr;
     int rounds = 0;           // rounds of the batch whose flags are being read back
@@ -692,7 +744,9 @@ struct JdecSlot {
         if (!ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
         return ev;
     }
-    int *hflags() { return reinterpret_cast<int *>(pin.as<uint8_t>() + sizeof(JdecTables) + 64); }
+    // read-back block: the four counters at `removed`, then the 32 flags
+    unsigned long long *hcounters() { return reinterpret_cast<unsigned long long *>(pin.as<uint8_t>() + sizeof(JdecTables) + 64); }
+    int *hflags() { return reinterpret_cast<int *>(hcounters() + 4); }
 };
 
 static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
@@ -700,11 +754,12 @@ static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
     const unsigned gs = (unsigned)((S.nsub + 127) / 128);
     for (int r = 1; r <= rounds; r++)
         jdec_sync_kernel<<<gs, 128, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used,
-                                                S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags);
+                                                S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags, S.rst, S.nrst);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += rounds;
     S.rounds = rounds;
-    OICS_CUDA_TRY(cudaMemcpyAsync(S.hflags(), S.flags, 32 * sizeof(int), cudaMemcpyDeviceToHost, S.st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(S.hcounters(), S.removed, 4 * sizeof(unsigned long long) + 32 * sizeof(int), cudaMemcpyDeviceToHost,
+                                  S.st));
     return OICS_OK;
 }
 
@@ -712,9 +767,10 @@ static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
 static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_t n)
 {
     cudaStream_t st = S.st;
-    OICS_TRY(S.pin.ensure(sizeof(JdecTables) + 64 + 32 * sizeof(int)));
+    OICS_TRY(S.pin.ensure(sizeof(JdecTables) + 64 + 4 * sizeof(unsigned long long) + 32 * sizeof(int)));
     OICS_CUDA_TRY(cudaStreamSynchronize(st));   // the staging block may still be in flight from the previous file
     JdecTables *T = S.pin.as<JdecTables>();
+    S.H = JdecHeader();                         // the slot is reused: nothing of the previous file may survive
     OICS_TRY(parse_header(file, n, &S.H, T));
     const JdecHeader &H = S.H;
     JdecGeom &G = S.G;
@@ -738,7 +794,8 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     OICS_TRY(S.file.ensure(slen + 64));
     OICS_TRY(S.words.ensure(slen + 8704));   // the last CTA stages a whole window: zero padding behind the stream
     OICS_TRY(S.tables.ensure(sizeof(JdecTables)));
-    const size_t n_state = nchunks + nsum_c + 3 * nsub + S.nsum_s + S.nmcu + S.nsum_m + 2 * nsub * JD_M + 64;
+    S.nrst = H.restart ? (unsigned)((S.nmcu + H.restart - 1) / H.restart - 1) : 0u;
+    const size_t n_state = nchunks + nsum_c + 3 * nsub + S.nsum_s + S.nmcu + S.nsum_m + 2 * nsub * JD_M + 64 + S.nrst + 1;
     OICS_TRY(S.state.ensure(n_state * sizeof(unsigned long long) + (nsub * (JD_M + 1) + 64) * sizeof(unsigned)));
     OICS_TRY(S.coef.ensure(S.nblocks * 64 * sizeof(int16_t) + 256));
     OICS_TRY(S.planes.ensure(off + 256));
@@ -753,7 +810,8 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     S.mout = S.mkey + nsub * JD_M;
     S.removed = S.mout + nsub * JD_M;                       // [0] removed bytes, [1] blocks, [2] DC total, [4..] flags
     S.flags = reinterpret_cast<int *>(S.removed + 4);       // [0]: a marker inside the scan; [r]: round r changed something
-    S.mnb = reinterpret_cast<unsigned *>(S.removed + 64);
+    S.rst = S.removed + 64;                                 // restart boundaries (bit positions); all ones = none
+    S.mnb = reinterpret_cast<unsigned *>(S.rst + S.nrst + 1);
     S.mcnt = S.mnb + nsub * JD_M;
     uint8_t *d_scan = S.file.as<uint8_t>();
     uint32_t *words = S.words.as<uint32_t>();
@@ -762,15 +820,16 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     OICS_CUDA_TRY(cudaMemsetAsync(words, 0, slen + 8704, st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.nblk, 0, nsub * sizeof(unsigned long long), st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.removed, 0, 64 * sizeof(unsigned long long), st));
+    OICS_CUDA_TRY(cudaMemsetAsync(S.rst, 0xFF, ((size_t)S.nrst + 1) * sizeof(unsigned long long), st));
     OICS_CUDA_TRY(cudaMemsetAsync(S.coef.p, 0, S.nblocks * 64 * sizeof(int16_t), st));
     const unsigned gc = (unsigned)((nchunks + 255) / 256), gs = (unsigned)((nsub + 127) / 128);
-    jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, S.flags);
+    jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, S.flags);
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums_c, S.removed, nullptr));
-    jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, cnt, reinterpret_cast<uint8_t *>(words));
+    jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, reinterpret_cast<uint8_t *>(words), S.rst, S.nrst);
     // every thread is fed its predecessor's exit state until a round changes nothing; the host looks at
     // the flags after 4 rounds (each launch advances the chain through whole CTAs), then every 8
     jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
-                                          S.mnb, S.mcnt, 0, S.flags);
+                                          S.mnb, S.mcnt, 0, S.flags, S.rst, S.nrst);
     ctx->launches += 3;
     return jdec_rounds(ctx, S, 4);
 }
@@ -781,8 +840,12 @@ static int32_t jdec_poll(oics_ctx *ctx, JdecSlot &S, bool *done)
     OICS_CUDA_TRY(cudaStreamSynchronize(S.st));
     const int *hf = S.hflags();
     if (hf[0] & 1) {
-        set_error("jpeg: a marker inside the scan (restart interval or truncated file) is not covered by the CUDA decoder");
+        set_error("jpeg: a marker inside the scan (truncated file, or restart markers without DRI) is not covered by the CUDA decoder");
         return OICS_ERR_UNSUPPORTED;
+    }
+    if ((unsigned)(S.hcounters()[0] >> 32) != S.nrst) {
+        set_error("jpeg: %u restart markers in the scan, the header announces %u", (unsigned)(S.hcounters()[0] >> 32), S.nrst);
+        return OICS_ERR_INVALID_ARG;
     }
     *done = !hf[S.rounds];
     if (*done) return OICS_OK;
@@ -798,10 +861,10 @@ static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t st
     int16_t *coef = S.coef.as<int16_t>();
     OICS_TRY(exclusive_scan(ctx, st, S.nblk, S.nsub, S.sums_s, S.removed + 1, nullptr));
     jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
-                                           (unsigned long long)S.nblocks, coef);
+                                           (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
     jdec_mcu_dc_kernel<<<(unsigned)((S.nmcu + 255) / 256), 256, 0, st>>>(coef, S.G, S.mcu);
     OICS_TRY(exclusive_scan(ctx, st, S.mcu, S.nmcu, S.sums_m, S.removed + 2, nullptr));
-    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.G, S.planes.as<uint8_t>());
+    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.G, S.H.restart, S.planes.as<uint8_t>());
     jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;

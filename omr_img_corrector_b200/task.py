@@ -10,7 +10,7 @@ caller's encoder (None = do not write).  `run_file_tasks`: a task carries `input
 `output_path` exactly as the reference's `add_task` does (task.rs:19-30); the JPEG file is read
 from disk as bytes, decoded, deskewed and re-encoded on the GPU (`oics_correct_batch_files`:
 imread, omr.rs:349, and imwrite(JPEG, 100), omr.rs:447-448, included) and the output bytes are
-written to `output_path`.  Files the CUDA decoder does not cover (progressive, restart intervals,
+written to `output_path`.  Files the CUDA decoder does not cover (progressive, Exif-turned,
 other formats) come back as "error" unless the caller passes `fallback_decode` (e.g. cv2.imdecode),
 in which case they take the pixel path.
 """

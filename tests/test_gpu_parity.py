@@ -605,9 +605,26 @@ def test_jpeg_decode_rejects_what_it_does_not_cover(ctx):
     prog = cv2.imencode(".jpg", np.zeros((16, 16, 3), np.uint8), [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()
     with pytest.raises(api.OicsError):
         ctx.jpeg_decode(prog)
-    rst = cv2.imencode(".jpg", np.zeros((64, 64, 3), np.uint8), [cv2.IMWRITE_JPEG_RST_INTERVAL, 2])[1].tobytes()
+
+
+@pytest.mark.parametrize("interval", [1, 2, 7, 64])
+def test_jpeg_decode_restart_intervals(ctx, orc, interval):
+    """Files with DRI / RSTn markers: every interval is byte-aligned and restarts the DC predictors."""
+    import cv2
+    rng = np.random.default_rng(interval)
+    img = np.full((150, 333, 3), 255, np.uint8)
+    img[20:90, 40:300] = rng.integers(0, 256, (70, 260, 3), dtype=np.uint8)
+    img[100:104] = (0, 0, 0)
+    for extra in ([], [cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_444]):
+        for q in (100, 60):
+            data = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, q, cv2.IMWRITE_JPEG_RST_INTERVAL, interval] + extra)[1].tobytes()
+            assert np.array_equal(ctx.jpeg_decode(data), orc.jpeg_decode(data)), (interval, q, bool(extra))
+    # a marker count that contradicts the header is an error, not a silent mis-decode
+    data = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 90, cv2.IMWRITE_JPEG_RST_INTERVAL, interval])[1].tobytes()
+    i = data.index(b"\xff\xdd")
+    broken = data[:i + 4] + (interval + 1000).to_bytes(2, "big") + data[i + 6:]
     with pytest.raises(api.OicsError):
-        ctx.jpeg_decode(rst)
+        ctx.jpeg_decode(broken)
 
 
 def test_correct_batch_files_jpeg_in_jpeg_out(ctx, orc, dataset_like):
