@@ -48,7 +48,9 @@ def workload_config(cards_per_gpu, n_gpus, distinct, e2e_cards):
         "sharding": f"cards sharded over {n_gpus} GPU(s), no collective on the data path",
         "l2": "inputs larger than L2 (cards_per_gpu x 8.7 MB binary cards streamed from HBM each step)",
         "e2e_workload": f"omr::correct_default via oics_correct_batch, {e2e_cards} pinned host BGR cards per GPU "
-                        "per step, deskewed BGR cards copied back",
+                        "per step, deskewed BGR cards copied back (e2e.value); e2e.jpeg_out: same input, the JPEG "
+                        "(quality 100) file of every deskewed card copied back (oics_correct_batch_jpeg); e2e.jpeg_io: "
+                        "JPEG files in, JPEG files out, both codecs on the device (oics_correct_batch_files)",
     }
 
 
