@@ -695,10 +695,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     if (files) {
         OICS_BATCH_TRY(decode_begin(0));
         OICS_BATCH_TRY(decode_finish(0));
-        if (n_sub > 1) {
-            OICS_BATCH_TRY(decode_begin(1));
-            OICS_BATCH_TRY(decode_finish(1));
-        }
+        if (n_sub > 1) OICS_BATCH_TRY(decode_begin(1));
     } else if (!dev_in) {
         OICS_BATCH_CUDA(upload(0));
         if (n_sub > 1) OICS_BATCH_CUDA(upload(1));
@@ -710,7 +707,6 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
         const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
         const size_t dcard = dev_in ? card_stride : card_bytes, dstride = dev_in ? (size_t)stride : row;
-        if (files && k + 2 < n_sub) OICS_BATCH_TRY(decode_begin(k + 2));   // its chains run beside this sub-batch's sweep
         if (!dev_in) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, in_ready[s], 0));
         // P0 for every card of the sub-batch (one launch), then one fused sweep over all of them
         OICS_BATCH_TRY(preprocess_batch_device(ctx, dsrc, nb, dcard, w, h, dstride, OICS_PRE_OMR, ow, oh, ctx->bin.as<uint8_t>()));
@@ -802,9 +798,13 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (rc != OICS_OK) break;
         if (!dev_in) {
             OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
-            if (k + 2 < n_sub) {
-                if (files) OICS_BATCH_TRY(decode_finish(k + 2));
-                else OICS_BATCH_CUDA(upload(k + 2));
+            if (files) {
+                // in the shadow of the deskew + encode kernels just enqueued: the next sub-batch's cards are
+                // written (its chains had this sub-batch's sweep to converge), then the one after it is begun
+                if (k + 1 < n_sub) OICS_BATCH_TRY(decode_finish(k + 1));
+                if (k + 2 < n_sub) OICS_BATCH_TRY(decode_begin(k + 2));
+            } else if (k + 2 < n_sub) {
+                OICS_BATCH_CUDA(upload(k + 2));
             }
         }
         if (jpeg_quality && dsts) {   // file sizes of the sub-batch: one read-back

@@ -738,6 +738,7 @@ struct JdecSlot {
     unsigned *mnb = nullptr, *mcnt = nullptr;
     int *flags = nullptr;
     int rounds = 0;           // rounds of the batch whose flags are being read back
+    bool in_flight = false;   // begun, and the host has not yet seen its chains converge
     cudaEvent_t ev = nullptr;
     cudaEvent_t done_ev()
     {
@@ -768,7 +769,10 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
 {
     cudaStream_t st = S.st;
     OICS_TRY(S.pin.ensure(sizeof(JdecTables) + 64 + 4 * sizeof(unsigned long long) + 32 * sizeof(int)));
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));   // the staging block may still be in flight from the previous file
+    // the pinned block (tables out, counters back) is reused: a previous file that was begun but never polled
+    // to the end (refused or abandoned) may still have copies in flight -- otherwise the last poll has waited
+    if (S.in_flight) OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    S.in_flight = true;
     JdecTables *T = S.pin.as<JdecTables>();
     S.H = JdecHeader();                         // the slot is reused: nothing of the previous file may survive
     OICS_TRY(parse_header(file, n, &S.H, T));
@@ -848,7 +852,10 @@ static int32_t jdec_poll(oics_ctx *ctx, JdecSlot &S, bool *done)
         return OICS_ERR_INVALID_ARG;
     }
     *done = !hf[S.rounds];
-    if (*done) return OICS_OK;
+    if (*done) {
+        S.in_flight = false;
+        return OICS_OK;
+    }
     OICS_CUDA_TRY(cudaMemsetAsync(S.flags + 1, 0, 31 * sizeof(int), S.st));
     return jdec_rounds(ctx, S, 8);
 }
