@@ -183,6 +183,16 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
                     }
                     memcpy(T->vals[t], v, 256);
                 }
+                // the commonest block of a scanned card -- DC difference 0, then end of block -- in ONE lookup:
+                // where a DC code of category 0 and the EOB code behind it fit the 8-bit window together, the DC
+                // entry carries bit 15 and the length of both
+                for (int idx = 0; idx < 256; idx++) {
+                    const unsigned e = T->lut[2 * c][idx];
+                    if (!e || (e & 255)) continue;
+                    const int l1 = (int)(e >> 8);
+                    const unsigned e2 = T->lut[2 * c + 1][(idx << l1) & 255];
+                    if (e2 && (e2 & 255) == 0 && l1 + (int)(e2 >> 8) <= 8) T->lut[2 * c][idx] = (uint16_t)(0x8000u | ((l1 + (e2 >> 8)) << 8));
+                }
                 for (int i = 0; i < hsf[c] * vsf[c]; i++) T->comp_of[nb++] = (uint8_t)c;
             }
             T->nbm = nb;
@@ -359,8 +369,18 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t
         const int t = tdc + (k ? 1 : 0);
         int len, sym;
         const unsigned e = S.lut[t][v >> 24];
+        if (e & 0x8000u) {                           // DC difference 0 and EOB together: the block is complete
+            const int both = (int)((e >> 8) & 0x7f);
+            if (p + both <= bound) {
+                p += both;
+                bi = bi + 1 == S.nbm ? 0 : bi + 1;
+                tdc = 2 * S.comp_of[bi];
+                done++;
+                continue;
+            }
+        }
         if (e) {
-            len = e >> 8;
+            len = (e >> 8) & 0x7f;
             sym = e & 255;
         } else {
             len = 16;
