@@ -352,13 +352,14 @@ struct EmitSink {
 
 __global__ void __launch_bounds__(256) jpeg_emit_kernel(const int16_t *__restrict__ coef, JpegGeom G,
                                                         const unsigned long long *__restrict__ offs,
+                                                        const unsigned long long *__restrict__ offs_base,
                                                         uint32_t *__restrict__ words)
 {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= G.nblocks) return;
     EmitSink s;
     s.words = words;
-    s.pos = offs[g];
+    s.pos = offs[g] + offs_base[g >> 10];
     walk_block(coef, G, g, s);
     s.finish();
 }
@@ -443,24 +444,16 @@ __global__ void __launch_bounds__(1024) scan_sums_kernel(unsigned long long *__r
     if (threadIdx.x == 0) *total = carry;
 }
 
-__global__ void __launch_bounds__(1024) scan_add_kernel(unsigned long long *__restrict__ v, size_t n,
-                                                        const unsigned long long *__restrict__ sums,
-                                                        const unsigned long long *__restrict__ tb)
-{
-    if (tb) n = stream_chunks(tb);
-    const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
-    if (i < n) v[i] += sums[blockIdx.x];
-}
-
+// Two launches: afterwards the exclusive prefix of element i is  v[i] + sums[i >> 10]  (the consumers add
+// the per-CTA base themselves; a third pass over the data would only do that addition).
 int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, size_t n, unsigned long long *sums,
                        unsigned long long *total, const unsigned long long *tb)
 {
     const int m = (int)((n + 1023) / 1024);
     scan_block_kernel<<<m, 1024, 0, st>>>(v, n, sums, tb);
     scan_sums_kernel<<<1, 1024, 0, st>>>(sums, m, total, tb);
-    scan_add_kernel<<<m, 1024, 0, st>>>(v, n, sums, tb);
     OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches += 3;
+    ctx->launches += 2;
     return OICS_OK;
 }
 
@@ -499,6 +492,7 @@ __global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *_
 __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *__restrict__ words,
                                                                const unsigned long long *__restrict__ total_bits,
                                                                const unsigned long long *__restrict__ off,
+                                                               const unsigned long long *__restrict__ off_base,
                                                                const uint8_t *__restrict__ header, int hdr, int sof, int w,
                                                                int h, uint8_t *__restrict__ file, size_t file_cap)
 {
@@ -518,7 +512,7 @@ __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *_
     const size_t cap = file_cap > (size_t)hdr ? file_cap - hdr : 0;
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
-    size_t o = 32 * i + (size_t)off[i];
+    size_t o = 32 * i + (size_t)(off[i] + off_base[i >> 10]);
     const unsigned long long j1 = min(nbytes, 32ull * i + 32ull);
     for (unsigned long long j = 32ull * i; j < j1; j++) {
         const uint32_t b = stream_byte(words, j, nbytes, pad);
@@ -657,13 +651,13 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     ctx->launches += 2;
     OICS_TRY(exclusive_scan(ctx, st, bits, nb, sums, d_totals, nullptr));
     jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
-    jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, words);
+    jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, sums, words);
     jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums2, d_totals + 1, d_totals));
     jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
-        words, d_totals, cnt, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
+        words, d_totals, cnt, sums2, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;

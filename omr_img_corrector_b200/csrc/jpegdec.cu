@@ -245,13 +245,15 @@ __global__ void __launch_bounds__(256) jdec_unstuff_count_kernel(const uint8_t *
 // behind the r-th RSTn marker (= where restart interval r + 1 begins) -> rst[r]
 __global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *__restrict__ s, size_t n, int restart,
                                                                  const unsigned long long *__restrict__ off,
+                                                                 const unsigned long long *__restrict__ off_base,
                                                                  uint8_t *__restrict__ out, unsigned long long *__restrict__ rst,
                                                                  unsigned nrst)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i * 32 >= n) return;
-    size_t o = i * 32 - (size_t)(off[i] & 0xffffffffull);
-    unsigned mark = (unsigned)(off[i] >> 32);
+    const unsigned long long before = off[i] + off_base[i >> 10];   // both fields at once: dropped bytes | markers << 32
+    size_t o = i * 32 - (size_t)(before & 0xffffffffull);
+    unsigned mark = (unsigned)(before >> 32);
     uint8_t prev = i ? s[i * 32 - 1] : 0;
     const size_t j1 = min(n, i * 32 + 32);
     for (size_t j = i * 32; j < j1; j++) {
@@ -532,6 +534,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
                                                          const unsigned long long *__restrict__ removed, size_t scan_len,
                                                          const unsigned long long *__restrict__ used,
                                                          const unsigned long long *__restrict__ first_block,
+                                                         const unsigned long long *__restrict__ first_block_base,
                                                          unsigned long long nblocks, int16_t *__restrict__ coef,
                                                          const unsigned long long *__restrict__ rst, unsigned nrst)
 {
@@ -549,7 +552,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
     // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
     // coefficients were stored by the predecessor under the same ordinal
-    CoefSink sink{coef, first_block[j], nblocks, zz};
+    CoefSink sink{coef, first_block[j] + first_block_base[j >> 10], nblocks, zz};
     jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
 }
 
@@ -619,7 +622,8 @@ __device__ __forceinline__ void idct_1d(const int (&in)[8], int (&o)[8], int shi
 
 // 256 threads = 32 blocks; thread = row r of its block (load, dequantise), then column r, then row r
 __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__restrict__ T, const int16_t *__restrict__ coef,
-                                                        const unsigned long long *__restrict__ dc_prefix, JdecGeom G,
+                                                        const unsigned long long *__restrict__ dc_prefix,
+                                                        const unsigned long long *__restrict__ dc_base, JdecGeom G,
                                                         int restart, uint8_t *__restrict__ planes)
 {
     __shared__ int sm[32][8][9];
@@ -640,7 +644,8 @@ __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__rest
     x[6] = (int)(int16_t)(raw.w & 0xffff); x[7] = raw.w >> 16;
     if (r == 0) {   // DC = the predictor carried into this MCU + the differences up to this block
         // the predictors restart at 0 with every restart interval: sums relative to the interval's first MCU
-        const long long P = (long long)(dc_prefix[mcu] - (restart ? dc_prefix[mcu - mcu % restart] : 0ull));
+        const int m0 = restart ? mcu - mcu % restart : 0;
+        const long long P = (long long)(dc_prefix[mcu] + dc_base[mcu >> 10] - (restart ? dc_prefix[m0] + dc_base[m0 >> 10] : 0ull));
         const long long fy = sext21(P), P1 = (P - fy) >> 21, fcb = sext21(P1), fcr = (P1 - fcb) >> 21;
         int dc = (int)(comp == 0 ? fy : comp == 1 ? fcb : fcr);
         const int b0 = comp == 0 ? 0 : bi;
@@ -849,7 +854,7 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     const unsigned gc = (unsigned)((nchunks + 255) / 256), gs = (unsigned)((nsub + 127) / 128);
     jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, S.flags);
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums_c, S.removed, nullptr));
-    jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, reinterpret_cast<uint8_t *>(words), S.rst, S.nrst);
+    jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, sums_c, reinterpret_cast<uint8_t *>(words), S.rst, S.nrst);
     // every thread is fed its predecessor's exit state until a round changes nothing; the host looks at
     // the flags after 4 rounds (each launch advances the chain through whole CTAs), then every 8
     jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
@@ -888,10 +893,10 @@ static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t st
     int16_t *coef = S.coef.as<int16_t>();
     OICS_TRY(exclusive_scan(ctx, st, S.nblk, S.nsub, S.sums_s, S.removed + 1, nullptr));
     jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
-                                           (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
+                                           S.sums_s, (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
     jdec_mcu_dc_kernel<<<(unsigned)((S.nmcu + 255) / 256), 256, 0, st>>>(coef, S.G, S.mcu);
     OICS_TRY(exclusive_scan(ctx, st, S.mcu, S.nmcu, S.sums_m, S.removed + 2, nullptr));
-    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.G, S.H.restart, S.planes.as<uint8_t>());
+    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.sums_m, S.G, S.H.restart, S.planes.as<uint8_t>());
     jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;
