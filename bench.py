@@ -386,6 +386,21 @@ def run_gpu(args, rank, local_rank, world):
                         "memory, so HBM is not the physical limiter (issue/ALU bound, ncu in profiles/) -- the "
                         "measured HBM copy peak is the stated denominator and frac may exceed 1"}
 
+    # the sweep re-reads one card 2N times, so its memory ceilings are on-chip.  Both are
+    # measured here, after the timed region, by the library's own probes (csrc/probe.cu).
+    try:
+        l2_gbs = ctx.probe_l2_read(32 << 20, 64)
+        smem_gbs = ctx.probe_smem_read(4096)
+        roofline["on_chip"] = {
+            "l2_read_peak": l2_gbs, "frac_of_l2": achieved / l2_gbs,
+            "smem_read_peak": smem_gbs, "frac_of_smem": achieved / smem_gbs, "unit": "GB/s",
+            "source": "measured live after the timed region: oics_probe_l2_read (32 MB buffer, 64 passes, "
+                      "ld.global.cg.v4) and oics_probe_smem_read (64 KB tile per CTA, LDS.128)",
+            "note": "same 1 B/sample algorithmic bytes over the on-chip peaks SURVEY 8(d) names as the sweep's "
+                    "real memory ceilings; the kernel fetches 1 bit per sample, so these are also upper bounds"}
+    except Exception as exc:  # a probe failure must not lose the bench line
+        roofline["on_chip"] = {"error": str(exc)}
+
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1

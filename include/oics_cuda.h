@@ -92,6 +92,14 @@ OICS_API int64_t oics_launch_count(oics_ctx *ctx);
 /* Device time, in ms, of the sweep kernel launches of the most recent sweep call
  * (CUDA events on the launching stream) and how many launches that was. */
 OICS_API int32_t oics_last_sweep_kernel_ms(oics_ctx *ctx, double *ms, int32_t *launches);
+/* Bandwidth probes for the roofline block of the bench (the sweep of omr.rs:147-221
+ * re-reads one card 2N times, so its memory ceilings are on-chip; MEASURED_PEAKS.json has none).
+ * oics_probe_l2_read: every CTA streams an L2-resident buffer of `bytes` `reps` times with
+ * L1-bypassing 16-byte loads; oics_probe_smem_read: every thread re-reads its CTA's 64 KB
+ * shared-memory tile with 16-byte loads.  Both time themselves with CUDA events on the context's
+ * stream and return GB/s of the whole device.  Measurement only; no product call uses them. */
+OICS_API int32_t oics_probe_l2_read(oics_ctx *ctx, size_t bytes, int32_t reps, double *gb_per_s);
+OICS_API int32_t oics_probe_smem_read(oics_ctx *ctx, int32_t iters, double *gb_per_s);
 
 /* ---- host-side geometry (pure functions, no device) --------------------- */
 /* cv::getRotationMatrix2D as called at omr.rs:157-163 / transfer.rs:472-475. */

@@ -42,6 +42,8 @@ SIGNATURES = {
     "oics_synchronize": (_i32, [_ctx]),
     "oics_launch_count": (C.c_int64, [_ctx]),
     "oics_last_sweep_kernel_ms": (_i32, [_ctx, _dp, _ip]),
+    "oics_probe_l2_read": (_i32, [_ctx, _sz, _i32, _dp]),
+    "oics_probe_smem_read": (_i32, [_ctx, _i32, _dp]),
     "oics_rotation_matrix_2d": (None, [C.c_float, C.c_float, _f64, _f64, _dp]),
     "oics_angle_half_range": (_i32, [C.c_uint32, _f64]),
     "oics_sweep_matrices": (_i32, [_i32, _i32, C.c_uint32, _f64, _f64, _dp, _i32, _ip]),

@@ -210,6 +210,18 @@ class Context:
         check(self._lib.oics_last_sweep_kernel_ms(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def probe_l2_read(self, nbytes=32 << 20, reps=64) -> float:
+        """GB/s of L2-resident 16-byte reads over the whole device (bench roofline denominator)."""
+        g = C.c_double()
+        check(self._lib.oics_probe_l2_read(self._h, C.c_size_t(nbytes), reps, C.byref(g)))
+        return g.value
+
+    def probe_smem_read(self, iters=4096) -> float:
+        """GB/s of shared-memory 16-byte reads over the whole device (bench roofline denominator)."""
+        g = C.c_double()
+        check(self._lib.oics_probe_smem_read(self._h, iters, C.byref(g)))
+        return g.value
+
     # -- P0
     def preprocess(self, bgr, mode=PRE_OMR, max_w=0, max_h=0, resize_scale=1.0):
         """-> (binary [oh, ow] uint8, scale)"""

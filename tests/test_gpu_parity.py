@@ -710,3 +710,16 @@ def test_jpeg_codecs_large_image(ctx, orc):
     data = ctx.jpeg_encode(img, 90)
     assert data == orc.jpeg_encode(img, 90)
     assert np.array_equal(ctx.jpeg_decode(data), orc.jpeg_decode(data))
+
+
+def test_on_chip_bandwidth_probes(ctx):
+    """bench.py's on-chip roofline denominators: an L2-resident read must beat the
+    HBM copy rate, shared memory must beat L2, and bad arguments come back as errors."""
+    l2 = ctx.probe_l2_read(32 << 20, 16)
+    sm = ctx.probe_smem_read(512)
+    assert 3000.0 < l2 < 100000.0
+    assert l2 < sm < 1000000.0
+    with pytest.raises(api.OicsError):
+        ctx.probe_l2_read(1024, 4)          # smaller than one pass of the grid
+    with pytest.raises(api.OicsError):
+        ctx.probe_smem_read(0)
