@@ -46,7 +46,8 @@ __global__ void __launch_bounds__(256) smem_read_kernel(int iters, unsigned *sin
             uint4 v;
             asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
                          : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                         : "r"(base + (unsigned)(((at + k * 256) & (n16 - 1)) * 16)));
+                         : "r"(base + (unsigned)(((at + it + k * 256) & (n16 - 1)) * 16))
+                         : "memory");  // the address moves with `it`: two iterations never share a load
             acc ^= v.x ^ v.y ^ v.z ^ v.w;
         }
     }
