@@ -32,6 +32,14 @@ def test_no_gpu_means_loud_failure():
     assert e.value.code == _lib.ERR_CUDA and "no CPU fallback" in str(e.value)
 
 
+def test_probes_reject_a_null_context_without_touching_cuda():
+    import ctypes as C
+    lib, g = _lib.load(), C.c_double()
+    assert lib.oics_probe_l2_read(None, 32 << 20, 4, C.byref(g)) == _lib.ERR_INVALID_ARG
+    assert lib.oics_probe_smem_read(None, 16, C.byref(g)) == _lib.ERR_INVALID_ARG
+    assert b"invalid argument" in lib.oics_last_error()
+
+
 def test_product_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "omr_img_corrector_b200")
     for dirpath, _, files in os.walk(pkg):
