@@ -89,6 +89,13 @@ OICS_API int32_t oics_set_stream(oics_ctx *ctx, void *cuda_stream);
 OICS_API int32_t oics_synchronize(oics_ctx *ctx);
 /* Number of kernels this context has launched since creation (bench evidence). */
 OICS_API int64_t oics_launch_count(oics_ctx *ctx);
+/* Opt-in per-kernel timing of everything this context launches (CUDA events around each launch on its own
+ * stream; no profiler, no added synchronisation).  oics_profile(ctx, 1) clears and starts, (ctx, 0) stops.
+ * oics_profile_report synchronises the device and writes a JSON array of
+ * {"kernel", "launches", "ms", "algorithmic_bytes"} aggregated by kernel name into buf (OICS_ERR_CAPACITY
+ * with *needed set when cap is too small).  Measurement plumbing: no reference counterpart. */
+OICS_API int32_t oics_profile(oics_ctx *ctx, int32_t enable);
+OICS_API int32_t oics_profile_report(oics_ctx *ctx, char *buf, size_t cap, size_t *needed);
 /* Device time, in ms, of the sweep kernel launches of the most recent sweep call
  * (CUDA events on the launching stream) and how many launches that was. */
 OICS_API int32_t oics_last_sweep_kernel_ms(oics_ctx *ctx, double *ms, int32_t *launches);
@@ -118,6 +125,12 @@ OICS_API int32_t oics_rotate_geometry(int32_t cols, int32_t rows, double angle, 
  * fewer or none).  No reference counterpart: the reference sweeps on one CPU. */
 OICS_API int32_t oics_shard_range(int32_t n_angles, int32_t rank, int32_t world, int32_t *first,
                                   int32_t *count);
+/* Gather layout of the sharded sweep: per = ceil(n_angles / world) slots per rank.  The exchange buffer is
+ * sd[world][2][per] doubles -- rank r's slice of v_sd, then of h_sd, each padded to `per` with zeros -- so ONE
+ * fixed-size all-gather of 2 * per doubles per rank (ncclAllGather in place over NVLink) completes it. */
+OICS_API int32_t oics_shard_layout(int32_t n_angles, int32_t world, int32_t *per_rank);
+/* Unpacks a gathered sd[world][2][per] buffer (host) into contiguous v_sd[n_angles], h_sd[n_angles]. */
+OICS_API int32_t oics_shard_unpack(const double *sd, int32_t n_angles, int32_t world, double *v_sd, double *h_sd);
 /* scale rule of omr.rs:60-82 */
 OICS_API double oics_projection_scale(int32_t w, int32_t h, int32_t max_w, int32_t max_h);
 
@@ -146,6 +159,16 @@ OICS_API int32_t oics_projection_sweep_batch(oics_ctx *ctx, const uint8_t *bins,
                                              size_t card_stride, int32_t w, int32_t h, int32_t stride,
                                              const double *M, int32_t n_angles, double *v_sd,
                                              double *h_sd);
+/* Single-huge-image mode (BASELINE config 5): the angle loop of omr.rs:153-208 / projection.rs:47-65 split
+ * over `world` GPUs.  Every rank holds the image and calls this with the SAME M[n_angles][6]; the rank
+ * evaluates its contiguous slice (oics_shard_range) and writes it into its block of the exchange buffer
+ * sd[world][2][per] (oics_shard_layout; host or device memory, the other ranks' blocks are not touched).
+ * The caller all-gathers the buffer (NCCL; 16 bytes per angle) and applies oics_rule_a / oics_rule_b to the
+ * unpacked arrays on every rank: the argmax has tie bookkeeping, so it is gather + local rule, not a max
+ * all-reduce.  first / count (nullable) return the slice. */
+OICS_API int32_t oics_sweep_sharded(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
+                                    const double *M, int32_t n_angles, int32_t rank, int32_t world, double *sd,
+                                    int32_t *first, int32_t *count);
 /* Parity hook for P3: the count vectors of one candidate angle. */
 OICS_API int32_t oics_projection_counts(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h,
                                         int32_t stride, const double M[6], int32_t *row_counts,
@@ -205,6 +228,15 @@ OICS_API int32_t oics_hough_dims(int32_t w, int32_t h, double rho, double theta,
 /* standard accumulator over all edge pixels, HoughLinesP vote formula: accum[numangle][numrho] */
 OICS_API int32_t oics_hough_accumulate(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h,
                                        int32_t stride, double rho, double theta, int32_t *accum);
+/* Peak extraction over a standard accumulator accum[numangle][numrho] (host or device), the local-maximum
+ * rule of cv::HoughLines (findLocalMaximums + sort): a cell is a peak when its count is > threshold, > its
+ * left (rho - 1) and upper (theta - 1) neighbours and >= its right and lower ones (outside = 0); peaks are
+ * ordered by count descending, then by (theta, rho) ascending, and the first `cap` are stored as
+ * peaks[i] = {theta index, rho index, count}; the line is rho = (r - (numrho - 1) / 2) * rho_step,
+ * theta = n * theta_step.  *n_peaks = number found (OICS_ERR_CAPACITY if > cap).  The reference calls
+ * hough_lines_p, not this (hough.rs:31-42); it completes the north star's "votes ... then extracts peaks". */
+OICS_API int32_t oics_hough_peaks(oics_ctx *ctx, const int32_t *accum, int32_t numangle, int32_t numrho,
+                                  int32_t threshold, int32_t *peaks, int32_t cap, int32_t *n_peaks);
 /* cv::HoughLinesP (hough.rs:31-42, omr.rs:245-253, fft.rs:183-191): lines [cap][4] int32,
  * *n_lines = number found (OICS_ERR_CAPACITY if > cap; the first cap are stored). */
 OICS_API int32_t oics_hough_lines_p(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h,
@@ -233,6 +265,21 @@ OICS_API int32_t oics_rotate(oics_ctx *ctx, const uint8_t *src, int32_t ch, int3
                              int32_t stride, double angle, double scale, int32_t interp,
                              const uint8_t border[4], int32_t clip, uint8_t *dst, size_t dst_cap,
                              int32_t *dst_w, int32_t *dst_h);
+
+/* ---- T1: the hot members of transfer::TransformableMatrix ------------------------ */
+/* TransformableMatrix::scale_self (transfer.rs:66-91): cv::resize to (((w as f64) * scale) as i32,
+ * ((h as f64) * scale) as i32) with INTER_AREA for scale < 1; scale == 1 returns the image unchanged
+ * (the early-out at :67-69).  scale > 1 (INTER_LINEAR enlargement) is not on the hot path -- every
+ * caller shrinks (core/src/main.rs:70, shrink_to) -- and returns OICS_ERR_UNSUPPORTED.  ch = 1 or 3;
+ * dst tightly packed (stride = *dst_w * ch), capacity dst_cap bytes. */
+OICS_API int32_t oics_scale(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                            double scale, uint8_t *dst, size_t dst_cap, int32_t *dst_w, int32_t *dst_h);
+/* TransformableMatrix::shrink_to (transfer.rs:93-126; called by app/src-tauri/src/test.rs:309-317):
+ * scale = min(max_w / w, max_h / h) with a non-positive bound meaning "no bound"; never upscales
+ * (scale >= 1 returns the image unchanged), else scale_self(scale).  *out_scale (nullable) = the scale used. */
+OICS_API int32_t oics_shrink_to(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                                int32_t max_w, int32_t max_h, uint8_t *dst, size_t dst_cap, int32_t *dst_w,
+                                int32_t *dst_h, double *out_scale);
 
 /* ---- N2: the file written at the end of omr::correct_default ---------------- */
 /* TransformableMatrix::im_write(path, ImageFormat::JPEG, quality) (transfer.rs:162-179, called with

@@ -41,6 +41,8 @@ SIGNATURES = {
     "oics_set_stream": (_i32, [_ctx, C.c_void_p]),
     "oics_synchronize": (_i32, [_ctx]),
     "oics_launch_count": (C.c_int64, [_ctx]),
+    "oics_profile": (_i32, [_ctx, _i32]),
+    "oics_profile_report": (_i32, [_ctx, C.c_char_p, _sz, C.POINTER(_sz)]),
     "oics_last_sweep_kernel_ms": (_i32, [_ctx, _dp, _ip]),
     "oics_probe_l2_read": (_i32, [_ctx, _sz, _i32, _dp]),
     "oics_probe_smem_read": (_i32, [_ctx, _i32, _dp]),
@@ -48,6 +50,12 @@ SIGNATURES = {
     "oics_angle_half_range": (_i32, [C.c_uint32, _f64]),
     "oics_sweep_matrices": (_i32, [_i32, _i32, C.c_uint32, _f64, _f64, _dp, _i32, _ip]),
     "oics_shard_range": (_i32, [_i32, _i32, _i32, _ip, _ip]),
+    "oics_shard_layout": (_i32, [_i32, _i32, _ip]),
+    "oics_shard_unpack": (_i32, [_dp, _i32, _i32, _dp, _dp]),
+    "oics_sweep_sharded": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _dp, _i32, _i32, _i32, C.c_void_p, _ip, _ip]),
+    "oics_hough_peaks": (_i32, [_ctx, C.c_void_p, _i32, _i32, _i32, C.c_void_p, _i32, _ip]),
+    "oics_scale": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _f64, _u8p, _sz, _ip, _ip]),
+    "oics_shrink_to": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _i32, _i32, _u8p, _sz, _ip, _ip, _dp]),
     "oics_rotate_geometry": (_i32, [_i32, _i32, _f64, _f64, _i32, _dp, _ip, _ip]),
     "oics_projection_scale": (_f64, [_i32, _i32, _i32, _i32]),
     "oics_preprocess": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _i32, _i32, _f64, _u8p, _sz, _ip, _ip, _dp]),

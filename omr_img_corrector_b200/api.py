@@ -49,6 +49,8 @@ class DeviceImage:
 
 def _describe(img):
     """-> (pointer, w, h, ch, stride, keepalive)"""
+    if hasattr(img, "get_mat") and hasattr(img, "matrix"):       # transfer.TransformableMatrix: the Mat it owns
+        img = img.matrix
     if isinstance(img, DeviceImage):
         return img.ptr, img.w, img.h, img.ch, img.stride, img
     if isinstance(img, np.ndarray):
@@ -68,6 +70,15 @@ def _describe(img):
         ch = 1 if img.dim() == 2 else int(img.shape[2])
         return img.data_ptr(), w, h, ch, w * ch, img
     raise TypeError(f"unsupported image type {type(img)!r}")
+
+
+def _buf_ptr(o) -> int:
+    """Address of an output buffer: numpy (host) or a torch tensor (host or CUDA)."""
+    return o.data_ptr() if hasattr(o, "data_ptr") else o.ctypes.data
+
+
+def _buf_size(o) -> int:
+    return int(o.numel()) if hasattr(o, "numel") else int(o.size)
 
 
 def _dptr(a):
@@ -110,6 +121,20 @@ def rotate_geometry(cols, rows, angle, scale=1.0, clip=CLIP_DEFAULT):
     dw, dh = C.c_int32(), C.c_int32()
     check(_lib.load().oics_rotate_geometry(cols, rows, float(angle), float(scale), clip, _dptr(M), C.byref(dw), C.byref(dh)))
     return M, dw.value, dh.value
+
+
+def shard_layout(n_angles, world) -> int:
+    per = C.c_int32()
+    check(_lib.load().oics_shard_layout(int(n_angles), int(world), C.byref(per)))
+    return per.value
+
+
+def shard_unpack(sd, n_angles, world):
+    """Gathered exchange buffer sd[world][2][per] -> (v_sd[n], h_sd[n])."""
+    sd = np.ascontiguousarray(sd, np.float64)
+    v, h = np.zeros(n_angles, np.float64), np.zeros(n_angles, np.float64)
+    check(_lib.load().oics_shard_unpack(_dptr(sd), int(n_angles), int(world), _dptr(v), _dptr(h)))
+    return v, h
 
 
 def projection_scale(w, h, max_w, max_h) -> float:
@@ -205,6 +230,24 @@ class Context:
     def launch_count(self) -> int:
         return int(self._lib.oics_launch_count(self._h))
 
+    def profile(self, enable=True):
+        """Opt-in per-kernel CUDA-event timing of this context's launches (oics_profile)."""
+        check(self._lib.oics_profile(self._h, 1 if enable else 0))
+
+    def profile_report(self):
+        """-> list of {"kernel", "launches", "ms", "algorithmic_bytes"} since profile(True)."""
+        import json
+        need = C.c_size_t()
+        cap = 1 << 16
+        while True:
+            buf = C.create_string_buffer(cap)
+            rc = self._lib.oics_profile_report(self._h, buf, cap, C.byref(need))
+            if rc == _lib.ERR_CAPACITY:
+                cap = need.value + 64
+                continue
+            check(rc)
+            return json.loads(buf.value.decode())
+
     def last_sweep_kernel_ms(self):
         ms, n = C.c_double(), C.c_int32()
         check(self._lib.oics_last_sweep_kernel_ms(self._h, C.byref(ms), C.byref(n)))
@@ -269,6 +312,22 @@ class Context:
         check(self._lib.oics_projection_sweep_batch(self._h, ptr, n_cards, card_stride, w, h, stride, _dptr(M), n,
                                                     v.ctypes.data, hh.ctypes.data))
         return v, hh
+
+    def sweep_sharded(self, binary, M, rank, world, sd=None):
+        """oics_sweep_sharded (config 5): evaluates this rank's slice of M [n, 6] into its block of the
+        exchange buffer sd[world][2][per] (numpy float64, or a CUDA tensor for an in-place NCCL all-gather).
+        -> (sd, first, count, per)"""
+        p, w, h, ch, stride, keep = _describe(binary)
+        M = np.ascontiguousarray(M, np.float64).reshape(-1, 6)
+        n = len(M)
+        per = shard_layout(n, world)
+        if sd is None:
+            sd = np.zeros((world, 2, per), np.float64)
+        ptr = sd.data_ptr() if hasattr(sd, "data_ptr") else sd.ctypes.data
+        first, count = C.c_int32(), C.c_int32()
+        check(self._lib.oics_sweep_sharded(self._h, p, w, h, stride, _dptr(M), n, int(rank), int(world), C.c_void_p(ptr),
+                                           C.byref(first), C.byref(count)))
+        return sd, first.value, count.value, per
 
     def projection_counts(self, binary, M):
         p, w, h, ch, stride, keep = _describe(binary)
@@ -341,6 +400,26 @@ class Context:
         check(self._lib.oics_hough_accumulate(self._h, p, w, h, stride, rho, theta, acc.ctypes.data))
         return acc
 
+    def hough_peaks(self, accum, threshold) -> np.ndarray:
+        """Local maxima of a standard accumulator [numangle, numrho] in cv::HoughLines' order
+        -> [n, 3] int32 rows {theta index, rho index, count}."""
+        if hasattr(accum, "data_ptr"):
+            ptr, (na, nr) = accum.data_ptr(), accum.shape
+        else:
+            accum = np.ascontiguousarray(accum, np.int32)
+            ptr, (na, nr) = accum.ctypes.data, accum.shape
+        cap = 1 << 12
+        while True:
+            peaks = np.zeros((cap, 3), np.int32)
+            n = C.c_int32()
+            rc = self._lib.oics_hough_peaks(self._h, C.c_void_p(ptr), int(na), int(nr), int(threshold), peaks.ctypes.data,
+                                            cap, C.byref(n))
+            if rc == _lib.ERR_CAPACITY:
+                cap = n.value
+                continue
+            check(rc)
+            return peaks[:n.value].copy()
+
     def hough_lines_p(self, edges, threshold, min_len, max_gap, rho=1.0, theta=math.pi / 180.0) -> np.ndarray:
         p, w, h, ch, stride, keep = _describe(edges)
         cap = 1 << 14
@@ -385,6 +464,30 @@ class Context:
         check(self._lib.oics_rotate(self._h, p, ch, w, h, stride, float(angle), float(scale), flags, b, clip,
                                     out.ctypes.data, out.size, C.byref(rw), C.byref(rh)))
         return out
+
+    # -- T1
+    def scale(self, src, scale):
+        """TransformableMatrix::scale_self (transfer.rs:66-91) -> scaled image."""
+        p, w, h, ch, stride, keep = _describe(src)
+        ow = w if scale == 1.0 else int(float(w) * scale)
+        oh = h if scale == 1.0 else int(float(h) * scale)
+        out = np.empty((max(oh, 1), max(ow, 1)) if ch == 1 else (max(oh, 1), max(ow, 1), ch), np.uint8)
+        rw, rh = C.c_int32(), C.c_int32()
+        check(self._lib.oics_scale(self._h, p, ch, w, h, stride, float(scale), out.ctypes.data, out.size, C.byref(rw),
+                                   C.byref(rh)))
+        return out
+
+    def shrink_to(self, src, max_w, max_h):
+        """TransformableMatrix::shrink_to (transfer.rs:93-126) -> (image, scale used); never upscales."""
+        p, w, h, ch, stride, keep = _describe(src)
+        s = min(1.0, projection_scale(w, h, max_w, max_h))
+        ow = w if s == 1.0 else int(float(w) * s)
+        oh = h if s == 1.0 else int(float(h) * s)
+        out = np.empty((max(oh, 1), max(ow, 1)) if ch == 1 else (max(oh, 1), max(ow, 1), ch), np.uint8)
+        rw, rh, rs = C.c_int32(), C.c_int32(), C.c_double()
+        check(self._lib.oics_shrink_to(self._h, p, ch, w, h, stride, int(max_w), int(max_h), out.ctypes.data, out.size,
+                                       C.byref(rw), C.byref(rh), C.byref(rs)))
+        return out, rs.value
 
     # -- N2: imwrite
     def jpeg_encode(self, bgr, quality=100, out=None) -> bytes:
@@ -467,8 +570,8 @@ class Context:
         sizes = np.zeros((2, n), np.int32)
         dsts = caps = None
         if outs is not None:
-            dsts = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
-            caps = (C.c_size_t * n)(*[o.size for o in outs])
+            dsts = (C.c_void_p * n)(*[_buf_ptr(o) for o in outs])
+            caps = (C.c_size_t * n)(*[_buf_size(o) for o in outs])
         ip = C.POINTER(C.c_int32)
         if jpeg_quality is None:
             check(self._lib.oics_correct_batch(self._h, ptr, n, w * h * 3, w, h, w * 3, int(max_angle), float(step), max_w,
@@ -499,8 +602,8 @@ class Context:
         sizes = np.zeros((2, n), np.int32)
         dsts = caps = None
         if outs is not None:
-            dsts = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
-            caps = (C.c_size_t * n)(*[o.size for o in outs])
+            dsts = (C.c_void_p * n)(*[_buf_ptr(o) for o in outs])
+            caps = (C.c_size_t * n)(*[_buf_size(o) for o in outs])
         ip = C.POINTER(C.c_int32)
         fsz = (C.c_size_t * n)()
         check(self._lib.oics_correct_batch_files(self._h, fptr, flen, n, int(max_angle), float(step), max_w, max_h,

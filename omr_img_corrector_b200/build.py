@@ -73,7 +73,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
                 with open(os.path.join(OBJ, f + ".ptxas.log"), "w") as fh:
                     fh.write(out)
     if force or jobs or _stale(SO, objs):
-        cmd = [nvcc, *ARCH, "-shared", "-cudart", "static", "-o", SO, *objs]
+        cmd = [nvcc, *ARCH, "-shared", "-cudart", "static", "-o", SO, *objs, "-ldl"]
         p = subprocess.run(cmd, capture_output=True, text=True)
         if p.returncode != 0:
             sys.stderr.write(p.stdout + p.stderr)

@@ -96,7 +96,7 @@ OICS_API int32_t oics_preprocess(oics_ctx *ctx, const uint8_t *bgr, int32_t w, i
                                  int32_t mode, int32_t max_w, int32_t max_h, double resize_scale, uint8_t *out_bin,
                                  size_t out_cap, int32_t *out_w, int32_t *out_h, double *out_scale)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(out_bin && out_w && out_h);
@@ -129,7 +129,7 @@ OICS_API int32_t oics_preprocess(oics_ctx *ctx, const uint8_t *bgr, int32_t w, i
 OICS_API int32_t oics_projection_sweep(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
                                        const double *M, int32_t n_angles, double *v_sd, double *h_sd, int64_t *sums)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bin, w, h, stride, 1));
     OICS_ARG(n_angles >= 0 && (n_angles == 0 || (M && v_sd && h_sd)));
@@ -144,7 +144,7 @@ OICS_API int32_t oics_projection_sweep_batch(oics_ctx *ctx, const uint8_t *bins,
                                              int32_t w, int32_t h, int32_t stride, const double *M,
                                              int32_t n_angles, double *v_sd, double *h_sd)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bins, w, h, stride, 1));
     OICS_ARG(n_cards >= 0 && n_angles >= 0);
@@ -167,10 +167,38 @@ OICS_API int32_t oics_projection_sweep_batch(oics_ctx *ctx, const uint8_t *bins,
     return sweep_to(ctx, dsrc, n_cards, dcard, w, h, dstride, M, n_angles, v_sd, h_sd, nullptr, nullptr);
 }
 
+OICS_API int32_t oics_sweep_sharded(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
+                                    const double *M, int32_t n_angles, int32_t rank, int32_t world, double *sd,
+                                    int32_t *first, int32_t *count)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_TRY(check_image(bin, w, h, stride, 1));
+    OICS_ARG(n_angles >= 0 && world > 0 && rank >= 0 && rank < world && (n_angles == 0 || (M && sd)));
+    int32_t f = 0, c = 0, per = 0;
+    OICS_TRY(oics_shard_range(n_angles, rank, world, &f, &c));
+    OICS_TRY(oics_shard_layout(n_angles, world, &per));
+    if (first) *first = f;
+    if (count) *count = c;
+    if (n_angles == 0) return OICS_OK;
+    double *blk = sd + (size_t)rank * 2 * per;   // this rank's block: v_sd slice, then h_sd slice
+    // the padding of the block travels through the all-gather too: define it
+    if (is_device_ptr(sd)) OICS_CUDA_TRY(cudaMemsetAsync(blk, 0, (size_t)2 * per * sizeof(double), ctx->stream));
+    else memset(blk, 0, (size_t)2 * per * sizeof(double));
+    if (c == 0) {
+        OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        return OICS_OK;
+    }
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, bin, (size_t)w, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    return sweep_to(ctx, dsrc, 1, 0, w, h, dstride, M + 6 * (size_t)f, c, blk, blk + per, nullptr, nullptr);
+}
+
 OICS_API int32_t oics_projection_counts(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h, int32_t stride,
                                         const double M[6], int32_t *row_counts, int32_t *col_counts)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bin, w, h, stride, 1));
     OICS_ARG(M && row_counts && col_counts);
@@ -190,7 +218,7 @@ OICS_API int32_t oics_projection_counts(oics_ctx *ctx, const uint8_t *bin, int32
 OICS_API int32_t oics_projection_standard_deviations(oics_ctx *ctx, const uint8_t *bin, int32_t w, int32_t h,
                                                      int32_t stride, double *v_sd, double *h_sd)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bin, w, h, stride, 1));
     OICS_ARG(v_sd && h_sd);
@@ -212,7 +240,7 @@ OICS_API int32_t oics_result_from_projection(oics_ctx *ctx, const uint8_t *bgr, 
                                              int32_t stride, uint16_t max_angle, double step, int32_t max_w,
                                              int32_t max_h, oics_omr_result *result)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(result);
@@ -232,7 +260,7 @@ OICS_API int32_t oics_angle_with_projections(oics_ctx *ctx, const uint8_t *bgr, 
                                              size_t threads, double *angle)
 {
     (void)threads;  // single-thread semantics, see header
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(angle);
@@ -251,7 +279,7 @@ OICS_API int32_t oics_warp_affine(oics_ctx *ctx, const uint8_t *src, int32_t ch,
                                   int32_t stride, const double M[6], int32_t interp, const uint8_t border[4],
                                   uint8_t *dst, int32_t dst_w, int32_t dst_h, int32_t dst_stride)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_ARG(ch >= 1 && ch <= 4);
     OICS_TRY(check_image(src, w, h, stride, ch));
@@ -287,10 +315,60 @@ OICS_API int32_t oics_rotate(oics_ctx *ctx, const uint8_t *src, int32_t ch, int3
     return oics_warp_affine(ctx, src, ch, w, h, stride, M, interp, border, dst, *dst_w, *dst_h, *dst_w * ch);
 }
 
+// T1: TransformableMatrix::scale_self (transfer.rs:66-91)
+OICS_API int32_t oics_scale(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                            double scale, uint8_t *dst, size_t dst_cap, int32_t *dst_w, int32_t *dst_h)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_ARG(ch == 1 || ch == 3);
+    OICS_TRY(check_image(src, w, h, stride, ch));
+    OICS_ARG(dst && dst_w && dst_h);
+    if (scale > 1.0) {
+        set_error("scale_self: enlarging (scale %g, INTER_LINEAR) is outside the accelerated path", scale);
+        return OICS_ERR_UNSUPPORTED;
+    }
+    const int ow = scale == 1.0 ? w : scaled_dim(w, scale), oh = scale == 1.0 ? h : scaled_dim(h, scale);
+    *dst_w = ow;
+    *dst_h = oh;
+    if (ow <= 0 || oh <= 0) { set_error("scaled size %dx%d is empty", ow, oh); return OICS_ERR_INVALID_ARG; }
+    const size_t row = (size_t)ow * ch, need = row * oh;
+    if (need > dst_cap) {
+        set_error("scaled image needs %zu bytes, capacity %zu", need, dst_cap);
+        return OICS_ERR_CAPACITY;
+    }
+    const uint8_t *dsrc;
+    size_t dstride;
+    OICS_TRY(stage_in(ctx, src, (size_t)w * ch, h, (size_t)stride, ctx->in_img, &dsrc, &dstride));
+    if (scale == 1.0) {   // the early-out: the Mat is left as it is
+        OICS_TRY(stage_out(ctx, dsrc, row, oh, dst, row));
+    } else if (is_device_ptr(dst)) {
+        OICS_TRY(resize_area_device(ctx, dsrc, ch, w, h, dstride, dst, ow, oh));
+    } else {
+        OICS_TRY(ctx->out_img.ensure(need));
+        OICS_TRY(resize_area_device(ctx, dsrc, ch, w, h, dstride, ctx->out_img.as<uint8_t>(), ow, oh));
+        OICS_TRY(copy_out(ctx, dst, ctx->out_img.p, need));
+    }
+    OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return OICS_OK;
+}
+
+// T1: TransformableMatrix::shrink_to (transfer.rs:93-126)
+OICS_API int32_t oics_shrink_to(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
+                                int32_t max_w, int32_t max_h, uint8_t *dst, size_t dst_cap, int32_t *dst_w,
+                                int32_t *dst_h, double *out_scale)
+{
+    if (w <= 0 || h <= 0) { set_error("image size %dx%d is empty", w, h); return OICS_ERR_INVALID_ARG; }
+    const double target = oics_projection_scale(w, h, max_w, max_h);   // the same min(max_w / w, max_h / h) rule
+    const double scale = target >= 1.0 ? 1.0 : target;                 // never upscales (transfer.rs:121-125)
+    if (out_scale) *out_scale = scale;
+    return oics_scale(ctx, src, ch, w, h, stride, scale, dst, dst_cap, dst_w, dst_h);
+}
+
 OICS_API int32_t oics_canny(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32_t w, int32_t h, int32_t stride,
                             double lo, double hi, uint8_t *edges, int32_t edges_stride)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_ARG(ch == 1 || ch == 3);
     OICS_TRY(check_image(src, w, h, stride, ch));
@@ -309,7 +387,7 @@ OICS_API int32_t oics_canny(oics_ctx *ctx, const uint8_t *src, int32_t ch, int32
 OICS_API int32_t oics_hough_accumulate(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h, int32_t stride,
                                        double rho, double theta, int32_t *accum)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(edges, w, h, stride, 1));
     OICS_ARG(accum && rho > 0 && theta > 0);
@@ -330,11 +408,40 @@ OICS_API int32_t oics_hough_accumulate(oics_ctx *ctx, const uint8_t *edges, int3
     return OICS_OK;
 }
 
+OICS_API int32_t oics_hough_peaks(oics_ctx *ctx, const int32_t *accum, int32_t numangle, int32_t numrho,
+                                  int32_t threshold, int32_t *peaks, int32_t cap, int32_t *n_peaks)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_ARG(accum && numangle > 0 && numrho > 0 && n_peaks && cap >= 0 && (cap == 0 || peaks));
+    const size_t bytes = (size_t)numangle * numrho * sizeof(int32_t);
+    const int32_t *dacc = accum;
+    if (!is_device_ptr(accum)) {
+        OICS_TRY(ctx->accum.ensure(bytes));
+        OICS_CUDA_TRY(cudaMemcpyAsync(ctx->accum.p, accum, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        dacc = ctx->accum.as<int32_t>();
+    }
+    std::vector<int32_t> found;
+    OICS_TRY(hough_peaks_device(ctx, dacc, numangle, numrho, threshold, &found));
+    const int n = (int)(found.size() / 3);
+    *n_peaks = n;
+    const int ncopy = std::min(n, cap);
+    if (ncopy > 0) {
+        if (is_device_ptr(peaks)) OICS_CUDA_TRY(cudaMemcpy(peaks, found.data(), sizeof(int32_t) * 3 * (size_t)ncopy, cudaMemcpyHostToDevice));
+        else memcpy(peaks, found.data(), sizeof(int32_t) * 3 * (size_t)ncopy);
+    }
+    if (n > cap) {
+        set_error("found %d peaks, capacity %d", n, cap);
+        return OICS_ERR_CAPACITY;
+    }
+    return OICS_OK;
+}
+
 OICS_API int32_t oics_hough_lines_p(oics_ctx *ctx, const uint8_t *edges, int32_t w, int32_t h, int32_t stride,
                                     double rho, double theta, int32_t threshold, double min_line_length,
                                     double max_line_gap, int32_t *lines, int32_t cap, int32_t *n_lines)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(edges, w, h, stride, 1));
     OICS_ARG(n_lines && cap >= 0 && (cap == 0 || lines) && rho > 0 && theta > 0);
@@ -356,7 +463,7 @@ OICS_API int32_t oics_result_from_edges_detection(oics_ctx *ctx, const uint8_t *
                                                   int32_t h, int32_t stride, double min_line_length,
                                                   double max_line_gap, oics_omr_result *result)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_ARG(ch == 1 || ch == 3);
     OICS_TRY(check_image(src, w, h, stride, ch));
@@ -370,7 +477,7 @@ OICS_API int32_t oics_result_from_edges_detection(oics_ctx *ctx, const uint8_t *
 OICS_API int32_t oics_angle_with_hough(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
                                        double min_line_length, double max_line_gap, double *angle)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(gray, w, h, stride, 1));
     OICS_ARG(angle);
@@ -386,7 +493,7 @@ OICS_API int32_t oics_angle_with_hough(oics_ctx *ctx, const uint8_t *gray, int32
 OICS_API int32_t oics_fft_image(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
                                 uint8_t *mag8, uint8_t *log8)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(gray, w, h, stride, 1));
     OICS_ARG(log8);
@@ -406,7 +513,7 @@ OICS_API int32_t oics_angle_with_fft(oics_ctx *ctx, const uint8_t *gray, int32_t
                                      double canny1, double canny2, double min_line_length, double max_line_gap,
                                      double *angle)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(gray, w, h, stride, 1));
     OICS_ARG(angle);
@@ -427,7 +534,7 @@ OICS_API int32_t oics_result_from_fourier_transform(oics_ctx *ctx, const uint8_t
                                                     double min_line_length, double max_line_gap,
                                                     oics_omr_result *result)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(result);
@@ -451,7 +558,7 @@ OICS_API int32_t oics_result_from_fourier_transform(oics_ctx *ctx, const uint8_t
 OICS_API int32_t oics_jpeg_encode(oics_ctx *ctx, const uint8_t *bgr, int32_t w, int32_t h, int32_t stride,
                                   int32_t quality, uint8_t *out, size_t out_cap, size_t *out_size)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(out && out_size);
@@ -486,7 +593,7 @@ OICS_API int32_t oics_jpeg_info(const uint8_t *file, size_t file_size, int32_t *
 OICS_API int32_t oics_jpeg_decode(oics_ctx *ctx, const uint8_t *file, size_t file_size, uint8_t *bgr, size_t stride,
                                   size_t bgr_cap, int32_t *w, int32_t *h)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_ARG(file && bgr && w && h);
     OICS_ARG(!is_device_ptr(file));
@@ -567,7 +674,7 @@ OICS_API int32_t oics_correct_default(oics_ctx *ctx, const uint8_t *bgr, int32_t
                                       size_t dst_cap, int32_t *dst_w, int32_t *dst_h, double *angle,
                                       int32_t *need_check)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_TRY(check_image(bgr, w, h, stride, 3));
     OICS_ARG(angle && need_check);
@@ -594,7 +701,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
 {
     // files != nullptr: the cards arrive as JPEG files in host memory (imread, omr.rs:349) and are decoded
     // on the device, each on its own stream, into the slot the upload would have filled
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     if (!files) OICS_TRY(check_image(bgrs, w, h, stride, 3));
     OICS_ARG(!files || (file_sizes && w > 0 && h > 0));

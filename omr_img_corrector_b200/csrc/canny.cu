@@ -197,12 +197,15 @@ int32_t canny_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, s
     uint8_t *map = ctx->mag.as<uint8_t>();
     OICS_CUDA_TRY(cudaMemsetAsync(qtail, 0, 16, st));
     dim3 grid(cdiv(w, CN_TX), cdiv(h, CN_TY));
-    if (ch == 1)
-        canny_nms_kernel<1><<<grid, 256, 0, st>>>(dsrc, w, h, stride, low, high, map, queue, qtail);
-    else
-        canny_nms_kernel<3><<<grid, 256, 0, st>>>(dsrc, w, h, stride, low, high, map, queue, qtail);
+    {
+        ProfScope ps(ctx, ch == 1 ? "canny_nms_kernel<1>" : "canny_nms_kernel<3>", (double)n * (ch + 1));
+        if (ch == 1)
+            canny_nms_kernel<1><<<grid, 256, 0, st>>>(dsrc, w, h, stride, low, high, map, queue, qtail);
+        else
+            canny_nms_kernel<3><<<grid, 256, 0, st>>>(dsrc, w, h, stride, low, high, map, queue, qtail);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
-    static int blocks_per_sm = 0;
+    int &blocks_per_sm = ctx->canny_blocks_per_sm;   // per context = per device, under ctx->mu
     if (!blocks_per_sm) {
         OICS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, canny_hysteresis_kernel, 256, 0));
         if (blocks_per_sm < 1) {
@@ -213,7 +216,10 @@ int32_t canny_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, s
     }
     int nblocks = ctx->sm_count * blocks_per_sm;
     void *args[] = {(void *)&map, (void *)&w, (void *)&h, (void *)&queue, (void *)&qtail, (void *)&dedges};
-    OICS_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)canny_hysteresis_kernel, dim3(nblocks), dim3(256), args, 0, st));
+    {
+        ProfScope ps(ctx, "canny_hysteresis_kernel", (double)n * 2);
+        OICS_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)canny_hysteresis_kernel, dim3(nblocks), dim3(256), args, 0, st));
+    }
     ctx->launches += 2;
     return OICS_OK;
 }

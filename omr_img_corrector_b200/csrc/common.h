@@ -83,6 +83,21 @@ struct SweepCache {
     size_t general_off = 0, kf_off = 0, fast_off = 0;
 };
 
+// Opt-in per-kernel timing (oics_profile / oics_profile_report): a ProfScope around a launch records two
+// CUDA events on the launching stream, so the figure is the kernel's own device time inside the real
+// pipeline (no profiler attached, no extra synchronisation).  `bytes` = the ALGORITHMIC bytes of that
+// launch, from which the bench derives achieved GB/s per kernel.
+struct ProfEntry {
+    const char *name;
+    cudaEvent_t e0, e1;
+    double bytes;
+};
+struct Profiler {
+    bool on = false;
+    std::vector<ProfEntry> entries;
+    std::vector<cudaEvent_t> pool;
+};
+
 }  // namespace oics
 
 #define OICS_JD_SLOTS 9
@@ -95,6 +110,10 @@ struct oics_ctx {
     int sm_count = 0;
     int smem_optin = 0;
     int64_t launches = 0;
+    // per-device function attributes / occupancy answers this context has already set up (a context is
+    // bound to one device; process-wide statics would leak one device's answer to another)
+    bool attr_sweepw = false, attr_sweeps = false, attr_sweep[5] = {false, false, false, false, false};
+    int canny_blocks_per_sm = 0;
     // sweep timing evidence
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_sweep_ms = 0.0;
@@ -111,6 +130,7 @@ struct oics_ctx {
     size_t jpeg_hdr_len = 0;
     uint8_t jpeg_hdr_host[1024];
     oics::SweepCache sweep_cache;
+    oics::Profiler prof;
 };
 
 namespace oics {
@@ -131,7 +151,19 @@ int32_t copy_in(oics_ctx *ctx, void *ddst, const void *src, size_t bytes);
 struct CtxGuard {
     std::unique_lock<std::mutex> lk;
     int32_t status;
-    explicit CtxGuard(oics_ctx *ctx);
+    bool ranged = false;
+    // `entry` names the C-ABI entry point: an NVTX range (visible in Nsight Systems / ncu --nvtx) spans the call
+    explicit CtxGuard(oics_ctx *ctx, const char *entry = nullptr);
+    ~CtxGuard();
+};
+
+// RAII timing scope around one kernel launch (or a tight group of launches of one kernel).
+struct ProfScope {
+    oics_ctx *ctx;
+    cudaStream_t st;
+    int idx = -1;
+    ProfScope(oics_ctx *ctx, const char *name, double bytes, cudaStream_t stream = nullptr);
+    ~ProfScope();
 };
 
 // ---- host logic (hostlogic.cpp) ----
@@ -151,6 +183,8 @@ int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size
 int32_t preprocess_batch_device(oics_ctx *ctx, const uint8_t *dbgrs, int n_cards, size_t card_stride, int w, int h,
                                 size_t stride, int mode, int ow, int oh, uint8_t *dbins /* n x ow x oh */);
 int32_t gray_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint8_t *dgray);
+int32_t resize_area_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, uint8_t *ddst, int dw,
+                           int dh);
 // canny.cu
 int32_t canny_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, int low, int high,
                      uint8_t *dedges /* tightly packed */);
@@ -161,6 +195,8 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
                              double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
                              int cap, int *n_lines);
 void hough_geometry(int w, int h, double rho, double theta, int *numangle, int *numrho, std::vector<float> *ttab);
+int32_t hough_peaks_device(oics_ctx *ctx, const int32_t *daccum, int numangle, int numrho, int threshold,
+                           std::vector<int32_t> *peaks /* {theta, rho, count} triples, sorted */);
 // fft.cu
 int32_t fft_image_device(oics_ctx *ctx, const uint8_t *dgray, int w, int h, size_t stride, uint8_t *dmag8,
                          uint8_t *dlog8);

@@ -1,4 +1,9 @@
 // Context, error and staging plumbing behind the C ABI (include/oics_cuda.h).
+#include <nvtx3/nvToolsExt.h>
+
+#include <algorithm>
+#include <map>
+
 #include "common.h"
 
 namespace oics {
@@ -73,9 +78,46 @@ bool is_device_ptr(const void *p)
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
-CtxGuard::CtxGuard(oics_ctx *ctx)
+ProfScope::ProfScope(oics_ctx *c, const char *name, double bytes, cudaStream_t stream) : ctx(c), st(stream ? stream : c->stream)
+{
+    if (!ctx->prof.on) return;
+    Profiler &P = ctx->prof;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    for (cudaEvent_t &e : ev) {
+        if (!P.pool.empty()) {
+            e = P.pool.back();
+            P.pool.pop_back();
+        } else if (cudaEventCreate(&e) != cudaSuccess) {
+            cudaGetLastError();
+            return;
+        }
+    }
+    if (cudaEventRecord(ev[0], st) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    idx = (int)P.entries.size();
+    P.entries.push_back({name, ev[0], ev[1], bytes});
+}
+
+ProfScope::~ProfScope()
+{
+    if (idx < 0) return;
+    if (cudaEventRecord(ctx->prof.entries[(size_t)idx].e1, st) != cudaSuccess) cudaGetLastError();
+}
+
+CtxGuard::~CtxGuard()
+{
+    if (ranged) nvtxRangePop();
+}
+
+CtxGuard::CtxGuard(oics_ctx *ctx, const char *entry)
 {
     status = OICS_OK;
+    if (entry) {
+        nvtxRangePushA(entry);
+        ranged = true;
+    }
     if (!ctx) {
         set_error("null context");
         status = OICS_ERR_INVALID_ARG;
@@ -190,6 +232,11 @@ OICS_API void oics_destroy(oics_ctx *ctx)
     ctx->pin_in.release();
     ctx->pin_out.release();
     ctx->pin_small.release();
+    for (ProfEntry &e : ctx->prof.entries) {
+        cudaEventDestroy(e.e0);
+        cudaEventDestroy(e.e1);
+    }
+    for (cudaEvent_t e : ctx->prof.pool) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -198,7 +245,7 @@ OICS_API void oics_destroy(oics_ctx *ctx)
 
 OICS_API int32_t oics_set_stream(oics_ctx *ctx, void *cuda_stream)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
@@ -207,13 +254,66 @@ OICS_API int32_t oics_set_stream(oics_ctx *ctx, void *cuda_stream)
 
 OICS_API int32_t oics_synchronize(oics_ctx *ctx)
 {
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     OICS_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     return OICS_OK;
 }
 
 OICS_API int64_t oics_launch_count(oics_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+OICS_API int32_t oics_profile(oics_ctx *ctx, int32_t enable)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_CUDA_TRY(cudaDeviceSynchronize());
+    for (ProfEntry &e : ctx->prof.entries) {
+        ctx->prof.pool.push_back(e.e0);
+        ctx->prof.pool.push_back(e.e1);
+    }
+    ctx->prof.entries.clear();
+    ctx->prof.on = enable != 0;
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_profile_report(oics_ctx *ctx, char *buf, size_t cap, size_t *needed)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_ARG(needed && (cap == 0 || buf));
+    OICS_CUDA_TRY(cudaDeviceSynchronize());
+    struct Agg { double ms = 0, bytes = 0; long long n = 0; };
+    std::map<std::string, Agg> agg;
+    std::vector<std::string> order;
+    for (const ProfEntry &e : ctx->prof.entries) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, e.e0, e.e1) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        if (!agg.count(e.name)) order.push_back(e.name);
+        Agg &a = agg[e.name];
+        a.ms += t;
+        a.bytes += e.bytes;
+        a.n++;
+    }
+    std::string out = "[";
+    char line[512];
+    for (size_t i = 0; i < order.size(); i++) {
+        const Agg &a = agg[order[i]];
+        snprintf(line, sizeof(line), "%s{\"kernel\": \"%s\", \"launches\": %lld, \"ms\": %.6f, \"algorithmic_bytes\": %.0f}",
+                 i ? ", " : "", order[i].c_str(), a.n, a.ms, a.bytes);
+        out += line;
+    }
+    out += "]";
+    *needed = out.size() + 1;
+    if (cap < out.size() + 1) {
+        set_error("profile report needs %zu bytes, capacity %zu", out.size() + 1, cap);
+        return OICS_ERR_CAPACITY;
+    }
+    memcpy(buf, out.c_str(), out.size() + 1);
+    return OICS_OK;
+}
 
 OICS_API int32_t oics_last_sweep_kernel_ms(oics_ctx *ctx, double *ms, int32_t *launches)
 {

@@ -394,14 +394,26 @@ int32_t fft_image_device(oics_ctx *ctx, const uint8_t *dgray, int w, int h, size
     const size_t smr = (size_t)Pr.m * sizeof(double2), smc = (size_t)Pc.m * sizeof(double2);
     OICS_CUDA_TRY(cudaFuncSetAttribute(fft_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smr, (size_t)1024)));
     OICS_CUDA_TRY(cudaFuncSetAttribute(fft_cols_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smc, (size_t)1024)));
-    fft_rows_kernel<<<h, FFT_THREADS, smr, st>>>(dgray, stride, w, Pr, spec);
+    {
+        ProfScope ps(ctx, "fft_rows_kernel", (double)n * (1 + sizeof(double2)));
+        fft_rows_kernel<<<h, FFT_THREADS, smr, st>>>(dgray, stride, w, Pr, spec);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
-    fft_cols_kernel<<<w, FFT_THREADS, smc, st>>>(spec, w, h, Pc, mag, gmm);
+    {
+        ProfScope ps(ctx, "fft_cols_kernel", (double)n * (sizeof(double2) + 4));
+        fft_cols_kernel<<<w, FFT_THREADS, smc, st>>>(spec, w, h, Pc, mag, gmm);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     const int blocks = ctx->sm_count * 8;
-    fft_log_kernel<<<blocks, 256, 0, st>>>(mag, n, gmm, dmag8, gmm + 2);
+    {
+        ProfScope ps(ctx, "fft_log_kernel", (double)n * 8);
+        fft_log_kernel<<<blocks, 256, 0, st>>>(mag, n, gmm, dmag8, gmm + 2);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
-    fft_log8_kernel<<<blocks, 256, 0, st>>>(mag, n, gmm + 2, dlog8);
+    {
+        ProfScope ps(ctx, "fft_log8_kernel", (double)n * 5);
+        fft_log8_kernel<<<blocks, 256, 0, st>>>(mag, n, gmm + 2, dlog8);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;
     // `init` is a stack temporary consumed by the async copy above

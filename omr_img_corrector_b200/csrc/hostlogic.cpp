@@ -124,6 +124,28 @@ OICS_API int32_t oics_shard_range(int32_t n_angles, int32_t rank, int32_t world,
     return OICS_OK;
 }
 
+OICS_API int32_t oics_shard_layout(int32_t n_angles, int32_t world, int32_t *per_rank)
+{
+    OICS_ARG(n_angles >= 0 && world > 0 && per_rank);
+    *per_rank = (n_angles + world - 1) / world;
+    return OICS_OK;
+}
+
+OICS_API int32_t oics_shard_unpack(const double *sd, int32_t n_angles, int32_t world, double *v_sd, double *h_sd)
+{
+    OICS_ARG(n_angles >= 0 && world > 0 && (n_angles == 0 || (sd && v_sd && h_sd)));
+    const int per = (n_angles + world - 1) / world;
+    for (int r = 0; r < world; r++) {
+        const int f = std::min(n_angles, r * per), c = std::min(per, n_angles - f);
+        const double *blk = sd + (size_t)r * 2 * per;
+        for (int i = 0; i < c; i++) {
+            v_sd[f + i] = blk[i];
+            h_sd[f + i] = blk[per + i];
+        }
+    }
+    return OICS_OK;
+}
+
 OICS_API int32_t oics_rotate_geometry(int32_t cols, int32_t rows, double angle, double scale, int32_t clip,
                                       double M[6], int32_t *dst_w, int32_t *dst_h)
 {
@@ -182,7 +204,13 @@ OICS_API int32_t oics_rule_a(const double *h_sd, const double *v_sd, int32_t N, 
             }
         }
     }
-    if (ties_h == 1 && ties_v == 1 && !most.empty())
+    if (ties_h == 1 && ties_v == 1 && most.empty()) {
+        // no candidate ever became the maximum (N == 0, i.e. max_angle / step < 1): the reference indexes
+        // most_possible_deg_vec[0] and panics (omr.rs:210-211); an error, not a fabricated result
+        set_error("empty angle range: the reference panics on most_possible_deg_vec[0] (omr.rs:211)");
+        return OICS_ERR_INVALID_ARG;
+    }
+    if (ties_h == 1 && ties_v == 1)
         fill_result(result, most[0], OICS_BELIEVED, most);
     else if (most.size() == 1)
         fill_result(result, most[0], OICS_NEED_CHECK, most);

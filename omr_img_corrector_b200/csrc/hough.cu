@@ -205,12 +205,91 @@ int32_t hough_accumulate_device(oics_ctx *ctx, const uint8_t *dedges, int w, int
     // one full wave, no tail: 4 CTAs fit an SM (48 KB histogram each), numangle x slices <= 4 x SMs
     int slices = std::max(1, (4 * ctx->sm_count) / numangle);
     dim3 grid(numangle, slices);
-    hough_accumulate_kernel<<<grid, 256, use_smem ? smem : 0, st>>>(d_pts, d_total, ctx->twid.as<float>(), numrho, slices,
-                                                                    use_smem, daccum);
+    {
+        ProfScope ps(ctx, "hough_accumulate_kernel", (double)w * h + (double)acc_bytes);
+        hough_accumulate_kernel<<<grid, 256, use_smem ? smem : 0, st>>>(d_pts, d_total, ctx->twid.as<float>(), numrho, slices,
+                                                                        use_smem, daccum);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     // ttab is a host temporary: the async copy above must have consumed it
     OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    return OICS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Peak extraction over the standard accumulator: cv::HoughLines' findLocalMaximums rule
+// (count > threshold, > left and upper neighbour, >= right and lower neighbour; outside = 0) followed
+// by its ordering (count descending, then cell index ascending).  One thread per cell, loads coalesced
+// along rho; peaks leave as 64-bit keys (count << 32 | ~cell) through a warp-aggregated append, so the
+// order of the appends does not matter: the host sorts the keys, which are unique.
+__global__ void __launch_bounds__(256) hough_peaks_kernel(const int32_t *__restrict__ accum, int numangle, int numrho,
+                                                          int threshold, unsigned long long *__restrict__ keys,
+                                                          unsigned int cap, unsigned int *__restrict__ count)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x, n = blockIdx.y;
+    bool peak = false;
+    int v = 0;
+    if (r < numrho) {
+        const int32_t *row = accum + (size_t)n * numrho;
+        v = row[r];
+        if (v > threshold) {
+            const int left = r > 0 ? row[r - 1] : 0, right = r + 1 < numrho ? row[r + 1] : 0;
+            const int up = n > 0 ? row[r - numrho] : 0, down = n + 1 < numangle ? row[r + numrho] : 0;
+            peak = v > left && v >= right && v > up && v >= down;
+        }
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, peak);
+    if (!m) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    unsigned int base = 0;
+    if (lane == leader) base = atomicAdd(count, (unsigned int)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (peak) {
+        const unsigned int slot = base + __popc(m & ((1u << lane) - 1u));
+        const uint32_t cell = (uint32_t)n * (uint32_t)numrho + (uint32_t)r;
+        if (slot < cap) keys[slot] = ((unsigned long long)(uint32_t)v << 32) | (uint32_t)~cell;
+    }
+}
+
+int32_t hough_peaks_device(oics_ctx *ctx, const int32_t *daccum, int numangle, int numrho, int threshold,
+                           std::vector<int32_t> *peaks)
+{
+    cudaStream_t st = ctx->stream;
+    const size_t cells = (size_t)numangle * numrho;
+    if (cells == 0 || cells > 0x7fffffffull) {
+        set_error("hough peaks: accumulator of %d x %d cells is not supported", numangle, numrho);
+        return OICS_ERR_INVALID_ARG;
+    }
+    // a peak is strictly greater than its left neighbour: at most every second cell of a row
+    const size_t cap = (size_t)numangle * ((size_t)numrho / 2 + 1);
+    OICS_TRY(ctx->lines.ensure(16 + cap * sizeof(unsigned long long)));
+    unsigned int *d_count = ctx->lines.as<unsigned int>();
+    unsigned long long *d_keys = reinterpret_cast<unsigned long long *>(ctx->lines.as<uint8_t>() + 16);
+    OICS_CUDA_TRY(cudaMemsetAsync(d_count, 0, 16, st));
+    dim3 grid(cdiv(numrho, 256), numangle);
+    {
+        ProfScope ps(ctx, "hough_peaks_kernel", (double)cells * sizeof(int32_t));
+        hough_peaks_kernel<<<grid, 256, 0, st>>>(daccum, numangle, numrho, threshold, d_keys, (unsigned int)cap, d_count);
+    }
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    unsigned int n = 0;
+    OICS_CUDA_TRY(cudaMemcpyAsync(&n, d_count, sizeof(n), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    std::vector<unsigned long long> keys(n);
+    if (n) {
+        OICS_CUDA_TRY(cudaMemcpyAsync(keys.data(), d_keys, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    std::sort(keys.begin(), keys.end(), [](unsigned long long a, unsigned long long b) { return a > b; });
+    peaks->resize((size_t)n * 3);
+    for (unsigned int i = 0; i < n; i++) {
+        const uint32_t cell = ~(uint32_t)(keys[i] & 0xffffffffull);
+        (*peaks)[3 * (size_t)i + 0] = (int32_t)(cell / (uint32_t)numrho);
+        (*peaks)[3 * (size_t)i + 1] = (int32_t)(cell % (uint32_t)numrho);
+        (*peaks)[3 * (size_t)i + 2] = (int32_t)(keys[i] >> 32);
+    }
     return OICS_OK;
 }
 
@@ -692,7 +771,10 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
     A.cap = cap;
     A.n_lines = reinterpret_cast<int *>(base + off_nl);
     A.list = reinterpret_cast<uint32_t *>(base + off_list);
-    ppht_kernel<<<PPHT_C, PPHT_T, 0, st>>>(A);   // one cluster (__cluster_dims__)
+    {
+        ProfScope ps(ctx, "ppht_kernel", 0.0);
+        ppht_kernel<<<PPHT_C, PPHT_T, 0, st>>>(A);   // one cluster (__cluster_dims__)
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     int n = 0;

@@ -645,19 +645,31 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     unsigned long long *cnt = ctx->mag.as<unsigned long long>(), *sums2 = cnt + nchunks;
     uint32_t *words = ctx->cplx2.as<uint32_t>();
     const int strips = cdiv(G.mcux, JD_MCU);
-    jpeg_dct_kernel<<<G.mcuy * strips, JD_T, 0, st>>>(dbgr, stride, G, Q, strips, coef);
-    jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
+    {   // algorithmic bytes: the BGR image in, 16-bit coefficients of the 4:2:0 planes out (1.5 x 2 B per pixel)
+        ProfScope ps(ctx, "jpeg_dct_kernel", 3.0 * w * h + 2.0 * 64 * nb);
+        jpeg_dct_kernel<<<G.mcuy * strips, JD_T, 0, st>>>(dbgr, stride, G, Q, strips, coef);
+    }
+    {
+        ProfScope ps(ctx, "jpeg_bits_kernel", 2.0 * 64 * nb + 8.0 * nb);
+        jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     OICS_TRY(exclusive_scan(ctx, st, bits, nb, sums, d_totals, nullptr));
     jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
-    jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, sums, words);
+    {
+        ProfScope ps(ctx, "jpeg_emit_kernel", 2.0 * 64 * nb + 8.0 * nb);
+        jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, sums, words);
+    }
     jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums2, d_totals + 1, d_totals));
-    jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
-        words, d_totals, cnt, sums2, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
+    {
+        ProfScope ps(ctx, "jpeg_stuff_write_kernel", 0.0);
+        jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
+            words, d_totals, cnt, sums2, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;

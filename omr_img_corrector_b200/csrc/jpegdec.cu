@@ -778,9 +778,11 @@ struct JdecSlot {
 static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
 {
     const unsigned gs = (unsigned)((S.nsub + 127) / 128);
-    for (int r = 1; r <= rounds; r++)
+    for (int r = 1; r <= rounds; r++) {
+        ProfScope ps(ctx, "jdec_sync_kernel<chain>", 0.0, S.st);
         jdec_sync_kernel<<<gs, 128, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used,
                                                 S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags, S.rst, S.nrst);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += rounds;
     S.rounds = rounds;
@@ -857,8 +859,11 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, sums_c, reinterpret_cast<uint8_t *>(words), S.rst, S.nrst);
     // every thread is fed its predecessor's exit state until a round changes nothing; the host looks at
     // the flags after 4 rounds (each launch advances the chain through whole CTAs), then every 8
-    jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
-                                          S.mnb, S.mcnt, 0, S.flags, S.rst, S.nrst);
+    {
+        ProfScope ps(ctx, "jdec_sync_kernel<round0>", (double)slen, st);
+        jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+                                              S.mnb, S.mcnt, 0, S.flags, S.rst, S.nrst);
+    }
     ctx->launches += 3;
     return jdec_rounds(ctx, S, 4);
 }
@@ -892,12 +897,21 @@ static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t st
     const unsigned gs = (unsigned)((S.nsub + 127) / 128);
     int16_t *coef = S.coef.as<int16_t>();
     OICS_TRY(exclusive_scan(ctx, st, S.nblk, S.nsub, S.sums_s, S.removed + 1, nullptr));
-    jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
-                                           S.sums_s, (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
+    {
+        ProfScope ps(ctx, "jdec_write_kernel", (double)S.H.scan_len + 128.0 * (double)S.nblocks, st);
+        jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
+                                               S.sums_s, (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
+    }
     jdec_mcu_dc_kernel<<<(unsigned)((S.nmcu + 255) / 256), 256, 0, st>>>(coef, S.G, S.mcu);
     OICS_TRY(exclusive_scan(ctx, st, S.mcu, S.nmcu, S.sums_m, S.removed + 2, nullptr));
-    jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.sums_m, S.G, S.H.restart, S.planes.as<uint8_t>());
-    jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
+    {
+        ProfScope ps(ctx, "jdec_idct_kernel", (128.0 + 64.0) * (double)S.nblocks, st);
+        jdec_idct_kernel<<<(unsigned)((S.nblocks + 31) / 32), 256, 0, st>>>(S.tables.as<JdecTables>(), coef, S.mcu, S.sums_m, S.G, S.H.restart, S.planes.as<uint8_t>());
+    }
+    {
+        ProfScope ps(ctx, "jdec_color_kernel", 64.0 * (double)S.nblocks + 3.0 * (double)S.H.w * (double)S.H.h, st);
+        jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
+    }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;
     return OICS_OK;

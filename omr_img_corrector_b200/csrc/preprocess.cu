@@ -301,12 +301,14 @@ static int32_t launch_gray_erode(oics_ctx *ctx, const uint8_t *dbgr, int w, int 
 {
     if ((radius == 0 || radius == 3) && do_threshold) {
         dim3 grid(cdiv(w, GB_TW), cdiv(h, GB_TH), n_cards);
+        ProfScope ps(ctx, radius == 3 ? "gray_erode_bits_kernel<3>" : "gray_erode_bits_kernel<0>", 4.0 * w * h * n_cards);
         if (radius == 3) gray_erode_bits_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, dst, dst_card, dstride);
         else gray_erode_bits_kernel<0><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, dst, dst_card, dstride);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;
     } else if (radius == 0 || radius == 3) {
         dim3 grid(cdiv(w, GF_TW), cdiv(h, GF_TH), n_cards);
+        ProfScope ps(ctx, radius == 3 ? "gray_erode_fast_kernel<3>" : "gray_erode_fast_kernel<0>", 4.0 * w * h * n_cards);
         if (radius == 3)
             gray_erode_fast_kernel<3><<<grid, 256, 0, ctx->stream>>>(dbgr, src_card, w, h, stride, do_threshold, dst, dst_card, dstride);
         else
@@ -415,6 +417,7 @@ static int32_t launch_resize(oics_ctx *ctx, const uint8_t *src, int ch, int w, i
     const int fast = fabs(sx - ix) < 2.220446049250313e-16 && fabs(sy - iy) < 2.220446049250313e-16;
     const float inv_area = 1.f / (float)(ix * iy);
     dim3 grid(cdiv(dw, 256), dh);
+    ProfScope ps(ctx, ch == 1 ? "resize_area_kernel<1>" : "resize_area_kernel<3>", (double)ch * ((double)w * h + (double)dw * dh));
     if (ch == 1)
         resize_area_kernel<1><<<grid, 256, 0, ctx->stream>>>(src, w, h, stride, dst, dw, dh, (size_t)dw, sx, sy, fast, ix,
                                                              iy, inv_area, do_threshold);
@@ -424,6 +427,13 @@ static int32_t launch_resize(oics_ctx *ctx, const uint8_t *src, int ch, int w, i
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;
+}
+
+// cv::resize(INTER_AREA) of a 1- or 3-channel image (TransformableMatrix::scale_self, transfer.rs:66-91)
+int32_t resize_area_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, uint8_t *ddst, int dw,
+                           int dh)
+{
+    return launch_resize(ctx, dsrc, ch, w, h, stride, ddst, dw, dh, 0);
 }
 
 int32_t gray_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, uint8_t *dgray)

@@ -63,7 +63,7 @@ extern "C" {
 OICS_API int32_t oics_probe_l2_read(oics_ctx *ctx, size_t bytes, int32_t reps, double *gb_per_s)
 {
     OICS_ARG(ctx && gb_per_s && reps > 0 && reps <= 4096);
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     const int threads = 256, grid = ctx->sm_count * 8;
     const size_t quantum = (size_t)4 * threads * grid * sizeof(uint4);
@@ -93,7 +93,7 @@ OICS_API int32_t oics_probe_l2_read(oics_ctx *ctx, size_t bytes, int32_t reps, d
 OICS_API int32_t oics_probe_smem_read(oics_ctx *ctx, int32_t iters, double *gb_per_s)
 {
     OICS_ARG(ctx && gb_per_s && iters > 0 && iters <= (1 << 20));
-    CtxGuard g(ctx);
+    CtxGuard g(ctx, __func__);
     if (g.status) return g.status;
     const int threads = 256, grid = ctx->sm_count * 3, smem = 65536;
     OICS_TRY(ctx->misc.ensure(256));

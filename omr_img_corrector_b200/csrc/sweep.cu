@@ -34,8 +34,10 @@ static constexpr int SW_GROUP = 32;  // rows per warp pass
 __global__ void sweep_tables_kernel(const double *__restrict__ Minv, int w, int h, int wpad, int hpad,
                                     int *__restrict__ ad, int *__restrict__ bd, int2 *__restrict__ xy)
 {
-    const int a = blockIdx.y;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    // 1-D grid: angle-major (2N can exceed the 65535 limit of grid.y: N = (max_angle / step) as u16)
+    const int nbx = (max(wpad, hpad) + blockDim.x - 1) / blockDim.x;
+    const int a = blockIdx.x / nbx;
+    const int i = (blockIdx.x - a * nbx) * blockDim.x + threadIdx.x;
     const double *M = Minv + 6 * (size_t)a;
     if (i < wpad) {
         // adelta[x] = saturate_cast<int>(M[0]*x*AB_SCALE): (M0*x) rounded, then *1024 (exact).
@@ -384,13 +386,12 @@ static int pick_cpl(int w)
 }
 
 template <int CPL>
-static cudaError_t launch_sweep(const SweepArgs &A, dim3 grid, size_t smem, cudaStream_t st)
+static cudaError_t launch_sweep(oics_ctx *ctx, const SweepArgs &A, dim3 grid, size_t smem, cudaStream_t st)
 {
-    static bool attr_set = false;
-    if (!attr_set || smem > 48 * 1024) {
+    if (!ctx->attr_sweep[CPL]) {   // per context = per device
         cudaError_t e = cudaFuncSetAttribute(sweep_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        ctx->attr_sweep[CPL] = true;
     }
     sweep_kernel<CPL><<<grid, SW_THREADS, smem, st>>>(A);
     return cudaGetLastError();
@@ -423,7 +424,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const size_t plan_per_angle = (size_t)wj * h * sizeof(uint2);
     const long long plan_budget_angles = std::max<long long>(1, (long long)(((size_t)3 << 30) / plan_per_angle));
     int cards_per_chunk, angles_per_chunk;
-    if (chunk_items >= n_angles && n_angles <= plan_budget_angles) {
+    if (chunk_items >= n_angles && n_angles <= plan_budget_angles && n_angles <= 65535) {
         angles_per_chunk = n_angles;
         cards_per_chunk = (int)std::min<long long>(n_cards, chunk_items / n_angles);
         cards_per_chunk = std::max(1, std::min(cards_per_chunk, 65535 / n_angles));
@@ -450,7 +451,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     SweepTables T;
     T.ad = ad; T.bd = bd; T.xy = xy; T.wpad = wpad; T.hpad = hpad;
     if (!same_geometry) {
-        dim3 grid(cdiv(max(wpad, hpad), 256), n_angles);
+        const unsigned grid = (unsigned)cdiv(max(wpad, hpad), 256) * (unsigned)n_angles;
         sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;
@@ -581,6 +582,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
             packed_first = c0;
             packed_n = std::min(cards_per_pack, n_cards - c0);
             dim3 g(cdiv(wp, 128), h, packed_n);
+            ProfScope ps(ctx, "pack_bits_kernel", (double)packed_n * ((double)w * h + (double)h * wp * 4));
             pack_bits_kernel<<<g, 128, 0, st>>>(dbins + (size_t)packed_first * card_stride, card_stride, stride, w, h, wp,
                                                 ctx->bits.as<uint32_t>(), packed_n);
             OICS_CUDA_TRY(cudaGetLastError());
@@ -620,9 +622,10 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                     A.bits = bits_base;
                     A.I = I;
                     dim3 grid(tiles_x * tiles_y, (unsigned)(nc * I.n_list));
-                    cudaError_t le = CPL == 2 ? launch_sweep<2>(A, grid, smem, st)
-                                     : CPL == 3 ? launch_sweep<3>(A, grid, smem, st)
-                                                : launch_sweep<4>(A, grid, smem, st);
+                    ProfScope ps(ctx, "sweep_kernel<general>", (double)nc * I.n_list * (double)w * h);
+                    cudaError_t le = CPL == 2 ? launch_sweep<2>(ctx, A, grid, smem, st)
+                                     : CPL == 3 ? launch_sweep<3>(ctx, A, grid, smem, st)
+                                                : launch_sweep<4>(ctx, A, grid, smem, st);
                     OICS_CUDA_TRY(le);
                     ctx->launches++;
                     ctx->last_sweep_launches++;
@@ -642,6 +645,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                     G.alist = d_fast;
                     G.groups = reinterpret_cast<const int4 *>(d_err + cache.groups_off) + g_lo;
                     G.n_groups = g_hi - g_lo;
+                    G.n_angles = f_hi - f_lo;
                     G.a0 = a0;
                     G.na_chunk = na;
                     G.card0 = c0;
@@ -651,8 +655,11 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
             }
             OICS_CUDA_TRY(cudaEventRecord(e1, st));
             const size_t item0 = (size_t)c0 * n_angles + a0;
-            sweep_finalize_kernel<<<(unsigned)(nc * na), 64, 0, st>>>(ctx->counts.as<int>(), w, h, (long long)item0, d_vsd,
-                                                                     d_hsd, reinterpret_cast<long long *>(d_sums));
+            {
+                ProfScope ps(ctx, "sweep_finalize_kernel", (double)nc * na * per_item);
+                sweep_finalize_kernel<<<(unsigned)(nc * na), 64, 0, st>>>(ctx->counts.as<int>(), w, h, (long long)item0, d_vsd,
+                                                                         d_hsd, reinterpret_cast<long long *>(d_sums));
+            }
             OICS_CUDA_TRY(cudaGetLastError());
             ctx->launches++;
             if (d_counts_out && c0 == 0)

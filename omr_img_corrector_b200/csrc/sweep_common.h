@@ -69,6 +69,7 @@ struct SweepWGroups {
     const int *alist;       // fast angle list (device)
     const int4 *groups;     // {first index into alist, count, class (source rows per word), -} (device)
     int n_groups;
+    int n_angles;           // candidate angles these groups hold (profiling: algorithmic bytes)
     int a0, na_chunk, card0;
 };
 

@@ -41,7 +41,8 @@ namespace oics {
 __global__ void __launch_bounds__(32) sweepw_meta_kernel(SweepTables T, int w, int wj, uint32_t *__restrict__ meta,
                                                          SweepWClass *__restrict__ cls)
 {
-    const int j = blockIdx.x, ang = blockIdx.y, lane = threadIdx.x;
+    // 1-D grid, angle-major (the angle count may exceed the 65535 limit of grid.y)
+    const int ang = blockIdx.x / wj, j = blockIdx.x - ang * wj, lane = threadIdx.x;
     const int x = 32 * j + lane;  // < wpad: the tables are filled beyond w
     const bool valid = x < w;
     const int a = T.ad[(size_t)ang * T.wpad + x], b = T.bd[(size_t)ang * T.wpad + x];
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(1024) sweepw_planes_kernel(SweepTables T, cons
 {
     __shared__ int sfg[32], sfh[32];
     __shared__ uint32_t tabC[1024], tabD[1024];
-    const int j = blockIdx.x, k = blockIdx.y, tid = threadIdx.x;
+    const int k = blockIdx.x / wj, j = blockIdx.x - k * wj, tid = threadIdx.x;
     const int ang = fast_angles[k];
     const uint32_t *m = meta + ((size_t)ang * wj + j) * SWW_META;
     const uint32_t s1 = m[11];
@@ -120,7 +121,7 @@ int32_t sweepw_classify(oics_ctx *ctx, const SweepTables &T, int n_angles, int w
 {
     const int wj = cdiv(w, 32);
     OICS_CUDA_TRY(cudaMemsetAsync(d_cls, 0, (size_t)n_angles * sizeof(SweepWClass), ctx->stream));
-    sweepw_meta_kernel<<<dim3(wj, n_angles), 32, 0, ctx->stream>>>(T, w, wj, d_meta, d_cls);
+    sweepw_meta_kernel<<<(unsigned)wj * (unsigned)n_angles, 32, 0, ctx->stream>>>(T, w, wj, d_meta, d_cls);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;
@@ -131,7 +132,8 @@ int32_t sweepw_build_planes(oics_ctx *ctx, const SweepTables &T, const uint32_t 
 {
     if (n_fast <= 0) return OICS_OK;
     const int wj = cdiv(w, 32);
-    sweepw_planes_kernel<<<dim3(wj, n_fast), 1024, 0, ctx->stream>>>(T, d_meta, d_fast_angles, h, wj, d_planes);
+    ProfScope ps(ctx, "sweepw_planes_kernel", (double)n_fast * wj * h * sizeof(uint2));
+    sweepw_planes_kernel<<<(unsigned)wj * (unsigned)n_fast, 1024, 0, ctx->stream>>>(T, d_meta, d_fast_angles, h, wj, d_planes);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;
@@ -474,10 +476,9 @@ int32_t sweepw_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_word
                       const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts)
 {
     if (G.n_groups <= 0 || n_cards <= 0) return OICS_OK;
-    static bool attr = false;
-    if (!attr) {
+    if (!ctx->attr_sweepw) {   // per context = per device (a process-wide flag would skip the opt-in on a second GPU)
         OICS_CUDA_TRY(cudaFuncSetAttribute(sweepw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWW_SMEM));
-        attr = true;
+        ctx->attr_sweepw = true;
     }
     SweepWArgs A;
     A.bits = bits;
@@ -488,6 +489,7 @@ int32_t sweepw_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_word
     A.tiles_x = cdiv(A.wj, SWW_TJ);
     A.n_cards = n_cards;
     dim3 grid(A.tiles_x * cdiv(h, SWW_TH), (unsigned)(n_cards * G.n_groups));
+    ProfScope ps(ctx, "sweepw_kernel", (double)n_cards * G.n_angles * (double)w * h);   // 1 B per (angle, pixel) sample
     sweepw_kernel<<<grid, 256, SWW_SMEM, ctx->stream>>>(A);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;

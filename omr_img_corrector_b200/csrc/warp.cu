@@ -233,6 +233,7 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
 #define OICS_WARPF(CH, LIN)                                                                                          \
     warp_flat_kernel<CH, LIN><<<blocks, 256, 0, st>>>(s32, w, h, (uint32_t)sstride, d32, (uint32_t)dw, (uint32_t)dh, \
                                                       (uint32_t)npix, ab, xy, bcol, last_word)
+        ProfScope ps(ctx, lin ? "warp_flat_kernel<LINEAR>" : "warp_flat_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix));
         if (ch == 1) { if (lin) OICS_WARPF(1, true); else OICS_WARPF(1, false); }
         else if (ch == 3) { if (lin) OICS_WARPF(3, true); else OICS_WARPF(3, false); }
         else { if (lin) OICS_WARPF(4, true); else OICS_WARPF(4, false); }
@@ -242,6 +243,7 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
         dim3 grid(cdiv(cdiv(dw, 4), 256), dh);
 #define OICS_WARP(CH, LIN) \
     warp_kernel<CH, LIN><<<grid, 256, 0, st>>>(dsrc, w, h, sstride, ddst, dw, dh, dstride, ab, xy, bv, aligned)
+        ProfScope ps(ctx, lin ? "warp_kernel<LINEAR>" : "warp_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix));
         if (ch == 1) { if (lin) OICS_WARP(1, true); else OICS_WARP(1, false); }
         else if (ch == 3) { if (lin) OICS_WARP(3, true); else OICS_WARP(3, false); }
         else { if (lin) OICS_WARP(4, true); else OICS_WARP(4, false); }

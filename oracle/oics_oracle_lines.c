@@ -141,6 +141,47 @@ ORC_API void orc_hough_accumulate(const uint8_t *edges, int w, int h, int stride
     free(g.ttab);
 }
 
+/* Peak extraction of cv::HoughLines (HoughLinesStandard: findLocalMaximums + sort by hough_cmp_gt) over a
+ * given accumulator accum[numangle][numrho]: OpenCV keeps a zero frame around the accumulator, so
+ * neighbours outside it read 0.  A cell is kept when
+ *     accum > threshold && accum > left && accum >= right && accum > up && accum >= down
+ * (left/right = rho -/+ 1, up/down = theta -/+ 1); cells are ordered by count descending, ties by cell
+ * index ascending.  peaks: up to cap x 3 int32 {theta index, rho index, count}; returns the number found.
+ * Not called by the reference (it uses hough_lines_p, hough.rs:31-42); it is the CPU definition of the
+ * north star's "extracts peaks".  Pinned against cv2.HoughLines in tests/test_oracle_vs_cv2.py. */
+typedef struct { int32_t cnt; int32_t cell; } orc_peak;
+static int orc_peak_cmp(const void *a, const void *b)
+{
+    const orc_peak *p = (const orc_peak *)a, *q = (const orc_peak *)b;
+    if (p->cnt != q->cnt) return p->cnt > q->cnt ? -1 : 1;
+    return p->cell < q->cell ? -1 : p->cell > q->cell;
+}
+ORC_API int orc_hough_peaks(const int32_t *accum, int numangle, int numrho, int threshold, int32_t *peaks, int cap)
+{
+    orc_peak *list = (orc_peak *)malloc(sizeof(orc_peak) * ((size_t)numangle * numrho / 2 + numangle + 1));
+    int n = 0;
+    for (int a = 0; a < numangle; a++)
+        for (int r = 0; r < numrho; r++) {
+            const int32_t *row = accum + (size_t)a * numrho;
+            const int v = row[r];
+            const int left = r > 0 ? row[r - 1] : 0, right = r + 1 < numrho ? row[r + 1] : 0;
+            const int up = a > 0 ? row[r - numrho] : 0, down = a + 1 < numangle ? row[r + numrho] : 0;
+            if (v > threshold && v > left && v >= right && v > up && v >= down) {
+                list[n].cnt = v;
+                list[n].cell = a * numrho + r;
+                n++;
+            }
+        }
+    qsort(list, (size_t)n, sizeof(orc_peak), orc_peak_cmp);
+    for (int i = 0; i < n && i < cap; i++) {
+        peaks[3 * i + 0] = list[i].cell / numrho;
+        peaks[3 * i + 1] = list[i].cell % numrho;
+        peaks[3 * i + 2] = list[i].cnt;
+    }
+    free(list);
+    return n;
+}
+
 /* H2: cv::HoughLinesP(edges, rho, theta, threshold, minLineLength, maxLineGap)
  * = HoughLinesProbabilistic, as called at hough.rs:31-42, omr.rs:245-253
  * (threshold 0) and fft.rs:183-191 (threshold 100).  Sequential, RNG-ordered

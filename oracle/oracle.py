@@ -286,6 +286,38 @@ def hough_accumulate(edges, rho=1.0, theta=math.pi / 180.0):
     return acc
 
 
+def hough_peaks(accum, threshold):
+    """cv::HoughLines' local-maximum rule + ordering over accum [numangle, numrho]
+    -> int32 [n, 3] {theta index, rho index, count}."""
+    accum = np.ascontiguousarray(accum, np.int32)
+    na, nr = accum.shape
+    cap = 1 << 12
+    while True:
+        peaks = np.zeros((cap, 3), np.int32)
+        n = lib().orc_hough_peaks(_p(accum, C.c_int32), na, nr, int(threshold), _p(peaks, C.c_int32), cap)
+        if n <= cap:
+            return peaks[:n].copy()
+        cap = n
+
+
+def scale_self(img, scale):
+    """TransformableMatrix::scale_self (transfer.rs:66-91), shrinking side only."""
+    if scale == 1.0:
+        return img
+    assert scale < 1.0, "INTER_LINEAR enlargement is outside the restated path"
+    h, w = img.shape[:2]
+    return resize_area(img, int(float(w) * scale), int(float(h) * scale))
+
+
+def shrink_to(img, max_w, max_h):
+    """TransformableMatrix::shrink_to (transfer.rs:93-126) -> (image, scale used)."""
+    h, w = img.shape[:2]
+    s = projection_scale(w, h, max_w, max_h)
+    if s >= 1.0:
+        return img, 1.0
+    return scale_self(img, s), s
+
+
 def hough_lines_p(edges, threshold, min_len, max_gap, rho=1.0, theta=math.pi / 180.0):
     """cv::HoughLinesP (hough.rs:31-42, omr.rs:245-253, fft.rs:183-191) -> int32 [n,4]."""
     edges, w, h, ch = _img(edges)

@@ -236,3 +236,42 @@ def test_task_events_follow_the_reference_vocabulary():
         i0 = next(i for i, (e, p) in enumerate(events) if e == "start_running_task" and p["task_id"] == tid)
         i1 = next(i for i, (e, p) in enumerate(events) if e == "task_completed" and p["task_id"] == tid)
         assert i0 < i1
+
+
+def test_shard_layout_and_unpack():
+    """Config 5's gather layout sd[world][2][per] (oics_shard_layout / oics_shard_unpack)."""
+    from omr_img_corrector_b200 import sharded
+    for n, world in [(9000, 8), (9000, 7), (5, 8), (1, 1), (0, 3), (300, 2)]:
+        per = api.shard_layout(n, world)
+        assert per == (n + world - 1) // world
+        sd = np.zeros((world, 2, max(per, 1)))[:, :, :per]
+        sd = np.ascontiguousarray(sd)
+        v0, h0 = np.arange(n, dtype=np.float64), -np.arange(n, dtype=np.float64) - 0.5
+        for r in range(world):
+            f, c = sharded.shard_range(n, r, world)
+            sd[r, 0, :c] = v0[f:f + c]
+            sd[r, 1, :c] = h0[f:f + c]
+        v, h = api.shard_unpack(sd, n, world)
+        assert np.array_equal(v, v0) and np.array_equal(h, h0)
+
+
+def test_rule_a_empty_range_mirrors_the_panic():
+    """omr.rs:210-211: with N == 0 the reference indexes an empty Vec and panics."""
+    import pytest
+    with pytest.raises(api.OicsError) as e:
+        api.rule_a(np.zeros(0), np.zeros(0), 0, 0.2)
+    assert e.value.code == -1
+
+
+def test_transformable_matrix_host_members():
+    """transfer::TransformableMatrix (transfer.rs:16-277): construction, deep copies, accessors (no device)."""
+    from omr_img_corrector_b200 import transfer
+    img = np.arange(24, dtype=np.uint8).reshape(2, 4, 3)
+    tm = transfer.TransformableMatrix.from_matrix(img)
+    img[0, 0, 0] = 99
+    assert tm.get_mat()[0, 0, 0] == 0                                  # from_matrix deep-copies (transfer.rs:55-59)
+    c = tm.clone()
+    c.matrix[0, 0, 0] = 7
+    assert tm.get_mat()[0, 0, 0] == 0 and tm.get_bytes() == bytes(range(24))
+    assert tm.scale_self(1.0) is tm                                    # the early-out of transfer.rs:67-69
+    assert transfer.TransformableMatrix.default().get_mat().size == 0

@@ -283,3 +283,63 @@ def test_jpeg_decode_exif_orientation(orc):
     assert cv2.imdecode(np.frombuffer(turned, np.uint8), cv2.IMREAD_COLOR).shape[:2] == (40, 24)   # cv2 does rotate
     with pytest.raises(ValueError):
         orc.jpeg_decode(turned)
+
+
+def _standard_accumulator(edges, rho=1.0, theta=math.pi / 180.0):
+    """cv::HoughLinesStandard's stage 1 restated in numpy: its trig table accumulates the angle in
+    float32 (createTrigTable), unlike HoughLinesP's (float)(n * theta)."""
+    h, w = edges.shape
+    numangle = int(math.floor(math.pi / np.float32(theta))) + 1
+    if numangle > 1 and abs(math.pi - (numangle - 1) * float(np.float32(theta))) < float(np.float32(theta)) / 2:
+        numangle -= 1
+    numrho = int(round(((w + h) * 2 + 1) / rho))
+    irho = np.float32(1.0) / np.float32(rho)
+    ang = np.float32(0.0)
+    tab_sin, tab_cos = np.zeros(numangle, np.float32), np.zeros(numangle, np.float32)
+    for n in range(numangle):
+        tab_sin[n] = np.float32(math.sin(float(ang)) * float(irho))
+        tab_cos[n] = np.float32(math.cos(float(ang)) * float(irho))
+        ang = np.float32(ang + np.float32(theta))
+    ys, xs = np.nonzero(edges)
+    acc = np.zeros((numangle, numrho), np.int32)
+    for n in range(numangle):
+        v = xs.astype(np.float32) * tab_cos[n] + ys.astype(np.float32) * tab_sin[n]
+        r = np.rint(v).astype(np.int64) + (numrho - 1) // 2
+        np.add.at(acc[n], r, 1)
+    return acc, numangle, numrho
+
+
+@pytest.mark.parametrize("threshold", [40, 80, 150])
+def test_hough_peaks_match_cv2_hough_lines(orc, threshold):
+    """Pins the peak-extraction oracle (local-maximum rule + ordering) to cv2.HoughLines: the same
+    accumulator (restated above with HoughLinesStandard's own trig table) must yield cv2's line list,
+    in cv2's order."""
+    rng = np.random.default_rng(5)
+    img = np.zeros((240, 320), np.uint8)
+    cv2.line(img, (10, 20), (300, 200), 255, 1)
+    cv2.line(img, (20, 220), (310, 30), 255, 1)
+    cv2.line(img, (160, 0), (160, 239), 255, 1)
+    cv2.line(img, (0, 120), (319, 121), 255, 1)
+    img[rng.random(img.shape) < 0.01] = 255
+    ref = cv2.HoughLines(img, 1.0, math.pi / 180.0, threshold)
+    ref = np.zeros((0, 2), np.float32) if ref is None else ref.reshape(-1, 2)
+    acc, numangle, numrho = _standard_accumulator(img)
+    peaks = orc.hough_peaks(acc, threshold)
+    got = np.stack([(peaks[:, 1].astype(np.float32) - np.float32((numrho - 1) * 0.5)) * np.float32(1.0),
+                    (peaks[:, 0].astype(np.float32) * np.float32(math.pi / 180.0))], axis=1).astype(np.float32)
+    assert len(got) == len(ref) and len(ref) > 0
+    assert np.array_equal(got, ref)
+
+
+def test_scale_self_and_shrink_to_match_cv2(orc, small_card):
+    """T1: TransformableMatrix::scale_self / shrink_to (transfer.rs:66-126) = cv::resize(INTER_AREA)."""
+    bgr, _ = small_card
+    h, w = bgr.shape[:2]
+    for s in [0.2, 0.5, 0.37]:
+        ref = cv2.resize(bgr, (int(w * s), int(h * s)), fx=s, fy=s, interpolation=cv2.INTER_AREA)
+        assert np.array_equal(orc.scale_self(bgr, s), ref)
+    out, s = orc.shrink_to(bgr, 248, 230)
+    assert s == min(248 / w, 230 / h)
+    assert np.array_equal(out, cv2.resize(bgr, (int(w * s), int(h * s)), fx=s, fy=s, interpolation=cv2.INTER_AREA))
+    same, s1 = orc.shrink_to(bgr, 0, 5000)
+    assert s1 == 1.0 and same is bgr                       # never upscales
