@@ -590,6 +590,17 @@ def run_configs(args, ctx, api, sharded, synth, orc, timed, torch, dist, dev, ra
         if orc is not None:
             o2 = orc.get_result_from_edges_detection(bgr, 125.0, 15.0)
             c2["oracle_equal"] = bool((o2.angle, o2.status, o2.candidates) == (r2.angle, r2.status, r2.candidates))
+        # the same with 32 cards in flight (one thread-block cluster per card in one PPHT launch): the reference's
+        # thread-pool concurrency (thread_pool.rs:41-73) for this estimator
+        nb2 = args.hough_batch
+        if nb2 > 0:
+            d32 = d_bgr[None].repeat(nb2, 1, 1, 1).contiguous()
+            ctx.result_from_edges_detection_batch(d32, 125.0, 15.0)
+            tb, rb = ev_time(lambda: ctx.result_from_edges_detection_batch(d32, 125.0, 15.0))
+            c2["batch"] = {"cards_in_flight": nb2, "seconds": tb, "cards_per_s": nb2 / tb,
+                           "equal_to_single_call": bool(all(float(x) == r2.angle for x in rb[0]) and
+                                                        all(int(x) == r2.status for x in rb[1]) and not rb[2].any())}
+            del d32
         out["c2_hough"] = c2
         # config 3: FFT dominant-line deskew (fft.rs:145-256) of the gray card
         d_gray = torch.from_numpy(np.ascontiguousarray(bgr[:, :, 0])).to(dev)     # the card is gray-in-BGR
@@ -606,13 +617,19 @@ def run_configs(args, ctx, api, sharded, synth, orc, timed, torch, dist, dev, ra
         del d_bgr, d_gray
 
         # the reference's shipped operating point (lib.rs:92-97): 1240x1150 cards, +-45 deg at 0.2 deg, shrink to 248x230
+        # skews spread over the test's own range (lib.rs:151-152: -45 .. 45 deg), so the Hough fallback of
+        # omr.rs:366-403 is exercised at its natural rate
         P = DEFAULT_OP
-        nd, ncards = 8, args.default_op_cards
+        nd, ncards = 32, args.default_op_cards
         small, sk = [], []
+        rng = np.random.default_rng(20261105)
+        bases = []
+        for i in range(8):
+            g, _ = synth.base_card(1000 + i)
+            bases.append(synth.to_bgr(np.ascontiguousarray(g[200:1350, 100:1340])))
         for i in range(nd):
-            g, a_i = synth.base_card(1000 + i)
-            s_bgr = synth.to_bgr(np.ascontiguousarray(g[200:1350, 100:1340]))
-            small.append(ctx.rotate_mat(s_bgr, -a_i, 1.0, api.INTER_LINEAR, api.WHITE, api.CLIP_DEFAULT))
+            a_i = round(float(rng.uniform(-44.0, 44.0)), 1)
+            small.append(ctx.rotate_mat(bases[i % 8], -a_i, 1.0, api.INTER_LINEAR, api.WHITE, api.CLIP_DEFAULT))
             sk.append(a_i)
         h_in = torch.empty((ncards, 1150, 1240, 3), dtype=torch.uint8).pin_memory()
         for i in range(ncards):
@@ -631,11 +648,14 @@ def run_configs(args, ctx, api, sharded, synth, orc, timed, torch, dist, dev, ra
         dop = {"params": list(P), "cards": ncards, "card_size": [1240, 1150],
                "host_cards_per_s": ncards / t_h, "device_resident_cards_per_s": ncards / t_d,
                "need_check": int(np.sum(rd_[1])), "errors": int(np.sum(rd_[2] != 0)),
+               "within_0.4_deg_of_skew": int(sum(1 for i in range(ncards) if abs(float(rd_[0][i]) - sk[i % nd]) <= 0.4 + 1e-9)),
+               "skews": "32 distinct cards, skews uniform in [-44, 44] deg (the reference test sweeps -45 .. 45)",
                "what": "oics_correct_batch at the reference's default parameters; host = pinned BGR in / deskewed BGR out, "
                        "device_resident = cards and outputs in HBM"}
         if orc is not None:
             eq = 0
-            for i in range(nd):
+            chk = list(range(0, nd, 4))
+            for i in chk:
                 oa, oneed, oimg = orc.correct_default(small[i], *P)
                 dw, dh = int(rh_[3][i][0]), int(rh_[3][i][1])
                 same = (oa == float(rh_[0][i]) and bool(oneed) == bool(rh_[1][i]) and oimg.shape == (dh, dw, 3)
@@ -643,7 +663,7 @@ def run_configs(args, ctx, api, sharded, synth, orc, timed, torch, dist, dev, ra
                         and float(rd_[0][i]) == oa)
                 eq += int(same)
             dop["oracle_equal"] = eq
-            dop["oracle_checked"] = nd
+            dop["oracle_checked"] = len(chk)
         out["default_op"] = dop
         del h_in, h_out, d_in, d_out
 
@@ -700,6 +720,7 @@ def main():
     ap.add_argument("--oracle-cards", dest="oracle_cards", type=int, default=2,
                     help="distinct cards whose 300 std-dev pairs are compared with the oracle (rank 0, untimed)")
     ap.add_argument("--default-op-cards", dest="default_op_cards", type=int, default=128)
+    ap.add_argument("--hough-batch", dest="hough_batch", type=int, default=32, help="A4 cards in flight in the config-2 batch line (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the configs 2 / 3 / 5 / default-op block")
     ap.add_argument("--no-config5", action="store_true")

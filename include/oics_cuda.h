@@ -204,6 +204,15 @@ OICS_API int32_t oics_result_from_edges_detection(oics_ctx *ctx, const uint8_t *
                                                   int32_t w, int32_t h, int32_t stride,
                                                   double min_line_length, double max_line_gap,
                                                   oics_omr_result *result);
+/* The same for n equally sized cards `card_stride` bytes apart (host or device) IN FLIGHT TOGETHER: the
+ * reference runs one OS thread per card (thread_pool.rs:41-73); here the cards' Canny passes are followed by
+ * ONE HoughLinesP launch with a thread-block cluster per card.  Per card: the angle, the ResultStatus
+ * (OICS_BELIEVED / NEED_CHECK / NOT_A_RESULT) and statuses[i] = OICS_OK or that card's error (e.g.
+ * OICS_ERR_NO_LINES where the reference panics).  Results are identical to n single calls. */
+OICS_API int32_t oics_result_from_edges_detection_batch(oics_ctx *ctx, const uint8_t *srcs, int32_t n_cards,
+                                                        size_t card_stride, int32_t ch, int32_t w, int32_t h,
+                                                        int32_t stride, double min_line_length, double max_line_gap,
+                                                        double *angles, int32_t *result_statuses, int32_t *statuses);
 /* hough::get_angle_with_hough (hough.rs:17-23) without the debug image. */
 OICS_API int32_t oics_angle_with_hough(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h,
                                        int32_t stride, double min_line_length, double max_line_gap,

@@ -69,6 +69,7 @@ SIGNATURES = {
     "oics_result_from_projection": (_i32, [_ctx, _u8p, _i32, _i32, _i32, C.c_uint16, _f64, _i32, _i32, C.POINTER(OmrResultC)]),
     "oics_angle_with_projections": (_i32, [_ctx, _u8p, _i32, _i32, _i32, C.c_uint16, _f64, _f64, _sz, _dp]),
     "oics_result_from_edges_detection": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _i32, _f64, _f64, C.POINTER(OmrResultC)]),
+    "oics_result_from_edges_detection_batch": (_i32, [_ctx, _u8p, _i32, _sz, _i32, _i32, _i32, _i32, _f64, _f64, _dp, _ip, _ip]),
     "oics_angle_with_hough": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _f64, _f64, _dp]),
     "oics_angle_with_fft": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _f64, _f64, _f64, _f64, _dp]),
     "oics_result_from_fourier_transform": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _f64, _f64, _f64, _f64, C.POINTER(OmrResultC)]),

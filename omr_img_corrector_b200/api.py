@@ -365,6 +365,25 @@ class Context:
                                                          C.byref(r)))
         return _unpack(r, buf)
 
+    def result_from_edges_detection_batch(self, imgs, min_len, max_gap):
+        """omr::get_result_from_edges_detection for n equally sized cards in flight together
+        (numpy [n, h, w(, 3)] or a CUDA tensor of that shape) -> (angles, result statuses, error statuses)."""
+        if isinstance(imgs, np.ndarray):
+            imgs = np.ascontiguousarray(imgs, np.uint8)
+            ptr = imgs.ctypes.data
+        else:
+            ptr = imgs.data_ptr()
+        n, h, w = int(imgs.shape[0]), int(imgs.shape[1]), int(imgs.shape[2])
+        ch = 1 if len(imgs.shape) == 3 else int(imgs.shape[3])
+        angles = np.zeros(n, np.float64)
+        rstat = np.zeros(n, np.int32)
+        stat = np.zeros(n, np.int32)
+        ip = C.POINTER(C.c_int32)
+        check(self._lib.oics_result_from_edges_detection_batch(self._h, ptr, n, w * h * ch, ch, w, h, w * ch, float(min_len),
+                                                               float(max_gap), _dptr(angles), rstat.ctypes.data_as(ip),
+                                                               stat.ctypes.data_as(ip)))
+        return angles, rstat, stat
+
     def angle_with_hough(self, gray, min_len, max_gap) -> float:
         p, w, h, ch, stride, keep = _describe(gray)
         a = C.c_double()

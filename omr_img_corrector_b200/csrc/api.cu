@@ -67,6 +67,33 @@ static int32_t estimate_projection(oics_ctx *ctx, const uint8_t *dbgr, int w, in
                     h_sd->data(), nullptr, nullptr);
 }
 
+// Canny -> HoughLinesP -> segment-angle rule for n equally sized device images AT ONCE (the reference runs one
+// OS thread per card, thread_pool.rs:41-73: here the cards' PPHTs run as one launch, a cluster per card).
+// results[i] = {angle, status, n_candidates} (no candidate list), statuses[i] = OICS_OK or that image's error.
+static int32_t edges_results_batch(oics_ctx *ctx, const uint8_t *const *dsrcs, int n, int ch, int w, int h, size_t stride,
+                                   double lo, double hi, int threshold, double min_len, double max_gap, int variant,
+                                   std::vector<oics_omr_result> *results, std::vector<int32_t> *statuses)
+{
+    results->assign((size_t)n, oics_omr_result{0, 0, 0, nullptr, 0});
+    statuses->assign((size_t)n, OICS_OK);
+    if (n <= 0) return OICS_OK;
+    const size_t npx = (size_t)w * h;
+    OICS_TRY(ctx->edges.ensure((size_t)n * npx));
+    if (lo > hi) std::swap(lo, hi);
+    std::vector<const uint8_t *> edges((size_t)n);
+    for (int i = 0; i < n; i++) {
+        edges[(size_t)i] = ctx->edges.as<uint8_t>() + (size_t)i * npx;
+        OICS_TRY(canny_device(ctx, dsrcs[i], ch, w, h, stride, (int)std::floor(lo), (int)std::floor(hi),
+                              ctx->edges.as<uint8_t>() + (size_t)i * npx));
+    }
+    std::vector<std::vector<int32_t>> lines;
+    OICS_TRY(hough_lines_p_batch_device(ctx, edges.data(), n, w, h, (size_t)w, 1.0, 3.14159265358979323846 / 180.0, threshold,
+                                        (int)std::lrint(min_len), (int)std::lrint(max_gap), &lines));
+    for (int i = 0; i < n; i++)
+        (*statuses)[(size_t)i] = oics_lines_angle(lines[(size_t)i].data(), (int)(lines[(size_t)i].size() / 4), variant, &(*results)[(size_t)i]);
+    return OICS_OK;
+}
+
 static int32_t edges_result(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t stride, double lo,
                             double hi, int threshold, double min_len, double max_gap, int variant,
                             oics_omr_result *result)
@@ -74,16 +101,11 @@ static int32_t edges_result(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, i
     OICS_TRY(ctx->edges.ensure((size_t)w * h));
     if (lo > hi) std::swap(lo, hi);
     OICS_TRY(canny_device(ctx, dsrc, ch, w, h, stride, (int)std::floor(lo), (int)std::floor(hi), ctx->edges.as<uint8_t>()));
-    std::vector<int32_t> lines;
-    int cap = 1 << 14, n = 0;
-    for (;;) {
-        lines.resize((size_t)cap * 4);
-        OICS_TRY(hough_lines_p_device(ctx, ctx->edges.as<uint8_t>(), w, h, (size_t)w, 1.0, 3.14159265358979323846 / 180.0,
-                                      threshold, (int)std::lrint(min_len), (int)std::lrint(max_gap), lines.data(), cap, &n));
-        if (n <= cap) break;
-        cap = n;
-    }
-    return oics_lines_angle(lines.data(), n, variant, result);
+    std::vector<std::vector<int32_t>> lines;
+    const uint8_t *e = ctx->edges.as<uint8_t>();
+    OICS_TRY(hough_lines_p_batch_device(ctx, &e, 1, w, h, (size_t)w, 1.0, 3.14159265358979323846 / 180.0, threshold,
+                                        (int)std::lrint(min_len), (int)std::lrint(max_gap), &lines));
+    return oics_lines_angle(lines[0].data(), (int)(lines[0].size() / 4), variant, result);
 }
 
 }  // namespace oics
@@ -474,6 +496,52 @@ OICS_API int32_t oics_result_from_edges_detection(oics_ctx *ctx, const uint8_t *
     return edges_result(ctx, dsrc, ch, w, h, dstride, 50.0, 150.0, 0, min_line_length, max_line_gap, OICS_LINES_OMR, result);
 }
 
+OICS_API int32_t oics_result_from_edges_detection_batch(oics_ctx *ctx, const uint8_t *srcs, int32_t n_cards,
+                                                        size_t card_stride, int32_t ch, int32_t w, int32_t h,
+                                                        int32_t stride, double min_line_length, double max_line_gap,
+                                                        double *angles, int32_t *result_statuses, int32_t *statuses)
+{
+    CtxGuard g(ctx, __func__);
+    if (g.status) return g.status;
+    OICS_ARG(ch == 1 || ch == 3);
+    OICS_ARG(n_cards >= 0 && angles && result_statuses && statuses);
+    if (n_cards == 0) return OICS_OK;
+    OICS_TRY(check_image(srcs, w, h, stride, ch));
+    OICS_ARG(card_stride >= (size_t)stride * (size_t)h);
+    const size_t row = (size_t)w * ch, card_bytes = row * h;
+    const bool dev_in = is_device_ptr(srcs);
+    // cards in flight: bounded by the per-card Hough scratch (7 B per pixel + the accumulator)
+    const size_t per_card = (size_t)w * h * 7 + (size_t)180 * ((size_t)(w + h) * 2 + 1) * 4 + card_bytes;
+    const int chunk = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)3 << 30) / per_card));
+    for (int c0 = 0; c0 < n_cards; c0 += chunk) {
+        const int nb = std::min(chunk, n_cards - c0);
+        std::vector<const uint8_t *> ptrs((size_t)nb);
+        size_t dstride = (size_t)stride;
+        if (dev_in) {
+            for (int i = 0; i < nb; i++) ptrs[(size_t)i] = srcs + (size_t)(c0 + i) * card_stride;
+        } else {
+            OICS_TRY(ctx->in_img.ensure((size_t)nb * card_bytes));
+            for (int i = 0; i < nb; i++) {
+                OICS_CUDA_TRY(cudaMemcpy2DAsync(ctx->in_img.as<uint8_t>() + (size_t)i * card_bytes, row,
+                                                srcs + (size_t)(c0 + i) * card_stride, (size_t)stride, row, (size_t)h,
+                                                cudaMemcpyHostToDevice, ctx->stream));
+                ptrs[(size_t)i] = ctx->in_img.as<uint8_t>() + (size_t)i * card_bytes;
+            }
+            dstride = row;
+        }
+        std::vector<oics_omr_result> res;
+        std::vector<int32_t> sts;
+        OICS_TRY(edges_results_batch(ctx, ptrs.data(), nb, ch, w, h, dstride, 50.0, 150.0, 0, min_line_length, max_line_gap,
+                                     OICS_LINES_OMR, &res, &sts));
+        for (int i = 0; i < nb; i++) {
+            angles[c0 + i] = res[(size_t)i].angle;
+            result_statuses[c0 + i] = res[(size_t)i].status;
+            statuses[c0 + i] = sts[(size_t)i];
+        }
+    }
+    return OICS_OK;
+}
+
 OICS_API int32_t oics_angle_with_hough(oics_ctx *ctx, const uint8_t *gray, int32_t w, int32_t h, int32_t stride,
                                        double min_line_length, double max_line_gap, double *angle)
 {
@@ -712,7 +780,11 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     if (n_cards == 0) return OICS_OK;
     const bool dev_in = !files && is_device_ptr(bgrs);
     const size_t row = (size_t)w * 3, card_bytes = row * h;
-    const int B = std::min<int>(n_cards, 8);    // cards per sub-batch
+    // cards per sub-batch: 8 A4 cards (209 MB) amortise the per-sub-batch host round trip (rule A needs the
+    // std-devs on the host); small cards get proportionally more, up to 64 (the file path decodes at most 8
+    // files at a time, one stream each)
+    const int B_target = files ? 8 : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
+    const int B = std::min<int>(n_cards, B_target);
     std::vector<int32_t> file_status((size_t)n_cards, OICS_OK);
     const int n_sub = cdiv(n_cards, B);
     cudaStream_t st = ctx->stream, up = nullptr, down = nullptr;
@@ -734,8 +806,20 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     bool host_out = false;
     if (dsts)
         for (int c = 0; c < n_cards; c++) host_out = host_out || (dsts[c] && !is_device_ptr(dsts[c]));
-    if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_totals.ensure((size_t)B * 2 * sizeof(unsigned long long)));
+    // Cards whose projection estimate is not Believed wait in a device-side queue: their Canny + HoughLinesP
+    // fallbacks (omr.rs:366-403) run TOGETHER, one thread-block cluster per card in one launch, when the queue
+    // is full or the batch ends -- the reference's concurrency (one OS thread per card, thread_pool.rs:41-73)
+    // instead of one 20-100 ms sequential transform stalling every sub-batch.
+    const size_t hough_per_card = (size_t)w * h * 7 + (size_t)180 * ((size_t)(w + h) * 2 + 1) * 4;
+    const int FQ = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)3 << 30) / (hough_per_card + card_bytes + out_card_cap)));
+    if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_totals.ensure((size_t)std::max(B, FQ) * 2 * sizeof(unsigned long long)));
     if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_raw.ensure(out_card_cap));   // the deskewed pixels of the card being encoded
+    struct Deferred {
+        int c;
+        oics_omr_result p;
+        std::vector<double> cand;
+    };
+    std::vector<Deferred> queue;
 
     int32_t rc = OICS_OK;
     auto cleanup = [&]() {
@@ -810,6 +894,100 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
 
     std::vector<double> v((size_t)B * std::max(1, 2 * N)), hh((size_t)B * std::max(1, 2 * N)), cand((size_t)std::max(1, 2 * N));
     const uint8_t white[4] = {255, 255, 255, 0};
+    // the queued fallbacks: Canny on every card, ONE PPHT launch (a cluster per card), reconcile (omr.rs:352-403),
+    // then the final warp (+ encode) of each and its copy to the caller
+    auto flush_fallbacks = [&]() -> int32_t {
+        const int nq = (int)queue.size();
+        if (nq == 0) return OICS_OK;
+        std::vector<const uint8_t *> srcs((size_t)nq);
+        for (int i = 0; i < nq; i++) srcs[(size_t)i] = ctx->fb_in.as<uint8_t>() + (size_t)i * card_bytes;
+        std::vector<oics_omr_result> er;
+        std::vector<int32_t> es;
+        OICS_TRY(edges_results_batch(ctx, srcs.data(), nq, 3, w, h, row, 50.0, 150.0, 0, hough_min_line_length, hough_max_line_gap,
+                                     OICS_LINES_OMR, &er, &es));
+        bool any_host = false;
+        if (dsts)
+            for (int i = 0; i < nq; i++) any_host = any_host || (dsts[queue[(size_t)i].c] && !is_device_ptr(dsts[queue[(size_t)i].c]));
+        if (any_host) OICS_TRY(ctx->fb_out.ensure((size_t)FQ * out_card_cap));
+        std::vector<size_t> obytes((size_t)nq, 0), jcap((size_t)nq, 0);
+        size_t jhdr = 0;
+        for (int i = 0; i < nq; i++) {
+            Deferred &d = queue[(size_t)i];
+            const int c = d.c;
+            int32_t stc = es[(size_t)i];
+            double a = 0.0;
+            int32_t need = 0;
+            if (stc == OICS_OK) {
+                d.p.candidates = d.cand.empty() ? nullptr : d.cand.data();
+                d.p.cap = (int32_t)d.cand.size();
+                stc = oics_reconcile(&d.p, er[(size_t)i].angle, &a, &need);
+            }
+            double Mw[6];
+            int dw = 0, dh = 0;
+            if (stc == OICS_OK) stc = oics_rotate_geometry(w, h, a, 1.0, OICS_CLIP_CONTAIN, Mw, &dw, &dh);
+            angles[c] = a;
+            need_checks[c] = need;
+            if (dst_ws) dst_ws[c] = dw;
+            if (dst_hs) dst_hs[c] = dh;
+            uint8_t *dst = dsts ? dsts[c] : nullptr;
+            const size_t need_bytes = (size_t)dw * 3 * dh;
+            if (stc == OICS_OK && dst) {
+                const bool ddev = is_device_ptr(dst);
+                uint8_t *area = ddev ? dst : ctx->fb_out.as<uint8_t>() + (size_t)i * out_card_cap;
+                const size_t area_cap = ddev ? dst_caps[c] : std::min(out_card_cap, dst_caps[c]);
+                if (jpeg_quality) {
+                    if (need_bytes > out_card_cap) {
+                        set_error("internal: CONTAIN bound %zu < %zu", out_card_cap, need_bytes);
+                        stc = OICS_ERR_CAPACITY;
+                    } else {
+                        stc = warp_device(ctx, srcs[(size_t)i], 3, w, h, row, Mw, OICS_INTER_NEAREST, white, ctx->jpeg_raw.as<uint8_t>(), dw, dh,
+                                          (size_t)dw * 3);
+                        if (stc == OICS_OK)
+                            stc = jpeg_encode_enqueue(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality, area, area_cap,
+                                                      ctx->jpeg_totals.as<unsigned long long>() + 2 * i, &jhdr);
+                        if (stc == OICS_OK) jcap[(size_t)i] = area_cap;
+                    }
+                } else {
+                    if (dst_sizes) dst_sizes[c] = need_bytes;
+                    if (need_bytes > dst_caps[c] || need_bytes > (ddev ? need_bytes : out_card_cap)) {
+                        set_error("deskewed card needs %zu bytes, capacity %zu", need_bytes, dst_caps[c]);
+                        stc = OICS_ERR_CAPACITY;
+                    } else {
+                        stc = warp_device(ctx, srcs[(size_t)i], 3, w, h, row, Mw, OICS_INTER_NEAREST, white, area, dw, dh, (size_t)dw * 3);
+                        if (stc == OICS_OK && !ddev) obytes[(size_t)i] = need_bytes;
+                    }
+                }
+            }
+            statuses[c] = stc;
+            if (stc == OICS_ERR_CUDA) return OICS_ERR_CUDA;
+        }
+        if (jpeg_quality && dsts) {
+            std::vector<unsigned long long> totals((size_t)2 * nq, 0ull);
+            OICS_CUDA_TRY(cudaMemcpyAsync(totals.data(), ctx->jpeg_totals.p, totals.size() * sizeof(unsigned long long),
+                                          cudaMemcpyDeviceToHost, st));
+            OICS_CUDA_TRY(cudaStreamSynchronize(st));
+            for (int i = 0; i < nq; i++) {
+                if (!jcap[(size_t)i]) continue;
+                const int c = queue[(size_t)i].c;
+                const size_t fsz = jpeg_file_size(jhdr, &totals[(size_t)2 * i]);
+                dst_sizes[c] = fsz;
+                if (fsz > jcap[(size_t)i]) {
+                    set_error("jpeg: the file needs %zu bytes, capacity %zu", fsz, jcap[(size_t)i]);
+                    statuses[c] = OICS_ERR_CAPACITY;
+                } else if (!is_device_ptr(dsts[c])) {
+                    obytes[(size_t)i] = fsz;
+                }
+            }
+        }
+        for (int i = 0; i < nq; i++)
+            if (obytes[(size_t)i])
+                OICS_CUDA_TRY(cudaMemcpyAsync(dsts[queue[(size_t)i].c], ctx->fb_out.as<uint8_t>() + (size_t)i * out_card_cap, obytes[(size_t)i],
+                                              cudaMemcpyDeviceToHost, st));
+        // fb_in / fb_out are reused by the next flush: everything above must have drained
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        queue.clear();
+        return OICS_OK;
+    };
     for (int k = 0; k < n_sub && rc == OICS_OK; k++) {
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
         const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
@@ -843,10 +1021,22 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                 if (p.status == OICS_BELIEVED) {
                     a = p.angle;
                 } else {
-                    oics_omr_result e = {0, 0, 0, nullptr, 0};   // omr.rs:366: Canny runs on the 3-channel source
-                    stc = edges_result(ctx, card, 3, w, h, dstride, 50.0, 150.0, 0, hough_min_line_length,
-                                       hough_max_line_gap, OICS_LINES_OMR, &e);
-                    if (stc == OICS_OK) stc = oics_reconcile(&p, e.angle, &a, &need);
+                    // omr.rs:366: the fallback needs the 3-channel source; keep a copy (the input slot is recycled)
+                    const int slot = (int)queue.size();
+                    OICS_BATCH_TRY(ctx->fb_in.ensure((size_t)FQ * card_bytes));
+                    OICS_BATCH_CUDA(cudaMemcpy2DAsync(ctx->fb_in.as<uint8_t>() + (size_t)slot * card_bytes, row, card, dstride, row,
+                                                      (size_t)h, cudaMemcpyDeviceToDevice, st));
+                    Deferred d;
+                    d.c = c;
+                    d.cand.assign(cand.begin(), cand.begin() + std::min<size_t>(cand.size(), (size_t)std::max(0, p.n_candidates)));
+                    d.p = p;
+                    queue.push_back(std::move(d));
+                    statuses[c] = OICS_OK;
+                    angles[c] = 0.0;
+                    need_checks[c] = 0;
+                    if (dst_sizes) dst_sizes[c] = 0;
+                    if ((int)queue.size() == FQ) OICS_BATCH_TRY(flush_fallbacks());
+                    continue;
                 }
             }
             double Mw[6];
@@ -941,6 +1131,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             OICS_BATCH_CUDA(cudaEventRecord(out_free[s], down));
         }
     }
+    if (rc == OICS_OK) OICS_BATCH_TRY(flush_fallbacks());
     cleanup();
 #undef OICS_BATCH_TRY
 #undef OICS_BATCH_CUDA

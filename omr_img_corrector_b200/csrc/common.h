@@ -70,6 +70,8 @@ struct SweepCache {
     int w = 0, h = 0;
     std::vector<double> inv;        // inverse matrices the tables were built from
     int plan_a0 = -1, plan_a1 = -1; // angle range the word-kernel planes cover
+    bool small = false;             // geometry served by the small-card kernel (sweeps.cu): boxes instead of classes
+    bool boxes_ready = false;
     int angles_per_chunk = 0;
     // classification (meta kernel verdicts) and the launch lists derived from it
     std::vector<int> general;       // angles the general kernel takes
@@ -124,6 +126,7 @@ struct oics_ctx {
     oics::PinnedBuf pin_in, pin_out, pin_small;
     oics::FftPlan fft_row, fft_col;
     oics::DevBuf wplanes, wmeta, wlists, jpeg_raw, jpeg_hdr, jpeg_totals;
+    oics::DevBuf fb_in, fb_out;   // batch driver: cards waiting for the batched Hough fallback, and their outputs
     void *jd_slots[OICS_JD_SLOTS] = {};   // jpegdec.cu: decodes in flight (slot 0 = ctx->stream, the others own a stream)
     // jpeg.cu: the file header of the last quality used (host copy and its device cache)
     int jpeg_hdr_quality = 0, jpeg_hdr_sof = 0;
@@ -194,6 +197,9 @@ int32_t hough_accumulate_device(oics_ctx *ctx, const uint8_t *dedges, int w, int
 int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
                              double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
                              int cap, int *n_lines);
+int32_t hough_lines_p_batch_device(oics_ctx *ctx, const uint8_t *const *dedges, int n_img, int w, int h, size_t stride,
+                                   double rho, double theta, int threshold, int line_length, int line_gap,
+                                   std::vector<std::vector<int32_t>> *lines_out);
 void hough_geometry(int w, int h, double rho, double theta, int *numangle, int *numrho, std::vector<float> *ttab);
 int32_t hough_peaks_device(oics_ctx *ctx, const int32_t *daccum, int numangle, int numrho, int threshold,
                            std::vector<int32_t> *peaks /* {theta, rho, count} triples, sorted */);

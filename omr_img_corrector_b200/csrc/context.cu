@@ -221,7 +221,8 @@ OICS_API void oics_destroy(oics_ctx *ctx)
                       &ctx->bin,    &ctx->bits,    &ctx->mats,    &ctx->tabs,  &ctx->counts, &ctx->sd,
                       &ctx->sums,   &ctx->edges,   &ctx->mag,     &ctx->dxy,   &ctx->labels, &ctx->accum,
                       &ctx->lines,  &ctx->misc,    &ctx->cplx,    &ctx->cplx2, &ctx->twid,   &ctx->fmag,
-                      &ctx->wplanes, &ctx->wmeta,  &ctx->wlists, &ctx->jpeg_raw, &ctx->jpeg_hdr, &ctx->jpeg_totals};
+                      &ctx->wplanes, &ctx->wmeta,  &ctx->wlists, &ctx->jpeg_raw, &ctx->jpeg_hdr, &ctx->jpeg_totals,
+                      &ctx->fb_in,  &ctx->fb_out};
     for (DevBuf *b : bufs) b->release();
     jpeg_decode_release(ctx);
     for (FftPlan *pl : {&ctx->fft_row, &ctx->fft_col}) {

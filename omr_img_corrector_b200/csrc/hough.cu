@@ -23,7 +23,9 @@
 //        * a commit clears the step range and, for accepted segments, un-votes its live pixels.
 //      Latency-bound per image (like the CPU), throughput comes from images in flight.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <thread>
 
 #include <cooperative_groups.h>
 
@@ -376,10 +378,16 @@ __device__ __forceinline__ unsigned long long ppht_key(int bv, int bn)   // larg
     return ((unsigned long long)(uint32_t)(bv + 0x40000000) << 32) | (uint32_t)(0x7fffffff - bn);
 }
 
-__global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_kernel(const PphtArgs A)
+__global__ void __cluster_dims__(PPHT_C, 1, 1) __launch_bounds__(PPHT_T) ppht_kernel(const PphtArgs *__restrict__ images)
 {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
+    // one cluster per image of the batch (images in flight = the reference's one thread per card,
+    // thread_pool.rs:41-73); the image's arguments are staged in shared memory once
+    __shared__ PphtArgs sArgs;
+    if (threadIdx.x == 0) sArgs = images[blockIdx.x / PPHT_C];
+    __syncthreads();
+    const PphtArgs &A = sArgs;
     __shared__ unsigned long long sKey[2][PPHT_C][PPHT_K];   // [group parity][source CTA][point] arg-max keys
     __shared__ unsigned long long sPart[PPHT_W][PPHT_K];     // [warp][point] partial keys of this CTA
     __shared__ int sRes[PPHT_K][2];                          // [point] last accepted step forwards / backwards
@@ -700,11 +708,22 @@ static void ppht_order(int n, int *order, int *arr)
     }
 }
 
-int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
-                             double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
-                             int cap, int *n_lines)
+// cv::HoughLinesP for a BATCH of equally sized edge maps, all images in flight at once: per image the ordered
+// edge compaction, then ONE host round trip for the point counts (the visiting orders are expanded on host
+// threads meanwhile -- they depend on the counts only), one gather per image and ONE launch of ppht_kernel
+// with a cluster per image.  lines_out[i] receives image i's segments (x0, y0, x1, y1 each).
+static int32_t hough_lines_p_batch_once(oics_ctx *ctx, const uint8_t *const *dedges, int n_img, int w, int h, size_t stride,
+                                        double rho, double theta, int threshold, int line_length, int line_gap, int cap,
+                                        std::vector<std::vector<int32_t>> *lines_out, int *max_found)
 {
     cudaStream_t st = ctx->stream;
+    *max_found = 0;
+    lines_out->assign((size_t)n_img, std::vector<int32_t>());
+    if (n_img <= 0) return OICS_OK;
+    if (w > 32767 || h > 32767) {
+        set_error("hough: image larger than 32767 px per side is not supported");
+        return OICS_ERR_UNSUPPORTED;
+    }
     int numangle, numrho;
     std::vector<float> ttab;
     hough_geometry(w, h, rho, theta, &numangle, &numrho, &ttab);
@@ -724,70 +743,146 @@ int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h,
         }
         dirs[4 * n] = xflag; dirs[4 * n + 1] = dx0; dirs[4 * n + 2] = dy0; dirs[4 * n + 3] = 0;
     }
-    int *d_total;
-    uint32_t *d_pts;
-    uint8_t *d_mask;
-    OICS_TRY(compact_edges(ctx, dedges, w, h, stride, true, &d_total, &d_pts, &d_mask));
-    int npts = 0;
-    OICS_CUDA_TRY(cudaMemcpyAsync(&npts, d_total, sizeof(int), cudaMemcpyDeviceToHost, st));
-    OICS_CUDA_TRY(cudaStreamSynchronize(st));
-    *n_lines = 0;
-    if (npts == 0) return OICS_OK;
-
-    // the order is expanded in pinned memory the context keeps (no page faults, asynchronous upload);
-    // the stream is idle here, so nothing else is reading pin_small
-    OICS_TRY(ctx->pin_small.ensure(2 * sizeof(int) * (size_t)npts));
-    int *order = ctx->pin_small.as<int>();
-    ppht_order(npts, order, order + npts);
-    const size_t acc_bytes = (size_t)numangle * numrho * sizeof(int32_t);
-    OICS_TRY(ctx->accum.ensure(acc_bytes));
-    // misc: [order npts][seq npts][ttab][dirs][n_lines][lines cap*4]
-    const size_t off_seq = sizeof(int) * (size_t)npts;
-    const size_t off_ttab = (off_seq + sizeof(uint32_t) * (size_t)npts + 15) & ~(size_t)15;
-    const size_t off_dirs = (off_ttab + sizeof(float) * ttab.size() + 15) & ~(size_t)15;   // int4 loads
-    const size_t off_nl = off_dirs + sizeof(int) * dirs.size();
-    const size_t off_lines = off_nl + 16;
-    const int dcap = std::max(cap, 1);
-    const size_t off_list = off_lines + sizeof(int32_t) * 4 * (size_t)dcap;
-    OICS_TRY(ctx->misc.ensure(off_list + sizeof(uint32_t) * (2 * (size_t)std::max(w, h) + 2)));
-    uint8_t *base = ctx->misc.as<uint8_t>();
-    OICS_CUDA_TRY(cudaMemcpyAsync(base, order, sizeof(int) * (size_t)npts, cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_ttab, ttab.data(), sizeof(float) * ttab.size(), cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_dirs, dirs.data(), sizeof(int) * dirs.size(), cudaMemcpyHostToDevice, st));
-    OICS_CUDA_TRY(cudaMemsetAsync(ctx->accum.p, 0, acc_bytes, st));
-    gather_points_kernel<<<cdiv(npts, 256), 256, 0, st>>>(d_pts, reinterpret_cast<const int *>(base), npts,
-                                                         reinterpret_cast<uint32_t *>(base + off_seq));
-    PphtArgs A;
-    A.seq = reinterpret_cast<const uint32_t *>(base + off_seq);
-    A.npts = npts;
-    A.mask = d_mask;
-    A.w = w; A.h = h;
-    A.accum = ctx->accum.as<int32_t>();
-    A.ttab = reinterpret_cast<const float *>(base + off_ttab);
-    A.dirs = reinterpret_cast<const int *>(base + off_dirs);
-    A.numangle = numangle; A.numrho = numrho;
-    A.threshold = threshold; A.line_length = line_length; A.line_gap = line_gap;
-    A.lines = reinterpret_cast<int32_t *>(base + off_lines);
-    A.cap = cap;
-    A.n_lines = reinterpret_cast<int *>(base + off_nl);
-    A.list = reinterpret_cast<uint32_t *>(base + off_list);
-    {
-        ProfScope ps(ctx, "ppht_kernel", 0.0);
-        ppht_kernel<<<PPHT_C, PPHT_T, 0, st>>>(A);   // one cluster (__cluster_dims__)
+    // ---- per-image scratch (hough_img): [total 16 B][rowoff h ints][pts w*h u32][mask w*h]; accum separately
+    const size_t npx = (size_t)w * h;
+    const size_t off_pts = (16 + sizeof(int) * (size_t)h + 15) & ~(size_t)15;
+    const size_t off_mask = off_pts + sizeof(uint32_t) * npx;
+    const size_t img_bytes = (off_mask + npx + 255) & ~(size_t)255;
+    const size_t acc_bytes = ((size_t)numangle * numrho * sizeof(int32_t) + 255) & ~(size_t)255;
+    OICS_TRY(ctx->labels.ensure((size_t)n_img * img_bytes));
+    OICS_TRY(ctx->accum.ensure((size_t)n_img * acc_bytes));
+    uint8_t *ibase = ctx->labels.as<uint8_t>();
+    for (int i = 0; i < n_img; i++) {
+        int *total = reinterpret_cast<int *>(ibase + (size_t)i * img_bytes);
+        int *rowoff = total + 4;
+        uint32_t *pts = reinterpret_cast<uint32_t *>(ibase + (size_t)i * img_bytes + off_pts);
+        uint8_t *mask = ibase + (size_t)i * img_bytes + off_mask;
+        edge_row_count_kernel<<<cdiv(h, 8), 256, 0, st>>>(dedges[i], w, h, stride, rowoff);
+        edge_row_scan_kernel<<<1, 1024, 0, st>>>(rowoff, h, total);
+        edge_row_write_kernel<<<cdiv(h, 8), 256, 0, st>>>(dedges[i], w, h, stride, rowoff, pts, mask);
     }
     OICS_CUDA_TRY(cudaGetLastError());
-    ctx->launches += 2;
-    int n = 0;
-    OICS_CUDA_TRY(cudaMemcpyAsync(&n, A.n_lines, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ctx->launches += 3 * n_img;
+    // the point counts: one read-back (strided: the first int of every image block)
+    OICS_TRY(ctx->pin_small.ensure(sizeof(int) * (size_t)n_img));
+    OICS_CUDA_TRY(cudaMemcpy2DAsync(ctx->pin_small.p, sizeof(int), ibase, img_bytes, sizeof(int), (size_t)n_img, cudaMemcpyDeviceToHost, st));
     OICS_CUDA_TRY(cudaStreamSynchronize(st));
+    std::vector<int> npts((size_t)n_img);
+    std::vector<size_t> off((size_t)n_img + 1, 0);
+    for (int i = 0; i < n_img; i++) {
+        npts[(size_t)i] = ctx->pin_small.as<int>()[i];
+        off[(size_t)i + 1] = off[(size_t)i] + (size_t)npts[(size_t)i];
+    }
+    const size_t total_pts = off[(size_t)n_img];
+    if (total_pts == 0) return OICS_OK;
+
+    // ---- visiting orders, expanded in pinned memory on host threads (data-independent, like the trig table)
+    OICS_TRY(ctx->pin_in.ensure(2 * sizeof(int) * total_pts));
+    int *order = ctx->pin_in.as<int>();
+    {
+        const int nthr = std::max(1, std::min<int>(n_img, (int)std::thread::hardware_concurrency()));
+        std::atomic<int> next(0);
+        auto work = [&]() {
+            for (int i = next.fetch_add(1); i < n_img; i = next.fetch_add(1))
+                if (npts[(size_t)i] > 0) ppht_order(npts[(size_t)i], order + off[(size_t)i], order + total_pts + off[(size_t)i]);
+        };
+        if (nthr == 1) {
+            work();
+        } else {
+            std::vector<std::thread> pool;
+            for (int t = 0; t < nthr; t++) pool.emplace_back(work);
+            for (std::thread &t : pool) t.join();
+        }
+    }
+    // misc: [order total_pts][seq total_pts][ttab][dirs][PphtArgs n][n_lines n x 16 B][lines n x cap x 4]
+    const size_t off_seq = sizeof(int) * total_pts;
+    const size_t off_ttab = (off_seq + sizeof(uint32_t) * total_pts + 15) & ~(size_t)15;
+    const size_t off_dirs = (off_ttab + sizeof(float) * ttab.size() + 15) & ~(size_t)15;   // int4 loads
+    const size_t off_args = (off_dirs + sizeof(int) * dirs.size() + 15) & ~(size_t)15;
+    const size_t off_nl = (off_args + sizeof(PphtArgs) * (size_t)n_img + 15) & ~(size_t)15;
+    const size_t off_lines = off_nl + 16 * (size_t)n_img;
+    const size_t misc_bytes = off_lines + sizeof(int32_t) * 4 * (size_t)cap * n_img;
+    OICS_TRY(ctx->misc.ensure(misc_bytes));
+    uint8_t *base = ctx->misc.as<uint8_t>();
+    OICS_CUDA_TRY(cudaMemcpyAsync(base, order, sizeof(int) * total_pts, cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_ttab, ttab.data(), sizeof(float) * ttab.size(), cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_dirs, dirs.data(), sizeof(int) * dirs.size(), cudaMemcpyHostToDevice, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(ctx->accum.p, 0, (size_t)n_img * acc_bytes, st));
+    OICS_CUDA_TRY(cudaMemsetAsync(base + off_nl, 0, 16 * (size_t)n_img, st));
+    std::vector<PphtArgs> args((size_t)n_img);
+    for (int i = 0; i < n_img; i++) {
+        PphtArgs &A = args[(size_t)i];
+        const uint32_t *pts = reinterpret_cast<const uint32_t *>(ibase + (size_t)i * img_bytes + off_pts);
+        uint32_t *seq = reinterpret_cast<uint32_t *>(base + off_seq) + off[(size_t)i];
+        if (npts[(size_t)i] > 0)
+            gather_points_kernel<<<cdiv(npts[(size_t)i], 256), 256, 0, st>>>(pts, reinterpret_cast<const int *>(base) + off[(size_t)i],
+                                                                            npts[(size_t)i], seq);
+        A.seq = seq;
+        A.npts = npts[(size_t)i];
+        A.mask = ibase + (size_t)i * img_bytes + off_mask;
+        A.w = w; A.h = h;
+        A.accum = reinterpret_cast<int32_t *>(ctx->accum.as<uint8_t>() + (size_t)i * acc_bytes);
+        A.ttab = reinterpret_cast<const float *>(base + off_ttab);
+        A.dirs = reinterpret_cast<const int *>(base + off_dirs);
+        A.numangle = numangle; A.numrho = numrho;
+        A.threshold = threshold; A.line_length = line_length; A.line_gap = line_gap;
+        A.lines = reinterpret_cast<int32_t *>(base + off_lines) + 4 * (size_t)cap * i;
+        A.cap = cap;
+        A.n_lines = reinterpret_cast<int *>(base + off_nl + 16 * (size_t)i);
+        A.list = nullptr;
+    }
+    OICS_CUDA_TRY(cudaGetLastError());
+    OICS_CUDA_TRY(cudaMemcpyAsync(base + off_args, args.data(), sizeof(PphtArgs) * (size_t)n_img, cudaMemcpyHostToDevice, st));
+    {
+        ProfScope ps(ctx, "ppht_kernel", 0.0);
+        ppht_kernel<<<PPHT_C * n_img, PPHT_T, 0, st>>>(reinterpret_cast<const PphtArgs *>(base + off_args));   // a cluster per image
+    }
+    OICS_CUDA_TRY(cudaGetLastError());
+    ctx->launches += 1 + n_img;
+    // results: counts and segment lists in one read-back each
+    std::vector<int> nl(4 * (size_t)n_img);
+    std::vector<int32_t> all(4 * (size_t)cap * n_img);
+    OICS_CUDA_TRY(cudaMemcpyAsync(nl.data(), base + off_nl, 16 * (size_t)n_img, cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaMemcpyAsync(all.data(), base + off_lines, sizeof(int32_t) * all.size(), cudaMemcpyDeviceToHost, st));
+    OICS_CUDA_TRY(cudaStreamSynchronize(st));   // also: args / ttab / dirs (host temporaries) have been consumed
+    for (int i = 0; i < n_img; i++) {
+        const int n = nl[4 * (size_t)i];
+        *max_found = std::max(*max_found, n);
+        const int keep = std::min(n, cap);
+        (*lines_out)[(size_t)i].assign(all.begin() + 4 * (size_t)cap * i, all.begin() + 4 * (size_t)cap * i + 4 * (size_t)keep);
+    }
+    return OICS_OK;
+}
+
+int32_t hough_lines_p_batch_device(oics_ctx *ctx, const uint8_t *const *dedges, int n_img, int w, int h, size_t stride,
+                                   double rho, double theta, int threshold, int line_length, int line_gap,
+                                   std::vector<std::vector<int32_t>> *lines_out)
+{
+    // 4096 segments per image fit the device list; the count the kernel reports is exact, so a longer list
+    // (threshold 0 on noise) re-runs the batch once with room for it -- the edge maps are untouched by a run
+    int cap = 4096, found = 0;
+    OICS_TRY(hough_lines_p_batch_once(ctx, dedges, n_img, w, h, stride, rho, theta, threshold, line_length, line_gap, cap,
+                                      lines_out, &found));
+    if (found > cap)
+        OICS_TRY(hough_lines_p_batch_once(ctx, dedges, n_img, w, h, stride, rho, theta, threshold, line_length, line_gap, found,
+                                          lines_out, &found));
+    return OICS_OK;
+}
+
+int32_t hough_lines_p_device(oics_ctx *ctx, const uint8_t *dedges, int w, int h, size_t stride, double rho,
+                             double theta, int threshold, int line_length, int line_gap, int32_t *h_lines,
+                             int cap, int *n_lines)
+{
+    std::vector<std::vector<int32_t>> out;
+    OICS_TRY(hough_lines_p_batch_device(ctx, &dedges, 1, w, h, stride, rho, theta, threshold, line_length, line_gap, &out));
+    const int n = (int)(out[0].size() / 4);
     *n_lines = n;
     const int ncopy = std::min(n, cap);
     if (ncopy > 0) {
         if (is_device_ptr(h_lines))
-            OICS_CUDA_TRY(cudaMemcpyAsync(h_lines, A.lines, sizeof(int32_t) * 4 * (size_t)ncopy, cudaMemcpyDeviceToDevice, st));
+            OICS_CUDA_TRY(cudaMemcpy(h_lines, out[0].data(), sizeof(int32_t) * 4 * (size_t)ncopy, cudaMemcpyHostToDevice));
         else
-            OICS_CUDA_TRY(cudaMemcpyAsync(h_lines, A.lines, sizeof(int32_t) * 4 * (size_t)ncopy, cudaMemcpyDeviceToHost, st));
-        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+            memcpy(h_lines, out[0].data(), sizeof(int32_t) * 4 * (size_t)ncopy);
     }
     return OICS_OK;
 }

@@ -364,13 +364,15 @@ __device__ __forceinline__ float tap_weight(const AreaTaps &t, int k)
 }
 
 template <int CH>
-__global__ void __launch_bounds__(256) resize_area_kernel(const uint8_t *__restrict__ src, int w, int h, size_t stride,
-                                                          uint8_t *__restrict__ dst, int dw, int dh, size_t dstride,
-                                                          double scale_x, double scale_y, int fast, int ix, int iy,
-                                                          float inv_area, int do_threshold)
+__global__ void __launch_bounds__(256) resize_area_kernel(const uint8_t *__restrict__ src0, size_t src_card, int w, int h,
+                                                          size_t stride, uint8_t *__restrict__ dst0, size_t dst_card, int dw,
+                                                          int dh, size_t dstride, double scale_x, double scale_y, int fast,
+                                                          int ix, int iy, float inv_area, int do_threshold)
 {
     const int dx = blockIdx.x * blockDim.x + threadIdx.x, dy = blockIdx.y;
     if (dx >= dw) return;
+    const uint8_t *src = src0 + (size_t)blockIdx.z * src_card;   // one card of a batch per grid.z
+    uint8_t *dst = dst0 + (size_t)blockIdx.z * dst_card;
     int out[CH];
     if (fast) {
 #pragma unroll
@@ -406,7 +408,7 @@ __global__ void __launch_bounds__(256) resize_area_kernel(const uint8_t *__restr
 }
 
 static int32_t launch_resize(oics_ctx *ctx, const uint8_t *src, int ch, int w, int h, size_t stride, uint8_t *dst,
-                             int dw, int dh, int do_threshold)
+                             int dw, int dh, int do_threshold, int n_cards = 1, size_t src_card = 0, size_t dst_card = 0)
 {
     const double sx = (double)w / dw, sy = (double)h / dh;
     if (sx < 1 || sy < 1) {
@@ -416,14 +418,19 @@ static int32_t launch_resize(oics_ctx *ctx, const uint8_t *src, int ch, int w, i
     const int ix = (int)lrint(sx), iy = (int)lrint(sy);
     const int fast = fabs(sx - ix) < 2.220446049250313e-16 && fabs(sy - iy) < 2.220446049250313e-16;
     const float inv_area = 1.f / (float)(ix * iy);
-    dim3 grid(cdiv(dw, 256), dh);
-    ProfScope ps(ctx, ch == 1 ? "resize_area_kernel<1>" : "resize_area_kernel<3>", (double)ch * ((double)w * h + (double)dw * dh));
+    if (n_cards > 65535) {
+        set_error("resize: at most 65535 cards per launch");
+        return OICS_ERR_INVALID_ARG;
+    }
+    dim3 grid(cdiv(dw, 256), dh, n_cards);
+    ProfScope ps(ctx, ch == 1 ? "resize_area_kernel<1>" : "resize_area_kernel<3>",
+                 (double)n_cards * ch * ((double)w * h + (double)dw * dh));
     if (ch == 1)
-        resize_area_kernel<1><<<grid, 256, 0, ctx->stream>>>(src, w, h, stride, dst, dw, dh, (size_t)dw, sx, sy, fast, ix,
-                                                             iy, inv_area, do_threshold);
+        resize_area_kernel<1><<<grid, 256, 0, ctx->stream>>>(src, src_card, w, h, stride, dst, dst_card, dw, dh, (size_t)dw, sx, sy,
+                                                             fast, ix, iy, inv_area, do_threshold);
     else
-        resize_area_kernel<3><<<grid, 256, 0, ctx->stream>>>(src, w, h, stride, dst, dw, dh, (size_t)dw * 3, sx, sy, fast,
-                                                             ix, iy, inv_area, do_threshold);
+        resize_area_kernel<3><<<grid, 256, 0, ctx->stream>>>(src, src_card, w, h, stride, dst, dst_card, dw, dh, (size_t)dw * 3, sx,
+                                                             sy, fast, ix, iy, inv_area, do_threshold);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return OICS_OK;
@@ -476,6 +483,15 @@ int32_t preprocess_batch_device(oics_ctx *ctx, const uint8_t *dbgrs, int n_cards
 {
     if (mode == OICS_PRE_OMR && ow == w && oh == h)
         return launch_gray_erode(ctx, dbgrs, w, h, stride, 3, 1, dbins, (size_t)w, n_cards, card_stride, (size_t)w * h);
+    if (mode == OICS_PRE_OMR && n_cards <= 65535 && ow > 0 && oh > 0) {
+        // the shrinking operating point (omr.rs:114-127): gray + erode of every card in one launch, then one
+        // INTER_AREA + threshold launch over the batch
+        OICS_TRY(ctx->tmp8a.ensure((size_t)n_cards * w * h));
+        OICS_TRY(launch_gray_erode(ctx, dbgrs, w, h, stride, 3, 0, ctx->tmp8a.as<uint8_t>(), (size_t)w, n_cards, card_stride,
+                                   (size_t)w * h));
+        return launch_resize(ctx, ctx->tmp8a.as<uint8_t>(), 1, w, h, (size_t)w, dbins, ow, oh, 1, n_cards, (size_t)w * h,
+                             (size_t)ow * oh);
+    }
     for (int c = 0; c < n_cards; c++)
         OICS_TRY(preprocess_device(ctx, dbgrs + (size_t)c * card_stride, w, h, stride, mode, ow, oh,
                                    dbins + (size_t)c * ow * oh));

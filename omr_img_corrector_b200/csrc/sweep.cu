@@ -414,7 +414,9 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const int wp = cdiv(w, 32), wj = wp;
     const size_t tab_ints = (size_t)n_angles * (2 * (size_t)wpad + 2 * (size_t)hpad);
     SweepCache &cache = ctx->sweep_cache;
-    const bool same_geometry = cache.w == w && cache.h == h && cache.inv == inv && ctx->tabs.p &&
+    const char *force = getenv("OICS_SWEEP_KERNEL");  // "general": only the general kernel; "word": no small-card kernel (A/B tests)
+    const bool small = sweeps_eligible(w, h) && !(force && (force[0] == 'g' || force[0] == 'w'));
+    const bool same_geometry = cache.w == w && cache.h == h && cache.small == small && cache.inv == inv && ctx->tabs.p &&
                                ctx->tabs.cap >= tab_ints * sizeof(int) && ctx->wlists.p;
 
     // ---- chunking: counts buffer (256 MB) and word-kernel planes (3 GB) bound a chunk
@@ -455,6 +457,51 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         sweep_tables_kernel<<<grid, 256, 0, st>>>(ctx->mats.as<double>(), w, h, wpad, hpad, ad, bd, xy);
         OICS_CUDA_TRY(cudaGetLastError());
         ctx->launches++;
+        cache.small = small;
+        cache.boxes_ready = false;
+    }
+    if (small) {
+        // ---- small-card path: the whole card in one CTA, one warp per angle, std-devs fused (sweeps.cu).
+        // wlists holds the per-angle sample boxes; no classification, no count buffer, no finalize pass.
+        OICS_TRY(ctx->wlists.ensure((size_t)n_angles * sizeof(int4)));
+        const size_t card_words = (size_t)h * wp;
+        // bit planes for as many cards as 256 MB hold (a 248 x 230 card is 7 KB)
+        const int cards_per_pack = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_cards, ((size_t)256 << 20) / (card_words * 4)));
+        OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * card_words * sizeof(uint32_t)));
+        ctx->last_sweep_launches = 0;
+        cudaEvent_t e0, e1;
+        OICS_CUDA_TRY(cudaEventCreate(&e0));
+        OICS_CUDA_TRY(cudaEventCreate(&e1));
+        OICS_CUDA_TRY(cudaEventRecord(e0, st));
+        for (int c0 = 0; c0 < n_cards; c0 += cards_per_pack) {
+            const int nc = std::min(cards_per_pack, n_cards - c0);
+            for (int z0 = 0; z0 < nc; z0 += 65535) {
+                const int nz = std::min(65535, nc - z0);
+                dim3 g(cdiv(wp, 128), h, nz);
+                ProfScope ps(ctx, "pack_bits_kernel", (double)nz * ((double)w * h + (double)h * wp * 4));
+                pack_bits_kernel<<<g, 128, 0, st>>>(dbins + (size_t)(c0 + z0) * card_stride, card_stride, stride, w, h, wp,
+                                                    ctx->bits.as<uint32_t>() + (size_t)z0 * card_words, nz);
+                OICS_CUDA_TRY(cudaGetLastError());
+                ctx->launches++;
+            }
+            OICS_TRY(sweeps_launch(ctx, ctx->bits.as<uint32_t>(), card_words, w, h, T, inv.data(), n_angles, ctx->wlists.as<int4>(),
+                                   nc, d_vsd, d_hsd, reinterpret_cast<long long *>(d_sums), c0 == 0 ? d_counts_out : nullptr,
+                                   (size_t)c0 * n_angles, cache.boxes_ready));
+            cache.boxes_ready = true;
+        }
+        OICS_CUDA_TRY(cudaEventRecord(e1, st));
+        OICS_CUDA_TRY(cudaStreamSynchronize(st));
+        float t = 0.f;
+        cudaEventElapsedTime(&t, e0, e1);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        ctx->last_sweep_ms = t;
+        cache.w = w;
+        cache.h = h;
+        cache.inv.swap(inv);
+        return OICS_OK;
+    }
+    if (!same_geometry) {
 
         // ---- classify the angles on the device: word kernel (by source rows per word) or general
         const size_t meta_bytes = (size_t)n_angles * wj * SWW_META * sizeof(uint32_t);
@@ -465,7 +512,6 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         std::vector<SweepWClass> cls((size_t)n_angles);
         OICS_CUDA_TRY(cudaMemcpyAsync(cls.data(), d_cls, cls.size() * sizeof(SweepWClass), cudaMemcpyDeviceToHost, st));
         OICS_CUDA_TRY(cudaStreamSynchronize(st));
-        const char *force = getenv("OICS_SWEEP_KERNEL");  // "general" disables the word kernel (A/B tests)
         const bool allow_word = !(force && force[0] == 'g');
         const char *genv = getenv("OICS_SWEEP_GROUP");    // max angles per CTA (tuning)
         const int gmax = genv ? std::max(1, std::min(SWW_GMAX, atoi(genv))) : SWW_GMAX;

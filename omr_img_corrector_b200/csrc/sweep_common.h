@@ -80,6 +80,11 @@ int32_t sweepw_classify(oics_ctx *ctx, const SweepTables &T, int n_angles, int w
 bool sweepw_group_fits(const double *inv, int first, int cnt, int kr, int w, int h);
 int32_t sweepw_build_planes(oics_ctx *ctx, const SweepTables &T, const uint32_t *d_meta, const int *d_fast_angles,
                             int n_fast, int w, int h, uint2 *d_planes);
+// small-card kernel (sweeps.cu): the whole card in one CTA, one warp per candidate angle, std-devs fused
+bool sweeps_eligible(int w, int h);
+int32_t sweeps_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_words, int w, int h, const SweepTables &T,
+                      const double *inv_host, int n_angles, int4 *d_boxes, int n_cards, double *d_vsd, double *d_hsd,
+                      long long *d_sums, int *d_counts_out, size_t item0, bool boxes_ready);
 int32_t sweepw_launch(oics_ctx *ctx, const uint32_t *bits, size_t bits_card_words, int wp, int w, int h,
                       const SweepTables &T, const SweepWPlan &P, const SweepWGroups &G, int n_cards, int *counts);
 

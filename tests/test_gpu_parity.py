@@ -893,3 +893,105 @@ def test_more_than_65535_angles(ctx, orc):
     idx = np.array([0, 1, 65534, 65535, 65536, 100000, 131069])
     rv, rh = orc.projection_sweep(b, M[idx], threads=4)
     assert np.array_equal(v[idx], rv) and np.array_equal(h[idx], rh)
+
+
+def test_accuracy_regression_reference_dataset(ctx):
+    """lib.rs:131-245 on the reference's OWN fixtures (tests/fixtures/dataset = dataset/dataset/*.jpg, copied by
+    tools/fetch_fixtures.py): a spread of the 104 scanned cards x skews over +-45 degrees, file to file through
+    oics_correct_batch_files; every 5th input is re-run through the oracle from the card (rotate, tmp.jpg,
+    imread, correct_default, imwrite) and angle, need_check, the tmp.jpg bytes and the output file bytes must
+    be identical, as must imread of the dataset file itself.  Most inputs land in the test's SUCCESS class."""
+    import glob
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    dataset = os.path.join(root, "tests", "fixtures", "dataset")
+    if not glob.glob(os.path.join(dataset, "*.jpg")):
+        pytest.skip("reference fixture images absent (tools/fetch_fixtures.py copies them where the reference tree exists)")
+    sys.path.insert(0, os.path.join(root, "tools"))
+    import accuracy_regression as ar
+    cards, source = ar.load_cards(ctx, dataset, 8)
+    assert source == "reference dataset" and len(cards) == 8
+    skews = [-45.0 + 3.7 * i for i in range(25)]
+    res = ar.run(ctx, cards, skews, files_mode=True, oracle_every=5, chunk=25)
+    assert res["inputs"] == 200 and res["histogram"]["error_status"] == 0
+    assert res["oracle_checked"] == 40 and res["oracle_mismatches"] == []
+    assert res["histogram"]["SUCCESS"] >= 150
+
+
+# ----------------------------------------------------------------------------- batched Hough fallback
+def _fallback_card(orc, i):
+    """Thick-framed cards whose 26x30 sweep (scale 0.1 re-applied in the rotation, omr.rs:157-163) is ambiguous
+    (NotAResult with several candidates) while the full-resolution card has long edges for HoughLinesP."""
+    c = np.full((300, 260, 3), 255, np.uint8)
+    c[30 + i % 7:50 + i % 7, 30:230] = 0
+    c[250:270, 30 + i % 5:230] = 0
+    c[30:270, 30:50 + i % 3] = 0
+    c[30:270, 210 - i % 4:230] = 0
+    c[140:160, 60:200 - (i % 9) * 3] = 0
+    return orc.rotate_mat(c, -3.0 + 0.2 * i, 1.0, 1, orc.WHITE, 0)
+
+
+def test_batched_hough_fallback_equals_one_by_one(ctx, orc):
+    """omr.rs:352-403 for a batch in which EVERY card takes the Hough fallback: 70 cards = three flushes of the
+    deferred queue (32 clusters in flight per PPHT launch).  Angle, need_check and deskewed pixels must equal
+    omr::correct_default card by card, the oracle on a sample, and the JPEG variant must encode those pixels."""
+    cards = np.stack([_fallback_card(orc, i) for i in range(70)])
+    params = (5, 0.5, 26, 30, 50.0, 5.0)
+    statuses = [ctx.result_from_projection(cards[i], 5, 0.5, 26, 30).status for i in range(0, 70, 7)]
+    assert all(s != api.BELIEVED for s in statuses)                   # the family really is ambiguous
+    outs = [np.zeros(520 * 520 * 3, np.uint8) for _ in cards]
+    ang, need, stat, sizes = ctx.correct_batch(cards, *params, outs=outs)
+    assert not stat.any() and need.sum() >= 60
+    for i in range(len(cards)):
+        ga, gneed, gout = ctx.correct_default(cards[i], *params)
+        assert (ang[i], bool(need[i])) == (ga, gneed), i
+        dw, dh = sizes[i]
+        assert (dh, dw) == gout.shape[:2] and np.array_equal(outs[i][:dw * dh * 3].reshape(dh, dw, 3), gout), i
+    for i in (0, 2, 33, 69):
+        ra, rneed, rout = orc.correct_default(cards[i], *params)
+        dw, dh = sizes[i]
+        assert (ang[i], bool(need[i])) == (ra, rneed) and np.array_equal(outs[i][:dw * dh * 3].reshape(dh, dw, 3), rout), i
+    jouts = [np.zeros(1 << 20, np.uint8) for _ in cards]
+    a2, n2, s2, z2, fsz = ctx.correct_batch(cards, *params, outs=jouts, jpeg_quality=100)
+    assert not s2.any() and np.array_equal(a2, ang) and np.array_equal(n2, need)
+    for i in (0, 31, 32, 69):
+        dw, dh = sizes[i]
+        assert jouts[i][:int(fsz[i])].tobytes() == orc.jpeg_encode(outs[i][:dw * dh * 3].reshape(dh, dw, 3), 100), i
+    # device-resident cards and outputs take the same queue
+    import torch
+    t = torch.from_numpy(cards[:40]).cuda()
+    douts = [torch.zeros(520 * 520 * 3, dtype=torch.uint8, device="cuda") for _ in range(40)]
+    a3, n3, s3, z3 = ctx.correct_batch(t, *params, outs=douts)
+    assert np.array_equal(a3, ang[:40]) and not s3.any()
+    for i in (0, 39):
+        dw, dh = z3[i]
+        assert np.array_equal(douts[i][:dw * dh * 3].cpu().numpy(), outs[i][:dw * dh * 3])
+
+
+def test_edges_detection_batch_equals_single(ctx, orc, dataset_like):
+    """oics_result_from_edges_detection_batch: n cards' Canny + HoughLinesP in flight together (a cluster per
+    card) give exactly the single-call results -- the oracle's on a sample -- and a card without segments
+    gets OICS_ERR_NO_LINES in its own status while the others complete."""
+    bgr, _ = dataset_like
+    cards = [_fallback_card(orc, i) for i in range(35)]
+    cards[17] = np.full((300, 260, 3), 255, np.uint8)                 # no edges: the reference panics (omr.rs:272)
+    cards = np.stack(cards)
+    ang, rstat, stat = ctx.result_from_edges_detection_batch(cards, 50.0, 5.0)
+    assert stat[17] == -3 and not np.delete(stat, 17).any()
+    for i in range(len(cards)):
+        if i == 17:
+            continue
+        r = ctx.result_from_edges_detection(cards[i], 50.0, 5.0)
+        assert (r.angle, r.status) == (ang[i], rstat[i]), i
+    for i in (0, 16, 34):
+        o = orc.get_result_from_edges_detection(cards[i], 50.0, 5.0)
+        assert (o.angle, o.status) == (ang[i], rstat[i]), i
+    # gray cards, device-resident, at the dataset size
+    import torch
+    g = orc.gray(bgr)
+    gs = np.stack([g, np.ascontiguousarray(g[::-1]), np.ascontiguousarray(g[:, ::-1])])
+    a1, r1, s1 = ctx.result_from_edges_detection_batch(torch.from_numpy(gs).cuda(), 125.0, 15.0)
+    for i in range(3):
+        o = orc.get_result_from_edges_detection(gs[i], 125.0, 15.0)
+        assert s1[i] == 0 and (o.angle, o.status) == (a1[i], r1[i]), i
