@@ -783,7 +783,14 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // cards per sub-batch: 8 A4 cards (209 MB) amortise the per-sub-batch host round trip (rule A needs the
     // std-devs on the host); small cards get proportionally more, up to 64 (the file path decodes at most 8
     // files at a time, one stream each)
-    const int B_target = files ? 8 : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
+    const int B_max = files ? 8 : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
+    // with host buffers on either side the copies of one sub-batch overlap the kernels of another: keep at least
+    // eight stages in the pipeline; device-resident batches have nothing to overlap and take the largest sub-batch
+    bool any_host_dst = false;
+    if (dsts)
+        for (int c = 0; c < n_cards && !any_host_dst; c++) any_host_dst = dsts[c] && !is_device_ptr(dsts[c]);
+    const bool pipelined = files || !is_device_ptr(bgrs) || any_host_dst;
+    const int B_target = pipelined ? std::max(8, std::min(B_max, cdiv(n_cards, 8))) : B_max;
     const int B = std::min<int>(n_cards, B_target);
     std::vector<int32_t> file_status((size_t)n_cards, OICS_OK);
     const int n_sub = cdiv(n_cards, B);

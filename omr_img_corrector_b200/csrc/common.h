@@ -116,6 +116,7 @@ struct oics_ctx {
     // bound to one device; process-wide statics would leak one device's answer to another)
     bool attr_sweepw = false, attr_sweeps = false, attr_sweep[5] = {false, false, false, false, false};
     int canny_blocks_per_sm = 0;
+    size_t counts_clean = 0;            // leading bytes of `counts` known to be zero (the finalize pass clears what it read)
     // sweep timing evidence
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_sweep_ms = 0.0;

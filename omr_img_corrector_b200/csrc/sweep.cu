@@ -283,8 +283,8 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
 // per vector: lanes stage a chunk, lane 0 runs the dependent f64 chain.
 static constexpr int FIN_CHUNK = 1024;
 
-__device__ double seq_std_dev(const int *__restrict__ v, int n, double *stage, int lane, long long *sum_out,
-                              long long *sq_out)
+__device__ double seq_std_dev(int *__restrict__ v, int n, double *stage, int lane, long long *sum_out,
+                              long long *sq_out, bool zero_after)
 {
     long long s = 0, q = 0;
     for (int i = lane; i < n; i += 32) {
@@ -307,6 +307,7 @@ __device__ double seq_std_dev(const int *__restrict__ v, int n, double *stage, i
         for (int i = lane; i < m; i += 32) {
             const double d = __dsub_rn((double)v[base + i], mean);
             stage[i] = __dmul_rn(d, d);
+            if (zero_after) v[base + i] = 0;   // the next launch accumulates into a clean buffer: no memset pass
         }
         __syncwarp();
         // ... lane 0 runs the strictly sequential sum: one dependent DADD per element
@@ -326,23 +327,24 @@ __device__ double seq_std_dev(const int *__restrict__ v, int n, double *stage, i
     return __dsqrt_rn(__ddiv_rn(acc, (double)n));
 }
 
-__global__ void __launch_bounds__(64) sweep_finalize_kernel(const int *__restrict__ counts, int w, int h,
+__global__ void __launch_bounds__(64) sweep_finalize_kernel(int *__restrict__ counts, int w, int h,
                                                             long long item0, double *__restrict__ v_sd,
-                                                            double *__restrict__ h_sd, long long *__restrict__ sums)
+                                                            double *__restrict__ h_sd, long long *__restrict__ sums,
+                                                            int zero_after)
 {
     __shared__ double stage[2][FIN_CHUNK];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int *base = counts + (size_t)blockIdx.x * (h + w);
+    int *base = counts + (size_t)blockIdx.x * (h + w);
     const size_t item = (size_t)item0 + blockIdx.x;
     long long s, q;
     if (warp == 0) {
-        double sd = seq_std_dev(base, h, stage[0], lane, &s, &q);
+        double sd = seq_std_dev(base, h, stage[0], lane, &s, &q, zero_after != 0);
         if (lane == 0) {
             h_sd[item] = sd;
             if (sums) { sums[4 * item + 0] = s; sums[4 * item + 1] = q; }
         }
     } else {
-        double sd = seq_std_dev(base + h, w, stage[1], lane, &s, &q);
+        double sd = seq_std_dev(base + h, w, stage[1], lane, &s, &q, zero_after != 0);
         if (lane == 0) {
             v_sd[item] = sd;
             if (sums) { sums[4 * item + 2] = s; sums[4 * item + 3] = q; }
@@ -602,7 +604,11 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
     const size_t smem = (fixed_words + cap_words) * 4;
     const int tiles_x = cdiv(w, TW), tiles_y = cdiv(h, tile_h);
 
-    OICS_TRY(ctx->counts.ensure((size_t)cards_per_chunk * angles_per_chunk * per_item));
+    {
+        const void *before = ctx->counts.p;
+        OICS_TRY(ctx->counts.ensure((size_t)cards_per_chunk * angles_per_chunk * per_item));
+        if (ctx->counts.p != before) ctx->counts_clean = 0;
+    }
     const int cards_per_pack = std::min(n_cards, std::max(cards_per_chunk, 8));
     OICS_TRY(ctx->bits.ensure((size_t)cards_per_pack * h * wp * sizeof(uint32_t)));
     if (n_fast) {
@@ -638,7 +644,11 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         const uint32_t *bits_base = ctx->bits.as<uint32_t>() - (size_t)packed_first * A.bits_card_words;
         for (int a0 = 0; a0 < n_angles; a0 += angles_per_chunk) {
             const int a1 = std::min(n_angles, a0 + angles_per_chunk), na = a1 - a0;
-            OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nc * na * per_item, st));
+            // the finalize pass zeroes what it has read, so only a region it has not cleaned yet needs a memset
+            const size_t need_clean = (size_t)nc * na * per_item;
+            if (ctx->counts_clean < need_clean) OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, need_clean, st));
+            const bool keep_counts = d_counts_out && c0 == 0;
+            ctx->counts_clean = keep_counts ? 0 : std::max(ctx->counts_clean, need_clean);
             // word-kernel planes for the fast angles of this range
             const int f_lo = (int)(std::lower_bound(fast.begin(), fast.end(), a0) - fast.begin());
             const int f_hi = (int)(std::lower_bound(fast.begin(), fast.end(), a1) - fast.begin());
@@ -704,7 +714,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
             {
                 ProfScope ps(ctx, "sweep_finalize_kernel", (double)nc * na * per_item);
                 sweep_finalize_kernel<<<(unsigned)(nc * na), 64, 0, st>>>(ctx->counts.as<int>(), w, h, (long long)item0, d_vsd,
-                                                                         d_hsd, reinterpret_cast<long long *>(d_sums));
+                                                                         d_hsd, reinterpret_cast<long long *>(d_sums), keep_counts ? 0 : 1);
             }
             OICS_CUDA_TRY(cudaGetLastError());
             ctx->launches++;
@@ -743,13 +753,14 @@ int32_t plain_std_devs_device(oics_ctx *ctx, const uint8_t *dbin, int w, int h, 
     const int wp = cdiv(w, 32);
     OICS_TRY(ctx->bits.ensure((size_t)h * wp * sizeof(uint32_t)));
     OICS_TRY(ctx->counts.ensure((size_t)(h + w) * sizeof(int)));
+    ctx->counts_clean = 0;
     dim3 g(cdiv(wp, 128), h, 1);
     pack_bits_kernel<<<g, 128, 0, st>>>(dbin, 0, stride, w, h, wp, ctx->bits.as<uint32_t>(), 1);
     OICS_CUDA_TRY(cudaGetLastError());
     OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)(h + w) * sizeof(int), st));
     plain_counts_kernel<<<cdiv(h, 8), 256, 0, st>>>(ctx->bits.as<uint32_t>(), wp, w, h, ctx->counts.as<int>());
     OICS_CUDA_TRY(cudaGetLastError());
-    sweep_finalize_kernel<<<1, 64, 0, st>>>(ctx->counts.as<int>(), w, h, 0, d_vsd, d_hsd, nullptr);
+    sweep_finalize_kernel<<<1, 64, 0, st>>>(ctx->counts.as<int>(), w, h, 0, d_vsd, d_hsd, nullptr, 0);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     return OICS_OK;

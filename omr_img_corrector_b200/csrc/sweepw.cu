@@ -357,14 +357,20 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
     // half a warp per source row, lane = word column
     {
         const int c = lane & 15, gc = colw0 + c;
-        const bool cin = gc >= 0 && gc < A.wp;
-        const uint32_t *colp = bits + gc;
+        const bool cin = c < nW && gc >= 0 && gc < A.wp;
         if (nW <= 16) {
-            for (int r = warp * 2 + (lane >> 4); r < nR; r += 16) {
-                const int gr = row0 + r;
-                uint32_t v = 0;
-                if (cin && gr >= 0 && gr < A.h) v = __ldg(colp + (size_t)gr * A.wp);
-                if (c < nW) tile[r * SWW_P + c] = v;
+            // asynchronous copies (LDGSTS), zero-filled outside the image: no register round trip, every row
+            // of the footprint in flight at once; 32-bit offsets, one add per row
+            int r = warp * 2 + (lane >> 4);
+            int goff = (row0 + r) * A.wp + gc;                                    // word offset into this card's plane
+            unsigned sdst = (unsigned)__cvta_generic_to_shared(tile + r * SWW_P + c);
+            const int gstep = 16 * A.wp;
+            if (c < nW) {
+                for (; r < nR; r += 16, goff += gstep, sdst += 16 * SWW_P * 4) {
+                    const bool ok = cin && (unsigned)(row0 + r) < (unsigned)A.h;
+                    const uint32_t *src = ok ? bits + goff : bits;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(sdst), "l"(src), "r"(ok ? 4 : 0) : "memory");
+                }
             }
         } else {
             for (int i = tid; i < nR * SWW_P; i += 256) {
