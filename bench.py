@@ -337,8 +337,9 @@ def run_gpu(args, rank, local_rank, world):
     for i in range(D):
         cards[i::D] = torch.from_numpy(bins[i]).to(dev)
     torch.cuda.synchronize()
-    out_v = np.zeros((args.cards, N_ANGLES), np.float64)
-    out_h = np.zeros((args.cards, N_ANGLES), np.float64)
+    # pinned result buffers: the std-devs come back with an asynchronous copy, not through pageable staging
+    out_v = torch.zeros((args.cards, N_ANGLES), dtype=torch.float64).pin_memory().numpy()
+    out_h = torch.zeros((args.cards, N_ANGLES), dtype=torch.float64).pin_memory().numpy()
 
     def step():
         v, h = ctx.projection_sweep_batch(cards.data_ptr(), args.cards, W, H, M, out=(out_v, out_h))
@@ -720,7 +721,7 @@ def main():
     ap.add_argument("--oracle-cards", dest="oracle_cards", type=int, default=2,
                     help="distinct cards whose 300 std-dev pairs are compared with the oracle (rank 0, untimed)")
     ap.add_argument("--default-op-cards", dest="default_op_cards", type=int, default=128)
-    ap.add_argument("--hough-batch", dest="hough_batch", type=int, default=32, help="A4 cards in flight in the config-2 batch line (0 = skip)")
+    ap.add_argument("--hough-batch", dest="hough_batch", type=int, default=36, help="A4 cards in flight in the config-2 batch line (0 = skip); 36 clusters of 4 CTAs fill 144 of the 148 SMs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the configs 2 / 3 / 5 / default-op block")
     ap.add_argument("--no-config5", action="store_true")

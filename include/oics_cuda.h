@@ -89,6 +89,12 @@ OICS_API int32_t oics_set_stream(oics_ctx *ctx, void *cuda_stream);
 OICS_API int32_t oics_synchronize(oics_ctx *ctx);
 /* Number of kernels this context has launched since creation (bench evidence). */
 OICS_API int64_t oics_launch_count(oics_ctx *ctx);
+/* Page-locked host memory for the buffers a caller hands to the batch entries: copies from / to pinned memory
+ * are asynchronous and overlap the kernels (pageable buffers are staged by the driver and serialise the
+ * pipeline).  No context needed; free with oics_free_pinned.  The reference allocates its Mats on the heap
+ * (imread, transfer.rs:43): this replaces that allocation on the caller's side of the boundary. */
+OICS_API int32_t oics_alloc_pinned(size_t bytes, void **out);
+OICS_API void oics_free_pinned(void *p);
 /* Opt-in per-kernel timing of everything this context launches (CUDA events around each launch on its own
  * stream; no profiler, no added synchronisation).  oics_profile(ctx, 1) clears and starts, (ctx, 0) stops.
  * oics_profile_report synchronises the device and writes a JSON array of

@@ -41,6 +41,8 @@ SIGNATURES = {
     "oics_set_stream": (_i32, [_ctx, C.c_void_p]),
     "oics_synchronize": (_i32, [_ctx]),
     "oics_launch_count": (C.c_int64, [_ctx]),
+    "oics_alloc_pinned": (_i32, [_sz, C.POINTER(C.c_void_p)]),
+    "oics_free_pinned": (None, [C.c_void_p]),
     "oics_profile": (_i32, [_ctx, _i32]),
     "oics_profile_report": (_i32, [_ctx, C.c_char_p, _sz, C.POINTER(_sz)]),
     "oics_last_sweep_kernel_ms": (_i32, [_ctx, _dp, _ip]),

@@ -192,6 +192,29 @@ def hough_dims(w, h, rho=1.0, theta=math.pi / 180.0):
     return na.value, nr.value
 
 
+class PinnedArray:
+    """A page-locked uint8 host buffer (oics_alloc_pinned) exposed as a numpy array: `.array`.
+    Keep the object alive as long as views of the array are in use."""
+
+    def __init__(self, nbytes: int):
+        self._lib = _lib.load()
+        self._p = C.c_void_p()
+        check(self._lib.oics_alloc_pinned(int(nbytes), C.byref(self._p)))
+        self.array = np.ctypeslib.as_array(C.cast(self._p, C.POINTER(C.c_uint8)), shape=(int(nbytes),))
+
+    def close(self):
+        if getattr(self, "_p", None) is not None and self._p.value:
+            self.array = None
+            self._lib.oics_free_pinned(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # --------------------------------------------------------------------------- device context
 class Context:
     """One CUDA context handle (oics_ctx): device scratch + stream.  Use one per host thread."""

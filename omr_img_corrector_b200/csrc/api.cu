@@ -1,6 +1,7 @@
 // The compute entry points of include/oics_cuda.h: argument checks, host/device
 // staging, and the reference's call sequences expressed over the device kernels.
 #include <cmath>
+#include <cstdlib>
 
 #include "common.h"
 
@@ -512,7 +513,8 @@ OICS_API int32_t oics_result_from_edges_detection_batch(oics_ctx *ctx, const uin
     const bool dev_in = is_device_ptr(srcs);
     // cards in flight: bounded by the per-card Hough scratch (7 B per pixel + the accumulator)
     const size_t per_card = (size_t)w * h * 7 + (size_t)180 * ((size_t)(w + h) * 2 + 1) * 4 + card_bytes;
-    const int chunk = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)3 << 30) / per_card));
+    // and by the device: 37 clusters of 4 CTAs are co-resident on 148 SMs
+    const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, ctx->sm_count / 4), ((size_t)4 << 30) / per_card));
     for (int c0 = 0; c0 < n_cards; c0 += chunk) {
         const int nb = std::min(chunk, n_cards - c0);
         std::vector<const uint8_t *> ptrs((size_t)nb);
@@ -783,14 +785,18 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // cards per sub-batch: 8 A4 cards (209 MB) amortise the per-sub-batch host round trip (rule A needs the
     // std-devs on the host); small cards get proportionally more, up to 64 (the file path decodes at most 8
     // files at a time, one stream each)
-    const int B_max = files ? 8 : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
+    // files: the cards of a sub-batch are decoded concurrently, one stream each -- the Huffman synchronisation is
+    // latency-bound per card, so cards in flight are what fills the device (OICS_FILES_SUBBATCH: tuning)
+    int files_b = 16;
+    if (const char *fb = getenv("OICS_FILES_SUBBATCH")) files_b = std::max(1, std::min(OICS_JD_SLOTS - 1, atoi(fb)));
+    const int B_max = files ? files_b : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
     // with host buffers on either side the copies of one sub-batch overlap the kernels of another: keep at least
     // eight stages in the pipeline; device-resident batches have nothing to overlap and take the largest sub-batch
     bool any_host_dst = false;
     if (dsts)
         for (int c = 0; c < n_cards && !any_host_dst; c++) any_host_dst = dsts[c] && !is_device_ptr(dsts[c]);
     const bool pipelined = files || !is_device_ptr(bgrs) || any_host_dst;
-    const int B_target = pipelined ? std::max(8, std::min(B_max, cdiv(n_cards, 8))) : B_max;
+    const int B_target = files ? B_max : pipelined ? std::max(8, std::min(B_max, cdiv(n_cards, 8))) : B_max;
     const int B = std::min<int>(n_cards, B_target);
     std::vector<int32_t> file_status((size_t)n_cards, OICS_OK);
     const int n_sub = cdiv(n_cards, B);
@@ -818,7 +824,8 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // is full or the batch ends -- the reference's concurrency (one OS thread per card, thread_pool.rs:41-73)
     // instead of one 20-100 ms sequential transform stalling every sub-batch.
     const size_t hough_per_card = (size_t)w * h * 7 + (size_t)180 * ((size_t)(w + h) * 2 + 1) * 4;
-    const int FQ = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)3 << 30) / (hough_per_card + card_bytes + out_card_cap)));
+    const int FQ = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, ctx->sm_count / 4),
+                                                            ((size_t)4 << 30) / (hough_per_card + card_bytes + out_card_cap)));
     if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_totals.ensure((size_t)std::max(B, FQ) * 2 * sizeof(unsigned long long)));
     if (jpeg_quality && dsts) OICS_TRY(ctx->jpeg_raw.ensure(out_card_cap));   // the deskewed pixels of the card being encoded
     struct Deferred {

@@ -102,7 +102,7 @@ struct Profiler {
 
 }  // namespace oics
 
-#define OICS_JD_SLOTS 9
+#define OICS_JD_SLOTS 33
 
 struct oics_ctx {
     int device = 0;

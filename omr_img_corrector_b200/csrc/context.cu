@@ -263,6 +263,28 @@ OICS_API int32_t oics_synchronize(oics_ctx *ctx)
 
 OICS_API int64_t oics_launch_count(oics_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+OICS_API int32_t oics_alloc_pinned(size_t bytes, void **out)
+{
+    if (!out || bytes == 0) {
+        set_error("invalid argument: out, bytes");
+        return OICS_ERR_INVALID_ARG;
+    }
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *out = nullptr;
+        set_error("cudaMallocHost(%zu) failed: %s", bytes, cudaGetErrorString(e));
+        return e == cudaErrorMemoryAllocation ? OICS_ERR_NOMEM : OICS_ERR_CUDA;
+    }
+    return OICS_OK;
+}
+
+OICS_API void oics_free_pinned(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
 OICS_API int32_t oics_profile(oics_ctx *ctx, int32_t enable)
 {
     CtxGuard g(ctx, __func__);

@@ -33,42 +33,78 @@ class Task:
     output_path: str = ""
 
 
+class _HostBuffer:
+    """Page-locked when the CUDA runtime can provide it, pageable otherwise (a buffer, not a compute path)."""
+
+    def __init__(self, nbytes: int):
+        self._pin = None
+        try:
+            self._pin = api.PinnedArray(nbytes)
+            self.array = self._pin.array
+        except api.OicsError:
+            self.array = np.empty(nbytes, np.uint8)
+
+    def close(self):
+        if self._pin is not None:
+            self._pin.close()
+        self.array = None
+
+
 def run_tasks(ctx: "api.Context", tasks: List[Task], projection_max_angle: int, projection_angle_step: float,
               projection_max_width: int, projection_max_height: int, hough_min_line_length: float,
               hough_max_line_gap: float, emit: Callable[[str, dict], None],
-              write: Optional[Callable[[str, np.ndarray], None]] = None) -> None:
-    """Runs the tasks and emits the reference's events through `emit(event_name, payload)`."""
+              write: Optional[Callable[[str, np.ndarray], None]] = None, chunk: int = 32) -> None:
+    """Runs the tasks and emits the reference's events through `emit(event_name, payload)`.
+
+    The tasks of one card size go through `oics_correct_batch` in chunks of `chunk` cards: `start_running_task`
+    is emitted when a chunk is handed to the device and every `task_completed` of the chunk as soon as the chunk
+    returns -- the reference emits per task as its thread finishes (task.rs:32-67); a chunk is the unit the
+    pipeline completes.  Cards are gathered into, and deskewed cards returned through, page-locked buffers
+    (oics_alloc_pinned) so the copies overlap the kernels."""
     by_shape = {}
     for t in tasks:
         by_shape.setdefault(tuple(t.card.shape), []).append(t)
     for shape, group in by_shape.items():
-        for t in group:
-            emit("start_running_task", {"task_id": t.task_id})
         if len(shape) != 3 or shape[2] != 3:
             for t in group:
+                emit("start_running_task", {"task_id": t.task_id})
                 emit("task_completed", {"task_id": t.task_id, "output_path": t.output_path, "result": "error"})
             continue
         h, w = shape[:2]
         side = int(np.ceil((w + h) * 0.70710678118654757)) + 2          # CONTAIN bound of any rotation
-        outs = [np.empty(side * side * 3, np.uint8) for _ in group] if write else None
+        n_chunk = max(1, min(chunk, len(group)))
+        card_bytes, out_bytes = h * w * 3, side * side * 3
+        pin_in = _HostBuffer(n_chunk * card_bytes)
+        pin_out = _HostBuffer(n_chunk * out_bytes) if write else None
         try:
-            ang, need, stat, sizes = ctx.correct_batch(np.stack([t.card for t in group]), projection_max_angle,
-                                                       projection_angle_step, projection_max_width,
-                                                       projection_max_height, hough_min_line_length,
-                                                       hough_max_line_gap, outs=outs)
-        except api.OicsError:
-            for t in group:
-                emit("task_completed", {"task_id": t.task_id, "output_path": t.output_path, "result": "error"})
-            continue
-        for i, t in enumerate(group):
-            if stat[i] != 0:
-                result = "error"                                            # task.rs:58-62: any Err
-            else:
-                result = "debatable" if need[i] else "finished"             # task.rs:47-57
-                if write:
-                    dw, dh = int(sizes[i][0]), int(sizes[i][1])
-                    write(t.output_path, outs[i][:dw * dh * 3].reshape(dh, dw, 3))
-            emit("task_completed", {"task_id": t.task_id, "output_path": t.output_path, "result": result})
+            for c0 in range(0, len(group), n_chunk):
+                part = group[c0:c0 + n_chunk]
+                cards = pin_in.array[:len(part) * card_bytes].reshape(len(part), h, w, 3)
+                for i, t in enumerate(part):
+                    emit("start_running_task", {"task_id": t.task_id})
+                    cards[i] = t.card
+                outs = [pin_out.array[i * out_bytes:(i + 1) * out_bytes] for i in range(len(part))] if write else None
+                try:
+                    ang, need, stat, sizes = ctx.correct_batch(cards, projection_max_angle, projection_angle_step,
+                                                               projection_max_width, projection_max_height,
+                                                               hough_min_line_length, hough_max_line_gap, outs=outs)
+                except api.OicsError:
+                    for t in part:
+                        emit("task_completed", {"task_id": t.task_id, "output_path": t.output_path, "result": "error"})
+                    continue
+                for i, t in enumerate(part):
+                    if stat[i] != 0:
+                        result = "error"                                            # task.rs:58-62: any Err
+                    else:
+                        result = "debatable" if need[i] else "finished"             # task.rs:47-57
+                        if write:
+                            dw, dh = int(sizes[i][0]), int(sizes[i][1])
+                            write(t.output_path, outs[i][:dw * dh * 3].reshape(dh, dw, 3))
+                    emit("task_completed", {"task_id": t.task_id, "output_path": t.output_path, "result": result})
+        finally:
+            pin_in.close()
+            if pin_out is not None:
+                pin_out.close()
 
 
 @dataclass

@@ -933,8 +933,8 @@ def _fallback_card(orc, i):
 
 
 def test_batched_hough_fallback_equals_one_by_one(ctx, orc):
-    """omr.rs:352-403 for a batch in which EVERY card takes the Hough fallback: 70 cards = three flushes of the
-    deferred queue (32 clusters in flight per PPHT launch).  Angle, need_check and deskewed pixels must equal
+    """omr.rs:352-403 for a batch in which EVERY card takes the Hough fallback: 70 cards = two or three flushes of the
+    deferred queue (up to 37 clusters in flight per PPHT launch).  Angle, need_check and deskewed pixels must equal
     omr::correct_default card by card, the oracle on a sample, and the JPEG variant must encode those pixels."""
     cards = np.stack([_fallback_card(orc, i) for i in range(70)])
     params = (5, 0.5, 26, 30, 50.0, 5.0)
