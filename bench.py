@@ -406,8 +406,34 @@ def run_gpu(args, rank, local_rank, world):
             host_files[i, :len(d)] = torch.frombuffer(bytearray(d), dtype=torch.uint8)
             files.append(host_files[i].numpy()[:len(d)])
 
+        # the reference runs correct_default on `MAX_WORKERS_COUNT` OS threads at once (thread_pool.rs:41-73); the
+        # library's rule is one context per host thread (oics_cuda.h).  With --e2e-contexts T > 1 the files of a step
+        # are split over T host threads, each with its own context and stream on this GPU, so one context's host
+        # round trips (rule A between the sweep and the warp of a sub-batch) are covered by another's kernels.
+        T = max(1, args.e2e_contexts)
+        ctxs = [ctx] + [api.Context(local_rank) for _ in range(T - 1)]
+        parts = [list(range(t, E, T)) for t in range(T)]
+
+        def files_part(t):
+            idx = parts[t]
+            return ctxs[t].correct_batch_files([files[i] for i in idx], MAX_ANGLE, STEP, 0, 0, 125.0, 15.0,
+                                               outs=[outs[i] for i in idx], jpeg_quality=100)
+
         def e2e_files_step():
-            return ctx.correct_batch_files(files, MAX_ANGLE, STEP, 0, 0, 125.0, 15.0, outs=outs, jpeg_quality=100)
+            if T == 1:
+                return files_part(0)
+            res = [None] * T
+            ths = [threading.Thread(target=lambda t=t: res.__setitem__(t, files_part(t))) for t in range(T)]
+            [th.start() for th in ths]
+            [th.join() for th in ths]
+            for c in ctxs[1:]:
+                c.synchronize()
+            ang_, need_, stat_ = np.zeros(E), np.zeros(E, bool), np.zeros(E, np.int32)
+            sizes_, fsz_ = np.zeros((E, 2), np.int32), np.zeros(E, np.int64)
+            for t in range(T):
+                a_, n_, s_, z_, f_ = res[t]
+                ang_[parts[t]], need_[parts[t]], stat_[parts[t]], sizes_[parts[t]], fsz_[parts[t]] = a_, n_, s_, z_, f_
+            return ang_, need_, stat_, sizes_, fsz_
 
         for _ in range(2):
             ang3, need3, stat3, sizes3, fsz3 = e2e_files_step()
@@ -426,7 +452,8 @@ def run_gpu(args, rank, local_rank, world):
                "what": "oics_correct_batch_files: JPEG (quality 100) files in pinned host memory in, JPEG files out; "
                        "decode, deskew and encode on the device",
                "h2d_bytes_per_step": int(sum(f.size for f in files)), "d2h_bytes_per_step": int(fsz3.sum()) + E * 16,
-               "cards_per_gpu_per_step": E, "steps": ksteps, "skew_not_recovered": f_not_recovered,
+               "cards_per_gpu_per_step": E, "steps": ksteps, "host_threads_and_contexts_per_gpu": T,
+               "skew_not_recovered": f_not_recovered,
                "oracle": oracle_files, "numa_node": numa}
 
         # (2) side fields: raw pixels over PCIe (26 MB in + 33 MB out per card), fewer steps
@@ -718,6 +745,8 @@ def main():
     ap.add_argument("--e2e-cards", dest="e2e_cards", type=int, default=128)
     ap.add_argument("--e2e-distinct", dest="e2e_distinct", type=int, default=8)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=10)
+    ap.add_argument("--e2e-contexts", dest="e2e_contexts", type=int, default=1,
+                    help="host threads (one context each) that share a GPU in the file-to-file e2e")
     ap.add_argument("--oracle-cards", dest="oracle_cards", type=int, default=2,
                     help="distinct cards whose 300 std-dev pairs are compared with the oracle (rank 0, untimed)")
     ap.add_argument("--default-op-cards", dest="default_op_cards", type=int, default=128)

@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *
 // k of the block being filled, block bi of the MCU).  One step = one Huffman symbol plus its value
 // bits.  SINK receives (block ordinal since the start, zigzag position, value) of every coefficient
 // (the DC value is the DIFFERENCE; prediction is a later scan).
-#define JD_SUB 1024   // bits per subsequence
+#define JD_SUB 1024   // bits per subsequence (r02m: 2048 measured -- every pass twice as long on one card, the same cards/s in the batch)
 
 struct JdecShared {
     uint16_t lut[6][256];
@@ -778,8 +778,10 @@ struct JdecSlot {
 static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
 {
     const unsigned gs = (unsigned)((S.nsub + 127) / 128);
+    static const char *const kRoundNames[] = {"jdec_sync_kernel<round0>", "jdec_sync_kernel<chain 1>", "jdec_sync_kernel<chain 2>",
+                                              "jdec_sync_kernel<chain 3>", "jdec_sync_kernel<chain 4>", "jdec_sync_kernel<chain 5+>"};
     for (int r = 1; r <= rounds; r++) {
-        ProfScope ps(ctx, "jdec_sync_kernel<chain>", 0.0, S.st);
+        ProfScope ps(ctx, kRoundNames[r < 5 ? r : 5], 0.0, S.st);
         jdec_sync_kernel<<<gs, 128, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used,
                                                 S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags, S.rst, S.nrst);
     }

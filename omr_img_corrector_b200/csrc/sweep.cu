@@ -281,7 +281,12 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
 // integers, any order), then a strictly sequential sum of (c - mean)^2 with each
 // square rounded before the add (powf(2.0)), divided by n, square root.  One warp
 // per vector: lanes stage a chunk, lane 0 runs the dependent f64 chain.
-static constexpr int FIN_CHUNK = 1024;
+// The pass is bound by the LATENCY of the ordered sum (one dependent DADD per element on lane 0, ~26 cycles
+// each with its shared-memory operand), so what matters is how many chains an SM holds: a 256-element staging
+// chunk keeps a CTA at 4 KB of shared memory and 32 CTAs (64 chains) resident per SM.  (Measured and rejected,
+// r02i/j: 32 chains per warp, every lane on its own -- FP64 issue then bounds it, slower; tabulating the
+// squares per distinct count -- no gain, the squares were never the limiter.)
+static constexpr int FIN_CHUNK = 256;
 
 __device__ double seq_std_dev(int *__restrict__ v, int n, double *stage, int lane, long long *sum_out,
                               long long *sq_out, bool zero_after)
@@ -307,7 +312,7 @@ __device__ double seq_std_dev(int *__restrict__ v, int n, double *stage, int lan
         for (int i = lane; i < m; i += 32) {
             const double d = __dsub_rn((double)v[base + i], mean);
             stage[i] = __dmul_rn(d, d);
-            if (zero_after) v[base + i] = 0;   // the next launch accumulates into a clean buffer: no memset pass
+            if (zero_after) v[base + i] = 0;
         }
         __syncwarp();
         // ... lane 0 runs the strictly sequential sum: one dependent DADD per element
@@ -351,6 +356,9 @@ __global__ void __launch_bounds__(64) sweep_finalize_kernel(int *__restrict__ co
         }
     }
 }
+
+// (Measured and rejected, r02i: a finalize pass with 32 vectors per warp and every lane on its own chain --
+// the FP64 lane-operations are the same, and they, not latency, bound the pass.)
 
 // Plain zero counts of an image as is (transfer::get_projection_standard_deviations
 // on an un-rotated Mat): identity sampling of the bit plane.
@@ -644,11 +652,10 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         const uint32_t *bits_base = ctx->bits.as<uint32_t>() - (size_t)packed_first * A.bits_card_words;
         for (int a0 = 0; a0 < n_angles; a0 += angles_per_chunk) {
             const int a1 = std::min(n_angles, a0 + angles_per_chunk), na = a1 - a0;
-            // the finalize pass zeroes what it has read, so only a region it has not cleaned yet needs a memset
-            const size_t need_clean = (size_t)nc * na * per_item;
-            if (ctx->counts_clean < need_clean) OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, need_clean, st));
-            const bool keep_counts = d_counts_out && c0 == 0;
-            ctx->counts_clean = keep_counts ? 0 : std::max(ctx->counts_clean, need_clean);
+            // (measured and rejected: letting the finalize pass clear what it has read instead of this memset --
+            // the latency-bound 64-thread CTAs take 2x as long with the extra stores, r02h)
+            OICS_CUDA_TRY(cudaMemsetAsync(ctx->counts.p, 0, (size_t)nc * na * per_item, st));
+            const bool keep_counts = true;
             // word-kernel planes for the fast angles of this range
             const int f_lo = (int)(std::lower_bound(fast.begin(), fast.end(), a0) - fast.begin());
             const int f_hi = (int)(std::lower_bound(fast.begin(), fast.end(), a1) - fast.begin());

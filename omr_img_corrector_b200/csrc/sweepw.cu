@@ -267,7 +267,7 @@ __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, co
         const int xq = p.x + arefp, yq = p.y + brefp;
         const int cb = xq >> 10;
         const uint32_t *src = tile + (yq >> 10) * SWW_P + (cb >> 5);
-        const int sh = cb & 31;
+        const int sh = cb;   // the funnel shift wraps its amount modulo 32: no mask needed
         uint32_t v;
         if (S1 == 0) v = assemble_word<KR, false>(src, sh, m.x, m.y, 0u, Q);
         else v = assemble_word<KR, true>(src, sh, m.x, m.y, S1 & ~m.y, Q);
