@@ -782,14 +782,14 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     if (n_cards == 0) return OICS_OK;
     const bool dev_in = !files && is_device_ptr(bgrs);
     const size_t row = (size_t)w * 3, card_bytes = row * h;
-    // cards per sub-batch: 8 A4 cards (209 MB) amortise the per-sub-batch host round trip (rule A needs the
-    // std-devs on the host); small cards get proportionally more, up to 64 (the file path decodes at most 8
-    // files at a time, one stream each)
+    // cards per sub-batch: 16 A4 cards (418 MB) amortise the per-sub-batch host round trip (rule A needs the
+    // std-devs on the host) and share one read of the sweep's plane set; small cards get proportionally more,
+    // up to 64
     // files: the cards of a sub-batch are decoded concurrently, one stream each -- the Huffman synchronisation is
     // latency-bound per card, so cards in flight are what fills the device (OICS_FILES_SUBBATCH: tuning)
     int files_b = 16;
     if (const char *fb = getenv("OICS_FILES_SUBBATCH")) files_b = std::max(1, std::min(OICS_JD_SLOTS - 1, atoi(fb)));
-    const int B_max = files ? files_b : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)209 << 20) / std::max<size_t>(1, card_bytes)));
+    const int B_max = files ? files_b : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
     // with host buffers on either side the copies of one sub-batch overlap the kernels of another: keep at least
     // eight stages in the pipeline; device-resident batches have nothing to overlap and take the largest sub-batch
     bool any_host_dst = false;
