@@ -787,7 +787,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // up to 64
     // files: the cards of a sub-batch are decoded concurrently, one stream each -- the Huffman synchronisation is
     // latency-bound per card, so cards in flight are what fills the device (OICS_FILES_SUBBATCH: tuning)
-    int files_b = 16;
+    int files_b = (int)std::max<size_t>(8, std::min<size_t>(OICS_JD_SLOTS - 1, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
     if (const char *fb = getenv("OICS_FILES_SUBBATCH")) files_b = std::max(1, std::min(OICS_JD_SLOTS - 1, atoi(fb)));
     const int B_max = files ? files_b : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
     // with host buffers on either side the copies of one sub-batch overlap the kernels of another: keep at least

@@ -531,9 +531,10 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         std::vector<int> kr_of;  // class of fast[k]
         for (int i = 0; i < n_angles; i++) {
             int kr = 0;
-            if (allow_word && !cls[i].bad && cls[i].rows >= 2 && cls[i].rows <= SWW_KRMAX &&
+            // class = source rows per word, + 256 when the angle has two-column steps (its own kernel body)
+            if (allow_word && !(cls[i].bad & 1) && cls[i].rows >= 2 && cls[i].rows <= SWW_KRMAX &&
                 sweepw_group_fits(inv.data(), i, 1, cls[i].rows, w, h))
-                kr = cls[i].rows;
+                kr = cls[i].rows | ((cls[i].bad & 2) ? 256 : 0);
             if (!kr) { cache.general.push_back(i); continue; }
             // extend the last group: consecutive angle, same class, same chunk, footprints share a tile
             bool extend = false;
@@ -541,7 +542,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                 const SweepCache::Group &g = cache.groups.back();
                 extend = g.count < gmax && g.kr == kr && g.first + g.count == i &&
                          g.first / angles_per_chunk == i / angles_per_chunk &&
-                         sweepw_group_fits(inv.data(), g.first, g.count + 1, kr, w, h);
+                         sweepw_group_fits(inv.data(), g.first, g.count + 1, kr & 255, w, h);
             }
             if (extend) cache.groups.back().count++;
             else cache.groups.push_back({(int)cache.fast.size(), 1, kr, i});
@@ -551,7 +552,7 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
         std::stable_sort(cache.groups.begin(), cache.groups.end(), [&](const SweepCache::Group &a, const SweepCache::Group &b) {
             const int ca = a.first / angles_per_chunk, cb = b.first / angles_per_chunk;
             if (ca != cb) return ca < cb;
-            return a.kr > b.kr;
+            return (a.kr & 255) > (b.kr & 255);
         });
         const int n_chunks = cdiv(n_angles, angles_per_chunk);
         cache.chunk_group_begin.assign((size_t)n_chunks + 1, (int)cache.groups.size());

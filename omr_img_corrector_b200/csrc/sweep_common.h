@@ -53,7 +53,8 @@ static constexpr size_t SWW_PLANES_PAD = 256 * sizeof(uint2);
 // many source rows per output word.
 struct SweepWClass {
     int rows;   // max over word columns of (source rows one word draws from); 0 = not computed
-    int bad;    // != 0: a column map outside the supported range (scale, shear, |angle| too large)
+    int bad;    // bit 0: a column map outside the supported range (scale, shear, |angle| too large);
+                // bit 1: some word has a two-column step (the kernel then needs the third shifted copy of the window)
 };
 
 struct SweepWPlan {

@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(32) sweepw_meta_kernel(SweepTables T, int w, i
         m[15] = 0;
         atomicMax(&cls[ang].rows, hmax + 2);
         if (!all_ok) atomicOr(&cls[ang].bad, 1);
+        if (s1) atomicOr(&cls[ang].bad, 2);   // bit 1: some word of this angle has a two-column step (|angle| > 14.6 degrees)
     }
 }
 
@@ -247,7 +248,7 @@ __device__ __forceinline__ int unpack_columns(uint32_t c0, uint32_t c1, uint32_t
 // Four 32-row groups of one word column: lane = row.  `sxy`, `rowp`, `plp` already point at
 // this lane's first row; cd[] holds the planes of these four words (prefetched one round
 // ahead) and is refilled for the next round.
-template <int KR, bool CHECK>
+template <int KR, bool NT2, bool CHECK>
 __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, const int2 *__restrict__ sxy,
                                            uint8_t *__restrict__ rowp, const uint2 *__restrict__ plp, uint2 (&cd)[4],
                                            int arefp, int brefp, uint32_t S1, const uint32_t (&Q)[SWW_KRMAX - 1],
@@ -268,9 +269,10 @@ __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, co
         const int cb = xq >> 10;
         const uint32_t *src = tile + (yq >> 10) * SWW_P + (cb >> 5);
         const int sh = cb;   // the funnel shift wraps its amount modulo 32: no mask needed
-        uint32_t v;
-        if (S1 == 0) v = assemble_word<KR, false>(src, sh, m.x, m.y, 0u, Q);
-        else v = assemble_word<KR, true>(src, sh, m.x, m.y, S1 & ~m.y, Q);
+        // NT2 is a property of the whole angle (class bit): no per-word test of S1
+        const uint32_t v0 = NT2 ? assemble_word<KR, true>(src, sh, m.x, m.y, S1 & ~m.y, Q)
+                                : assemble_word<KR, false>(src, sh, m.x, m.y, 0u, Q);
+        uint32_t v = v0;
         if (CHECK) {
             const bool valid = 32 * u + lane < rows_total;
             v = valid ? v : 0u;
@@ -294,7 +296,7 @@ __device__ __forceinline__ void four_words(const uint32_t *__restrict__ tile, co
     c4 ^= t2;
 }
 
-template <int KR>
+template <int KR, bool NT2>
 __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, const int card_local)
 {
     extern __shared__ uint32_t smem[];
@@ -419,11 +421,11 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
             for (int u = 0; u < 4; u++) cd[u] = __ldg(plp + 32 * u);
             int done = 0;
             for (; done + 128 <= th; done += 128) {  // four full 32-row groups
-                four_words<KR, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2, c3, c4);
+                four_words<KR, NT2, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2, c3, c4);
                 sxy += 128; rowp += 128; plp += 128;
             }
             if (done < th)   // the tile's last, partial round: row 32 u + lane is valid iff < th - done
-                four_words<KR, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done, lane, c0, c1, c2, c3, c4);
+                four_words<KR, NT2, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done, lane, c0, c1, c2, c3, c4);
             // unpack: lane L receives bit L of every lane's plane = pixel 31 - L of the word
             const uint32_t hi = c2 | c3 | c4;
             if (__any_sync(0xffffffffu, (c0 | c1 | hi) != 0)) {
@@ -464,17 +466,32 @@ __global__ void __launch_bounds__(256, 4) sweepw_kernel(const SweepWArgs A)
 {
     const int grp = blockIdx.y / A.n_cards, card_local = blockIdx.y - grp * A.n_cards;
     const int4 gd = A.G.groups[grp];
+    // gd.z = source rows per word (+ 256: the angles of the group have two-column steps)
     switch (gd.z) {
-    case 2: sweepw_body<2>(A, gd, card_local); break;
-    case 3: sweepw_body<3>(A, gd, card_local); break;
-    case 4: sweepw_body<4>(A, gd, card_local); break;
-    case 5: sweepw_body<5>(A, gd, card_local); break;
-    case 6: sweepw_body<6>(A, gd, card_local); break;
-    case 7: sweepw_body<7>(A, gd, card_local); break;
-    case 8: sweepw_body<8>(A, gd, card_local); break;
-    case 9: sweepw_body<9>(A, gd, card_local); break;
-    case 10: sweepw_body<10>(A, gd, card_local); break;
-    default: sweepw_body<11>(A, gd, card_local); break;
+    case 2: sweepw_body<2, false>(A, gd, card_local); break;
+    case 3: sweepw_body<3, false>(A, gd, card_local); break;
+    case 4: sweepw_body<4, false>(A, gd, card_local); break;
+    case 5: sweepw_body<5, false>(A, gd, card_local); break;
+    case 6: sweepw_body<6, false>(A, gd, card_local); break;
+    case 7: sweepw_body<7, false>(A, gd, card_local); break;
+    case 8: sweepw_body<8, false>(A, gd, card_local); break;
+    case 9: sweepw_body<9, false>(A, gd, card_local); break;
+    case 10: sweepw_body<10, false>(A, gd, card_local); break;
+    case 11: sweepw_body<11, false>(A, gd, card_local); break;
+    case 256 + 8: sweepw_body<8, true>(A, gd, card_local); break;
+    case 256 + 9: sweepw_body<9, true>(A, gd, card_local); break;
+    case 256 + 10: sweepw_body<10, true>(A, gd, card_local); break;
+    case 256 + 11: sweepw_body<11, true>(A, gd, card_local); break;
+    default:   // a two-column step with few source rows (not a plain rotation): the general body of its row class
+        switch (gd.z & 255) {
+        case 2: sweepw_body<2, true>(A, gd, card_local); break;
+        case 3: sweepw_body<3, true>(A, gd, card_local); break;
+        case 4: sweepw_body<4, true>(A, gd, card_local); break;
+        case 5: sweepw_body<5, true>(A, gd, card_local); break;
+        case 6: sweepw_body<6, true>(A, gd, card_local); break;
+        default: sweepw_body<7, true>(A, gd, card_local); break;
+        }
+        break;
     }
 }
 

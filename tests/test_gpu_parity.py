@@ -999,3 +999,50 @@ def test_edges_detection_batch_equals_single(ctx, orc, dataset_like):
             assert s1[i] == -3, i
         else:
             assert s1[i] == 0 and (o.angle, o.status) == (a1[i], r1[i]), i
+
+
+def _nccl_worker(rank, world, port, out_dir):
+    import os
+    import torch
+    import torch.distributed as dist
+    from omr_img_corrector_b200 import sharded
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        g, a = synth.base_card(7)
+        binary = np.ascontiguousarray(((g[300:1450, 200:1440] > 127) * 255).astype(np.uint8))      # 1240 x 1150
+        d_bin = torch.from_numpy(binary).to(dev)
+        with api.Context(rank) as c:
+            res = sharded.result_from_projection_sharded(c, d_bin, 45, 0.1, 1.0, rank, world, None, dev, rule="a")
+            N, angles, M = api.sweep_matrices(binary.shape[1], binary.shape[0], 45, 0.1, 1.0)
+            v, h = sharded.sweep_sharded_device(c, d_bin, M, rank, world, None, dev)
+            np.savez(os.path.join(out_dir, f"r{rank}.npz"), v=v, h=h, angle=res.angle, status=res.status)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sweep_sharded_nccl_two_gpus(ctx, tmp_path):
+    """BASELINE config 5's exchange at world 2 over NCCL (one process per GPU): oics_sweep_sharded writes each
+    rank's slice into its block of the device exchange buffer, ONE in-place all-gather, exact rule A on every
+    rank.  Both ranks must hold the one-GPU sweep bit for bit and the same decision."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_nccl_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    g, a = synth.base_card(7)
+    binary = np.ascontiguousarray(((g[300:1450, 200:1440] > 127) * 255).astype(np.uint8))
+    N, angles, M = api.sweep_matrices(binary.shape[1], binary.shape[0], 45, 0.1, 1.0)
+    v0, h0 = ctx.projection_sweep(binary, M)
+    ref = api.rule_a(h0, v0, N, 0.1)
+    for r in range(2):
+        R = np.load(tmp_path / f"r{r}.npz")
+        assert np.array_equal(R["v"], v0) and np.array_equal(R["h"], h0)
+        assert (float(R["angle"]), int(R["status"])) == (ref.angle, ref.status)

@@ -275,3 +275,21 @@ def test_transformable_matrix_host_members():
     assert tm.get_mat()[0, 0, 0] == 0 and tm.get_bytes() == bytes(range(24))
     assert tm.scale_self(1.0) is tm                                    # the early-out of transfer.rs:67-69
     assert transfer.TransformableMatrix.default().get_mat().size == 0
+
+
+def test_bench_reference_arm_sample(orc):
+    """bench.py's CPU arm: card-parallel workers, file to file, sweep bounded to a sample of the 300 angles; the
+    two rates it reports are the sweep-only region (`value`) and the whole of correct_default with codecs (`e2e`)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    ref = bench.CpuReference(threads=2, n_sample=2)
+    r = ref.step()
+    assert r["sweep_cards_per_s"] > r["e2e_cards_per_s"] > 0
+    assert abs(r["sweep_cards_per_s"] - 2 / (300 * r["t_angle_s"])) < 1e-9
+    per_card = r["t_decode_s"] + r["t_pre_s"] + 300 * r["t_angle_s"] + r["t_warp_s"] + r["t_encode_s"]
+    assert abs(r["e2e_cards_per_s"] - 2 / per_card) < 1e-9
+    assert "300 sweep angles" in ref.sample_text()
+    cfg_a = bench.workload_config(512, 1, 16, 128)
+    assert cfg_a == bench.workload_config(512, 1, 16, 128) and "workload" in cfg_a     # both arms print the same config

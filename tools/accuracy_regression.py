@@ -64,7 +64,7 @@ def load_cards(ctx, dataset, n_cards):
     return out, "synthetic dataset-like cards (fixture directory absent)"
 
 
-def run(ctx, cards, skews, files_mode=True, oracle_every=97, chunk=128, oracle_threads=None, progress=False):
+def run(ctx, cards, skews, files_mode=True, oracle_every=97, chunk=450, oracle_threads=None, progress=False):
     import torch
     hist = {"SUCCESS": 0, "NOT_SO_RIGHT": 0, "ERROR": 0, "NOT_BELIEVED": 0, "error_status": 0}
     total_mistake, n_total, t_gpu = 0.0, 0, 0.0
@@ -153,7 +153,7 @@ def main():
     ap.add_argument("--cards", type=int, default=0, help="number of cards (0 = every dataset card; 2 synthetic ones without a dataset)")
     ap.add_argument("--skew-step", type=float, default=0.1)
     ap.add_argument("--oracle-every", type=int, default=97, help="check every k-th input against the CPU oracle (0 = none)")
-    ap.add_argument("--chunk", type=int, default=128)
+    ap.add_argument("--chunk", type=int, default=450, help="inputs per oics_correct_batch_files call (the fallback queue is flushed per call)")
     ap.add_argument("--files", dest="files", action="store_true", default=True)
     ap.add_argument("--no-files", dest="files", action="store_false")
     args = ap.parse_args()
