@@ -306,7 +306,6 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
     int *sBox = reinterpret_cast<int *>(tile + SWW_TROWS * SWW_P);                   // the pad words
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int *alist = A.G.alist + gd.x;
     const int n_ang = gd.y;
     const int card = A.G.card0 + card_local;
     const int tx = blockIdx.x % A.tiles_x, ty = blockIdx.x / A.tiles_x;
@@ -320,7 +319,7 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
         // lane -> (angle = lane >> 2, corner = lane & 3)
         int cmin = 0x7fffffff, cmax = -0x7fffffff, rmin = 0x7fffffff, rmax = -0x7fffffff;
         if ((lane >> 2) < n_ang) {
-            const int ang = alist[lane >> 2];
+            const int ang = gd.w + (lane >> 2);
             const int *ad_g = A.T.ad + (size_t)ang * A.T.wpad, *bd_g = A.T.bd + (size_t)ang * A.T.wpad;
             const int2 p = A.T.xy[(size_t)ang * A.T.hpad + ((lane & 1) ? y0 + th - 1 : y0)];
             const int xb = x0 + 32 * nj - 1;
@@ -387,20 +386,20 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
     // per-row {X0, Y0} of the first angle: a 4 KB copy (the tables are padded to whole tiles,
     // rows past the image repeat its last row, so every lane computes in-bounds addresses)
     const int xoff = (colw0 * 32) << 10, yoff = row0 << 10;
-    copy_rows_async(sXY, A.T.xy + (size_t)alist[0] * A.T.hpad + y0, tid);
+    copy_rows_async(sXY, A.T.xy + (size_t)gd.w * A.T.hpad + y0, tid);
     cp_async_wait_all();
     __syncthreads();
 
     const int j = j0 + warp;
     const bool active = warp < nj;
     for (int ai = 0; ai < n_ang; ai++) {
-        const int ang = alist[ai];
+        const int ang = gd.w + ai;   // the angles of a group are consecutive (and so are their places in the fast list)
         const int slot = card_local * A.G.na_chunk + (ang - A.G.a0);
         int *rows_out = A.counts + (size_t)slot * (A.h + A.w);
         int *cols_out = rows_out + A.h;
         uint8_t *rowbuf = sRow + (ai & 1) * (SWW_TJ * SWW_TH);
         if (ai + 1 < n_ang)  // next angle's rows, in flight during this angle's loop
-            copy_rows_async(sXY + ((ai + 1) & 1) * SWW_TH, A.T.xy + (size_t)alist[ai + 1] * A.T.hpad + y0, tid);
+            copy_rows_async(sXY + ((ai + 1) & 1) * SWW_TH, A.T.xy + (size_t)(ang + 1) * A.T.hpad + y0, tid);
         if (active) {
             const uint4 *m4 = reinterpret_cast<const uint4 *>(A.P.meta + ((size_t)ang * A.wj + j) * SWW_META);
             const uint4 ma = __ldg(m4), mb = KR > 5 ? __ldg(m4 + 1) : make_uint4(0, 0, 0, 0);
@@ -411,8 +410,9 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
             for (int r = 0; r < SWW_KRMAX - 1; r++) Q[r] = r < KR - 1 ? Qall[r] : 0u;
             const uint32_t S1 = mc.w;
             const int arefp = (int)md.y - xoff, brefp = (int)md.z - yoff;
-            const int kslot = A.P.kf[ang] - A.P.kf0;
-            const uint2 *plp = A.P.planes + ((size_t)kslot * A.wj + j) * A.h + y0 + lane;
+            const uint32_t kslot = (uint32_t)(gd.x + ai - A.P.kf0);
+            // 32-bit element index: a chunk's planes stay below 2^32 elements (3 GB budget / 8 bytes)
+            const uint2 *plp = A.P.planes + ((kslot * (uint32_t)A.wj + (uint32_t)j) * (uint32_t)A.h + (uint32_t)(y0 + lane));
             const int2 *sxy = sXY + (ai & 1) * SWW_TH + lane;
             uint8_t *rowp = rowbuf + warp * SWW_TH + lane;
             uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;  // bit-sliced column counters (<= 16 rows per lane)
