@@ -313,7 +313,11 @@ def run_gpu(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     ctx = api.Context(local_rank)
-    stream = torch.cuda.Stream(device=dev)
+    # the context's stream above the decoder's per-card streams (created at the default = lowest priority): when
+    # an SM frees resources the sweep / encode CTAs of the main pipeline are placed first and the latency-bound
+    # decode CTAs fill what is left (OICS_BENCH_STREAM_PRIORITY=0 restores equal priorities for A/B runs)
+    prio = int(os.environ.get("OICS_BENCH_STREAM_PRIORITY", "-1"))
+    stream = torch.cuda.Stream(device=dev, priority=prio)
     ctx.set_stream(stream.cuda_stream)
     timed = Timed(torch, dist, stream, dev, world)
     orc = None

@@ -367,9 +367,10 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
             unsigned sdst = (unsigned)__cvta_generic_to_shared(tile + r * SWW_P + c);
             const int gstep = 16 * A.wp;
             if (c < nW) {
+#pragma unroll 4
                 for (; r < nR; r += 16, goff += gstep, sdst += 16 * SWW_P * 4) {
                     const bool ok = cin && (unsigned)(row0 + r) < (unsigned)A.h;
-                    const uint32_t *src = ok ? bits + goff : bits;
+                    const uint32_t *src = bits + (ok ? goff : 0);   // one 32-bit select, one wide add
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(sdst), "l"(src), "r"(ok ? 4 : 0) : "memory");
                 }
             }
@@ -420,9 +421,16 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
 #pragma unroll
             for (int u = 0; u < 4; u++) cd[u] = __ldg(plp + 32 * u);
             int done = 0;
-            for (; done + 128 <= th; done += 128) {  // four full 32-row groups
+            for (; done + 256 <= th; done += 256) {  // two rounds of four full 32-row groups per trip
+                four_words<KR, NT2, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2, c3, c4);
+                four_words<KR, NT2, false>(tile, sxy + 128, rowp + 128, plp + 128, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2,
+                                           c3, c4);
+                sxy += 256; rowp += 256; plp += 256;
+            }
+            if (done + 128 <= th) {
                 four_words<KR, NT2, false>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, 128, lane, c0, c1, c2, c3, c4);
                 sxy += 128; rowp += 128; plp += 128;
+                done += 128;
             }
             if (done < th)   // the tile's last, partial round: row 32 u + lane is valid iff < th - done
                 four_words<KR, NT2, true>(tile, sxy, rowp, plp, cd, arefp, brefp, S1, Q, th - done, lane, c0, c1, c2, c3, c4);
@@ -442,12 +450,18 @@ __device__ __forceinline__ void sweepw_body(const SweepWArgs &A, const int4 gd, 
         // rows: thread t sums the 8 per-column bytes of rows 4t..4t+3 as packed 16-bit lanes
         if (tid < SWW_TH / 4 && 4 * tid < th) {
             const uint32_t *rb = reinterpret_cast<const uint32_t *>(rowbuf) + tid;
-            uint32_t lo = 0, hi = 0;
-            for (int k = 0; k < nj; k++) {
-                const uint32_t v = rb[k * (SWW_TH / 4)];
-                lo += v & 0x00FF00FFu;
-                hi += (v >> 8) & 0x00FF00FFu;
-            }
+            // a byte holds at most 32, so four columns add up inside their bytes (<= 128): two packed sums,
+            // widened to 16-bit lanes once
+            static_assert(SWW_TJ == 8, "the row sums add the columns in two packed groups of four");
+            uint32_t a = 0, b = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (k < nj) a += rb[k * (SWW_TH / 4)];
+#pragma unroll
+            for (int k = 4; k < 8; k++)
+                if (k < nj) b += rb[k * (SWW_TH / 4)];
+            const uint32_t lo = (a & 0x00FF00FFu) + (b & 0x00FF00FFu);
+            const uint32_t hi = ((a >> 8) & 0x00FF00FFu) + ((b >> 8) & 0x00FF00FFu);
             int *ro = rows_out + y0 + 4 * tid;
             const int n = th - 4 * tid;   // rows of this quad inside the tile (bytes past it are stale)
             if (lo & 0xFFFFu) atomicAdd(ro, (int)(lo & 0xFFFFu));
