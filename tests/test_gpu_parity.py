@@ -1046,3 +1046,37 @@ def test_sweep_sharded_nccl_two_gpus(ctx, tmp_path):
         R = np.load(tmp_path / f"r{r}.npz")
         assert np.array_equal(R["v"], v0) and np.array_equal(R["h"], h0)
         assert (float(R["angle"]), int(R["status"])) == (ref.angle, ref.status)
+
+
+def test_profile_report_and_pinned_buffers(ctx, orc, dataset_like):
+    """Measurement plumbing of the boundary: oics_profile / oics_profile_report (CUDA events around every launch,
+    aggregated by kernel with the algorithmic bytes of DESIGN.md section 4) and oics_alloc_pinned buffers as batch
+    inputs and outputs.  The results through pinned buffers equal the pageable ones."""
+    bgr, _ = dataset_like
+    h, w = bgr.shape[:2]
+    pin_in = api.PinnedArray(2 * bgr.size)
+    pin_out = api.PinnedArray(2 * 1800 * 1800 * 3)
+    try:
+        cards = pin_in.array.reshape(2, h, w, 3)
+        cards[0] = bgr
+        cards[1] = bgr[::-1]
+        outs = [pin_out.array[i * 1800 * 1800 * 3:(i + 1) * 1800 * 1800 * 3] for i in range(2)]
+        ctx.profile(True)
+        ang, need, stat, sizes = ctx.correct_batch(cards, 15, 0.5, 0, 0, 125.0, 15.0, outs=outs)
+        rep = ctx.profile_report()
+        ctx.profile(False)
+        assert not stat.any()
+        names = {r["kernel"] for r in rep}
+        assert {"gray_erode_bits_kernel<3>", "pack_bits_kernel", "sweepw_kernel", "sweep_finalize_kernel",
+                "warp_flat_kernel<NEAREST>"} <= names
+        for r in rep:
+            assert r["launches"] >= 1 and r["ms"] > 0 and r["algorithmic_bytes"] >= 0
+        sw = next(r for r in rep if r["kernel"] == "sweepw_kernel")
+        assert sw["algorithmic_bytes"] == 2 * 60 * w * h            # 1 B per (card, angle, pixel) sample
+        ra, rneed, rout = orc.correct_default(np.ascontiguousarray(cards[0]), 15, 0.5, 0, 0, 125.0, 15.0)
+        dw, dh = sizes[0]
+        assert (ang[0], bool(need[0])) == (ra, rneed) and np.array_equal(outs[0][:dw * dh * 3].reshape(dh, dw, 3), rout)
+        assert ctx.profile_report() == []                               # stopped and cleared
+    finally:
+        pin_in.close()
+        pin_out.close()
