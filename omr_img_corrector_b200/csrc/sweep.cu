@@ -119,7 +119,9 @@ __device__ __forceinline__ uint32_t sample_bit(const uint32_t *__restrict__ tile
     } else {
         wv = tile[ry * P + (a >> 15)];
     }
-    const uint32_t top = wv << ((a >> 10) & 31);
+    // rotate instead of shift: bit 31 of the result is pixel sx either way, and the funnel shift wraps its
+    // amount modulo 32, so (a >> 10) needs no mask
+    const uint32_t top = __funnelshift_l(wv, wv, a >> 10);
     return __funnelshift_l(top, acc, 1);  // (acc << 1) | (top >> 31)
 }
 
@@ -230,9 +232,28 @@ __global__ void __launch_bounds__(SW_THREADS) sweep_kernel(const SweepArgs A)
         sXY[i] = make_int2(p.x - xoff, p.y - yoff);
     }
     if (staged) {
-        for (int i = tid; i < nR * nW; i += SW_THREADS) {
-            int r = i / nW, j = i - r * nW;
-            tile[r * P + j] = __ldg(bits + (size_t)(cy0 + r) * A.wp + wx0 + j);
+        // the footprint is clipped to the image, so every staged word exists: asynchronous 4-byte copies with
+        // incremental addresses (a (half-)warp per source row); the integer divide per word of a flat loop was a
+        // fifth of the kernel's instructions on config 5's large angles
+        if (nW <= 32) {
+            const int lanes = nW <= 16 ? 16 : 32, rows_per_pass = SW_THREADS / lanes;
+            const int c = tid & (lanes - 1);
+            int r = tid / lanes;
+            if (c < nW) {
+                const uint32_t *src = bits + (size_t)(cy0 + r) * A.wp + wx0 + c;
+                unsigned sdst = (unsigned)__cvta_generic_to_shared(tile + r * P + c);
+                const size_t gstep = (size_t)rows_per_pass * A.wp;
+                const unsigned sstep = (unsigned)(rows_per_pass * P * 4);
+#pragma unroll 4
+                for (; r < nR; r += rows_per_pass, src += gstep, sdst += sstep)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sdst), "l"(src) : "memory");
+            }
+            asm volatile("cp.async.wait_all;\n" ::: "memory");
+        } else {
+            for (int i = tid; i < nR * nW; i += SW_THREADS) {
+                int r = i / nW, j = i - r * nW;
+                tile[r * P + j] = __ldg(bits + (size_t)(cy0 + r) * A.wp + wx0 + j);
+            }
         }
     }
     // else: footprint larger than the shared-memory budget (strong down-scaling inside
