@@ -31,9 +31,11 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t v, int lane)
     for (int j = 16; j >= 1; j >>= 1) {
         const uint32_t lowmask = j == 16 ? 0x0000FFFFu : j == 8 ? 0x00FF00FFu : j == 4 ? 0x0F0F0F0Fu
                                  : j == 2 ? 0x33333333u : 0x55555555u;
-        uint32_t other = __shfl_xor_sync(0xffffffffu, v, j);
-        if (lane & j) v = (v & ~lowmask) | ((other >> j) & lowmask);
-        else v = (v & lowmask) | ((other << j) & ~lowmask);
+        // one rotate + one select per stage: the bits a plain shift would drop are masked off anyway
+        const uint32_t other = __shfl_xor_sync(0xffffffffu, v, j);
+        const bool up = (lane & j) != 0;
+        const uint32_t keep = up ? ~lowmask : lowmask;
+        v = (v & keep) | (__funnelshift_l(other, other, up ? 32 - j : j) & ~keep);
     }
     return v;
 }
