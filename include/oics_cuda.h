@@ -182,6 +182,17 @@ OICS_API int32_t oics_projection_counts(oics_ctx *ctx, const uint8_t *bin, int32
 /* transfer::get_projection_standard_deviations (transfer.rs:527-536) of an image as is. */
 OICS_API int32_t oics_projection_standard_deviations(oics_ctx *ctx, const uint8_t *bin, int32_t w,
                                                      int32_t h, int32_t stride, double *v_sd, double *h_sd);
+/* NO counterpart in the reference: added for callers that may not
+ * call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  The same result as
+ * oics_projection_standard_deviations, bit for bit, but it allocates NOTHING and takes no context: the
+ * zero counts live in a file-scope static __device__ array (noalloc.cu) of 128 KB that every GPU loading
+ * the library holds until exit.  Limit: w <= 16384 and h <= 16384 -- beyond that OICS_ERR_CAPACITY.
+ * d_bin (8-bit, 1 channel) and d_sd (double[2]: [0] = v_sd, [1] = h_sd) are DEVICE memory of the CURRENT
+ * device; the three kernels are enqueued on cuda_stream (NULL = the default stream) and the call does not
+ * synchronize.  All calls on a device share the array (it is cleared at the start of each call): calls on
+ * one stream follow each other safely, calls that overlap on the GPU race. */
+OICS_API int32_t oics_projection_standard_deviations_static(const uint8_t *d_bin, int32_t w, int32_t h,
+                                                            int32_t stride, double *d_sd, void *cuda_stream);
 
 /* ---- P5: argmax rules (host, exact scalar logic) ------------------------ */
 /* rule A: omr.rs:147-221 */

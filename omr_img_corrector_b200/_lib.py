@@ -65,6 +65,7 @@ SIGNATURES = {
     "oics_projection_sweep_batch": (_i32, [_ctx, _u8p, _i32, _sz, _i32, _i32, _i32, _dp, _i32, C.c_void_p, C.c_void_p]),
     "oics_projection_counts": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _dp, C.c_void_p, C.c_void_p]),
     "oics_projection_standard_deviations": (_i32, [_ctx, _u8p, _i32, _i32, _i32, _dp, _dp]),
+    "oics_projection_standard_deviations_static": (_i32, [_u8p, _i32, _i32, _i32, C.c_void_p, C.c_void_p]),
     "oics_rule_a": (_i32, [_dp, _dp, _i32, _f64, C.POINTER(OmrResultC)]),
     "oics_rule_a_batch": (_i32, [_dp, _dp, _i32, _i32, _f64, _dp, _ip, _ip]),
     "oics_rule_b": (_i32, [_dp, _dp, _i32, _f64, _dp]),

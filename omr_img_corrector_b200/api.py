@@ -129,6 +129,16 @@ def shard_layout(n_angles, world) -> int:
     return per.value
 
 
+def projection_standard_deviations_static(d_bin, d_sd, stream=0) -> None:
+    """oics_projection_standard_deviations_static (no counterpart in the reference): the std-devs of a
+    DEVICE-resident binary image into a DEVICE double[2] (v_sd, h_sd), without any allocation and without
+    a context.  `d_bin`, `d_sd`: objects with data_ptr() (torch CUDA tensors) on the current device;
+    at most 16384 x 16384; enqueued on `stream` (a raw cudaStream_t), not synchronised."""
+    h, w = int(d_bin.shape[0]), int(d_bin.shape[1])
+    check(_lib.load().oics_projection_standard_deviations_static(
+        C.c_void_p(d_bin.data_ptr()), w, h, int(d_bin.stride(0)), C.c_void_p(d_sd.data_ptr()), C.c_void_p(stream)))
+
+
 def shard_unpack(sd, n_angles, world):
     """Gathered exchange buffer sd[world][2][per] -> (v_sd[n], h_sd[n])."""
     sd = np.ascontiguousarray(sd, np.float64)
