@@ -37,6 +37,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # see omr_img_corrector_b200/_lib.py: one work queue per decode stream
 sys.path.insert(0, ROOT)
 
 W, H = 2480, 3508

@@ -7,6 +7,12 @@ from __future__ import annotations
 import ctypes as C
 import os
 
+# The file-to-file batch driver decodes the cards of a sub-batch on one stream each (up to 32): with the CUDA
+# default of 8 hardware work queues those streams alias and 7 decodes run at a time.  Only read at CUDA
+# initialisation, so it is set when the package is imported (a value the caller exported wins); the library's
+# own load-time constructor (context.cu) does the same for hosts that bind the C ABI directly.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(HERE, "liboics_cuda.so")
 

@@ -114,7 +114,7 @@ struct oics_ctx {
     int64_t launches = 0;
     // per-device function attributes / occupancy answers this context has already set up (a context is
     // bound to one device; process-wide statics would leak one device's answer to another)
-    bool attr_sweepw = false, attr_sweeps = false, attr_sweep[5] = {false, false, false, false, false};
+    bool attr_sweepw = false, attr_sweeps = false, attr_jdec = false, attr_sweep[5] = {false, false, false, false, false};
     int canny_blocks_per_sm = 0;
     size_t counts_clean = 0;            // leading bytes of `counts` known to be zero (the finalize pass clears what it read)
     // sweep timing evidence

@@ -178,6 +178,11 @@ OICS_API const char *oics_last_error(void) { return g_err; }
 
 OICS_API int32_t oics_version(void) { return 100; }
 
+// The batch driver keeps up to 32 decode streams busy (jpegdec.cu); the CUDA default of 8 hardware work queues
+// makes them alias.  The variable is read once, at CUDA initialisation: set here, when the library is loaded,
+// unless the host exported its own value (no effect if the process initialised CUDA earlier).
+__attribute__((constructor)) static void oics_on_load(void) { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+
 OICS_API int32_t oics_create(int32_t device, oics_ctx **out)
 {
     if (!out) {
@@ -319,6 +324,26 @@ OICS_API int32_t oics_profile_report(oics_ctx *ctx, char *buf, size_t cap, size_
         a.ms += t;
         a.bytes += e.bytes;
         a.n++;
+    }
+    // OICS_PROFILE_TIMELINE=<prefix>: every launch of the recording as "kernel,start_us,end_us" (relative to the
+    // first launch) into <prefix>.<n>.csv -- the step's timeline across the context's streams
+    if (const char *prefix = getenv("OICS_PROFILE_TIMELINE")) {
+        static int dumps = 0;
+        if (!ctx->prof.entries.empty()) {
+            const std::string path = std::string(prefix) + "." + std::to_string(dumps++) + ".csv";
+            if (FILE *f = fopen(path.c_str(), "w")) {
+                const cudaEvent_t base = ctx->prof.entries.front().e0;
+                for (const ProfEntry &e : ctx->prof.entries) {
+                    float t0 = 0.f, t1 = 0.f;
+                    if (cudaEventElapsedTime(&t0, base, e.e0) != cudaSuccess || cudaEventElapsedTime(&t1, base, e.e1) != cudaSuccess) {
+                        cudaGetLastError();
+                        continue;
+                    }
+                    fprintf(f, "\"%s\",%.1f,%.1f\n", e.name, 1000.0 * t0, 1000.0 * t1);
+                }
+                fclose(f);
+            }
+        }
     }
     std::string out = "[";
     char line[512];

@@ -36,9 +36,30 @@ static const uint8_t d_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 1
                                  30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
 // What the kernels need from the header; uploaded once per file.
+// Huffman lookup in two levels, every entry ready for the walker's two recurrences (cursor, coefficient index):
+//   bits 0-5   bits the symbol consumes: code length + value bits     bits 8-14  what it adds to k: 1 for a DC symbol;
+//   bits 16-19 value bits (the symbol's low nibble)                    run + 1 for a coefficient, 16 for ZRL,
+//   bits 20-24 code length                                             64 for EOB (= the block is complete)
+//   JD_BOTH    a DC table entry that stands for "DC difference 0" AND the EOB behind it (the empty block of a
+//              white card in one lookup): consumes both codes, adds 64
+//   JD_L2      the first JD_LBITS bits are the prefix of longer codes: bits 0-5 = sub-table i, the symbol is
+//              lut2[t][i * 64 + next 6 bits]
+// 0 = not in the tables (an invalid code, or more long prefixes than JD_L2SUBS -- the standard tables have 1 to 6, and
+// long codes are the rare symbols of any table): jdhuff.c's canonical walk decides.
+#define JD_LBITS 10
+#define JD_BOTH 0x80000000u
+#define JD_L2 0x40000000u
+#define JD_L2SUBS 8
+static inline uint32_t jdec_entry(int len, int sym, bool dc)
+{
+    const int s = sym & 15, r = sym >> 4;
+    const int kinc = dc ? 1 : s ? r + 1 : r == 15 ? 16 : 64;
+    return (uint32_t)(len + s) | ((uint32_t)kinc << 8) | ((uint32_t)s << 16) | ((uint32_t)len << 20);
+}
 struct JdecTables {
-    uint16_t lut[6][256];     // [2 * comp + (0 DC, 1 AC)]: (length << 8) | symbol for codes of <= 8 bits, else 0
-    int32_t maxcode[6][18];   // canonical decode of the longer codes (jdhuff.c)
+    uint32_t lut[6][1 << JD_LBITS];   // [2 * comp + (0 DC, 1 AC)]
+    uint32_t lut2[6][JD_L2SUBS * 64];
+    int32_t maxcode[6][18];   // canonical decode (jdhuff.c)
     int32_t valptr[6][18];
     uint8_t vals[6][256];
     uint16_t quant[3][64];    // natural order
@@ -170,13 +191,24 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
                 for (int a = 0; a < 2; a++) {
                     const uint8_t *b = bits[a ? 4 + ta : td], *v = vals[a ? 4 + ta : td];
                     const int t = 2 * c + a;
-                    int code = 0, k = 0;
+                    int code = 0, k = 0, nsubs = 0;
                     for (int l = 1; l <= 16; l++) {
                         T->valptr[t][l] = k - code;
                         for (int i = 0; i < b[l]; i++, code++, k++) {
-                            if (l <= 8)
-                                for (int fill = 0; fill < (1 << (8 - l)); fill++)
-                                    T->lut[t][((code << (8 - l)) | fill) & 255] = (uint16_t)((l << 8) | v[k]);
+                            if (code >> l) continue;                      // an over-subscribed table: the canonical walk decides
+                            const unsigned c16 = (unsigned)code << (16 - l);   // the code, left-aligned in 16 bits
+                            const uint32_t ent = jdec_entry(l, v[k], a == 0);
+                            if (l <= JD_LBITS) {
+                                for (unsigned fill = 0; fill < (1u << (JD_LBITS - l)); fill++)
+                                    T->lut[t][(c16 >> (16 - JD_LBITS)) + fill] = ent;
+                                continue;
+                            }
+                            uint32_t &pe = T->lut[t][c16 >> (16 - JD_LBITS)];
+                            if (pe == 0 && nsubs < JD_L2SUBS) pe = JD_L2 | (uint32_t)nsubs++;
+                            if (!(pe & JD_L2)) continue;                  // no sub-table left (or a shorter code owns the prefix)
+                            uint32_t *sub = T->lut2[t] + (pe & 63u) * 64;
+                            const unsigned rest = c16 & 63u;
+                            for (unsigned fill = 0; fill < (1u << (16 - l)); fill++) sub[rest + fill] = ent;
                         }
                         T->maxcode[t][l] = b[l] ? code - 1 : -1;
                         code <<= 1;
@@ -184,14 +216,15 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
                     memcpy(T->vals[t], v, 256);
                 }
                 // the commonest block of a scanned card -- DC difference 0, then end of block -- in ONE lookup:
-                // where a DC code of category 0 and the EOB code behind it fit the 8-bit window together, the DC
-                // entry carries bit 15 and the length of both
-                for (int idx = 0; idx < 256; idx++) {
-                    const unsigned e = T->lut[2 * c][idx];
-                    if (!e || (e & 255)) continue;
-                    const int l1 = (int)(e >> 8);
-                    const unsigned e2 = T->lut[2 * c + 1][(idx << l1) & 255];
-                    if (e2 && (e2 & 255) == 0 && l1 + (int)(e2 >> 8) <= 8) T->lut[2 * c][idx] = (uint16_t)(0x8000u | ((l1 + (e2 >> 8)) << 8));
+                // where a DC code of category 0 and the EOB code behind it fit the window together
+                for (int idx = 0; idx < (1 << JD_LBITS); idx++) {
+                    const uint32_t e = T->lut[2 * c][idx];
+                    if (!e || (e & JD_L2) || ((e >> 16) & 15u)) continue;           // a DC code whose low nibble is 0
+                    const int l1 = (int)((e >> 20) & 31u);
+                    const uint32_t e2 = T->lut[2 * c + 1][(idx << l1) & ((1 << JD_LBITS) - 1)];
+                    if (!e2 || (e2 & JD_L2) || ((e2 >> 8) & 127u) != 64u) continue;  // an EOB behind it
+                    const int l2 = (int)((e2 >> 20) & 31u);
+                    if (l1 + l2 <= JD_LBITS) T->lut[2 * c][idx] = JD_BOTH | (uint32_t)(l1 + l2) | (64u << 8) | ((uint32_t)(l1 + l2) << 20);
                 }
                 for (int i = 0; i < hsf[c] * vsf[c]; i++) T->comp_of[nb++] = (uint8_t)c;
             }
@@ -282,26 +315,33 @@ __global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *
 #define JD_SUB 1024   // bits per subsequence (r02m: 2048 measured -- every pass twice as long on one card, the same cards/s in the batch)
 
 struct JdecShared {
-    uint16_t lut[6][256];
+    uint32_t lut[6][1 << JD_LBITS];
+    uint32_t lut2[6][JD_L2SUBS * 64];
     int32_t maxcode[6][18];
     int32_t valptr[6][18];
     uint8_t vals[6][256];
-    uint8_t comp_of[8];
+    uint32_t comps;           // component of block i of the MCU in bits 2i, 2i + 1
     int32_t nbm;
 };
 
 __device__ __forceinline__ void jdec_load_tables(JdecShared &S, const JdecTables *__restrict__ T)
 {
-    for (int i = threadIdx.x; i < 6 * 256; i += blockDim.x) {
-        (&S.lut[0][0])[i] = (&T->lut[0][0])[i];
-        (&S.vals[0][0])[i] = (&T->vals[0][0])[i];
-    }
+    for (int i = threadIdx.x; i < 6 * (1 << JD_LBITS) / 4; i += blockDim.x)
+        reinterpret_cast<uint4 *>(&S.lut[0][0])[i] = __ldg(reinterpret_cast<const uint4 *>(&T->lut[0][0]) + i);
+    for (int i = threadIdx.x; i < 6 * JD_L2SUBS * 64 / 4; i += blockDim.x)
+        reinterpret_cast<uint4 *>(&S.lut2[0][0])[i] = __ldg(reinterpret_cast<const uint4 *>(&T->lut2[0][0]) + i);
+    for (int i = threadIdx.x; i < 6 * 256 / 4; i += blockDim.x)
+        reinterpret_cast<uint32_t *>(&S.vals[0][0])[i] = __ldg(reinterpret_cast<const uint32_t *>(&T->vals[0][0]) + i);
     for (int i = threadIdx.x; i < 6 * 18; i += blockDim.x) {
         (&S.maxcode[0][0])[i] = (&T->maxcode[0][0])[i];
         (&S.valptr[0][0])[i] = (&T->valptr[0][0])[i];
     }
-    if (threadIdx.x < 8) S.comp_of[threadIdx.x] = T->comp_of[threadIdx.x];
-    if (threadIdx.x == 0) S.nbm = T->nbm;
+    if (threadIdx.x == 0) {
+        uint32_t cs = 0;
+        for (int i = 0; i < 8; i++) cs |= (uint32_t)(T->comp_of[i] & 3) << (2 * i);
+        S.comps = cs;
+        S.nbm = T->nbm;
+    }
     __syncthreads();
 }
 
@@ -322,6 +362,7 @@ struct NoSink {
 #define JD_WIN (128 * (JD_SUB / 32) + 2)
 #define JD_WPS (JD_SUB / 32)   // words per subsequence
 #define JD_WIN_WORDS (JD_WIN + JD_WIN / JD_WPS + 1)
+#define JD_DYN_SMEM (sizeof(JdecShared) + JD_WIN_WORDS * sizeof(uint32_t))   // above the 48 KB a kernel gets unasked
 
 __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *__restrict__ words)
 {
@@ -335,104 +376,159 @@ __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *_
 // padding: the decoder drops it and continues at the boundary with the state of a fresh interval
 // (k = 0, block 0; the DC predictors are reset by the DC scan).  The interval of a state follows from its
 // bit position alone.
-template <typename SINK>
-__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const uint32_t *sw, unsigned long long &p,
-                                             int &k, int &bi, unsigned long long end, SINK &sink,
-                                             const unsigned long long *__restrict__ rst, unsigned nrst)
+//
+// Where the walker takes the stream's words from -- word(i), i relative to the window's first word: the CTA's
+// staged window (128 subsequences), or the one subsequence the chunk walk has just staged.
+struct WinWords {
+    const uint32_t *sw;
+    __device__ __forceinline__ uint32_t operator()(int i) const
+    {
+        i = min(i, JD_WIN - 1);
+        return sw[i + i / JD_WPS];
+    }
+};
+struct SubWords {
+    const uint32_t *sw;       // JD_WPS + 2 words
+    __device__ __forceinline__ uint32_t operator()(int i) const { return sw[min(i, JD_WPS + 1)]; }
+};
+
+// The walk is a chain of dependent symbols, so its speed is the latency of ONE trip:
+//   cursor -> funnel shift -> table entry -> cursor          and          entry -> k -> table of the next symbol.
+// Everything is 32-bit and relative to the window (`base` = its first bit), the entry carries the sums both
+// recurrences need (jdec_entry), the stream is read through three registers (the two words under the cursor and
+// the next one, fetched a symbol ahead), the component of the next block comes from a packed register, and
+// value bits / stores hang off the chain.  Branches are structured (no continue), so the lanes of a warp that
+// walk different subsequences re-join after every symbol.
+template <typename SINK, typename WORDS>
+__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const WORDS &word, unsigned long long base, unsigned long long &p_io, int &k_io, int &bi_io,
+                                             unsigned long long end, SINK &sink, const unsigned long long *__restrict__ rst,
+                                             unsigned nrst)
 {
     unsigned ri = 0;                                 // boundaries at or before p
     if (nrst) {
         unsigned lo = 0, hi = nrst;
         while (lo < hi) {
             const unsigned mid = (lo + hi) >> 1;
-            if (__ldg(rst + mid) <= p) lo = mid + 1;
+            if (__ldg(rst + mid) <= p_io) lo = mid + 1;
             else hi = mid;
         }
         ri = lo;
     }
-    unsigned long long bound = ri < nrst ? __ldg(rst + ri) : ~0ull;
-    const unsigned long long wbase = (unsigned long long)blockIdx.x * 128 * (JD_SUB / 32);
-    auto word = [&](unsigned long long w) {
-        const int i = min((int)(w - wbase), JD_WIN - 1);
-        return sw[i + i / JD_WPS];
-    };
+    auto rel = [&](unsigned long long x) { return x - base > 0x3fffffffull ? 0x3fffffff : (int)(x - base); };
+    int bound = ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
+    int q = (int)(p_io - base), k = k_io, bi = bi_io;
+    const int endq = rel(end), nbm = S.nbm;
+    const uint32_t comps = S.comps;
+    // tables as entry offsets into S.lut (32-bit arithmetic): the block's DC table, its AC table behind it, and the
+    // DC table of the block after it (looked up while this block is walked, so a block end costs a move)
+    const uint32_t *const L = &S.lut[0][0];
+    auto dc_of = [&](int blk) { return (int)(((comps >> (2 * blk)) & 3u) << (JD_LBITS + 1)); };
+    int dc = dc_of(bi), dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
+    int tb = k ? dc + (1 << JD_LBITS) : dc;
+    uint32_t a = word(q >> 5), b = word((q >> 5) + 1), c = word((q >> 5) + 2);
     unsigned done = 0;
-    unsigned long long wi = ~0ull - 1;   // never the predecessor of a real word index
-    int tdc = 2 * S.comp_of[bi];         // table pair of the current block (off the per-symbol path)
-    uint32_t a = 0, b = 0;
-    while (p < end) {
-        const unsigned long long w = p >> 5;
-        if (w != wi) {
-            if (w == wi + 1) { a = b; b = word(w + 1); }
-            else { a = word(w); b = word(w + 1); }
-            wi = w;
-        }
-        const uint32_t v = __funnelshift_l(b, a, (int)(p & 31));   // the next 32 bits of the stream
-        const int t = tdc + (k ? 1 : 0);
-        int len, sym;
-        const unsigned e = S.lut[t][v >> 24];
-        if (e & 0x8000u) {                           // DC difference 0 and EOB together: the block is complete
-            const int both = (int)((e >> 8) & 0x7f);
-            if (p + both <= bound) {
-                p += both;
-                bi = bi + 1 == S.nbm ? 0 : bi + 1;
-                tdc = 2 * S.comp_of[bi];
-                done++;
-                continue;
+    // Runs of empty MCUs (the white of a card: every block "DC difference 0, EOB"): once one MCU has been parsed
+    // that way from its first bit, every following copy of its bits (at most 32) parses the same way -- a Huffman
+    // parse depends on the state and the bits consumed only -- so the run advances one compare per MCU instead
+    // of one table walk per block.  A copy is taken only while it ends at or before `end` and the restart
+    // boundary: every state inside it lies before `end`, so the exit state is the one the block-by-block walk
+    // reaches.  The blocks of such an MCU store nothing (the coefficient buffer starts at zero).
+    int mstart = 0, patlen = 0;
+    uint32_t vstart = 0, pat = 0;
+    bool plain = false;
+    while (q < endq) {
+        const int sh = q & 31;
+        const uint32_t v = __funnelshift_l(b, a, sh);   // the next 32 bits of the stream
+        int adv;
+        bool refill = false;
+        bool run = false;
+        if ((k | bi) == 0) {
+            run = patlen && (v >> (32 - patlen)) == pat && q + patlen <= min(endq, bound);
+            if (!run) {
+                mstart = q;
+                vstart = v;
+                plain = true;
             }
         }
-        if (e) {
-            len = (e >> 8) & 0x7f;
-            sym = e & 255;
+        if (run) {
+            adv = patlen;
+            done += nbm;
         } else {
-            len = 16;
-            sym = 0;
-            const int code16 = (int)(v >> 16);
+            uint32_t e = L[tb + (int)(v >> (32 - JD_LBITS))];
+            if ((e & JD_L2) || e == 0) {
+                const int t = tb >> JD_LBITS;
+                if (e) e = S.lut2[t][(e & 63u) * 64 + ((v >> (32 - JD_LBITS - 6)) & 63u)];
+                if (e == 0) {                                    // not in the tables: jdhuff.c's canonical walk
+                    int len = 16, sym = 0;
+                    const int code16 = (int)(v >> 16);
 #pragma unroll 1
-            for (int l = 9; l <= 16; l++) {
-                const int c = code16 >> (16 - l);
-                if (c <= S.maxcode[t][l]) {
-                    len = l;
-                    sym = S.vals[t][(c + S.valptr[t][l]) & 255];
-                    break;
+                    for (int l = 1; l <= 16; l++) {
+                        const int cd = code16 >> (16 - l);
+                        if (cd <= S.maxcode[t][l]) {
+                            len = l;
+                            sym = S.vals[t][(cd + S.valptr[t][l]) & 255];
+                            break;
+                        }
+                    }
+                    const int s = sym & 15, r = sym >> 4;
+                    const int kinc = k == 0 ? 1 : s ? r + 1 : r == 15 ? 16 : 64;
+                    e = (uint32_t)(len + s) | ((uint32_t)kinc << 8) | ((uint32_t)s << 16) | ((uint32_t)len << 20);
+                }
+            }
+            adv = (int)(e & 63u);
+            if (q + adv > bound) {                               // padding in front of a restart marker
+                q = bound;
+                adv = 0;
+                k = 0;
+                bi = 0;
+                dc = dc_of(0);
+                dc_next = dc_of(nbm > 1 ? 1 : 0);
+                tb = dc;
+                ri++;
+                bound = ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
+                plain = false;
+                refill = true;
+            } else {
+                const int s = (int)((e >> 16) & 15u);
+                const int pos = k + (int)((e >> 8) & 127u) - 1;  // where the coefficient goes (zigzag order)
+                if (s && pos < 64) {
+                    const int len = (int)((e >> 20) & 31u);
+                    int val = (int)((v << len) >> (32 - s));
+                    if (val < (1 << (s - 1))) val += 1 - (1 << s);
+                    sink(done, pos, val);
+                }
+                k = pos + 1;
+                if (!(e & JD_BOTH)) plain = false;
+                if (k >= 64) {                                   // the block is complete
+                    k = 0;
+                    bi = bi + 1 == nbm ? 0 : bi + 1;
+                    dc = dc_next;
+                    dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
+                    tb = dc;
+                    done++;
+                    if (bi == 0 && plain && q + adv - mstart <= 32) {
+                        patlen = q + adv - mstart;
+                        pat = vstart >> (32 - patlen);
+                    }
+                } else {
+                    tb = dc + (1 << JD_LBITS);
                 }
             }
         }
-        const int s = sym & 15;
-        if (p + len + s > bound) {                   // padding in front of a restart marker
-            p = bound;
-            k = 0;
-            bi = 0;
-            tdc = 2 * S.comp_of[0];
-            ri++;
-            bound = ri < nrst ? __ldg(rst + ri) : ~0ull;
-            continue;
-        }
-        int val = s ? (int)((v << len) >> (32 - s)) : 0;
-        if (s && val < (1 << (s - 1))) val += 1 - (1 << s);
-        p += len + s;
-        if (k == 0) {
-            sink(done, 0, val);
-            k = 1;
-        } else {
-            const int r = sym >> 4;
-            if (s) {
-                k += r;
-                if (k < 64) sink(done, k, val);
-                k++;
-            } else if (r == 15) {
-                k += 16;
-            } else {
-                k = 64;
-            }
-        }
-        if (k >= 64) {
-            k = 0;
-            bi = bi + 1 == S.nbm ? 0 : bi + 1;
-            tdc = 2 * S.comp_of[bi];
-            done++;
+        q += adv;
+        if (refill) {
+            a = word(q >> 5);
+            b = word((q >> 5) + 1);
+            c = word((q >> 5) + 2);
+        } else if (sh + adv >= 32) {                             // at most one word per trip (adv <= 32)
+            a = b;
+            b = c;
+            c = word((q >> 5) + 2);
         }
     }
+    p_io = base + (unsigned long long)q;
+    k_io = k;
+    bi_io = bi;
     return done;
 }
 
@@ -451,11 +547,12 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
                                                         unsigned long long *used, unsigned long long *out,
                                                         unsigned long long *__restrict__ nblk, unsigned long long *mkey,
                                                         unsigned long long *mout, unsigned *mnb, unsigned *mcnt, int round,
-                                                        int *__restrict__ changed, const unsigned long long *__restrict__ rst,
-                                                        unsigned nrst)
+                                                        int max_it, int *__restrict__ changed,
+                                                        const unsigned long long *__restrict__ rst, unsigned nrst)
 {
-    __shared__ JdecShared S;
-    __shared__ uint32_t sw[JD_WIN_WORDS];
+    extern __shared__ uint4 jdec_dyn[];                       // JdecShared, then the staged window (JD_DYN_SMEM bytes)
+    JdecShared &S = *reinterpret_cast<JdecShared *>(jdec_dyn);
+    uint32_t *sw = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(jdec_dyn) + sizeof(JdecShared));
     const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = j * JD_SUB < total;
@@ -464,7 +561,9 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
     unsigned cnt = live && round > 0 ? mcnt[j] : 0;
     // Inside the CTA the chain advances without leaving the kernel: one iteration = every thread looks
     // at its predecessor's exit again.  Across CTAs it advances with the next launch.
-    for (int it = 0; it < (round ? 128 : 1); it++) {
+    const WinWords win{sw};
+    const unsigned long long wbits = (unsigned long long)blockIdx.x * 128 * JD_SUB;   // first bit of the staged window
+    for (int it = 0; it < (round ? max_it : 1); it++) {
         bool need = false, hit = false;
         unsigned long long x = jdec_pack(j * JD_SUB, 0, 0);
         if (live) {
@@ -499,7 +598,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
             unsigned long long p = x >> 12;
             int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
             NoSink sink;
-            const unsigned n = jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
+            const unsigned n = jdec_run(S, win, wbits, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
             const unsigned long long e = jdec_pack(p, k, bi);
             mine = x;
             __stcg(out + j, e);
@@ -516,6 +615,83 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
         used[j] = mine;
         mcnt[j] = cnt;
     }
+}
+
+// The chunk walk.  Where the stream rarely holds an EOB (quality ~100: nearly every block has all 63 AC
+// coefficients) a decoder that entered with a wrong (k, block) never re-aligns, so the true state has to be
+// carried through such stretches subsequence by subsequence.  In the kernel above that keeps a 128-thread CTA
+// resident per 128 subsequences with one lane decoding.  Here ONE lane per warp
+// walks a chunk of 128 subsequences in order, carrying the exit state along and decoding only where the
+// entry differs from the one last used; the other lanes fetch: the chunk's stored states once, and the 34 words
+// of the subsequence about to be decoded.  The same decodes as the chain's critical path with a quarter of
+// the resident warps and no barriers.  Chunks are walked concurrently; a chunk re-walks when its predecessor's
+// last exit changes under it, and the next launch catches what the last one missed (`changed[round]` says
+// whether a launch decoded anything).  from_guess: the first walk of a stream whose wide rounds were skipped.
+#define JD_CHUNK 128
+#define JD_WALK_WARPS 4
+__global__ void __launch_bounds__(32 * JD_WALK_WARPS) jdec_walk_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
+                                                                      const unsigned long long *__restrict__ removed, size_t scan_len,
+                                                                      unsigned long long *used, unsigned long long *out,
+                                                                      unsigned long long *__restrict__ nblk, int round, int from_guess,
+                                                                      int *__restrict__ changed, const unsigned long long *__restrict__ rst,
+                                                                      unsigned nrst)
+{
+    __shared__ JdecShared S;
+    __shared__ unsigned long long s_used[JD_WALK_WARPS][JD_CHUNK], s_out[JD_WALK_WARPS][JD_CHUNK];
+    __shared__ uint32_t s_words[JD_WALK_WARPS][JD_WPS + 2];
+    jdec_load_tables(S, T);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
+    const unsigned long long nsub = (total + JD_SUB - 1) / JD_SUB;
+    const unsigned long long j0 = ((unsigned long long)blockIdx.x * JD_WALK_WARPS + warp) * JD_CHUNK;
+    if (j0 >= nsub) return;                                   // whole warps leave: no barrier below
+    const int n = (int)min((unsigned long long)JD_CHUNK, nsub - j0);
+    for (int i = lane; i < n; i += 32) {
+        s_used[warp][i] = from_guess ? ~0ull : used[j0 + i];
+        s_out[warp][i] = from_guess ? 0ull : out[j0 + i];
+    }
+    __syncwarp();
+    bool any = false;
+    unsigned long long entry = 0;
+    for (int pass = 0; pass < 4; pass++) {
+        // the state my predecessor chunk ends in right now (it may still be walking)
+        unsigned long long e0 = j0 == 0 || from_guess ? jdec_pack(j0 * JD_SUB, 0, 0) : __ldcg(out + j0 - 1);
+        e0 = __shfl_sync(0xffffffffu, e0, 0);
+        if (pass && e0 == entry) break;
+        entry = e0;
+        unsigned long long prev = entry;
+        for (int i = 0; i < n; i++) {
+            // lane 0 knows whether subsequence i needs a decode; everybody follows its decision
+            const bool need = __shfl_sync(0xffffffffu, (int)(prev != s_used[warp][i]), 0) != 0;
+            if (!need) {
+                prev = s_out[warp][i];
+                continue;
+            }
+            const unsigned long long wbase = (j0 + i) * JD_WPS;
+            s_words[warp][lane] = __ldg(words + wbase + lane);
+            if (lane < 2) s_words[warp][JD_WPS + lane] = __ldg(words + wbase + JD_WPS + lane);
+            __syncwarp();
+            if (lane == 0) {
+                const SubWords cw{s_words[warp]};
+                unsigned long long pp = prev >> 12;
+                int k = (int)((prev >> 4) & 255), bi = (int)(prev & 15);
+                NoSink sink;
+                const unsigned nb = jdec_run(S, cw, (j0 + i) * JD_SUB, pp, k, bi, min(total, (j0 + i + 1) * JD_SUB), sink,
+                                             rst, nrst);
+                const unsigned long long e = jdec_pack(pp, k, bi);
+                s_used[warp][i] = prev;
+                s_out[warp][i] = e;
+                used[j0 + i] = prev;
+                __stcg(out + j0 + i, e);
+                nblk[j0 + i] = nb;
+                prev = e;
+            }
+            __syncwarp();
+            any = true;
+        }
+        if (from_guess) break;
+    }
+    if (any && lane == 0) changed[round] = 1;
 }
 
 struct CoefSink {
@@ -538,22 +714,26 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
                                                          unsigned long long nblocks, int16_t *__restrict__ coef,
                                                          const unsigned long long *__restrict__ rst, unsigned nrst)
 {
-    __shared__ JdecShared S;
+    extern __shared__ uint4 jdec_dyn[];
+    JdecShared &S = *reinterpret_cast<JdecShared *>(jdec_dyn);
+    uint32_t *sw = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(jdec_dyn) + sizeof(JdecShared));
     __shared__ uint8_t zz[64];
-    __shared__ uint32_t sw[JD_WIN_WORDS];
     if (threadIdx.x < 64) zz[threadIdx.x] = T->zz[threadIdx.x];
     jdec_load_tables(S, T);
     jdec_stage_words(sw, words);
     const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j * JD_SUB >= total) return;
-    const unsigned long long x = used[j];
+    const bool live = j * JD_SUB < total;
+    const unsigned long long x = live ? used[j] : 0ull;
     unsigned long long p = x >> 12;
     int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
     // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
     // coefficients were stored by the predecessor under the same ordinal
-    CoefSink sink{coef, first_block[j] + first_block_base[j >> 10], nblocks, zz};
-    jdec_run(S, sw, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
+    CoefSink sink{coef, live ? first_block[j] + first_block_base[j >> 10] : nblocks, nblocks, zz};
+    const WinWords win{sw};
+    if (live)
+        jdec_run(S, win, (unsigned long long)blockIdx.x * 128 * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst,
+                 nrst);
 }
 
 // ---------------------------------------------------------------------------
@@ -775,19 +955,20 @@ struct JdecSlot {
     int *hflags() { return reinterpret_cast<int *>(hcounters() + 4); }
 };
 
-static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
+// Rounds of the chunk walk (jdec_walk_kernel): `first` = ordinal of the first one (its slot in the flags).
+static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int first, int rounds, bool from_guess)
 {
-    const unsigned gs = (unsigned)((S.nsub + 127) / 128);
-    static const char *const kRoundNames[] = {"jdec_sync_kernel<round0>", "jdec_sync_kernel<chain 1>", "jdec_sync_kernel<chain 2>",
-                                              "jdec_sync_kernel<chain 3>", "jdec_sync_kernel<chain 4>", "jdec_sync_kernel<chain 5+>"};
-    for (int r = 1; r <= rounds; r++) {
-        ProfScope ps(ctx, kRoundNames[r < 5 ? r : 5], 0.0, S.st);
-        jdec_sync_kernel<<<gs, 128, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used,
-                                                S.out, S.nblk, S.mkey, S.mout, S.mnb, S.mcnt, r, S.flags, S.rst, S.nrst);
+    const unsigned nchunk = (unsigned)((S.nsub + JD_CHUNK - 1) / JD_CHUNK), gw = (nchunk + JD_WALK_WARPS - 1) / JD_WALK_WARPS;
+    static const char *const kRoundNames[] = {"jdec_walk_kernel<1>", "jdec_walk_kernel<2>", "jdec_walk_kernel<3>", "jdec_walk_kernel<4+>"};
+    for (int r = 0; r < rounds; r++) {
+        ProfScope ps(ctx, kRoundNames[std::min(3, first - 2 + r)], 0.0, S.st);
+        jdec_walk_kernel<<<gw, 32 * JD_WALK_WARPS, 0, S.st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len,
+                                                              S.used, S.out, S.nblk, first + r, from_guess && r == 0 ? 1 : 0, S.flags,
+                                                              S.rst, S.nrst);
     }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += rounds;
-    S.rounds = rounds;
+    S.rounds = first + rounds - 1;
     OICS_CUDA_TRY(cudaMemcpyAsync(S.hcounters(), S.removed, 4 * sizeof(unsigned long long) + 32 * sizeof(int), cudaMemcpyDeviceToHost,
                                   S.st));
     return OICS_OK;
@@ -797,6 +978,11 @@ static int32_t jdec_rounds(oics_ctx *ctx, JdecSlot &S, int rounds)
 static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_t n)
 {
     cudaStream_t st = S.st;
+    if (!ctx->attr_jdec) {   // per context = per device
+        OICS_CUDA_TRY(cudaFuncSetAttribute(jdec_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JD_DYN_SMEM));
+        OICS_CUDA_TRY(cudaFuncSetAttribute(jdec_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JD_DYN_SMEM));
+        ctx->attr_jdec = true;
+    }
     OICS_TRY(S.pin.ensure(sizeof(JdecTables) + 64 + 4 * sizeof(unsigned long long) + 32 * sizeof(int)));
     // the pinned block (tables out, counters back) is reused: a previous file that was begun but never polled
     // to the end (refused or abandoned) may still have copies in flight -- otherwise the last poll has waited
@@ -859,15 +1045,28 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     jdec_unstuff_count_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, S.flags);
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums_c, S.removed, nullptr));
     jdec_unstuff_write_kernel<<<gc, 256, 0, st>>>(d_scan, slen, H.restart, cnt, sums_c, reinterpret_cast<uint8_t *>(words), S.rst, S.nrst);
-    // every thread is fed its predecessor's exit state until a round changes nothing; the host looks at
-    // the flags after 4 rounds (each launch advances the chain through whole CTAs), then every 8
-    {
-        ProfScope ps(ctx, "jdec_sync_kernel<round0>", (double)slen, st);
-        jdec_sync_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
-                                              S.mnb, S.mcnt, 0, S.flags, S.rst, S.nrst);
+    // The synchronisation: round 0, every subsequence from the guess (its first bit, k = 0, block 0); then the wide
+    // kernel, every thread fed its predecessor's exit until nothing changes inside its CTA (several wavefronts per
+    // CTA advance side by side); then the chunk walks carry the states across the CTA borders, until one of them
+    // decodes nothing -- the host looks at the flags after 3, then every 4.  OICS_JD_WIDE: iterations of the wide
+    // kernel (tuning; 0 = walks only, measured slower on quality-100 cards: one wavefront per chunk).
+    static const int wide = [] { const char *e = getenv("OICS_JD_WIDE"); return e ? std::max(0, std::min(128, atoi(e))) : -1; }();
+    const int n_wide = wide >= 0 ? wide : 128;
+    if (n_wide > 0) {
+        {
+            ProfScope ps(ctx, "jdec_sync_kernel<round0>", (double)slen, st);
+            jdec_sync_kernel<<<gs, 128, JD_DYN_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+                                                  S.mnb, S.mcnt, 0, 1, S.flags, S.rst, S.nrst);
+        }
+        {
+            ProfScope ps(ctx, "jdec_sync_kernel<wide>", 0.0, st);
+            jdec_sync_kernel<<<gs, 128, JD_DYN_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+                                                  S.mnb, S.mcnt, 1, n_wide, S.flags, S.rst, S.nrst);
+        }
+        ctx->launches += 2;
     }
-    ctx->launches += 3;
-    return jdec_rounds(ctx, S, 4);
+    ctx->launches += 2;
+    return jdec_rounds(ctx, S, 2, 3, n_wide == 0);
 }
 
 // wait for the rounds in flight; *done = converged, else more rounds are enqueued
@@ -889,7 +1088,7 @@ static int32_t jdec_poll(oics_ctx *ctx, JdecSlot &S, bool *done)
         return OICS_OK;
     }
     OICS_CUDA_TRY(cudaMemsetAsync(S.flags + 1, 0, 31 * sizeof(int), S.st));
-    return jdec_rounds(ctx, S, 8);
+    return jdec_rounds(ctx, S, 5, 4, false);
 }
 
 // coefficients, DC prediction, IDCT, upsampling + colour -> d_bgr (enqueued on the slot's stream)
@@ -901,7 +1100,7 @@ static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t st
     OICS_TRY(exclusive_scan(ctx, st, S.nblk, S.nsub, S.sums_s, S.removed + 1, nullptr));
     {
         ProfScope ps(ctx, "jdec_write_kernel", (double)S.H.scan_len + 128.0 * (double)S.nblocks, st);
-        jdec_write_kernel<<<gs, 128, 0, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
+        jdec_write_kernel<<<gs, 128, JD_DYN_SMEM, st>>>(S.tables.as<JdecTables>(), S.words.as<uint32_t>(), S.removed, S.H.scan_len, S.used, S.nblk,
                                                S.sums_s, (unsigned long long)S.nblocks, coef, S.rst, S.nrst);
     }
     jdec_mcu_dc_kernel<<<(unsigned)((S.nmcu + 255) / 256), 256, 0, st>>>(coef, S.G, S.mcu);

@@ -17,7 +17,8 @@ for r in rows:
     elif r[0] == 'Line No':
         hdr = r
         iI, iS = hdr.index('Instructions Executed'), hdr.index('# Samples')
-        iW, iX = hdr.index('L1 Wavefronts Shared'), hdr.index('L1 Wavefronts Shared Excessive')
+        iW = hdr.index('L1 Wavefronts Shared') if 'L1 Wavefronts Shared' in hdr else iI
+        iX = hdr.index('L1 Wavefronts Shared Excessive') if 'L1 Wavefronts Shared Excessive' in hdr else iI
     elif hdr and r[0].isdigit():
         n=lambda v: int(v) if v.lstrip("-").isdigit() else 0; lines.append((cur_file, int(r[0]), r[1].strip(), n(r[iI]), n(r[iS]), n(r[iW]), n(r[iX])))
 totI = sum(l[3] for l in lines) or 1
