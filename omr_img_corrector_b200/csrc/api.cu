@@ -1,5 +1,6 @@
 // The compute entry points of include/oics_cuda.h: argument checks, host/device
 // staging, and the reference's call sequences expressed over the device kernels.
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 
@@ -1002,16 +1003,24 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         queue.clear();
         return OICS_OK;
     };
+    // OICS_BATCH_TRACE=1: host-side wall times of the phases of every sub-batch, on stderr (diagnostics)
+    static const bool trace = getenv("OICS_BATCH_TRACE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_start = trace ? now() : 0.0;
     for (int k = 0; k < n_sub && rc == OICS_OK; k++) {
+        double tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (trace) tr[0] = now();
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
         const uint8_t *dsrc = dev_in ? bgrs + (size_t)c0 * card_stride : in_slot[s]->as<uint8_t>();
         const size_t dcard = dev_in ? card_stride : card_bytes, dstride = dev_in ? (size_t)stride : row;
         if (!dev_in) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, in_ready[s], 0));
         // P0 for every card of the sub-batch (one launch), then one fused sweep over all of them
         OICS_BATCH_TRY(preprocess_batch_device(ctx, dsrc, nb, dcard, w, h, dstride, OICS_PRE_OMR, ow, oh, ctx->bin.as<uint8_t>()));
+        if (trace) tr[1] = now();
         if (N > 0)
             OICS_BATCH_TRY(sweep_to(ctx, ctx->bin.as<uint8_t>(), nb, (size_t)ow * oh, ow, oh, (size_t)ow, M.data(), n_angles,
                                     v.data(), hh.data(), nullptr, nullptr));
+        if (trace) tr[2] = now();
         // exact rule A (+ Hough fallback and reconcile, omr.rs:352-403) per card on the host
         if (host_out && k >= 2) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, out_free[s], 0));
         std::vector<size_t> out_off((size_t)nb, 0), out_bytes((size_t)nb, 0), jpeg_cap((size_t)nb, 0);
@@ -1107,17 +1116,20 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             if (stc == OICS_ERR_CUDA) rc = OICS_ERR_CUDA;
         }
         if (rc != OICS_OK) break;
+        if (trace) tr[3] = now();
         if (!dev_in) {
             OICS_BATCH_CUDA(cudaEventRecord(in_free[s], st));
             if (files) {
                 // in the shadow of the deskew + encode kernels just enqueued: the next sub-batch's cards are
                 // written (its chains had this sub-batch's sweep to converge), then the one after it is begun
                 if (k + 1 < n_sub) OICS_BATCH_TRY(decode_finish(k + 1));
+                if (trace) tr[4] = now();
                 if (k + 2 < n_sub) OICS_BATCH_TRY(decode_begin(k + 2));
             } else if (k + 2 < n_sub) {
                 OICS_BATCH_CUDA(upload(k + 2));
             }
         }
+        if (trace) tr[5] = now();
         if (jpeg_quality && dsts) {   // file sizes of the sub-batch: one read-back
             std::vector<unsigned long long> totals((size_t)2 * nb, 0ull);
             OICS_BATCH_CUDA(cudaMemcpyAsync(totals.data(), ctx->jpeg_totals.p, totals.size() * sizeof(unsigned long long),
@@ -1135,6 +1147,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                 }
             }
         }
+        if (trace) tr[6] = now();
         if (host_out) {
             OICS_BATCH_CUDA(cudaEventRecord(out_ready[s], st));
             OICS_BATCH_CUDA(cudaStreamWaitEvent(down, out_ready[s], 0));
@@ -1143,6 +1156,12 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                     OICS_BATCH_CUDA(cudaMemcpyAsync(dsts[c0 + i], out_slot[s]->as<uint8_t>() + out_off[i], out_bytes[i],
                                                     cudaMemcpyDeviceToHost, down));
             OICS_BATCH_CUDA(cudaEventRecord(out_free[s], down));
+        }
+        if (trace) {
+            tr[7] = now();
+            fprintf(stderr, "[oics batch] sub %d at %.2f ms: P0 enqueue %.2f | sweep (waits) %.2f | rule A + warp/encode enqueue %.2f | "
+                            "decode finish %.2f | decode begin %.2f | sizes read-back (waits) %.2f | copies out enqueue %.2f\n",
+                    k, tr[0] - t_start, tr[1] - tr[0], tr[2] - tr[1], tr[3] - tr[2], tr[4] - tr[3], tr[5] - tr[4], tr[6] - tr[5], tr[7] - tr[6]);
         }
     }
     if (rc == OICS_OK) OICS_BATCH_TRY(flush_fallbacks());

@@ -314,22 +314,27 @@ __global__ void __launch_bounds__(256) jdec_unstuff_write_kernel(const uint8_t *
 // (the DC value is the DIFFERENCE; prediction is a later scan).
 #define JD_SUB 1024   // bits per subsequence (r02m: 2048 measured -- every pass twice as long on one card, the same cards/s in the batch)
 
-struct JdecShared {
-    uint32_t lut[6][1 << JD_LBITS];
-    uint32_t lut2[6][JD_L2SUBS * 64];
+struct JdecSmall {            // what every walker keeps in shared memory
     int32_t maxcode[6][18];
     int32_t valptr[6][18];
     uint8_t vals[6][256];
     uint32_t comps;           // component of block i of the MCU in bits 2i, 2i + 1
     int32_t nbm;
 };
+// The lookup tables (36 KB): a shared-memory copy for the short-lived, all-lanes-busy kernels; the CTAs of the
+// synchronisation live long and mostly wait, so they read the tables in place (global memory through L1,
+// a few cycles more per symbol) and 13 of them fit an SM instead of 4.
+struct JdecLuts {
+    uint32_t lut[6][1 << JD_LBITS];
+    uint32_t lut2[6][JD_L2SUBS * 64];
+};
+struct JdecShared {
+    JdecLuts luts;            // first: filled with 16-byte copies
+    JdecSmall small;
+};
 
-__device__ __forceinline__ void jdec_load_tables(JdecShared &S, const JdecTables *__restrict__ T)
+__device__ __forceinline__ void jdec_load_small(JdecSmall &S, const JdecTables *__restrict__ T)
 {
-    for (int i = threadIdx.x; i < 6 * (1 << JD_LBITS) / 4; i += blockDim.x)
-        reinterpret_cast<uint4 *>(&S.lut[0][0])[i] = __ldg(reinterpret_cast<const uint4 *>(&T->lut[0][0]) + i);
-    for (int i = threadIdx.x; i < 6 * JD_L2SUBS * 64 / 4; i += blockDim.x)
-        reinterpret_cast<uint4 *>(&S.lut2[0][0])[i] = __ldg(reinterpret_cast<const uint4 *>(&T->lut2[0][0]) + i);
     for (int i = threadIdx.x; i < 6 * 256 / 4; i += blockDim.x)
         reinterpret_cast<uint32_t *>(&S.vals[0][0])[i] = __ldg(reinterpret_cast<const uint32_t *>(&T->vals[0][0]) + i);
     for (int i = threadIdx.x; i < 6 * 18; i += blockDim.x) {
@@ -342,6 +347,14 @@ __device__ __forceinline__ void jdec_load_tables(JdecShared &S, const JdecTables
         S.comps = cs;
         S.nbm = T->nbm;
     }
+}
+
+__device__ __forceinline__ void jdec_load_tables(JdecShared &S, const JdecTables *__restrict__ T)
+{
+    static_assert(offsetof(JdecTables, lut2) == offsetof(JdecTables, lut) + sizeof(JdecLuts::lut), "lut, lut2 adjacent");
+    for (int i = threadIdx.x; i < (int)(sizeof(JdecLuts) / 16); i += blockDim.x)
+        reinterpret_cast<uint4 *>(&S.luts)[i] = __ldg(reinterpret_cast<const uint4 *>(&T->lut[0][0]) + i);
+    jdec_load_small(S.small, T);
     __syncthreads();
 }
 
@@ -363,6 +376,7 @@ struct NoSink {
 #define JD_WPS (JD_SUB / 32)   // words per subsequence
 #define JD_WIN_WORDS (JD_WIN + JD_WIN / JD_WPS + 1)
 #define JD_DYN_SMEM (sizeof(JdecShared) + JD_WIN_WORDS * sizeof(uint32_t))   // above the 48 KB a kernel gets unasked
+#define JD_SYNC_SMEM (sizeof(JdecSmall) + 16 + JD_WIN_WORDS * sizeof(uint32_t))
 
 __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *__restrict__ words)
 {
@@ -399,8 +413,8 @@ struct SubWords {
 // the next one, fetched a symbol ahead), the component of the next block comes from a packed register, and
 // value bits / stores hang off the chain.  Branches are structured (no continue), so the lanes of a warp that
 // walk different subsequences re-join after every symbol.
-template <typename SINK, typename WORDS>
-__device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const WORDS &word, unsigned long long base, unsigned long long &p_io, int &k_io, int &bi_io,
+template <bool GLOBAL_LUTS, typename SINK, typename WORDS>
+__device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t *__restrict__ L, const WORDS &word, unsigned long long base, unsigned long long &p_io, int &k_io, int &bi_io,
                                              unsigned long long end, SINK &sink, const unsigned long long *__restrict__ rst,
                                              unsigned nrst)
 {
@@ -421,7 +435,7 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const WORDS &w
     const uint32_t comps = S.comps;
     // tables as entry offsets into S.lut (32-bit arithmetic): the block's DC table, its AC table behind it, and the
     // DC table of the block after it (looked up while this block is walked, so a block end costs a move)
-    const uint32_t *const L = &S.lut[0][0];
+    auto lut = [&](int i) { return GLOBAL_LUTS ? __ldg(L + i) : L[i]; };   // L: lut[6][..], then lut2[6][..]
     auto dc_of = [&](int blk) { return (int)(((comps >> (2 * blk)) & 3u) << (JD_LBITS + 1)); };
     int dc = dc_of(bi), dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
     int tb = k ? dc + (1 << JD_LBITS) : dc;
@@ -454,10 +468,10 @@ __device__ __forceinline__ unsigned jdec_run(const JdecShared &S, const WORDS &w
             adv = patlen;
             done += nbm;
         } else {
-            uint32_t e = L[tb + (int)(v >> (32 - JD_LBITS))];
+            uint32_t e = lut(tb + (int)(v >> (32 - JD_LBITS)));
             if ((e & JD_L2) || e == 0) {
                 const int t = tb >> JD_LBITS;
-                if (e) e = S.lut2[t][(e & 63u) * 64 + ((v >> (32 - JD_LBITS - 6)) & 63u)];
+                if (e) e = lut((6 << JD_LBITS) + t * (JD_L2SUBS * 64) + (int)((e & 63u) * 64 + ((v >> (32 - JD_LBITS - 6)) & 63u)));
                 if (e == 0) {                                    // not in the tables: jdhuff.c's canonical walk
                     int len = 16, sym = 0;
                     const int code16 = (int)(v >> 16);
@@ -550,9 +564,9 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
                                                         int max_it, int *__restrict__ changed,
                                                         const unsigned long long *__restrict__ rst, unsigned nrst)
 {
-    extern __shared__ uint4 jdec_dyn[];                       // JdecShared, then the staged window (JD_DYN_SMEM bytes)
-    JdecShared &S = *reinterpret_cast<JdecShared *>(jdec_dyn);
-    uint32_t *sw = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(jdec_dyn) + sizeof(JdecShared));
+    extern __shared__ uint4 jdec_dyn[];                       // JdecSmall, then the staged window (JD_SYNC_SMEM bytes)
+    JdecSmall &S = *reinterpret_cast<JdecSmall *>(jdec_dyn);
+    uint32_t *sw = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(jdec_dyn) + ((sizeof(JdecSmall) + 15) & ~(size_t)15));
     const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
     const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = j * JD_SUB < total;
@@ -590,7 +604,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
         if (!any_need && !any_hit) break;
         if (round > 0 && threadIdx.x == 0) changed[round] = 1;
         if (any_need && !tables) {
-            jdec_load_tables(S, T);
+            jdec_load_small(S, T);
             jdec_stage_words(sw, words);
             tables = true;
         }
@@ -598,7 +612,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
             unsigned long long p = x >> 12;
             int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
             NoSink sink;
-            const unsigned n = jdec_run(S, win, wbits, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
+            const unsigned n = jdec_run<true>(S, &T->lut[0][0], win, wbits, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
             const unsigned long long e = jdec_pack(p, k, bi);
             mine = x;
             __stcg(out + j, e);
@@ -676,7 +690,7 @@ __global__ void __launch_bounds__(32 * JD_WALK_WARPS) jdec_walk_kernel(const Jde
                 unsigned long long pp = prev >> 12;
                 int k = (int)((prev >> 4) & 255), bi = (int)(prev & 15);
                 NoSink sink;
-                const unsigned nb = jdec_run(S, cw, (j0 + i) * JD_SUB, pp, k, bi, min(total, (j0 + i + 1) * JD_SUB), sink,
+                const unsigned nb = jdec_run<false>(S.small, &S.luts.lut[0][0], cw, (j0 + i) * JD_SUB, pp, k, bi, min(total, (j0 + i + 1) * JD_SUB), sink,
                                              rst, nrst);
                 const unsigned long long e = jdec_pack(pp, k, bi);
                 s_used[warp][i] = prev;
@@ -732,7 +746,7 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     CoefSink sink{coef, live ? first_block[j] + first_block_base[j >> 10] : nblocks, nblocks, zz};
     const WinWords win{sw};
     if (live)
-        jdec_run(S, win, (unsigned long long)blockIdx.x * 128 * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst,
+        jdec_run<false>(S.small, &S.luts.lut[0][0], win, (unsigned long long)blockIdx.x * 128 * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst,
                  nrst);
 }
 
@@ -979,7 +993,6 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
 {
     cudaStream_t st = S.st;
     if (!ctx->attr_jdec) {   // per context = per device
-        OICS_CUDA_TRY(cudaFuncSetAttribute(jdec_sync_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JD_DYN_SMEM));
         OICS_CUDA_TRY(cudaFuncSetAttribute(jdec_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JD_DYN_SMEM));
         ctx->attr_jdec = true;
     }
@@ -1055,12 +1068,12 @@ static int32_t jdec_begin(oics_ctx *ctx, JdecSlot &S, const uint8_t *file, size_
     if (n_wide > 0) {
         {
             ProfScope ps(ctx, "jdec_sync_kernel<round0>", (double)slen, st);
-            jdec_sync_kernel<<<gs, 128, JD_DYN_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+            jdec_sync_kernel<<<gs, 128, JD_SYNC_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
                                                   S.mnb, S.mcnt, 0, 1, S.flags, S.rst, S.nrst);
         }
         {
             ProfScope ps(ctx, "jdec_sync_kernel<wide>", 0.0, st);
-            jdec_sync_kernel<<<gs, 128, JD_DYN_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
+            jdec_sync_kernel<<<gs, 128, JD_SYNC_SMEM, st>>>(S.tables.as<JdecTables>(), words, S.removed, slen, S.used, S.out, S.nblk, S.mkey, S.mout,
                                                   S.mnb, S.mcnt, 1, n_wide, S.flags, S.rst, S.nrst);
         }
         ctx->launches += 2;
