@@ -788,8 +788,9 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // up to 64
     // files: the cards of a sub-batch are decoded concurrently, one stream each -- the Huffman synchronisation is
     // latency-bound per card, so cards in flight are what fills the device (OICS_FILES_SUBBATCH: tuning)
-    int files_b = (int)std::max<size_t>(8, std::min<size_t>(OICS_JD_SLOTS - 1, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
-    if (const char *fb = getenv("OICS_FILES_SUBBATCH")) files_b = std::max(1, std::min(OICS_JD_SLOTS - 1, atoi(fb)));
+    const int slot_set = (OICS_JD_SLOTS - 1) / 2;     // sub-batches alternate between two sets of decode slots
+    int files_b = (int)std::max<size_t>(8, std::min<size_t>(slot_set, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
+    if (const char *fb = getenv("OICS_FILES_SUBBATCH")) files_b = std::max(1, std::min(slot_set, atoi(fb)));
     const int B_max = files ? files_b : (int)std::max<size_t>(8, std::min<size_t>(64, ((size_t)420 << 20) / std::max<size_t>(1, card_bytes)));
     // with host buffers on either side the copies of one sub-batch overlap the kernels of another: keep at least
     // eight stages in the pipeline; device-resident batches have nothing to overlap and take the largest sub-batch
@@ -802,7 +803,10 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     std::vector<int32_t> file_status((size_t)n_cards, OICS_OK);
     const int n_sub = cdiv(n_cards, B);
     cudaStream_t st = ctx->stream, up = nullptr, down = nullptr;
-    cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {};
+    cudaEvent_t in_ready[2] = {}, in_free[2] = {}, out_ready[2] = {}, out_free[2] = {}, lane_go = nullptr;
+    // encode lanes: the cards of a sub-batch are deskewed + encoded on this many streams side by side (0 = on ctx->stream)
+    static const int lanes_env = [] { const char *e = getenv("OICS_JPEG_LANES_N"); return e ? std::max(0, std::min(OICS_JPEG_LANES, atoi(e))) : OICS_JPEG_LANES; }();
+    const int n_lanes = jpeg_quality && dsts ? lanes_env : 0;
     DevBuf *in_slot[2] = {&ctx->in_img, &ctx->in_img2}, *out_slot[2] = {&ctx->out_img, &ctx->out_img2};
 
     // geometry shared by the batch
@@ -841,9 +845,12 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         cudaStreamSynchronize(st);
         if (up) { cudaStreamSynchronize(up); cudaStreamDestroy(up); }
         if (down) { cudaStreamSynchronize(down); cudaStreamDestroy(down); }
+        for (int li = 0; li < n_lanes; li++)
+            if (ctx->jpeg_lanes[li].st) cudaStreamSynchronize(ctx->jpeg_lanes[li].st);
         for (int i = 0; i < 2; i++)
             for (cudaEvent_t e : {in_ready[i], in_free[i], out_ready[i], out_free[i]})
                 if (e) cudaEventDestroy(e);
+        if (lane_go) cudaEventDestroy(lane_go);
     };
 #define OICS_BATCH_TRY(expr)                                   \
     do {                                                       \
@@ -860,6 +867,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         }                                                                                         \
     } while (0)
 
+    OICS_BATCH_CUDA(cudaEventCreateWithFlags(&lane_go, cudaEventDisableTiming));
     for (int i = 0; i < 2; i++) {
         for (cudaEvent_t *e : {&in_ready[i], &in_free[i], &out_ready[i], &out_free[i]})
             OICS_BATCH_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -891,17 +899,17 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
     // issued a whole sweep ahead; `finish` writes the cards once the slot is free
     auto decode_begin = [&](int k) -> int32_t {
         const int c0 = k * B, nb = std::min(B, n_cards - c0);
-        return jpeg_decode_batch_begin(ctx, files + c0, file_sizes + c0, nb, w, h, file_status.data() + c0);
+        return jpeg_decode_batch_begin(ctx, 1 + (k & 1) * slot_set, files + c0, file_sizes + c0, nb, w, h, file_status.data() + c0);
     };
     auto decode_finish = [&](int k) -> int32_t {
         const int s = k & 1, c0 = k * B, nb = std::min(B, n_cards - c0);
-        return jpeg_decode_batch_finish(ctx, nb, w, in_slot[s]->as<uint8_t>(), card_bytes, k >= 2 ? in_free[s] : nullptr, up,
+        return jpeg_decode_batch_finish(ctx, 1 + (k & 1) * slot_set, nb, w, in_slot[s]->as<uint8_t>(), card_bytes, k >= 2 ? in_free[s] : nullptr, up,
                                         in_ready[s], file_status.data() + c0);
     };
     if (files) {
         OICS_BATCH_TRY(decode_begin(0));
-        OICS_BATCH_TRY(decode_finish(0));
         if (n_sub > 1) OICS_BATCH_TRY(decode_begin(1));
+        OICS_BATCH_TRY(decode_finish(0));
     } else if (!dev_in) {
         OICS_BATCH_CUDA(upload(0));
         if (n_sub > 1) OICS_BATCH_CUDA(upload(1));
@@ -1025,6 +1033,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (host_out && k >= 2) OICS_BATCH_CUDA(cudaStreamWaitEvent(st, out_free[s], 0));
         std::vector<size_t> out_off((size_t)nb, 0), out_bytes((size_t)nb, 0), jpeg_cap((size_t)nb, 0);
         size_t jpeg_hdr = 0;
+        int lanes_used = 0;
         for (int i = 0; i < nb; i++) {
             const int c = c0 + i;
             const uint8_t *card = dsrc + (size_t)i * dcard;
@@ -1078,8 +1087,22 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                     set_error("internal: CONTAIN bound %zu < %zu", out_card_cap, need_bytes);
                     stc = OICS_ERR_CAPACITY;
                 } else {
-                    stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white, ctx->jpeg_raw.as<uint8_t>(), dw, dh,
-                                      (size_t)dw * 3);
+                    // the card's deskew + encode chain goes to one of the encode lanes (own stream and scratch, ordered
+                    // behind everything ctx->stream has been given so far; joined again below)
+                    JpegLane *lane = nullptr;
+                    if (n_lanes > 0) {
+                        const int li = lanes_used % n_lanes;
+                        OICS_BATCH_TRY(jpeg_lane_get(ctx, li, &lane));
+                        if (lanes_used < n_lanes) {
+                            if (lanes_used == 0) OICS_BATCH_CUDA(cudaEventRecord(lane_go, st));
+                            OICS_BATCH_CUDA(cudaStreamWaitEvent(lane->st, lane_go, 0));
+                        }
+                        lanes_used++;
+                        OICS_BATCH_TRY(lane->raw.ensure(out_card_cap));
+                    }
+                    uint8_t *raw = lane ? lane->raw.as<uint8_t>() : ctx->jpeg_raw.as<uint8_t>();
+                    stc = warp_device(ctx, card, 3, w, h, dstride, Mw, OICS_INTER_NEAREST, white, raw, dw, dh, (size_t)dw * 3,
+                                      lane ? lane->st : nullptr, lane ? &lane->tabs : nullptr);
                     if (stc == OICS_OK) {
                         // no host round trip here: the sizes of the sub-batch are read back together below
                         uint8_t *file = dst;
@@ -1089,8 +1112,8 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
                             file = out_slot[s]->as<uint8_t>() + out_off[i];
                             cap = std::min(out_card_cap, dst_caps[c]);
                         }
-                        stc = jpeg_encode_enqueue(ctx, ctx->jpeg_raw.as<uint8_t>(), dw, dh, (size_t)dw * 3, jpeg_quality, file, cap,
-                                                  ctx->jpeg_totals.as<unsigned long long>() + 2 * i, &jpeg_hdr);
+                        stc = jpeg_encode_enqueue(ctx, raw, dw, dh, (size_t)dw * 3, jpeg_quality, file, cap,
+                                                  ctx->jpeg_totals.as<unsigned long long>() + 2 * i, &jpeg_hdr, lane);
                         if (stc == OICS_OK) jpeg_cap[i] = cap;
                     }
                 }
@@ -1115,6 +1138,12 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             statuses[c] = stc;
             if (stc == OICS_ERR_CUDA) rc = OICS_ERR_CUDA;
         }
+        for (int li = 0; li < std::min(lanes_used, n_lanes); li++) {      // ctx->stream continues behind the lanes
+            JpegLane *lane = nullptr;
+            OICS_BATCH_TRY(jpeg_lane_get(ctx, li, &lane));
+            OICS_BATCH_CUDA(cudaEventRecord(lane->done, lane->st));
+            OICS_BATCH_CUDA(cudaStreamWaitEvent(st, lane->done, 0));
+        }
         if (rc != OICS_OK) break;
         if (trace) tr[3] = now();
         if (!dev_in) {
@@ -1122,9 +1151,12 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
             if (files) {
                 // in the shadow of the deskew + encode kernels just enqueued: the next sub-batch's cards are
                 // written (its chains had this sub-batch's sweep to converge), then the one after it is begun
-                if (k + 1 < n_sub) OICS_BATCH_TRY(decode_finish(k + 1));
-                if (trace) tr[4] = now();
+                // (the two sub-batches use different slot sets: sub-batch k + 2 is begun FIRST, so its chains have
+                // this whole deskew + encode phase and the next sweep to converge, and k + 1, begun a sub-batch ago,
+                // is normally converged by now: `finish` does not wait and its cards are written beside the encoder)
                 if (k + 2 < n_sub) OICS_BATCH_TRY(decode_begin(k + 2));
+                if (trace) tr[4] = now();
+                if (k + 1 < n_sub) OICS_BATCH_TRY(decode_finish(k + 1));
             } else if (k + 2 < n_sub) {
                 OICS_BATCH_CUDA(upload(k + 2));
             }
@@ -1160,7 +1192,7 @@ static int32_t correct_batch_impl(oics_ctx *ctx, const uint8_t *bgrs, int32_t n_
         if (trace) {
             tr[7] = now();
             fprintf(stderr, "[oics batch] sub %d at %.2f ms: P0 enqueue %.2f | sweep (waits) %.2f | rule A + warp/encode enqueue %.2f | "
-                            "decode finish %.2f | decode begin %.2f | sizes read-back (waits) %.2f | copies out enqueue %.2f\n",
+                            "decode begin %.2f | decode finish %.2f | sizes read-back (waits) %.2f | copies out enqueue %.2f\n",
                     k, tr[0] - t_start, tr[1] - tr[0], tr[2] - tr[1], tr[3] - tr[2], tr[4] - tr[3], tr[5] - tr[4], tr[6] - tr[5], tr[7] - tr[6]);
         }
     }

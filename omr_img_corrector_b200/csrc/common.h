@@ -58,6 +58,16 @@ struct PinnedBuf {
     template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// One encode in flight (jpeg.cu): its stream and scratch.  The batch driver spreads the cards of a sub-batch over
+// OICS_JPEG_LANES of them: one card's encoder is a chain of short kernels with scans between them, several
+// chains side by side keep the device busy through each other's tails.
+#define OICS_JPEG_LANES 4
+struct JpegLane {
+    cudaStream_t st = nullptr;
+    cudaEvent_t done = nullptr;
+    DevBuf tabs, raw, coef, bits, words, cnt;   // warp tables, deskewed pixels, coefficients, bit counts + sums, bit stream, 0xFF counts + sums
+};
+
 // Bluestein / radix-2 plan of one 1-D DFT length (fft.cu): device tables built on first use.
 struct FftPlan {
     int n = 0, m = 0, direct = 0;
@@ -102,7 +112,7 @@ struct Profiler {
 
 }  // namespace oics
 
-#define OICS_JD_SLOTS 33
+#define OICS_JD_SLOTS 65   // slot 0 = ctx->stream; two sets of 32 for the batch driver (sub-batches alternate)
 
 struct oics_ctx {
     int device = 0;
@@ -128,6 +138,7 @@ struct oics_ctx {
     oics::FftPlan fft_row, fft_col;
     oics::DevBuf wplanes, wmeta, wlists, jpeg_raw, jpeg_hdr, jpeg_totals;
     oics::DevBuf fb_in, fb_out;   // batch driver: cards waiting for the batched Hough fallback, and their outputs
+    oics::JpegLane jpeg_lanes[OICS_JPEG_LANES];
     void *jd_slots[OICS_JD_SLOTS] = {};   // jpegdec.cu: decodes in flight (slot 0 = ctx->stream, the others own a stream)
     // jpeg.cu: the file header of the last quality used (host copy and its device cache)
     int jpeg_hdr_quality = 0, jpeg_hdr_sof = 0;
@@ -180,7 +191,8 @@ int32_t sweep_device(oics_ctx *ctx, const uint8_t *dbins, int n_cards, size_t ca
                      int64_t *d_sums, int32_t *d_counts_out /* nullable: [n_angles][h+w] of card 0 */);
 // warp.cu
 int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t sstride, const double Mfwd[6],
-                    int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride);
+                    int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride, cudaStream_t on = nullptr,
+                    DevBuf *tables = nullptr);
 // preprocess.cu
 int32_t preprocess_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int mode, int ow,
                           int oh, uint8_t *dbin /* tightly packed ow x oh */);
@@ -212,16 +224,18 @@ int32_t jpeg_encode_device(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, siz
                            size_t d_cap, size_t *size);
 
 int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
-                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len);
+                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len, JpegLane *lane = nullptr);
+int32_t jpeg_lane_get(oics_ctx *ctx, int i, JpegLane **lane);
+void jpeg_lanes_release(oics_ctx *ctx);
 size_t jpeg_file_size(size_t hdr_len, const unsigned long long *totals);
 int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, size_t n, unsigned long long *sums,
                        unsigned long long *total, const unsigned long long *tb);
 // N2: imread(JPEG) (jpegdec.cu)
 int32_t jpeg_info_host(const uint8_t *file, size_t n, int *w, int *h, int *ncomp);
 int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t *d_bgr, size_t stride, int *w_out, int *h_out);
-int32_t jpeg_decode_batch_begin(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+int32_t jpeg_decode_batch_begin(oics_ctx *ctx, int slot0, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
                                 int32_t *statuses);
-int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
+int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int slot0, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
                                  cudaStream_t join, cudaEvent_t ready, int32_t *statuses);
 void jpeg_decode_release(oics_ctx *ctx);
 

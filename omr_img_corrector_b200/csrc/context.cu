@@ -230,6 +230,7 @@ OICS_API void oics_destroy(oics_ctx *ctx)
                       &ctx->fb_in,  &ctx->fb_out};
     for (DevBuf *b : bufs) b->release();
     jpeg_decode_release(ctx);
+    jpeg_lanes_release(ctx);
     for (FftPlan *pl : {&ctx->fft_row, &ctx->fft_col}) {
         pl->chirp.release();
         pl->bbr.release();

@@ -600,10 +600,34 @@ static int32_t fixed_tables(int device)
 // Enqueue the encoder on ctx->stream without a host round trip: the file lands in d_out (writes past
 // d_cap are dropped) and d_totals[0..1] (device) receive the entropy-coded bits and the stuffed 0xFF
 // count; the file size is jpeg_file_size(*hdr_len, totals) once the caller has read them back.
-int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
-                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len)
+int32_t jpeg_lane_get(oics_ctx *ctx, int i, JpegLane **lane)
 {
-    cudaStream_t st = ctx->stream;
+    JpegLane &L = ctx->jpeg_lanes[i];
+    if (!L.st) {
+        int lo = 0, hi = 0;   // beside the context's own stream, above the decode streams
+        OICS_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        OICS_CUDA_TRY(cudaStreamCreateWithPriority(&L.st, cudaStreamNonBlocking, hi));
+        OICS_CUDA_TRY(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+    }
+    *lane = &L;
+    return OICS_OK;
+}
+
+void jpeg_lanes_release(oics_ctx *ctx)
+{
+    for (JpegLane &L : ctx->jpeg_lanes) {
+        if (L.st) { cudaStreamSynchronize(L.st); cudaStreamDestroy(L.st); L.st = nullptr; }
+        if (L.done) { cudaEventDestroy(L.done); L.done = nullptr; }
+        for (DevBuf *b : {&L.tabs, &L.raw, &L.coef, &L.bits, &L.words, &L.cnt}) b->release();
+    }
+}
+
+// `lane`: encode on that lane's stream with its scratch (the caller orders the lane against ctx->stream);
+// null = ctx->stream and the context's scratch.
+int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, size_t stride, int quality, uint8_t *d_out,
+                            size_t d_cap, unsigned long long *d_totals, size_t *hdr_len, JpegLane *lane)
+{
+    cudaStream_t st = lane ? lane->st : ctx->stream;
     if (w <= 0 || h <= 0 || w > 65535 || h > 65535) {
         set_error("jpeg: image size %dx%d is outside 1..65535", w, h);
         return OICS_ERR_INVALID_ARG;
@@ -624,6 +648,7 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     if (ctx->jpeg_hdr_quality != quality) {                 // the header of this quality, cached on the device
         ctx->jpeg_hdr_len = host_header(Q.q[0], Q.q[1], ctx->jpeg_hdr_host, &ctx->jpeg_hdr_sof);
         OICS_TRY(ctx->jpeg_hdr.ensure(1024));
+        OICS_CUDA_TRY(cudaDeviceSynchronize());             // lanes may still read the header of the last quality
         OICS_CUDA_TRY(cudaMemcpyAsync(ctx->jpeg_hdr.p, ctx->jpeg_hdr_host, ctx->jpeg_hdr_len, cudaMemcpyHostToDevice, st));
         OICS_CUDA_TRY(cudaStreamSynchronize(st));
         ctx->jpeg_hdr_quality = quality;
@@ -636,21 +661,23 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     const size_t bound = nb * 208 + 64;                      // bytes: 20 DC + 63 * 26 AC bits per block at most
     const size_t nchunks = (bound + 31) / 32;
     const size_t nsums = (nb + 1023) / 1024 + 8, nsums2 = (nchunks + 1023) / 1024 + 8;
-    OICS_TRY(ctx->cplx.ensure(64 * G.cstride * sizeof(int16_t)));
-    OICS_TRY(ctx->labels.ensure((nb + nsums) * sizeof(unsigned long long)));
-    OICS_TRY(ctx->cplx2.ensure(bound + 64));
-    OICS_TRY(ctx->mag.ensure((nchunks + nsums2) * sizeof(unsigned long long)));
-    int16_t *coef = ctx->cplx.as<int16_t>();
-    unsigned long long *bits = ctx->labels.as<unsigned long long>(), *sums = bits + nb;
-    unsigned long long *cnt = ctx->mag.as<unsigned long long>(), *sums2 = cnt + nchunks;
-    uint32_t *words = ctx->cplx2.as<uint32_t>();
+    DevBuf &b_coef = lane ? lane->coef : ctx->cplx, &b_bits = lane ? lane->bits : ctx->labels;
+    DevBuf &b_words = lane ? lane->words : ctx->cplx2, &b_cnt = lane ? lane->cnt : ctx->mag;
+    OICS_TRY(b_coef.ensure(64 * G.cstride * sizeof(int16_t)));
+    OICS_TRY(b_bits.ensure((nb + nsums) * sizeof(unsigned long long)));
+    OICS_TRY(b_words.ensure(bound + 64));
+    OICS_TRY(b_cnt.ensure((nchunks + nsums2) * sizeof(unsigned long long)));
+    int16_t *coef = b_coef.as<int16_t>();
+    unsigned long long *bits = b_bits.as<unsigned long long>(), *sums = bits + nb;
+    unsigned long long *cnt = b_cnt.as<unsigned long long>(), *sums2 = cnt + nchunks;
+    uint32_t *words = b_words.as<uint32_t>();
     const int strips = cdiv(G.mcux, JD_MCU);
     {   // algorithmic bytes: the BGR image in, 16-bit coefficients of the 4:2:0 planes out (1.5 x 2 B per pixel)
-        ProfScope ps(ctx, "jpeg_dct_kernel", 3.0 * w * h + 2.0 * 64 * nb);
+        ProfScope ps(ctx, "jpeg_dct_kernel", 3.0 * w * h + 2.0 * 64 * nb, st);
         jpeg_dct_kernel<<<G.mcuy * strips, JD_T, 0, st>>>(dbgr, stride, G, Q, strips, coef);
     }
     {
-        ProfScope ps(ctx, "jpeg_bits_kernel", 2.0 * 64 * nb + 8.0 * nb);
+        ProfScope ps(ctx, "jpeg_bits_kernel", 2.0 * 64 * nb + 8.0 * nb, st);
         jpeg_bits_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits);
     }
     OICS_CUDA_TRY(cudaGetLastError());
@@ -658,7 +685,7 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     OICS_TRY(exclusive_scan(ctx, st, bits, nb, sums, d_totals, nullptr));
     jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
     {
-        ProfScope ps(ctx, "jpeg_emit_kernel", 2.0 * 64 * nb + 8.0 * nb);
+        ProfScope ps(ctx, "jpeg_emit_kernel", 2.0 * 64 * nb + 8.0 * nb, st);
         jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, sums, words);
     }
     jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
@@ -666,7 +693,7 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     ctx->launches += 3;
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums2, d_totals + 1, d_totals));
     {
-        ProfScope ps(ctx, "jpeg_stuff_write_kernel", 0.0);
+        ProfScope ps(ctx, "jpeg_stuff_write_kernel", 0.0, st);
         jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
             words, d_totals, cnt, sums2, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
     }

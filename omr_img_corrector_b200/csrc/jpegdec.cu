@@ -1183,13 +1183,13 @@ int32_t jpeg_decode_device(oics_ctx *ctx, const uint8_t *file, size_t n, uint8_t
 //   finish  wait for the chains (normally long converged by now), then coefficients .. colour into
 //           d_bgr + i * card_bytes; the slot streams wait for `free_ev` (may be null) before writing
 //           there, and `ready` is recorded on `join` once all cards are done
-int32_t jpeg_decode_batch_begin(oics_ctx *ctx, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
+int32_t jpeg_decode_batch_begin(oics_ctx *ctx, int slot0, const uint8_t *const *files, const size_t *sizes, int n_files, int w, int h,
                                 int32_t *statuses)
 {
-    if (n_files > OICS_JD_SLOTS - 1) { set_error("jpeg: at most %d files per call", OICS_JD_SLOTS - 1); return OICS_ERR_INVALID_ARG; }
+    if (slot0 < 1 || slot0 + n_files > OICS_JD_SLOTS) { set_error("jpeg: decode slots %d..%d of %d", slot0, slot0 + n_files - 1, OICS_JD_SLOTS); return OICS_ERR_INVALID_ARG; }
     for (int i = 0; i < n_files; i++) {
         statuses[i] = OICS_OK;
-        JdecSlot *S = jdec_slot(ctx, 1 + i);
+        JdecSlot *S = jdec_slot(ctx, slot0 + i);
         if (!S) { set_error("jpeg: no decode slot"); return OICS_ERR_CUDA; }
         S->rounds = 0;
         int32_t rc = files[i] ? jdec_begin(ctx, *S, files[i], sizes[i]) : OICS_ERR_INVALID_ARG;
@@ -1203,11 +1203,11 @@ int32_t jpeg_decode_batch_begin(oics_ctx *ctx, const uint8_t *const *files, cons
     return OICS_OK;
 }
 
-int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
+int32_t jpeg_decode_batch_finish(oics_ctx *ctx, int slot0, int n_files, int w, uint8_t *d_bgr, size_t card_bytes, cudaEvent_t free_ev,
                                  cudaStream_t join, cudaEvent_t ready, int32_t *statuses)
 {
     std::vector<JdecSlot *> slots((size_t)n_files, nullptr);
-    for (int i = 0; i < n_files; i++) slots[i] = jdec_slot(ctx, 1 + i);
+    for (int i = 0; i < n_files; i++) slots[i] = jdec_slot(ctx, slot0 + i);
     for (bool all = false; !all;) {
         all = true;
         for (int i = 0; i < n_files; i++) {

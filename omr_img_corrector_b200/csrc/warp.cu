@@ -191,9 +191,13 @@ __global__ void __launch_bounds__(256) warp_flat_kernel(const uint32_t *__restri
 }
 
 int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, size_t sstride, const double Mfwd[6],
-                    int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride)
+                    int interp, const uint8_t border[4], uint8_t *ddst, int dw, int dh, size_t dstride, cudaStream_t on,
+                    DevBuf *tables)
 {
-    cudaStream_t st = ctx->stream;
+    // on / tables: another stream of the context and the table scratch that goes with it (the encode lanes of the
+    // batch driver); null = ctx->stream and ctx->misc
+    cudaStream_t st = on ? on : ctx->stream;
+    DevBuf &tab = tables ? *tables : ctx->misc;
     if (ch != 1 && ch != 3 && ch != 4) {
         set_error("warp: %d channels not supported (1, 3 or 4)", ch);
         return OICS_ERR_UNSUPPORTED;
@@ -207,9 +211,9 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
     invert_affine(Mfwd, inv);
     // tables: [6 doubles][{ad, bd} dw][{X0, Y0} dh]
     const size_t bytes = 64 + sizeof(int2) * ((size_t)dw + (size_t)dh + 2);
-    OICS_TRY(ctx->misc.ensure(bytes));
-    double *dM = ctx->misc.as<double>();
-    int2 *ab = reinterpret_cast<int2 *>(ctx->misc.as<uint8_t>() + 64);
+    OICS_TRY(tab.ensure(bytes));
+    double *dM = tab.as<double>();
+    int2 *ab = reinterpret_cast<int2 *>(tab.as<uint8_t>() + 64);
     int2 *xy = ab + dw;
     OICS_CUDA_TRY(cudaMemcpyAsync(dM, inv, sizeof(inv), cudaMemcpyHostToDevice, st));
     warp_tables_kernel<<<cdiv(max(dw, dh), 256), 256, 0, st>>>(dM, dw, dh, interp == OICS_INTER_NEAREST ? 512 : 16, ab, xy);
@@ -233,7 +237,7 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
 #define OICS_WARPF(CH, LIN)                                                                                          \
     warp_flat_kernel<CH, LIN><<<blocks, 256, 0, st>>>(s32, w, h, (uint32_t)sstride, d32, (uint32_t)dw, (uint32_t)dh, \
                                                       (uint32_t)npix, ab, xy, bcol, last_word)
-        ProfScope ps(ctx, lin ? "warp_flat_kernel<LINEAR>" : "warp_flat_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix));
+        ProfScope ps(ctx, lin ? "warp_flat_kernel<LINEAR>" : "warp_flat_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix), st);
         if (ch == 1) { if (lin) OICS_WARPF(1, true); else OICS_WARPF(1, false); }
         else if (ch == 3) { if (lin) OICS_WARPF(3, true); else OICS_WARPF(3, false); }
         else { if (lin) OICS_WARPF(4, true); else OICS_WARPF(4, false); }
@@ -243,7 +247,7 @@ int32_t warp_device(oics_ctx *ctx, const uint8_t *dsrc, int ch, int w, int h, si
         dim3 grid(cdiv(cdiv(dw, 4), 256), dh);
 #define OICS_WARP(CH, LIN) \
     warp_kernel<CH, LIN><<<grid, 256, 0, st>>>(dsrc, w, h, sstride, ddst, dw, dh, dstride, ab, xy, bv, aligned)
-        ProfScope ps(ctx, lin ? "warp_kernel<LINEAR>" : "warp_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix));
+        ProfScope ps(ctx, lin ? "warp_kernel<LINEAR>" : "warp_kernel<NEAREST>", (double)ch * ((double)w * h + (double)npix), st);
         if (ch == 1) { if (lin) OICS_WARP(1, true); else OICS_WARP(1, false); }
         else if (ch == 3) { if (lin) OICS_WARP(3, true); else OICS_WARP(3, false); }
         else { if (lin) OICS_WARP(4, true); else OICS_WARP(4, false); }
