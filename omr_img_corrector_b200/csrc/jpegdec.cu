@@ -44,7 +44,7 @@ static const uint8_t d_zz[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 1
 //              white card in one lookup): consumes both codes, adds 64
 //   JD_L2      the first JD_LBITS bits are the prefix of longer codes: bits 0-5 = sub-table i, the symbol is
 //              lut2[t][i * 64 + next 6 bits]
-// 0 = not in the tables (an invalid code, or more long prefixes than JD_L2SUBS -- the standard tables have 1 to 6, and
+// JD_L2 | 63 in lut / 0 in lut2 = not in the tables (an invalid code, or more long prefixes than JD_L2SUBS -- the standard tables have 1 to 6, and
 // long codes are the rare symbols of any table): jdhuff.c's canonical walk decides.
 #define JD_LBITS 10
 #define JD_BOTH 0x80000000u
@@ -226,6 +226,10 @@ static int32_t parse_header(const uint8_t *f, size_t n, JdecHeader *H, JdecTable
                     const int l2 = (int)((e2 >> 20) & 31u);
                     if (l1 + l2 <= JD_LBITS) T->lut[2 * c][idx] = JD_BOTH | (uint32_t)(l1 + l2) | (64u << 8) | ((uint32_t)(l1 + l2) << 20);
                 }
+                // what no code of <= JD_LBITS bits and no long prefix claims: one flag test on the walker's path
+                for (int a = 0; a < 2; a++)
+                    for (int idx = 0; idx < (1 << JD_LBITS); idx++)
+                        if (T->lut[2 * c + a][idx] == 0) T->lut[2 * c + a][idx] = JD_L2 | 63u;
                 for (int i = 0; i < hsf[c] * vsf[c]; i++) T->comp_of[nb++] = (uint8_t)c;
             }
             T->nbm = nb;
@@ -368,20 +372,23 @@ struct NoSink {
 };
 
 // Decode from state (p, k, bi) until p >= end.  Returns the number of blocks completed.
-// The CTA's part of the stream (128 subsequences = 2048 words, + 2: a value field may reach into the
-// next word) staged in shared memory: in a warp some lane needs a new word at almost every symbol,
-// and a global load there stalls all 32.  One pad word per 16 keeps the lanes (16 words apart) in
-// different banks.
-#define JD_WIN (128 * (JD_SUB / 32) + 2)
+// The CTA's part of the stream (128 subsequences) staged in shared memory, one ROW per subsequence: its 32 words
+// and the 2 behind them (a symbol may start up to 31 bits past the subsequence and reach 32 further), so a
+// thread addresses its words with the cursor alone -- row[cursor >> 5] -- and rows 35 words apart keep the
+// lanes of a warp in different banks.
 #define JD_WPS (JD_SUB / 32)   // words per subsequence
-#define JD_WIN_WORDS (JD_WIN + JD_WIN / JD_WPS + 1)
+#define JD_ROW (JD_WPS + 3)    // 34 staged words + one slot the look-ahead may touch past the end
+#define JD_WIN_WORDS (128 * JD_ROW)
 #define JD_DYN_SMEM (sizeof(JdecShared) + JD_WIN_WORDS * sizeof(uint32_t))   // above the 48 KB a kernel gets unasked
 #define JD_SYNC_SMEM (sizeof(JdecSmall) + 16 + JD_WIN_WORDS * sizeof(uint32_t))
 
 __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *__restrict__ words)
 {
-    const size_t base = (size_t)blockIdx.x * 128 * (JD_SUB / 32);
-    for (int i = threadIdx.x; i < JD_WIN; i += blockDim.x) sw[i + i / JD_WPS] = __ldg(words + base + i);
+    const size_t base = (size_t)blockIdx.x * 128 * JD_WPS;
+    for (int i = threadIdx.x; i < 128 * (JD_WPS + 2); i += blockDim.x) {
+        const int row = i / (JD_WPS + 2), l = i - row * (JD_WPS + 2);
+        sw[row * JD_ROW + l] = __ldg(words + base + row * JD_WPS + l);      // (the stream is zero-padded behind its end)
+    }
     __syncthreads();
 }
 
@@ -391,35 +398,22 @@ __device__ __forceinline__ void jdec_stage_words(uint32_t *sw, const uint32_t *_
 // (k = 0, block 0; the DC predictors are reset by the DC scan).  The interval of a state follows from its
 // bit position alone.
 //
-// Where the walker takes the stream's words from -- word(i), i relative to the window's first word: the CTA's
-// staged window (128 subsequences), or the one subsequence the chunk walk has just staged.
-struct WinWords {
-    const uint32_t *sw;
-    __device__ __forceinline__ uint32_t operator()(int i) const
-    {
-        i = min(i, JD_WIN - 1);
-        return sw[i + i / JD_WPS];
-    }
-};
-struct SubWords {
-    const uint32_t *sw;       // JD_WPS + 2 words
-    __device__ __forceinline__ uint32_t operator()(int i) const { return sw[min(i, JD_WPS + 1)]; }
-};
-
 // The walk is a chain of dependent symbols, so its speed is the latency of ONE trip:
 //   cursor -> funnel shift -> table entry -> cursor          and          entry -> k -> table of the next symbol.
-// Everything is 32-bit and relative to the window (`base` = its first bit), the entry carries the sums both
-// recurrences need (jdec_entry), the stream is read through three registers (the two words under the cursor and
-// the next one, fetched a symbol ahead), the component of the next block comes from a packed register, and
-// value bits / stores hang off the chain.  Branches are structured (no continue), so the lanes of a warp that
-// walk different subsequences re-join after every symbol.
-template <bool GLOBAL_LUTS, typename SINK, typename WORDS>
-__device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t *__restrict__ L, const WORDS &word, unsigned long long base, unsigned long long &p_io, int &k_io, int &bi_io,
-                                             unsigned long long end, SINK &sink, const unsigned long long *__restrict__ rst,
-                                             unsigned nrst)
+// Everything is 32-bit and relative to the subsequence (`base` = its first bit; row = its staged words), the entry
+// carries the sums both recurrences need (jdec_entry), the stream is read through three registers (the two
+// words under the cursor and the next one, fetched a symbol ahead), and everything that is not per symbol is
+// kept out of the trip: restart boundaries are a template variant (HAS_RST), MCU bookkeeping (the pattern of
+// empty MCUs) lives in the block-end branch, value bits / stores hang off the chain.  Branches are structured
+// (no continue), so the lanes of a warp that walk different subsequences re-join after every symbol.
+template <bool GLOBAL_LUTS, bool HAS_RST, typename SINK>
+__device__ __forceinline__ unsigned jdec_run_t(const JdecSmall &S, const uint32_t *__restrict__ L, const uint32_t *row,
+                                               unsigned long long base, unsigned long long &p_io, int &k_io, int &bi_io,
+                                               unsigned long long end, SINK &sink, const unsigned long long *__restrict__ rst,
+                                               unsigned nrst)
 {
     unsigned ri = 0;                                 // boundaries at or before p
-    if (nrst) {
+    if (HAS_RST) {
         unsigned lo = 0, hi = nrst;
         while (lo < hi) {
             const unsigned mid = (lo + hi) >> 1;
@@ -429,17 +423,17 @@ __device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t 
         ri = lo;
     }
     auto rel = [&](unsigned long long x) { return x - base > 0x3fffffffull ? 0x3fffffff : (int)(x - base); };
-    int bound = ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
+    int bound = HAS_RST && ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
     int q = (int)(p_io - base), k = k_io, bi = bi_io;
     const int endq = rel(end), nbm = S.nbm;
     const uint32_t comps = S.comps;
-    // tables as entry offsets into S.lut (32-bit arithmetic): the block's DC table, its AC table behind it, and the
-    // DC table of the block after it (looked up while this block is walked, so a block end costs a move)
     auto lut = [&](int i) { return GLOBAL_LUTS ? __ldg(L + i) : L[i]; };   // L: lut[6][..], then lut2[6][..]
+    // tables as entry offsets into L: the block's DC table, its AC table behind it, and the DC table of the block
+    // after it (looked up while this block is walked, so a block end costs a move)
     auto dc_of = [&](int blk) { return (int)(((comps >> (2 * blk)) & 3u) << (JD_LBITS + 1)); };
     int dc = dc_of(bi), dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
     int tb = k ? dc + (1 << JD_LBITS) : dc;
-    uint32_t a = word(q >> 5), b = word((q >> 5) + 1), c = word((q >> 5) + 2);
+    uint32_t a = row[q >> 5], b = row[(q >> 5) + 1], c = row[(q >> 5) + 2];
     unsigned done = 0;
     // Runs of empty MCUs (the white of a card: every block "DC difference 0, EOB"): once one MCU has been parsed
     // that way from its first bit, every following copy of its bits (at most 32) parses the same way -- a Huffman
@@ -447,103 +441,116 @@ __device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t 
     // of one table walk per block.  A copy is taken only while it ends at or before `end` and the restart
     // boundary: every state inside it lies before `end`, so the exit state is the one the block-by-block walk
     // reaches.  The blocks of such an MCU store nothing (the coefficient buffer starts at zero).
-    int mstart = 0, patlen = 0;
-    uint32_t vstart = 0, pat = 0;
-    bool plain = false;
+    int mstart = q, patlen = 0;
+    uint32_t vstart = __funnelshift_l(b, a, q & 31), pat = 0;
+    bool plain = (k | bi) == 0;                      // the MCU under the cursor has been empty blocks only so far
     while (q < endq) {
         const int sh = q & 31;
         const uint32_t v = __funnelshift_l(b, a, sh);   // the next 32 bits of the stream
-        int adv;
-        bool refill = false;
-        bool run = false;
-        if ((k | bi) == 0) {
-            run = patlen && (v >> (32 - patlen)) == pat && q + patlen <= min(endq, bound);
-            if (!run) {
-                mstart = q;
-                vstart = v;
-                plain = true;
+        uint32_t e = lut(tb + (int)(v >> (32 - JD_LBITS)));
+        if (e & JD_L2) {                                 // a long code, or nothing in the first table
+            const int t = tb >> JD_LBITS;
+            const uint32_t sub = e & 63u;
+            e = sub < JD_L2SUBS ? lut((6 << JD_LBITS) + t * (JD_L2SUBS * 64) + (int)(sub * 64 + ((v >> (32 - JD_LBITS - 6)) & 63u))) : 0u;
+            if (e == 0) {                                // not in the tables: jdhuff.c's canonical walk
+                int len = 16, sym = 0;
+                const int code16 = (int)(v >> 16);
+#pragma unroll 1
+                for (int l = 1; l <= 16; l++) {
+                    const int cd = code16 >> (16 - l);
+                    if (cd <= S.maxcode[t][l]) {
+                        len = l;
+                        sym = S.vals[t][(cd + S.valptr[t][l]) & 255];
+                        break;
+                    }
+                }
+                const int s = sym & 15, r = sym >> 4;
+                const int kinc = k == 0 ? 1 : s ? r + 1 : r == 15 ? 16 : 64;
+                e = (uint32_t)(len + s) | ((uint32_t)kinc << 8) | ((uint32_t)s << 16) | ((uint32_t)len << 20);
             }
         }
-        if (run) {
-            adv = patlen;
-            done += nbm;
+        int adv = (int)(e & 63u);
+        if (HAS_RST && q + adv > bound) {                    // padding in front of a restart marker
+            q = bound;
+            k = 0;
+            bi = 0;
+            dc = dc_of(0);
+            dc_next = dc_of(nbm > 1 ? 1 : 0);
+            tb = dc;
+            ri++;
+            bound = ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
+            a = row[q >> 5];
+            b = row[(q >> 5) + 1];
+            c = row[(q >> 5) + 2];
+            mstart = q;
+            vstart = __funnelshift_l(b, a, q & 31);
+            plain = true;
         } else {
-            uint32_t e = lut(tb + (int)(v >> (32 - JD_LBITS)));
-            if ((e & JD_L2) || e == 0) {
-                const int t = tb >> JD_LBITS;
-                if (e) e = lut((6 << JD_LBITS) + t * (JD_L2SUBS * 64) + (int)((e & 63u) * 64 + ((v >> (32 - JD_LBITS - 6)) & 63u)));
-                if (e == 0) {                                    // not in the tables: jdhuff.c's canonical walk
-                    int len = 16, sym = 0;
-                    const int code16 = (int)(v >> 16);
-#pragma unroll 1
-                    for (int l = 1; l <= 16; l++) {
-                        const int cd = code16 >> (16 - l);
-                        if (cd <= S.maxcode[t][l]) {
-                            len = l;
-                            sym = S.vals[t][(cd + S.valptr[t][l]) & 255];
-                            break;
-                        }
-                    }
-                    const int s = sym & 15, r = sym >> 4;
-                    const int kinc = k == 0 ? 1 : s ? r + 1 : r == 15 ? 16 : 64;
-                    e = (uint32_t)(len + s) | ((uint32_t)kinc << 8) | ((uint32_t)s << 16) | ((uint32_t)len << 20);
-                }
+            const int s = (int)((e >> 16) & 15u);
+            const int pos = k + (int)((e >> 8) & 127u) - 1;  // where the coefficient goes (zigzag order)
+            if (s && pos < 64) {
+                const int len = (int)((e >> 20) & 31u);
+                int val = (int)((v << len) >> (32 - s));
+                if (val < (1 << (s - 1))) val += 1 - (1 << s);
+                sink(done, pos, val);
             }
-            adv = (int)(e & 63u);
-            if (q + adv > bound) {                               // padding in front of a restart marker
-                q = bound;
-                adv = 0;
+            k = pos + 1;
+            plain = plain && (e & JD_BOTH);
+            q += adv;
+            if (sh + adv >= 32) {                            // at most one word per trip (adv <= 32)
+                a = b;
+                b = c;
+                c = row[(q >> 5) + 2];
+            }
+            if (k >= 64) {                                   // the block is complete
                 k = 0;
-                bi = 0;
-                dc = dc_of(0);
-                dc_next = dc_of(nbm > 1 ? 1 : 0);
+                bi = bi + 1 == nbm ? 0 : bi + 1;
+                dc = dc_next;
+                dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
                 tb = dc;
-                ri++;
-                bound = ri < nrst ? rel(__ldg(rst + ri)) : 0x3fffffff;
-                plain = false;
-                refill = true;
-            } else {
-                const int s = (int)((e >> 16) & 15u);
-                const int pos = k + (int)((e >> 8) & 127u) - 1;  // where the coefficient goes (zigzag order)
-                if (s && pos < 64) {
-                    const int len = (int)((e >> 20) & 31u);
-                    int val = (int)((v << len) >> (32 - s));
-                    if (val < (1 << (s - 1))) val += 1 - (1 << s);
-                    sink(done, pos, val);
-                }
-                k = pos + 1;
-                if (!(e & JD_BOTH)) plain = false;
-                if (k >= 64) {                                   // the block is complete
-                    k = 0;
-                    bi = bi + 1 == nbm ? 0 : bi + 1;
-                    dc = dc_next;
-                    dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
-                    tb = dc;
-                    done++;
-                    if (bi == 0 && plain && q + adv - mstart <= 32) {
-                        patlen = q + adv - mstart;
+                done++;
+                if (bi == 0) {                               // ... and so is the MCU
+                    if (plain && q - mstart <= 32) {
+                        patlen = q - mstart;
                         pat = vstart >> (32 - patlen);
                     }
-                } else {
-                    tb = dc + (1 << JD_LBITS);
+                    uint32_t v2 = __funnelshift_l(b, a, q & 31);
+                    if (patlen) {
+                        const int lim = min(endq, bound);
+                        while ((v2 >> (32 - patlen)) == pat && q + patlen <= lim) {
+                            const int sh2 = q & 31;
+                            q += patlen;
+                            done += nbm;
+                            if (sh2 + patlen >= 32) {
+                                a = b;
+                                b = c;
+                                c = row[(q >> 5) + 2];
+                            }
+                            v2 = __funnelshift_l(b, a, q & 31);
+                        }
+                    }
+                    mstart = q;
+                    vstart = v2;
+                    plain = true;
                 }
+            } else {
+                tb = dc + (1 << JD_LBITS);
             }
-        }
-        q += adv;
-        if (refill) {
-            a = word(q >> 5);
-            b = word((q >> 5) + 1);
-            c = word((q >> 5) + 2);
-        } else if (sh + adv >= 32) {                             // at most one word per trip (adv <= 32)
-            a = b;
-            b = c;
-            c = word((q >> 5) + 2);
         }
     }
     p_io = base + (unsigned long long)q;
     k_io = k;
     bi_io = bi;
     return done;
+}
+
+template <bool GLOBAL_LUTS, typename SINK>
+__device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t *__restrict__ L, const uint32_t *row,
+                                             unsigned long long base, unsigned long long &p, int &k, int &bi, unsigned long long end,
+                                             SINK &sink, const unsigned long long *__restrict__ rst, unsigned nrst)
+{
+    return nrst ? jdec_run_t<GLOBAL_LUTS, true>(S, L, row, base, p, k, bi, end, sink, rst, nrst)
+                : jdec_run_t<GLOBAL_LUTS, false>(S, L, row, base, p, k, bi, end, sink, rst, nrst);
 }
 
 // One round of the synchronisation: thread j decodes subsequence j from its predecessor's exit state
@@ -575,8 +582,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
     unsigned cnt = live && round > 0 ? mcnt[j] : 0;
     // Inside the CTA the chain advances without leaving the kernel: one iteration = every thread looks
     // at its predecessor's exit again.  Across CTAs it advances with the next launch.
-    const WinWords win{sw};
-    const unsigned long long wbits = (unsigned long long)blockIdx.x * 128 * JD_SUB;   // first bit of the staged window
+    const uint32_t *row = sw + JD_ROW * threadIdx.x;          // this thread's subsequence
     for (int it = 0; it < (round ? max_it : 1); it++) {
         bool need = false, hit = false;
         unsigned long long x = jdec_pack(j * JD_SUB, 0, 0);
@@ -612,7 +618,7 @@ __global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__rest
             unsigned long long p = x >> 12;
             int k = (int)((x >> 4) & 255), bi = (int)(x & 15);
             NoSink sink;
-            const unsigned n = jdec_run<true>(S, &T->lut[0][0], win, wbits, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
+            const unsigned n = jdec_run<true>(S, &T->lut[0][0], row, j * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst, nrst);
             const unsigned long long e = jdec_pack(p, k, bi);
             mine = x;
             __stcg(out + j, e);
@@ -652,7 +658,7 @@ __global__ void __launch_bounds__(32 * JD_WALK_WARPS) jdec_walk_kernel(const Jde
 {
     __shared__ JdecShared S;
     __shared__ unsigned long long s_used[JD_WALK_WARPS][JD_CHUNK], s_out[JD_WALK_WARPS][JD_CHUNK];
-    __shared__ uint32_t s_words[JD_WALK_WARPS][JD_WPS + 2];
+    __shared__ uint32_t s_words[JD_WALK_WARPS][JD_ROW];
     jdec_load_tables(S, T);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned long long total = 8ull * (scan_len - (*removed & 0xffffffffull));
@@ -686,11 +692,10 @@ __global__ void __launch_bounds__(32 * JD_WALK_WARPS) jdec_walk_kernel(const Jde
             if (lane < 2) s_words[warp][JD_WPS + lane] = __ldg(words + wbase + JD_WPS + lane);
             __syncwarp();
             if (lane == 0) {
-                const SubWords cw{s_words[warp]};
                 unsigned long long pp = prev >> 12;
                 int k = (int)((prev >> 4) & 255), bi = (int)(prev & 15);
                 NoSink sink;
-                const unsigned nb = jdec_run<false>(S.small, &S.luts.lut[0][0], cw, (j0 + i) * JD_SUB, pp, k, bi, min(total, (j0 + i + 1) * JD_SUB), sink,
+                const unsigned nb = jdec_run<false>(S.small, &S.luts.lut[0][0], s_words[warp], (j0 + i) * JD_SUB, pp, k, bi, min(total, (j0 + i + 1) * JD_SUB), sink,
                                              rst, nrst);
                 const unsigned long long e = jdec_pack(pp, k, bi);
                 s_used[warp][i] = prev;
@@ -744,9 +749,8 @@ __global__ void __launch_bounds__(128) jdec_write_kernel(const JdecTables *__res
     // a block that straddles the boundary belongs to the subsequence it ends in: its earlier
     // coefficients were stored by the predecessor under the same ordinal
     CoefSink sink{coef, live ? first_block[j] + first_block_base[j >> 10] : nblocks, nblocks, zz};
-    const WinWords win{sw};
     if (live)
-        jdec_run<false>(S.small, &S.luts.lut[0][0], win, (unsigned long long)blockIdx.x * 128 * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst,
+        jdec_run<false>(S.small, &S.luts.lut[0][0], sw + JD_ROW * threadIdx.x, j * JD_SUB, p, k, bi, min(total, (j + 1) * JD_SUB), sink, rst,
                  nrst);
 }
 
