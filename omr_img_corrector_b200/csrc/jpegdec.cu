@@ -427,7 +427,15 @@ __device__ __forceinline__ unsigned jdec_run_t(const JdecSmall &S, const uint32_
     int q = (int)(p_io - base), k = k_io, bi = bi_io;
     const int endq = rel(end), nbm = S.nbm;
     const uint32_t comps = S.comps;
-    auto lut = [&](int i) { return GLOBAL_LUTS ? __ldg(L + i) : L[i]; };   // L: lut[6][..], then lut2[6][..]
+    // L: lut[6][..], then lut2[6][..] -- in global memory, or a shared-memory copy addressed as such (through the
+    // generic pointer the compiler rebuilds the shared window's base, a special-register read, on every trip)
+    const uint32_t lbase = GLOBAL_LUTS ? 0u : (uint32_t)__cvta_generic_to_shared(L);
+    auto lut = [&](int i) -> uint32_t {
+        if (GLOBAL_LUTS) return __ldg(L + i);
+        uint32_t r;
+        asm("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(lbase + 4u * (uint32_t)i));
+        return r;
+    };
     // tables as entry offsets into L: the block's DC table, its AC table behind it, and the DC table of the block
     // after it (looked up while this block is walked, so a block end costs a move)
     auto dc_of = [&](int blk) { return (int)(((comps >> (2 * blk)) & 3u) << (JD_LBITS + 1)); };
@@ -443,7 +451,9 @@ __device__ __forceinline__ unsigned jdec_run_t(const JdecSmall &S, const uint32_
     // reaches.  The blocks of such an MCU store nothing (the coefficient buffer starts at zero).
     int mstart = q, patlen = 0;
     uint32_t vstart = __funnelshift_l(b, a, q & 31), pat = 0;
-    bool plain = (k | bi) == 0;                      // the MCU under the cursor has been empty blocks only so far
+    uint32_t plain = (k | bi) == 0 ? JD_BOTH : 0u;   // bit 31: the MCU under the cursor has been empty blocks only so far
+    // The trip is straight-line code (selects, one look-ahead load) with three rarely taken branches: an entry
+    // outside the first table, a restart boundary, the end of a block.
     while (q < endq) {
         const int sh = q & 31;
         const uint32_t v = __funnelshift_l(b, a, sh);   // the next 32 bits of the stream
@@ -469,7 +479,7 @@ __device__ __forceinline__ unsigned jdec_run_t(const JdecSmall &S, const uint32_
                 e = (uint32_t)(len + s) | ((uint32_t)kinc << 8) | ((uint32_t)s << 16) | ((uint32_t)len << 20);
             }
         }
-        int adv = (int)(e & 63u);
+        const int adv = (int)(e & 63u);
         if (HAS_RST && q + adv > bound) {                    // padding in front of a restart marker
             q = bound;
             k = 0;
@@ -484,57 +494,58 @@ __device__ __forceinline__ unsigned jdec_run_t(const JdecSmall &S, const uint32_
             c = row[(q >> 5) + 2];
             mstart = q;
             vstart = __funnelshift_l(b, a, q & 31);
-            plain = true;
-        } else {
-            const int s = (int)((e >> 16) & 15u);
-            const int pos = k + (int)((e >> 8) & 127u) - 1;  // where the coefficient goes (zigzag order)
-            if (s && pos < 64) {
-                const int len = (int)((e >> 20) & 31u);
-                int val = (int)((v << len) >> (32 - s));
-                if (val < (1 << (s - 1))) val += 1 - (1 << s);
-                sink(done, pos, val);
-            }
-            k = pos + 1;
-            plain = plain && (e & JD_BOTH);
-            q += adv;
-            if (sh + adv >= 32) {                            // at most one word per trip (adv <= 32)
-                a = b;
-                b = c;
-                c = row[(q >> 5) + 2];
-            }
-            if (k >= 64) {                                   // the block is complete
-                k = 0;
-                bi = bi + 1 == nbm ? 0 : bi + 1;
-                dc = dc_next;
-                dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
-                tb = dc;
-                done++;
-                if (bi == 0) {                               // ... and so is the MCU
-                    if (plain && q - mstart <= 32) {
-                        patlen = q - mstart;
-                        pat = vstart >> (32 - patlen);
-                    }
-                    uint32_t v2 = __funnelshift_l(b, a, q & 31);
-                    if (patlen) {
-                        const int lim = min(endq, bound);
-                        while ((v2 >> (32 - patlen)) == pat && q + patlen <= lim) {
-                            const int sh2 = q & 31;
-                            q += patlen;
-                            done += nbm;
-                            if (sh2 + patlen >= 32) {
-                                a = b;
-                                b = c;
-                                c = row[(q >> 5) + 2];
-                            }
-                            v2 = __funnelshift_l(b, a, q & 31);
-                        }
-                    }
-                    mstart = q;
-                    vstart = v2;
-                    plain = true;
+            plain = JD_BOTH;
+            continue;
+        }
+        const int s = (int)((e >> 16) & 15u);
+        const int pos = k + (int)((e >> 8) & 127u) - 1;      // where the coefficient goes (zigzag order)
+        if (s && pos < 64) {
+            const int len = (int)((e >> 20) & 31u);
+            int val = (int)((v << len) >> (32 - s));
+            if (val < (1 << (s - 1))) val += 1 - (1 << s);
+            sink(done, pos, val);
+        }
+        k = pos + 1;
+        plain &= e;
+        q += adv;
+        {                                                    // at most one word per trip (adv <= 32)
+            const bool cross = sh + adv >= 32;
+            const uint32_t nw = row[(q >> 5) + 2];
+            a = cross ? b : a;
+            b = cross ? c : b;
+            c = cross ? nw : c;
+        }
+        tb = dc + (1 << JD_LBITS);
+        if (k >= 64) {                                       // the block is complete
+            k = 0;
+            bi = bi + 1 == nbm ? 0 : bi + 1;
+            dc = dc_next;
+            dc_next = dc_of(bi + 1 == nbm ? 0 : bi + 1);
+            tb = dc;
+            done++;
+            if (bi == 0) {                                   // ... and so is the MCU
+                if ((plain & JD_BOTH) && q - mstart <= 32) {
+                    patlen = q - mstart;
+                    pat = vstart >> (32 - patlen);
                 }
-            } else {
-                tb = dc + (1 << JD_LBITS);
+                uint32_t v2 = __funnelshift_l(b, a, q & 31);
+                if (patlen) {
+                    const int lim = min(endq, bound);
+                    while ((v2 >> (32 - patlen)) == pat && q + patlen <= lim) {
+                        const int sh2 = q & 31;
+                        q += patlen;
+                        done += nbm;
+                        if (sh2 + patlen >= 32) {
+                            a = b;
+                            b = c;
+                            c = row[(q >> 5) + 2];
+                        }
+                        v2 = __funnelshift_l(b, a, q & 31);
+                    }
+                }
+                mstart = q;
+                vstart = v2;
+                plain = JD_BOTH;
             }
         }
     }
