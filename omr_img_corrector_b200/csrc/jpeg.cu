@@ -606,7 +606,8 @@ int32_t jpeg_lane_get(oics_ctx *ctx, int i, JpegLane **lane)
     if (!L.st) {
         int lo = 0, hi = 0;   // beside the context's own stream, above the decode streams
         OICS_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        OICS_CUDA_TRY(cudaStreamCreateWithPriority(&L.st, cudaStreamNonBlocking, hi));
+        static const int prio_env = [] { const char *e = getenv("OICS_LANE_PRIORITY"); return e ? atoi(e) : 1000; }();
+        OICS_CUDA_TRY(cudaStreamCreateWithPriority(&L.st, cudaStreamNonBlocking, prio_env == 1000 ? hi : std::max(hi, std::min(lo, prio_env))));
         OICS_CUDA_TRY(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
     }
     *lane = &L;

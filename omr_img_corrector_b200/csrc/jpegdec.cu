@@ -574,7 +574,7 @@ __device__ __forceinline__ unsigned jdec_run(const JdecSmall &S, const uint32_t 
 // a lookup, so only the front of the true chain decodes.
 #define JD_M 4
 
-__global__ void __launch_bounds__(128) jdec_sync_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
+__global__ void __launch_bounds__(128, 10) jdec_sync_kernel(const JdecTables *__restrict__ T, const uint32_t *__restrict__ words,
                                                         const unsigned long long *__restrict__ removed, size_t scan_len,
                                                         unsigned long long *used, unsigned long long *out,
                                                         unsigned long long *__restrict__ nblk, unsigned long long *mkey,
