@@ -840,26 +840,34 @@ __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__rest
     for (int i = threadIdx.x; i < 192; i += 256) (&sq[0][0])[i] = (&T->quant[0][0])[i];
     __syncthreads();
     const int lb = threadIdx.x >> 3, r = threadIdx.x & 7;
-    const size_t g = (size_t)blockIdx.x * 32 + lb, nblocks = (size_t)G.mcux * G.mcuy * G.nbm;
+    // 32-bit indices: a baseline JPEG has at most 8192 x 8192 MCUs of at most 10 blocks (< 2^31 blocks x 64 < 2^37: the
+    // coefficient index alone is 64-bit)
+    const unsigned g = blockIdx.x * 32u + (unsigned)lb, nblocks = (unsigned)G.mcux * (unsigned)G.mcuy * (unsigned)G.nbm;
     const bool valid = g < nblocks;
-    const size_t gg = valid ? g : 0;
-    const int mcu = (int)(gg / G.nbm), bi = (int)(gg - (size_t)mcu * G.nbm);
+    const unsigned gg = valid ? g : 0u;
+    const int mcu = (int)(gg / (unsigned)G.nbm), bi = (int)(gg - (unsigned)mcu * (unsigned)G.nbm);
     const int ny = G.hs * G.vs, comp = bi < ny ? 0 : bi - ny + 1;
-    const int4 raw = *reinterpret_cast<const int4 *>(coef + gg * 64 + 8 * r);
+    const int4 raw = *reinterpret_cast<const int4 *>(coef + (size_t)gg * 64 + 8 * r);
     int x[8], o[8];
     x[0] = (int)(int16_t)(raw.x & 0xffff); x[1] = raw.x >> 16;
     x[2] = (int)(int16_t)(raw.y & 0xffff); x[3] = raw.y >> 16;
     x[4] = (int)(int16_t)(raw.z & 0xffff); x[5] = raw.z >> 16;
     x[6] = (int)(int16_t)(raw.w & 0xffff); x[7] = raw.w >> 16;
-    if (r == 0) {   // DC = the predictor carried into this MCU + the differences up to this block
-        // the predictors restart at 0 with every restart interval: sums relative to the interval's first MCU
-        const int m0 = restart ? mcu - mcu % restart : 0;
-        const long long P = (long long)(dc_prefix[mcu] + dc_base[mcu >> 10] - (restart ? dc_prefix[m0] + dc_base[m0 >> 10] : 0ull));
-        const long long fy = sext21(P), P1 = (P - fy) >> 21, fcb = sext21(P1), fcr = (P1 - fcb) >> 21;
-        int dc = (int)(comp == 0 ? fy : comp == 1 ? fcb : fcr);
+    {   // DC = the predictor carried into this MCU + the differences up to this block: the eight lanes of the block
+        // fetch one difference each (the luma blocks in front of it in the MCU, and its own) and add them up
         const int b0 = comp == 0 ? 0 : bi;
-        for (int b = b0; b <= bi; b++) dc += coef[((size_t)mcu * G.nbm + b) * 64];
-        x[0] = (int)(int16_t)dc;
+        int part = b0 + r <= bi ? (int)coef[((size_t)mcu * G.nbm + b0 + r) * 64] : 0;
+        if (r == 0) {
+            // the predictors restart at 0 with every restart interval: sums relative to the interval's first MCU
+            const int m0 = restart ? mcu - mcu % restart : 0;
+            const long long P = (long long)(dc_prefix[mcu] + dc_base[mcu >> 10] - (restart ? dc_prefix[m0] + dc_base[m0 >> 10] : 0ull));
+            const long long fy = sext21(P), P1 = (P - fy) >> 21, fcb = sext21(P1), fcr = (P1 - fcb) >> 21;
+            part += (int)(comp == 0 ? fy : comp == 1 ? fcb : fcr);
+        }
+        part += __shfl_xor_sync(0xffffffffu, part, 1);
+        part += __shfl_xor_sync(0xffffffffu, part, 2);
+        part += __shfl_xor_sync(0xffffffffu, part, 4);
+        if (r == 0) x[0] = (int)(int16_t)part;
     }
 #pragma unroll
     for (int i = 0; i < 8; i++) sm[lb][r][i] = x[i] * (int)sq[comp][8 * r + i];
@@ -880,11 +888,12 @@ __global__ void __launch_bounds__(256) jdec_idct_kernel(const JdecTables *__rest
         lo |= (uint32_t)min(255, max(0, o[i] + 128)) << (8 * i);
         hi |= (uint32_t)min(255, max(0, o[4 + i] + 128)) << (8 * i);
     }
-    const int my = mcu / G.mcux, mx = mcu - my * G.mcux;
+    const int my = (int)((unsigned)mcu / (unsigned)G.mcux), mx = mcu - my * G.mcux;
     int by = my, bx = mx;
     if (comp == 0) {
-        by = my * G.vs + bi / G.hs;
-        bx = mx * G.hs + bi % G.hs;
+        const int brow = G.hs == 2 ? bi >> 1 : bi;          // hs is 1 or 2 (parse_header)
+        by = my * G.vs + brow;
+        bx = mx * G.hs + (bi - brow * G.hs);
     }
     *reinterpret_cast<uint2 *>(planes + G.poff[comp] + ((size_t)by * 8 + r) * G.pw[comp] + (size_t)bx * 8) = make_uint2(lo, hi);
 }
@@ -940,6 +949,58 @@ __global__ void __launch_bounds__(256) jdec_color_kernel(const uint8_t *__restri
         o[3 * i] = (uint8_t)min(255, max(0, B));
         o[3 * i + 1] = (uint8_t)min(255, max(0, Gv));
         o[3 * i + 2] = (uint8_t)min(255, max(0, R));
+    }
+}
+
+// The common case -- 4:2:0, h2v2_fancy_upsample, rows of the output a multiple of 4 bytes apart: one thread = four
+// output pixels of a row (two chroma samples and their two neighbours), luma as one 32-bit load, the twelve
+// output bytes as three 32-bit stores.  Same arithmetic as the general kernel above.
+__global__ void __launch_bounds__(256) jdec_color420_kernel(const uint8_t *__restrict__ planes, JdecGeom G,
+                                                            uint8_t *__restrict__ bgr, size_t stride)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    const int x0 = 4 * t;
+    if (x0 >= G.w) return;
+    const int cw = (G.w + 1) >> 1, chh = (G.h + 1) >> 1;
+    const uint32_t yy4 = *reinterpret_cast<const uint32_t *>(planes + G.poff[0] + (size_t)y * G.pw[0] + x0);
+    const int r0 = y >> 1, r1 = min(chh - 1, max(0, (y & 1) ? r0 + 1 : r0 - 1));
+    const int c0 = 2 * t;
+    int cv[2][4];                                   // [Cb, Cr][pixel], minus 128
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const int pw = G.pw[1 + k];
+        const uint8_t *a = planes + G.poff[1 + k] + (size_t)r0 * pw, *b = planes + G.poff[1 + k] + (size_t)r1 * pw;
+        const uint32_t a2 = *reinterpret_cast<const uint16_t *>(a + c0), b2 = *reinterpret_cast<const uint16_t *>(b + c0);
+        const int im = max(c0 - 1, 0), ip = min(c0 + 2, pw - 1);
+        const int sm = a[im] * 3 + b[im], s0 = (int)(a2 & 255u) * 3 + (int)(b2 & 255u), s1 = (int)(a2 >> 8) * 3 + (int)(b2 >> 8),
+                  sp = a[ip] * 3 + b[ip];
+        cv[k][0] = (c0 == 0 ? (s0 * 4 + 8) >> 4 : (s0 * 3 + sm + 8) >> 4) - 128;
+        cv[k][1] = (c0 == cw - 1 ? (s0 * 4 + 7) >> 4 : (s0 * 3 + s1 + 7) >> 4) - 128;
+        cv[k][2] = ((s1 * 3 + s0 + 8) >> 4) - 128;
+        cv[k][3] = (c0 + 1 == cw - 1 ? (s1 * 4 + 7) >> 4 : (s1 * 3 + sp + 7) >> 4) - 128;
+    }
+    uint8_t o[12];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int yv = (int)((yy4 >> (8 * i)) & 255u), cb = cv[0][i], cr = cv[1][i];
+        const int R = yv + ((91881 * cr + 32768) >> 16);
+        const int Gv = yv + ((-22554 * cb + 32768 - 46802 * cr) >> 16);
+        const int B = yv + ((116130 * cb + 32768) >> 16);
+        o[3 * i] = (uint8_t)min(255, max(0, B));
+        o[3 * i + 1] = (uint8_t)min(255, max(0, Gv));
+        o[3 * i + 2] = (uint8_t)min(255, max(0, R));
+    }
+    uint8_t *dst = bgr + (size_t)y * stride + 3 * (size_t)x0;
+    if (x0 + 4 <= G.w) {
+        uint32_t *d32 = reinterpret_cast<uint32_t *>(dst);
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+            d32[j] = (uint32_t)o[4 * j] | ((uint32_t)o[4 * j + 1] << 8) | ((uint32_t)o[4 * j + 2] << 16) | ((uint32_t)o[4 * j + 3] << 24);
+    } else {
+        const int nbytes = 3 * (G.w - x0);
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            if (i < nbytes) dst[i] = o[i];
     }
 }
 
@@ -1139,7 +1200,12 @@ static int32_t jdec_finish(oics_ctx *ctx, JdecSlot &S, uint8_t *d_bgr, size_t st
     }
     {
         ProfScope ps(ctx, "jdec_color_kernel", 64.0 * (double)S.nblocks + 3.0 * (double)S.H.w * (double)S.H.h, st);
-        jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
+        const bool fast420 = S.G.ncomp == 3 && S.G.hs == 2 && S.G.vs == 2 && (S.H.w + 1) / 2 > 2 && stride % 4 == 0 &&
+                             (reinterpret_cast<uintptr_t>(d_bgr) & 3) == 0;
+        if (fast420)
+            jdec_color420_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 4), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
+        else
+            jdec_color_kernel<<<dim3((unsigned)cdiv(cdiv(S.H.w, 2), 256), (unsigned)S.H.h), 256, 0, st>>>(S.planes.as<uint8_t>(), S.G, d_bgr, stride);
     }
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 4;
