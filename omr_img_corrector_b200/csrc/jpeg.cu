@@ -376,9 +376,11 @@ __global__ void __launch_bounds__(1024) scan_block_kernel(unsigned long long *__
 {
     __shared__ unsigned long long ws[32];
     if (tb) n = stream_chunks(tb);
-    if ((size_t)blockIdx.x * 1024 >= n) return;
-    const size_t i = (size_t)blockIdx.x * 1024 + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // a CTA takes tiles blockIdx.x, + gridDim.x, ...: with `tb` the grid is sized for the host's bound, the real count
+    // is a few per cent of it
+    for (size_t tile = blockIdx.x; tile * 1024 < n; tile += gridDim.x) {
+    const size_t i = tile * 1024 + threadIdx.x;
     const unsigned long long x = i < n ? v[i] : 0ull;
     unsigned long long s = x;
 #pragma unroll
@@ -400,7 +402,9 @@ __global__ void __launch_bounds__(1024) scan_block_kernel(unsigned long long *__
     __syncthreads();
     const unsigned long long before = (warp ? ws[warp - 1] : 0ull) + s - x;
     if (i < n) v[i] = before;
-    if (threadIdx.x == 1023) sums[blockIdx.x] = before + x;
+    if (threadIdx.x == 1023) sums[tile] = before + x;
+    __syncthreads();                                 // ws is reused by the next tile
+    }
 }
 
 // one CTA: exclusive scan of the per-CTA sums (any count), total out
@@ -450,7 +454,7 @@ int32_t exclusive_scan(oics_ctx *ctx, cudaStream_t st, unsigned long long *v, si
                        unsigned long long *total, const unsigned long long *tb)
 {
     const int m = (int)((n + 1023) / 1024);
-    scan_block_kernel<<<m, 1024, 0, st>>>(v, n, sums, tb);
+    scan_block_kernel<<<tb ? std::min(m, 296) : m, 1024, 0, st>>>(v, n, sums, tb);
     scan_sums_kernel<<<1, 1024, 0, st>>>(sums, m, total, tb);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
@@ -471,21 +475,23 @@ __device__ __forceinline__ uint32_t stream_byte(const uint32_t *__restrict__ wor
 // size is read from *total_bits on the device, so that no host round trip sits between the kernels.
 __global__ void __launch_bounds__(256) jpeg_zero_kernel(uint4 *__restrict__ words, const unsigned long long *__restrict__ total_bits)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < ((*total_bits + 7) >> 3) / 16 + 2) words[i] = make_uint4(0u, 0u, 0u, 0u);
+    const size_t n = ((*total_bits + 7) >> 3) / 16 + 2;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        words[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 __global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *__restrict__ words,
                                                                const unsigned long long *__restrict__ total_bits,
                                                                unsigned long long *__restrict__ cnt)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= stream_chunks(total_bits)) return;
+    const size_t nch = stream_chunks(total_bits);
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
-    unsigned c = 0;
-    for (unsigned long long j = 32ull * i; j < min(nbytes, 32ull * i + 32ull); j++) c += stream_byte(words, j, nbytes, pad) == 0xFFu;
-    cnt[i] = c;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nch; i += (size_t)gridDim.x * blockDim.x) {
+        unsigned c = 0;
+        for (unsigned long long j = 32ull * i; j < min(nbytes, 32ull * i + 32ull); j++) c += stream_byte(words, j, nbytes, pad) == 0xFFu;
+        cnt[i] = c;
+    }
 }
 
 // header (cached on the device, SOF0 height / width patched in) + stuffed stream + EOI
@@ -506,12 +512,12 @@ __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *_
             if ((size_t)t < file_cap) file[t] = v;
         }
     }
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= stream_chunks(total_bits)) return;
+    const size_t nch = stream_chunks(total_bits);
     uint8_t *out = file + hdr;
     const size_t cap = file_cap > (size_t)hdr ? file_cap - hdr : 0;
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nch; i += (size_t)gridDim.x * blockDim.x) {
     size_t o = 32 * i + (size_t)(off[i] + off_base[i >> 10]);
     const unsigned long long j1 = min(nbytes, 32ull * i + 32ull);
     for (unsigned long long j = 32ull * i; j < j1; j++) {
@@ -526,6 +532,7 @@ __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *_
     if (j1 == nbytes) {   // EOI behind the last data byte
         if (o < cap) out[o] = 0xFF;
         if (o + 1 < cap) out[o + 1] = 0xD9;
+    }
     }
 }
 
@@ -684,18 +691,21 @@ int32_t jpeg_encode_enqueue(oics_ctx *ctx, const uint8_t *dbgr, int w, int h, si
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 2;
     OICS_TRY(exclusive_scan(ctx, st, bits, nb, sums, d_totals, nullptr));
-    jpeg_zero_kernel<<<(unsigned)((bound / 16 + 2 + 255) / 256), 256, 0, st>>>((uint4 *)words, d_totals);
+    // the grids below cover the real stream with a stride loop: the host only knows the bound (208 bytes per block,
+    // ~25 x the stream of a quality-100 card), and CTAs that find nothing to do are not free
+    const unsigned cap_grid = (unsigned)(ctx->sm_count * 8);
+    jpeg_zero_kernel<<<std::min<unsigned>(cap_grid, (unsigned)((bound / 16 + 2 + 255) / 256)), 256, 0, st>>>((uint4 *)words, d_totals);
     {
         ProfScope ps(ctx, "jpeg_emit_kernel", 2.0 * 64 * nb + 8.0 * nb, st);
         jpeg_emit_kernel<<<cdiv(G.nblocks, 256), 256, 0, st>>>(coef, G, bits, sums, words);
     }
-    jpeg_stuff_count_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(words, d_totals, cnt);
+    jpeg_stuff_count_kernel<<<std::min<unsigned>(cap_grid, (unsigned)((nchunks + 255) / 256)), 256, 0, st>>>(words, d_totals, cnt);
     OICS_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
     OICS_TRY(exclusive_scan(ctx, st, cnt, nchunks, sums2, d_totals + 1, d_totals));
     {
         ProfScope ps(ctx, "jpeg_stuff_write_kernel", 0.0, st);
-        jpeg_stuff_write_kernel<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(
+        jpeg_stuff_write_kernel<<<std::min<unsigned>(cap_grid, (unsigned)((nchunks + 255) / 256)), 256, 0, st>>>(
             words, d_totals, cnt, sums2, ctx->jpeg_hdr.as<uint8_t>(), (int)hdr, ctx->jpeg_hdr_sof, w, h, d_out, d_cap);
     }
     OICS_CUDA_TRY(cudaGetLastError());
