@@ -480,6 +480,21 @@ __global__ void __launch_bounds__(256) jpeg_zero_kernel(uint4 *__restrict__ word
         words[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
+// One LANE per 32-bit word of the stream, eight lanes per 32-byte chunk (the unit of the offsets' scan).
+__device__ __forceinline__ uint32_t stream_word(const uint32_t *__restrict__ words, size_t wi, unsigned long long nbytes, int pad_bits)
+{
+    // bytes at and behind nbytes are zero in `words` (jpeg_zero_kernel); the last real byte is padded with ones
+    uint32_t v = 4 * wi < nbytes ? words[wi] : 0u;
+    if ((nbytes - 1) >> 2 == wi) v |= ((1u << pad_bits) - 1u) << (24 - 8 * (int)((nbytes - 1) & 3));
+    return v;
+}
+__device__ __forceinline__ int ff_bytes(uint32_t v, int nvalid)      // 0xFF bytes among the first nvalid (MSB first)
+{
+    uint32_t m = __vcmpeq4(v, 0xFFFFFFFFu) & 0x01010101u;
+    if (nvalid < 4) m &= nvalid <= 0 ? 0u : ~(0xFFFFFFFFu >> (8 * nvalid));
+    return __popc(m);
+}
+
 __global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *__restrict__ words,
                                                                const unsigned long long *__restrict__ total_bits,
                                                                unsigned long long *__restrict__ cnt)
@@ -487,10 +502,16 @@ __global__ void __launch_bounds__(256) jpeg_stuff_count_kernel(const uint32_t *_
     const size_t nch = stream_chunks(total_bits);
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nch; i += (size_t)gridDim.x * blockDim.x) {
-        unsigned c = 0;
-        for (unsigned long long j = 32ull * i; j < min(nbytes, 32ull * i + 32ull); j++) c += stream_byte(words, j, nbytes, pad) == 0xFFu;
-        cnt[i] = c;
+    const size_t nw = nch * 8;                       // whole groups of eight lanes: the shuffles below are full-warp
+    // (the trip count is the same for the 32 lanes of a warp: the loop runs on the warp's first word)
+    for (size_t w0 = (size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); w0 < nw; w0 += (size_t)gridDim.x * blockDim.x) {
+        const size_t wi = w0 + (threadIdx.x & 31);
+        const long long left = (long long)nbytes - 4 * (long long)wi;
+        int c = wi < nw ? ff_bytes(stream_word(words, wi, nbytes, pad), (int)min(4ll, max(0ll, left))) : 0;
+        c += __shfl_xor_sync(0xffffffffu, c, 1);
+        c += __shfl_xor_sync(0xffffffffu, c, 2);
+        c += __shfl_xor_sync(0xffffffffu, c, 4);
+        if (wi < nw && (wi & 7) == 0) cnt[wi >> 3] = (unsigned long long)c;
     }
 }
 
@@ -517,22 +538,40 @@ __global__ void __launch_bounds__(256) jpeg_stuff_write_kernel(const uint32_t *_
     const size_t cap = file_cap > (size_t)hdr ? file_cap - hdr : 0;
     const unsigned long long T = *total_bits, nbytes = (T + 7) >> 3;
     const int pad = (int)(8 * nbytes - T);
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nch; i += (size_t)gridDim.x * blockDim.x) {
-    size_t o = 32 * i + (size_t)(off[i] + off_base[i >> 10]);
-    const unsigned long long j1 = min(nbytes, 32ull * i + 32ull);
-    for (unsigned long long j = 32ull * i; j < j1; j++) {
-        const uint32_t b = stream_byte(words, j, nbytes, pad);
-        if (o < cap) out[o] = (uint8_t)b;
-        o++;
-        if (b == 0xFFu) {
-            if (o < cap) out[o] = 0;
-            o++;
+    const size_t nw = nch * 8;
+    const int lane = threadIdx.x & 31;
+    for (size_t w0 = (size_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); w0 < nw; w0 += (size_t)gridDim.x * blockDim.x) {
+        const size_t wi = w0 + lane;
+        const long long left = (long long)nbytes - 4 * (long long)wi;
+        const int nvalid = wi < nw ? (int)min(4ll, max(0ll, left)) : 0;
+        const uint32_t v = wi < nw ? stream_word(words, wi, nbytes, pad) : 0u;
+        const int c = ff_bytes(v, nvalid);
+        // 0xFF bytes in the words of this chunk in front of this one: inclusive scan over the group of eight lanes
+        int inc = c;
+#pragma unroll
+        for (int d = 1; d < 8; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, d);
+            if ((lane & 7) >= d) inc += t;
         }
-    }
-    if (j1 == nbytes) {   // EOI behind the last data byte
-        if (o < cap) out[o] = 0xFF;
-        if (o + 1 < cap) out[o + 1] = 0xD9;
-    }
+        if (wi >= nw) continue;                      // (after the shuffles)
+        const size_t ch = wi >> 3;
+        size_t o = 4 * wi + (size_t)(off[ch] + off_base[ch >> 10]) + (size_t)(inc - c);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nvalid) {
+                const uint32_t byte = (v >> (24 - 8 * k)) & 0xFFu;
+                if (o < cap) out[o] = (uint8_t)byte;
+                o++;
+                if (byte == 0xFFu) {
+                    if (o < cap) out[o] = 0;
+                    o++;
+                }
+            }
+        }
+        if (nvalid > 0 && left <= 4) {   // EOI behind the last data byte
+            if (o < cap) out[o] = 0xFF;
+            if (o + 1 < cap) out[o + 1] = 0xD9;
+        }
     }
 }
 
