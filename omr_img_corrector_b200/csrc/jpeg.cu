@@ -278,8 +278,8 @@ __device__ __forceinline__ void walk_block(const int16_t *__restrict__ coef, con
     int t = resolved_dc(coef, G, mcu, b) - pred, t2 = t;
     if (t < 0) { t = -t; t2--; }
     int nb = bit_length(t);
-    sink(c_hcode[tdc][nb], c_hlen[tdc][nb]);
-    sink((unsigned)t2, nb);
+    // a Huffman code (<= 16 bits) and the value bits behind it (<= 11) leave as ONE field
+    sink(((unsigned)c_hcode[tdc][nb] << nb) | ((unsigned)t2 & ((1u << nb) - 1u)), c_hlen[tdc][nb] + nb);
     if (dummy) {                                            // all AC zero
         sink(c_hcode[tac][0], c_hlen[tac][0]);
         return;
@@ -298,8 +298,7 @@ __device__ __forceinline__ void walk_block(const int16_t *__restrict__ coef, con
             t2 = v;
             if (v < 0) { v = -v; t2--; }
             nb = bit_length(v);
-            sink(c_hcode[tac][(r << 4) + nb], c_hlen[tac][(r << 4) + nb]);
-            sink((unsigned)t2, nb);
+            sink(((unsigned)c_hcode[tac][(r << 4) + nb] << nb) | ((unsigned)t2 & ((1u << nb) - 1u)), c_hlen[tac][(r << 4) + nb] + nb);
             r = 0;
         }
     }
