@@ -24,6 +24,7 @@
 //      Latency-bound per image (like the CPU), throughput comes from images in flight.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <thread>
 
@@ -717,6 +718,11 @@ static int32_t hough_lines_p_batch_once(oics_ctx *ctx, const uint8_t *const *ded
                                         std::vector<std::vector<int32_t>> *lines_out, int *max_found)
 {
     cudaStream_t st = ctx->stream;
+    // OICS_HOUGH_TRACE=1: host-side wall times of the phases, on stderr (diagnostics)
+    static const bool trace = getenv("OICS_HOUGH_TRACE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = trace ? now() : 0.0;
+    double t1 = 0.0, t2 = 0.0;
     *max_found = 0;
     lines_out->assign((size_t)n_img, std::vector<int32_t>());
     if (n_img <= 0) return OICS_OK;
@@ -775,6 +781,7 @@ static int32_t hough_lines_p_batch_once(oics_ctx *ctx, const uint8_t *const *ded
     }
     const size_t total_pts = off[(size_t)n_img];
     if (total_pts == 0) return OICS_OK;
+    if (trace) t1 = now();
 
     // ---- visiting orders, expanded in pinned memory on host threads (data-independent, like the trig table)
     OICS_TRY(ctx->pin_in.ensure(2 * sizeof(int) * total_pts));
@@ -794,6 +801,7 @@ static int32_t hough_lines_p_batch_once(oics_ctx *ctx, const uint8_t *const *ded
             for (std::thread &t : pool) t.join();
         }
     }
+    if (trace) t2 = now();
     // misc: [order total_pts][seq total_pts][ttab][dirs][PphtArgs n][n_lines n x 16 B][lines n x cap x 4]
     const size_t off_seq = sizeof(int) * total_pts;
     const size_t off_ttab = (off_seq + sizeof(uint32_t) * total_pts + 15) & ~(size_t)15;
@@ -845,6 +853,9 @@ static int32_t hough_lines_p_batch_once(oics_ctx *ctx, const uint8_t *const *ded
     OICS_CUDA_TRY(cudaMemcpyAsync(nl.data(), base + off_nl, 16 * (size_t)n_img, cudaMemcpyDeviceToHost, st));
     OICS_CUDA_TRY(cudaMemcpyAsync(all.data(), base + off_lines, sizeof(int32_t) * all.size(), cudaMemcpyDeviceToHost, st));
     OICS_CUDA_TRY(cudaStreamSynchronize(st));   // also: args / ttab / dirs (host temporaries) have been consumed
+    if (trace)
+        fprintf(stderr, "[oics hough] %d images, %zu edge points: edge lists (waits for Canny) %.2f ms | visiting orders (host) %.2f | "
+                        "gather + PPHT + read-back %.2f\n", n_img, total_pts, t1 - t0, t2 - t1, now() - t2);
     for (int i = 0; i < n_img; i++) {
         const int n = nl[4 * (size_t)i];
         *max_found = std::max(*max_found, n);
