@@ -9,9 +9,15 @@
 //                     and every thread decodes one from a guessed state (bit position, coefficient
 //                     index, block of the MCU); Huffman streams self-synchronise, so feeding every
 //                     thread its predecessor's exit state and repeating until nothing changes
-//                     (a few rounds; unchanged threads leave at once) gives each subsequence its true
-//                     entry state (Weissenberger & Schmidt, "Massively parallel Huffman decoding on
-//                     GPUs", restated for JPEG's (position, k, block) state).
+//                     gives each subsequence its true entry state (Weissenberger & Schmidt, "Massively
+//                     parallel Huffman decoding on GPUs", restated for JPEG's (position, k, block)
+//                     state).  Round 0 from the guesses, then the "wide" launch: iterations inside each
+//                     128-subsequence CTA until nothing changes there.  A quality-100 stream hardly
+//                     self-synchronises (no EOBs), so the truth travels from the last empty MCU one
+//                     subsequence per iteration: the walker (jdec_run) is built for the latency of one symbol.
+//   jdec_walk_kernel  carries the states across the CTA borders: one lane per 128-subsequence chunk walks
+//                     it in order and decodes only where the entry state differs from the one last used;
+//                     launched until a launch decodes nothing.
 //   scan              blocks completed per subsequence -> first block index of every subsequence
 //   jdec_write_kernel the same decode once more, now storing coefficients [block][64] (natural order)
 //   jdec_mcu_dc_*     DC prediction: per-MCU sums of the DC differences (three 21-bit fields in one
@@ -19,7 +25,8 @@
 //   jdec_idct_kernel  8 threads per block: dequantise, jidctint.c islow IDCT (column then row through
 //                     a conflict-free transpose), range limit -> component planes
 //   jdec_color_kernel jdsample.c fancy h2v1 / h2v2 upsampling (jdmainct.c edge rows, jinit_upsampler's
-//                     width rule), jdcolor.c YCC -> RGB, BGR out
+//                     width rule), jdcolor.c YCC -> RGB, BGR out; jdec_color420_kernel: the 4:2:0 case,
+//                     four pixels per thread
 // Covered: 8-bit baseline / extended sequential, one interleaved scan, grey or Y Cb Cr with luma
 // sampling 1x1, 2x1 or 2x2, any Huffman tables, restart intervals.  Anything else:
 // OICS_ERR_UNSUPPORTED (the caller keeps its imread for those).
