@@ -293,3 +293,16 @@ def test_bench_reference_arm_sample(orc):
     assert "300 sweep angles" in ref.sample_text()
     cfg_a = bench.workload_config(512, 1, 16, 128)
     assert cfg_a == bench.workload_config(512, 1, 16, 128) and "workload" in cfg_a     # both arms print the same config
+
+
+def test_work_queue_default_respects_the_host(tmp_path):
+    """Importing the package asks for one hardware work queue per stream (the file path keeps ~24 busy) unless the
+    host exported its own CUDA_DEVICE_MAX_CONNECTIONS (process environment)."""
+    import subprocess
+    import sys
+    code = "import os, omr_img_corrector_b200; print(os.environ['CUDA_DEVICE_MAX_CONNECTIONS'])"
+    env = {k: v for k, v in os.environ.items() if k != "CUDA_DEVICE_MAX_CONNECTIONS"}
+    env["PYTHONPATH"] = ROOT
+    assert subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout.strip() == "32"
+    env["CUDA_DEVICE_MAX_CONNECTIONS"] = "4"
+    assert subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout.strip() == "4"
