@@ -627,6 +627,32 @@ def test_jpeg_decode_restart_intervals(ctx, orc, interval):
         ctx.jpeg_decode(broken)
 
 
+@pytest.mark.parametrize("wide", ["0", "2"])
+def test_jpeg_decode_other_synchronisation_schedules(orc, dataset_like, tmp_path, wide):
+    """OICS_JD_WIDE (read once per process, hence the child): 0 = the chunk walks alone, starting from the guess
+    (jdec_walk_kernel's from_guess launch); 2 = two wide iterations, the walks do the rest.  Same pixels as the
+    default schedule's, i.e. the oracle's -- quality 100 (no self-synchronisation), 75, and a file with DRI."""
+    import os
+    import subprocess
+    import sys
+    import cv2
+    bgr, _ = dataset_like
+    files = {"q100": orc.jpeg_encode(bgr, 100), "q75": orc.jpeg_encode(bgr, 75),
+             "dri": cv2.imencode(".jpg", bgr, [cv2.IMWRITE_JPEG_QUALITY, 95, cv2.IMWRITE_JPEG_RST_INTERVAL, 11])[1].tobytes()}
+    for name, data in files.items():
+        (tmp_path / f"{name}.jpg").write_bytes(data)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys, numpy as np\n"
+            "from omr_img_corrector_b200 import api\n"
+            "ctx = api.Context(0)\n"
+            "for name in ('q100', 'q75', 'dri'):\n"
+            "    np.save(sys.argv[1] + '/' + name + '.npy', ctx.jpeg_decode(open(sys.argv[1] + '/' + name + '.jpg', 'rb').read()))\n")
+    env = dict(os.environ, OICS_JD_WIDE=wide, PYTHONPATH=root)
+    subprocess.run([sys.executable, "-c", code, str(tmp_path)], env=env, check=True)
+    for name, data in files.items():
+        assert np.array_equal(np.load(tmp_path / f"{name}.npy"), orc.jpeg_decode(data)), (wide, name)
+
+
 def test_correct_batch_files_jpeg_in_jpeg_out(ctx, orc, dataset_like):
     """oics_correct_batch_files: omr::correct_default from imread (omr.rs:349) to imwrite (omr.rs:447-448)
     with both codecs on the device.  Every returned file equals the oracle's encoding of the oracle's
